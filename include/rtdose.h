@@ -1,0 +1,177 @@
+/*
+ * rtdose.h - C ABI of the B200-native proton pencil-beam dose engine (librtdose.so).
+ *
+ * This is the drop-in boundary for the reference's single hot-path entry point
+ *     void cudaWrapperProtons(HostPinnedImage3D<float>* imVol, HostPinnedImage3D<float>* doseVol,
+ *                             const std::vector<BeamSettings> beams, const EnergyStruct iddData,
+ *                             std::ostream& outStream);          (reference: src/kernel_wrapper.cuh:161,
+ *                                                                 implemented src/kernel_wrapper.cu:381-1369)
+ * Plain pointers and sizes only; no C++/torch types. include/rtdose_shim.hpp wraps these calls in a C++
+ * function with the reference's exact signature and value types (BeamSettings, EnergyStruct,
+ * HostPinnedImage3D), see INTEGRATION.md.
+ *
+ * Conventions (identical to the reference):
+ *   - CT voxels are float(HU + 1000), x fastest, dims (nx,ny,nz)       (src/dicom_reader.cpp:104, src/main.cu:42)
+ *   - dose is ACCUMULATED onto the caller's content                     (src/kernel_wrapper.cu:542, 91-93)
+ *   - spot weights are [layer][sy][sx]                                   (src/beam_settings.h:21)
+ *   - the beam travels along -z gantry (spotDelta[2] < 0)                (src/fill_idd_and_sigma_params.cu:22)
+ * Ownership: every pointer is borrowed for the duration of the call; the library frees only what it
+ * allocated and never resets the device (the reference deletes its inputs and calls cudaDeviceReset(),
+ * src/kernel_wrapper.cu:856,1366-1368 - the C++ shim reproduces that for main.cu-style callers).
+ * Threading: one context per device; calls on one context must not overlap.
+ */
+#ifndef RTDOSE_H
+#define RTDOSE_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RTD_MAX_SUPERP_R 32   /* maxSuperpR, src/kernel_wrapper.cuh:26 */
+#define RTD_TILE_X 32         /* superpTileX, src/kernel_wrapper.cuh:27 */
+#define RTD_TILE_Y 8          /* superpTileY, src/kernel_wrapper.cuh:28 */
+#define RTD_HIST_BINS 34      /* maxSuperpR + 2 radius counters, src/kernel_wrapper.cu:734 */
+
+typedef struct rtd_ctx rtd_ctx;
+
+typedef enum {
+    RTD_OK = 0,
+    RTD_ERR_INVALID = 1,   /* bad argument (replaces std::runtime_error("Empty list"), src/vector_find.h:22-25, etc.) */
+    RTD_ERR_CUDA = 2,      /* CUDA runtime / launch error (replaces cudaErrchk throw, src/cuda_errchk.cu:12-22) */
+    RTD_ERR_RADIUS = 3,    /* a tile needs a superposition radius > 32 (replaces throw("..."), src/kernel_wrapper.cu:965) */
+    RTD_ERR_STATE = 4,     /* LUTs / CT / dose grid not set */
+    RTD_ERR_NO_DEVICE = 5  /* no CUDA device: the product has no CPU fallback */
+} rtd_status;
+
+/* POD mirror of EnergyStruct (reference: src/energy_struct.h:13-38). */
+typedef struct {
+    int nEnergySamples;          /* depth samples per energy (1024) */
+    int nEnergies;               /* 147 */
+    const float* energiesPerU;   /* [nEnergies] ascending */
+    const float* peakDepths;     /* [nEnergies] mm */
+    const float* scaleFacts;     /* [nEnergies] depth-sample per mm WEPL */
+    const float* ciddMatrix;     /* [nEnergies][nEnergySamples] cumulative integral depth dose */
+    int nDensitySamples; float densityScaleFact; const float* densityVector;   /* HU+1000 -> g/cm3 */
+    int nSpSamples;      float spScaleFact;      const float* spVector;        /* HU+1000 -> relative stopping power */
+    int nRRlSamples;     float rRlScaleFact;     const float* rRlVector;       /* density*scale -> 1/X0 */
+} rtd_luts;
+
+/* POD mirror of BeamSettings (reference: src/beam_settings.h:101-109; ctor :32). */
+typedef struct {
+    const float* weights;        /* [nLayers][sy][sx] spot weights (host) */
+    int sx, sy, nLayers;
+    const float* energies;       /* [nLayers] MeV/u */
+    const float* sigmas;         /* [nLayers][2] spot sigma (x,y) at iso in air, mm */
+    float raySpacing[2];         /* ray pitch at iso, mm */
+    unsigned int steps;          /* tracer steps */
+    float sourceDist[2];         /* apparent source-to-iso distance x,y (INFINITY = parallel) */
+    float spotDelta[3];          /* spotIdxToGantry delta (z: signed step length, negative) */
+    float spotOffset[3];         /* spotIdxToGantry offset (z: start plane) */
+    float gantryToImIdxM[9];  float gantryToImIdxV[3];     /* row-major 3x3 + translation */
+    float gantryToDoseIdxM[9]; float gantryToDoseIdxV[3];
+} rtd_beam;
+
+/* Run-time equivalents of the reference's compile-time flags (reference: CMakeLists.txt:36-79). */
+typedef struct {
+    float bpDepthCutoff;     /* BP_DEPTH_CUTOFF   1.05 */
+    float convSigmaCutoff;   /* CONV_SIGMA_CUTOFF 3.0  */
+    float ksSigmaCutoff;     /* KS_SIGMA_CUTOFF   3.0  */
+    float rayWeightCutoff;   /* RAY_WEIGHT_CUTOFF 1.0  */
+    int   minTilesInBatch;   /* 16, src/kernel_wrapper.cuh:29 */
+    int   keepIntermediates; /* 1: keep per-beam BEV arrays of every layer for rtd_debug_fetch */
+    int   reserved[4];
+} rtd_opts;
+
+/* Stage timing of the last rtd_dose* call (CUDA events on the context's stream), the counterpart of the
+ * reference's FINE_GRAINED_TIMING report (src/kernel_wrapper.cu:1291-1311). */
+typedef struct {
+    float msTotal;       /* first event -> last event of the call */
+    float msUpload;      /* host->device copies inside the call (CT if dirty, dose-in, weights) */
+    float msTrace;       /* K1 trace + reductions, all beams */
+    float msSetup;       /* host logic + per-layer parameter upload + BEV clear */
+    float msConv;        /* K3a spot -> ray weights */
+    float msIddSigma;    /* K2 */
+    float msRadius;      /* tile radius + batching */
+    float msSuperp;      /* K3b kernel superposition */
+    float msTransfer;    /* K4 BEV -> dose grid */
+    float msDownload;    /* device->host dose */
+    int64_t updates;     /* U = sum_beams sum_layers Rx*Ry*(layerFirstPassive - beamFirstInside) */
+    int64_t ksTaps;      /* sum over updates of (2*rb+1)^2, rb = batch radius */
+    int     kernelLaunches;
+    int     hostSyncs;
+} rtd_timing;
+
+typedef struct {
+    int lSteps, bSteps, rSteps, tSteps;      /* src/kernel_wrapper.cu:650-653 */
+    int rayDimX, rayDimY, steps, nLayers;    /* src/kernel_wrapper.cu:659 */
+    int beamFirstInside, beamFirstOutside;   /* src/kernel_wrapper.cu:781-787 */
+    int beamFirstGuaranteedPassive;          /* src/kernel_wrapper.cu:796 */
+    int beamFirstCalculatedPassive;          /* src/kernel_wrapper.cu:955-957 */
+    int bboxMin[3], bboxMax[3];              /* src/kernel_wrapper.cu:1207-1208 */
+    float entryZ;
+    int64_t updates;
+} rtd_beam_report;
+
+typedef struct {
+    float energyIdx, energyScaleFact, peakDepth;   /* src/kernel_wrapper.cu:835-837 */
+    float entrySigmaX, entrySigmaY;                /* src/kernel_wrapper.cu:840-841 */
+    int afterLastStep;                             /* src/kernel_wrapper.cu:923-924 */
+    int layerFirstPassive;                         /* src/kernel_wrapper.cu:952-954 */
+    int radiusHist[RTD_HIST_BINS];                 /* tilePrimRadCtrs, src/kernel_wrapper.cu:959-963 */
+    int batchRadius[RTD_HIST_BINS];                /* radius actually applied to tiles of own radius r (cu:966-976) */
+} rtd_layer_report;
+
+typedef enum {
+    RTD_FETCH_DENSITY = 0,       /* float [steps][Ry][Rx]                         (bevDensity) */
+    RTD_FETCH_WEPL = 1,          /* float [steps][Ry][Rx]                         (bevCumulSp) */
+    RTD_FETCH_FIRST_INSIDE = 2,  /* int   [Ry][Rx] */
+    RTD_FETCH_FIRST_OUTSIDE = 3, /* int   [Ry][Rx] */
+    RTD_FETCH_WEPL_MIN = 4,      /* float [steps] */
+    RTD_FETCH_RAY_WEIGHTS = 5,   /* float [L][Ry][Rx] */
+    RTD_FETCH_IDD = 6,           /* float [nz][Ry][Rx] of one layer, nz = Zg - beamFirstInside, slice 0 = step beamFirstInside */
+    RTD_FETCH_RSIGMA = 7,        /* float [nz][Ry][Rx] of one layer */
+    RTD_FETCH_FIRST_PASSIVE = 8, /* int   [Ry][Rx] of one layer */
+    RTD_FETCH_BEV_DOSE = 9,      /* float [Zg][Ry+64][Rx+64] */
+    RTD_FETCH_TILE_RADIUS = 10   /* uint8 [nz][Ry/8][Rx/32] of one layer (own radius, before batching) */
+} rtd_fetch_what;
+
+void        rtd_default_opts(rtd_opts* o);
+rtd_status  rtd_create(rtd_ctx** out, int device);
+void        rtd_destroy(rtd_ctx* ctx);
+const char* rtd_last_error(const rtd_ctx* ctx);   /* message of the last non-OK status ("" if none) */
+const char* rtd_version(void);
+
+/* Uploads the LUTs (textures: IDD 2-D clamp, density/SP/1/X0 1-D clamp; src/kernel_wrapper.cu:453-537). */
+rtd_status rtd_set_luts(rtd_ctx* ctx, const rtd_luts* luts);
+/* Uploads the CT (3-D texture, linear, border; src/kernel_wrapper.cu:420-451). huPlus1000 is a HOST pointer. */
+rtd_status rtd_set_ct(rtd_ctx* ctx, const float* huPlus1000, int nx, int ny, int nz);
+/* Same, from a DEVICE pointer (device-resident benchmarking / multi-GPU broadcast). */
+rtd_status rtd_set_ct_device(rtd_ctx* ctx, const float* dHuPlus1000, int nx, int ny, int nz);
+/* Declares the dose grid dims (the reference takes them from doseVol->getDims()). */
+rtd_status rtd_set_dose_grid(rtd_ctx* ctx, int nx, int ny, int nz);
+
+/* The dose call. doseInOut: HOST float[nz][ny][nx], accumulated in place (H2D + all beams + D2H inside). */
+rtd_status rtd_dose(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* doseInOut,
+                    const rtd_opts* opts, rtd_timing* timing);
+/* Same with a DEVICE dose buffer (accumulated in place, no host copies of the dose); the call returns after the
+ * context's stream has been synchronised. */
+rtd_status rtd_dose_device(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* dDoseInOut,
+                           const rtd_opts* opts, rtd_timing* timing);
+
+/* Integer/index outputs of the last call (the reference's bit-exact quantities). */
+rtd_status rtd_get_beam_report(const rtd_ctx* ctx, int beamNo, rtd_beam_report* out);
+rtd_status rtd_get_layer_report(const rtd_ctx* ctx, int beamNo, int layerNo, rtd_layer_report* out);
+/* Copies an intermediate of the last call to host memory (needs opts.keepIntermediates=1 for per-layer arrays). */
+rtd_status rtd_debug_fetch(rtd_ctx* ctx, int beamNo, rtd_fetch_what what, int layerNo, void* dst, size_t dstBytes);
+
+/* The CUDA stream (cudaStream_t) all work of this context is issued on, for callers that order NCCL /
+ * torch work after rtd_dose_device. */
+void* rtd_stream(rtd_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RTDOSE_H */

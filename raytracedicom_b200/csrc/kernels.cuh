@@ -1,0 +1,582 @@
+// sm_100a kernels of the proton pencil-beam dose path. New code; the arithmetic of every quantity that feeds
+// an integer output of the reference (WEPL, sigma recurrence, ray weights, tile radius) is pinned with
+// explicit PTX so it evaluates the reference's formulas with the same roundings as the reference's own
+// compiled kernels (checked against its PTX: mul/add/fma .ftz, div.approx, sqrt.approx, lg2/ex2.approx).
+//
+// Reference formulas restated (all under /root/reference/src):
+//   K1  trace_bev_kernel      <- fillBevDensityAndSp kernel_wrapper.cu:130-187, density_and_sp_tracer_params.cu:15-36
+//       slice_reduce_kernel   <- sliceMinVar/sliceMaxVar kernel_wrapper.cuh:173-244 (launches cu:781-790)
+//   K3a spot_to_ray_kernel    <- xConvGathResampGpu / yConvGathResampGpu gpu_convolution_2d.cu:16-59
+//   K2  idd_sigma_kernel      <- fillIddAndSigma kernel_wrapper.cu:189-379, fill_idd_and_sigma_params.cu:28-83
+//       tile_radius_kernel    <- tileRadCalc kernel_wrapper.cuh:256-313 ; batch_kernel <- host batching cu:966-976
+//   K3b ks_kernel             <- kernelSuperposition<rad> kernel_wrapper.cuh:432-489
+//   K4  bev_to_grid_kernel    <- primTransfDiv kernel_wrapper.cu:69-97, transfer_param_struct_div3.cu:22-34
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "host_geom.hpp"
+
+namespace rtd {
+
+// ---------------------------------------------------------------------------------------------------------
+// pinned fp32 arithmetic
+__device__ __forceinline__ float f_add(float a, float b) { float r; asm("add.ftz.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b)); return r; }
+__device__ __forceinline__ float f_sub(float a, float b) { float r; asm("sub.ftz.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b)); return r; }
+__device__ __forceinline__ float f_mul(float a, float b) { float r; asm("mul.ftz.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b)); return r; }
+__device__ __forceinline__ float f_fma(float a, float b, float c) { float r; asm("fma.rn.ftz.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c)); return r; }
+__device__ __forceinline__ float f_div(float a, float b) { float r; asm("div.approx.ftz.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b)); return r; }
+__device__ __forceinline__ float f_sqrt(float a) { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a)); return r; }
+__device__ __forceinline__ float f_rsqrt(float a) { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a)); return r; }
+__device__ __forceinline__ float f_lg2(float a) { float r; asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a)); return r; }
+__device__ __forceinline__ float f_ex2(float a) { float r; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a)); return r; }
+__device__ __forceinline__ float f_neg(float a) { float r; asm("neg.ftz.f32 %0, %1;" : "=f"(r) : "f"(a)); return r; }
+__device__ __forceinline__ float f_abs(float a) { float r; asm("abs.ftz.f32 %0, %1;" : "=f"(r) : "f"(a)); return r; }
+__device__ __forceinline__ float f_ceil(float a) { float r; asm("cvt.rpi.ftz.f32.f32 %0, %1;" : "=f"(r) : "f"(a)); return r; }
+__device__ __forceinline__ int f_toint_rz(float a) { int r; asm("cvt.rzi.ftz.s32.f32 %0, %1;" : "=r"(r) : "f"(a)); return r; }
+__device__ __forceinline__ float u2f(unsigned a) { float r; asm("cvt.rn.f32.u32 %0, %1;" : "=f"(r) : "r"(a)); return r; }
+__device__ __forceinline__ float i2f(int a) { float r; asm("cvt.rn.f32.s32 %0, %1;" : "=f"(r) : "r"(a)); return r; }
+
+__device__ __forceinline__ float warp_min(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fminf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+__device__ __forceinline__ int warp_max_i(int v) { return __reduce_max_sync(0xffffffffu, v); }
+__device__ __forceinline__ int warp_min_i(int v) { return __reduce_min_sync(0xffffffffu, v); }
+
+// ---------------------------------------------------------------------------------------------------------
+// K1: fan-beam density / WEPL tracer.
+// One CTA = 32 x-adjacent rays (one warp width, so CT and LUT texture fetches of a warp are spatially coherent)
+// x 9 warps: warps 0..7 each fetch TR_CH consecutive depth samples per round (8 independent tex3D + 16 tex1D
+// in flight per thread), stage stopping power and HU in shared memory, and warp 8 performs the strictly
+// sequential WEPL / entry / exit scan of the previous round (the reference's per-thread serial loop,
+// cu:151-184, needs exactly this summation order for bit-identical WEPL). Position is advanced by repeated
+// addition like the reference (cu:183) so sample positions are bit-identical too.
+constexpr int TR_CH = 8;
+constexpr int TR_NW = 8;
+constexpr int TR_ROUND = TR_CH * TR_NW;
+constexpr int TR_THREADS = (TR_NW + 1) * 32;
+
+__global__ void __launch_bounds__(TR_THREADS)
+trace_bev_kernel(const TraceParams p, cudaTextureObject_t ctTex, cudaTextureObject_t densTex, cudaTextureObject_t spTex,
+                 float* __restrict__ density, float* __restrict__ wepl, int* __restrict__ firstInside,
+                 int* __restrict__ firstOutside, const int Rx, const int R) {
+    __shared__ float sSp[2][TR_ROUND][32];
+    __shared__ float sHu[2][TR_ROUND][32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int ray = blockIdx.x * 32 + lane;
+    const int ix = ray % Rx, iy = ray / Rx;
+    const int S = (int)p.steps;
+    const int nRounds = (S + TR_ROUND - 1) / TR_ROUND;
+    const float fi = i2f(ix), fj = i2f(iy);
+
+    if (warp < TR_NW) {
+        // getStart (density_and_sp_tracer_params.cu:15) + HALF, getInc (cu:17)
+        const float s1 = f_sub(1.0f, f_div(p.corner.z, p.distX));
+        const float s2 = f_sub(1.0f, f_div(p.corner.z, p.distY));
+        float px = f_add(f_add(p.transl.x, f_fma(f_mul(p.coefIdxI.x, fi), s1, f_mul(f_mul(p.coefIdxJ.x, fj), s2))), 0.5f);
+        float py = f_add(f_add(p.transl.y, f_fma(f_mul(p.coefIdxI.y, fi), s1, f_mul(f_mul(p.coefIdxJ.y, fj), s2))), 0.5f);
+        float pz = f_add(f_add(f_fma(f_mul(p.coefIdxI.z, fi), s1, f_mul(f_mul(p.coefIdxJ.z, fj), s2)), p.transl.z), 0.5f);
+        const float dx = f_mul(f_sub(f_sub(p.coefOffset.x, f_div(f_mul(p.coefIdxI.x, fi), p.distX)), f_div(f_mul(p.coefIdxJ.x, fj), p.distY)), p.delta.z);
+        const float dy = f_mul(f_sub(f_sub(p.coefOffset.y, f_div(f_mul(p.coefIdxI.y, fi), p.distX)), f_div(f_mul(p.coefIdxJ.y, fj), p.distY)), p.delta.z);
+        const float dz = f_mul(f_sub(f_sub(p.coefOffset.z, f_div(f_mul(p.coefIdxI.z, fi), p.distX)), f_div(f_mul(p.coefIdxJ.z, fj), p.distY)), p.delta.z);
+        for (int i = 0; i < warp * TR_CH; ++i) { px = f_add(dx, px); py = f_add(dy, py); pz = f_add(dz, pz); }
+        for (int r = 0; r <= nRounds; ++r) {
+            if (r < nRounds) {
+                const int base = r * TR_ROUND + warp * TR_CH;
+                float hu[TR_CH];
+#pragma unroll
+                for (int j = 0; j < TR_CH; ++j) {
+                    hu[j] = tex3D<float>(ctTex, px, py, pz);
+                    px = f_add(dx, px); py = f_add(dy, py); pz = f_add(dz, pz);
+                }
+#pragma unroll
+                for (int j = 0; j < TR_CH; ++j) {
+                    const float d = tex1D<float>(densTex, f_fma(hu[j], p.densityScale, 0.5f));
+                    const float s = tex1D<float>(spTex, f_fma(hu[j], p.spScale, 0.5f));
+                    if (base + j < S) density[(size_t)(base + j) * R + ray] = d;
+                    sSp[r & 1][warp * TR_CH + j][lane] = s;
+                    sHu[r & 1][warp * TR_CH + j][lane] = hu[j];
+                }
+                for (int i = 0; i < TR_ROUND - TR_CH; ++i) { px = f_add(dx, px); py = f_add(dy, py); pz = f_add(dz, pz); }
+            }
+            __syncthreads();
+        }
+    } else {
+        // stepLen (density_and_sp_tracer_params.cu:32-36)
+        const float ddx = f_div(f_fma(p.delta.x, fi, p.corner.x), p.distX);
+        const float ddy = f_div(f_fma(p.delta.y, fj, p.corner.y), p.distY);
+        const float stepLen = f_mul(f_abs(p.delta.z), f_sqrt(f_fma(ddy, ddy, f_fma(ddx, ddx, 1.0f))));
+        float cumSp = 0.0f, cumHu = 0.0f;
+        int before = -1, last = -1;
+        for (int r = 0; r <= nRounds; ++r) {
+            if (r > 0) {
+                const int base = (r - 1) * TR_ROUND;
+                const int n = min(TR_ROUND, S - base);
+#pragma unroll 8
+                for (int s = 0; s < n; ++s) {
+                    const float hu = sHu[(r - 1) & 1][s][lane];
+                    const float sp = sSp[(r - 1) & 1][s][lane];
+                    cumHu = f_add(cumHu, hu);
+                    cumSp = f_fma(stepLen, sp, cumSp);
+                    if (cumHu < 150.0f) before = base + s;
+                    if (hu > 150.0f) last = base + s;
+                    wepl[(size_t)(base + s) * R + ray] = cumSp;
+                }
+            }
+            __syncthreads();
+        }
+        firstInside[ray] = before + 1;
+        firstOutside[ray] = last + 1;
+    }
+}
+
+// Per-depth-slice minimum WEPL plus the beam-wide entry / exit steps (three reference launches + three D2H
+// copies, cu:781-790, become one launch and one copy). grid = steps, block = 256. out: [0]=min firstInside,
+// [1]=max firstOutside, weplMin[steps].
+__global__ void __launch_bounds__(256)
+slice_reduce_kernel(const float* __restrict__ wepl, const int* __restrict__ firstInside, const int* __restrict__ firstOutside,
+                    const int R, float* __restrict__ weplMin, int* __restrict__ beamFirstInside, int* __restrict__ beamFirstOutside) {
+    __shared__ float sMin[8];
+    __shared__ int sA[8], sB[8];
+    const int k = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const float4* row = reinterpret_cast<const float4*>(wepl + (size_t)k * R);
+    float m = __int_as_float(0x7f800000);
+    for (int i = threadIdx.x; i < R / 4; i += 256) { const float4 v = row[i]; m = fminf(fminf(m, v.x), fminf(v.y, fminf(v.z, v.w))); }
+    m = warp_min(m);
+    if (lane == 0) sMin[warp] = m;
+    if (k == 0) {
+        int a = 0x7fffffff, b = -0x7fffffff;
+        for (int i = threadIdx.x; i < R; i += 256) { a = min(a, firstInside[i]); b = max(b, firstOutside[i]); }
+        a = warp_min_i(a); b = warp_max_i(b);
+        if (lane == 0) { sA[warp] = a; sB[warp] = b; }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float mm = sMin[0];
+        for (int i = 1; i < 8; ++i) mm = fminf(mm, sMin[i]);
+        weplMin[k] = mm;
+        if (k == 0) {
+            int a = sA[0], b = sB[0];
+            for (int i = 1; i < 8; ++i) { a = min(a, sA[i]); b = max(b, sB[i]); }
+            *beamFirstInside = a; *beamFirstOutside = b;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// K3a: spot weights -> ray weights. One CTA = (32 ray columns, one layer): the x-pass result for all Sy spot
+// rows stays in shared memory and the y-pass reads it from there (the reference round-trips an intermediate
+// array through global memory between two launches, gpu_convolution_2d.cu:69-70).
+struct ConvParams {
+    int inW, inH, outW, outH;
+    float pixelSpX, pixelSpY, offX, offY, deltaX, deltaY, cutoff;
+};
+
+__device__ __forceinline__ float conv_weight(float dist, float rSig) {   // gpu_convolution_2d.cu:28
+    return f_mul(f_sub(erff(f_mul(rSig, f_add(dist, 0.5f))), erff(f_mul(rSig, f_add(dist, -0.5f)))), 0.5f);
+}
+
+__global__ void __launch_bounds__(256)
+spot_to_ray_kernel(const float* __restrict__ in, const float2* __restrict__ sigmas, float* __restrict__ out, const ConvParams c) {
+    extern __shared__ float sInterm[];   // [inH][32]
+    const int layer = blockIdx.y;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int ox = blockIdx.x * 32 + tx;
+    const float2 sg = sigmas[layer];
+    {   // x pass (gpu_convolution_2d.cu:16-35)
+        const float sigEff = f_div(sg.x, c.pixelSpX);
+        const float rSig = f_div(f_rsqrt(2.0f), sigEff);
+        const float lim = f_fma(sigEff, c.cutoff, 0.5f);
+        const float fo = i2f(ox);
+        const int c0 = f_toint_rz(f_ceil(f_div(f_sub(f_sub(fo, lim), c.offX), c.deltaX)));
+        for (int y = ty; y < c.inH; y += 8) {
+            const float* rowp = in + ((size_t)layer * c.inH + y) * c.inW;
+            float res = 0.0f;
+            int ci = c0;
+            float dist = f_sub(f_fma(c.deltaX, i2f(ci), c.offX), fo);
+            while (dist < lim) {
+                if (ci >= 0 && ci < c.inW) res = f_fma(rowp[ci], conv_weight(dist, rSig), res);
+                ++ci;
+                dist = f_sub(f_fma(c.deltaX, i2f(ci), c.offX), fo);
+            }
+            sInterm[y * 32 + tx] = res;
+        }
+    }
+    __syncthreads();
+    {   // y pass (gpu_convolution_2d.cu:37-59)
+        const float sigEff = f_div(sg.y, c.pixelSpY);
+        const float rSig = f_div(f_rsqrt(2.0f), sigEff);
+        const float lim = f_fma(sigEff, c.cutoff, 0.5f);
+        for (int oy = ty; oy < c.outH; oy += 8) {
+            const float fo = i2f(oy);
+            int ci = f_toint_rz(f_ceil(f_div(f_sub(f_sub(fo, lim), c.offY), c.deltaY)));
+            float res = 0.0f;
+            float dist = f_sub(f_fma(c.deltaY, i2f(ci), c.offY), fo);
+            while (dist < lim) {
+                if (ci >= 0 && ci < c.inH) res = f_fma(sInterm[ci * 32 + tx], conv_weight(dist, rSig), res);
+                ++ci;
+                dist = f_sub(f_fma(c.deltaY, i2f(ci), c.offY), fo);
+            }
+            out[((size_t)layer * c.outH + oy) * c.outW + ox] = res;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// K2: integrated depth dose + lateral sigma for ALL energy layers in one launch (grid.z = layer; the
+// reference launches once per layer and syncs with the host three times per layer, cu:916-976).
+struct LayerParams {          // per-layer constants, kernel_wrapper.cu:829-849, 922-925
+    float energyIdx, energyScale, peakDepth;
+    int afterLast;
+};
+struct IddParams {
+    FillGeom g;
+    float rrlScale, bpCutoff, rayWeightCutoff;
+    int first;                // beamFirstInside
+    int nz;                   // Zg - first: slices kept per layer
+    int Rx, Ry;
+    int nozzle;
+};
+
+__global__ void __launch_bounds__(256)
+idd_sigma_kernel(const float* __restrict__ density, const float* __restrict__ wepl, const float* __restrict__ rayWeights,
+                 const int* __restrict__ firstInside, const int* __restrict__ firstOutside,
+                 const LayerParams* __restrict__ layers, const IddParams q,
+                 cudaTextureObject_t iddTex, cudaTextureObject_t rrlTex,
+                 float* __restrict__ idd, float* __restrict__ rsig, float* __restrict__ rowMin,
+                 int* __restrict__ firstPassive, int* __restrict__ layerFirstPassive) {
+    const int l = blockIdx.z;
+    const int x = blockIdx.x * 32 + (threadIdx.x & 31);
+    const int y = blockIdx.y * 8 + (threadIdx.x >> 5);
+    const int R = q.Rx * q.Ry;
+    const int ray = y * q.Rx + x;
+    const LayerParams lp = layers[l];
+    const unsigned first = (unsigned)q.first;
+
+    const int firstIn = firstInside[ray];
+    unsigned afterLast = (unsigned)min(firstOutside[ray], lp.afterLast);
+    const float rayWeight = rayWeights[(size_t)l * R + ray];
+    bool live = true;
+    if (rayWeight < q.rayWeightCutoff || afterLast < first) { live = false; afterLast = 0; }
+
+    // initStepAndAirDiv (fill_idd_and_sigma_params.cu:28-40) with the device-side sigmaSqAirCoefs (cu:74-83)
+    float ca = 0.0f, cb = 0.0f;
+    if (q.nozzle) { ca = f_div(0.00270f, f_add(lp.peakDepth, -4.50f)); cb = f_div(-4.39f, f_add(lp.peakDepth, -3.86f)); }
+    const float dzs = q.g.delta.z;
+    const float airQuad = f_mul(dzs, f_mul(ca, dzs));
+    const float airLin = f_fma(cb, dzs, f_mul(q.g.corner.z, f_mul(f_add(ca, ca), dzs)));
+    const float stepLength = f_abs(dzs);
+
+    float incScat = 0.0f, incinc = 0.0f;
+    float incDiv = f_fma(airQuad, f_fma(u2f(first), 2.0f, -1.0f), airLin);
+    float sigmaSq = f_neg(incDiv);
+    float res = 0.0f, rs = 0.0f, wOld = 0.0f, dOld = 0.0f;
+    const float thr = f_mul(lp.peakDepth, q.bpCutoff);
+    const float inf = __int_as_float(0x7f800000);
+
+    size_t inIdx = (size_t)first * R + ray;
+    size_t outIdx = (size_t)l * q.nz * R + ray;
+    size_t rmIdx = ((size_t)l * q.nz * q.Ry + y) * (q.Rx / 32) + blockIdx.x;
+    const int lane = threadIdx.x & 31;
+    for (unsigned k = first; k < (unsigned)lp.afterLast; ++k) {
+        if (live) {
+            const float w = wepl[inIdx];
+            const float d = tex2D<float>(iddTex, f_fma(w, lp.energyScale, 0.5f), f_add(lp.energyIdx, 0.5f));
+            const float rho = density[inIdx];
+            if (w < lp.peakDepth) {
+                const float resE = f_ex2(f_mul(f_lg2(f_sub(lp.peakDepth, f_mul(f_add(wOld, w), 0.5f))), 0.5649718f));
+                const float e1 = f_fma(resE, 8.639415f, 938.3f);
+                const float betaP = f_sub(e1, f_div(880406.875f, e1));
+                const float rRl = f_mul(rho, tex1D<float>(rrlTex, f_fma(rho, q.rrlScale, 0.5f)));
+                const float t1 = f_mul(f_div(198.81f, f_mul(betaP, betaP)), stepLength);
+                const float thetaSq = f_mul(rRl, t1);
+                sigmaSq = f_add(sigmaSq, f_add(incScat, incDiv));
+                incinc = f_fma(stepLength, f_mul(stepLength, f_fma(rRl, t1, thetaSq)), incinc);
+                incScat = f_add(incScat, incinc);
+                incDiv = f_fma(airQuad, 2.0f, incDiv);
+            } else {
+                sigmaSq = f_fma(f_mul(f_add(incScat, incDiv), -1.5f), rho, sigmaSq);
+            }
+            // voxelWidth(k) (fill_idd_and_sigma_params.cu:42-46), stepVol(k) (cu:72)
+            const float fk = u2f(k);
+            const float zk = f_fma(q.g.delta.z, fk, q.g.corner.z);
+            const float vwx = f_mul(q.g.delta.x, f_sub(1.0f, f_div(zk, q.g.distX)));
+            const float vwy = f_mul(q.g.delta.y, f_sub(1.0f, f_div(zk, q.g.distY)));
+            rs = f_div(f_mul(f_add(vwx, vwy), 0.5f), f_mul(f_add(f_sqrt(sigmaSq), 0.21f), 1.41421356f));
+            const bool within = !(w > thr);
+            live = within && (k != afterLast);
+            afterLast = within ? afterLast : k;
+            const float vol = f_fma(q.g.volSq, u2f(k * k), f_fma(q.g.volLin, fk, q.g.volConst));
+            const float mass = f_mul(f_sub(w, wOld), vol);
+            if (mass > 1e-2f) res = f_div(f_mul(rayWeight, f_sub(d, dOld)), mass);
+            wOld = w; dOld = d;
+        }
+        const bool keep = live && ((int)k >= firstIn - 1);
+        res = keep ? res : 0.0f;
+        rs = keep ? rs : inf;
+        idd[outIdx] = res;
+        rsig[outIdx] = rs;
+        const float m = warp_min(rs);
+        if (lane == 0) rowMin[rmIdx] = m;
+        inIdx += R; outIdx += R; rmIdx += (size_t)q.Ry * (q.Rx / 32);
+    }
+    firstPassive[(size_t)l * R + ray] = (int)afterLast;
+    const int wm = warp_max_i((int)afterLast);
+    if (lane == 0) atomicMax(layerFirstPassive + l, wm);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Tile radius (own radius of every live 32x8 tile) + per-layer 34-bin histogram. One thread per (tile, slice);
+// grid = (ceil(nz*tiles/256), L).
+__global__ void __launch_bounds__(256)
+tile_radius_kernel(const float* __restrict__ rowMin, const int* __restrict__ layerFirstPassive, const int first, const int nz,
+                   const int Rx, const int Ry, const float ksCutoff, uint8_t* __restrict__ radMap, int* __restrict__ hist) {
+    __shared__ int sHist[34];
+    const int l = blockIdx.y;
+    if (threadIdx.x < 34) sHist[threadIdx.x] = 0;
+    __syncthreads();
+    const int tilesX = Rx / 32, tilesY = Ry / 8, tiles = tilesX * tilesY;
+    const int nLive = min(max(layerFirstPassive[l] - first, 0), nz);
+    const int idx = blockIdx.x * 256 + threadIdx.x;
+    if (idx < nz * tiles) {
+        const int kk = idx / tiles, t = idx % tiles, tx = t % tilesX, ty = t / tilesX;
+        uint8_t r8 = 255;
+        if (kk < nLive) {
+            const float* p = rowMin + (((size_t)l * nz + kk) * Ry + ty * 8) * tilesX + tx;
+            float m = p[0];
+#pragma unroll
+            for (int i = 1; i < 8; ++i) { const float v = p[(size_t)i * tilesX]; if (v < m) m = v; }
+            // kernel_wrapper.cuh:303
+            const unsigned rad = min((unsigned)f_toint_rz(f_add(f_div(ksCutoff, f_mul(f_sqrt(2.0f), m)), 0.5f)), 33u);
+            r8 = (uint8_t)rad;
+            atomicAdd(&sHist[rad], 1);
+        }
+        radMap[((size_t)l * nz + kk) * tiles + t] = r8;
+    }
+    __syncthreads();
+    if (threadIdx.x < 34 && sHist[threadIdx.x]) atomicAdd(hist + l * 34 + threadIdx.x, sHist[threadIdx.x]);
+}
+
+// Batching rule of the reference's host loop (kernel_wrapper.cu:966-976) evaluated on the device, plus the
+// work-list layout: tiles are ordered by descending applied radius (heavy work first).
+// block = 64 threads, thread l handles layer l. stats: [0]=error flag (radius>32), [1]=total live tiles.
+__global__ void batch_kernel(const int* __restrict__ hist, const int L, const int minTiles, int* __restrict__ batchRad,
+                             int* __restrict__ rbCount /*[33]*/, int* __restrict__ stats) {
+    __shared__ int sCount[33];
+    if (threadIdx.x < 33) sCount[threadIdx.x] = 0;
+    __syncthreads();
+    for (int l = threadIdx.x; l < L; l += blockDim.x) {
+        const int* c = hist + l * 34;
+        int* rb = batchRad + l * 34;
+        int layerMax = 0;
+        for (int i = 0; i < 34; ++i) { rb[i] = i; if (c[i] > 0) layerMax = i; }
+        if (c[33] > 0) atomicExch(&stats[0], 1);
+        int rec = min(layerMax, 32), acc = 0;
+        atomicAdd(&sCount[0], c[0]);
+        for (int rad = min(layerMax, 32); rad > 0; --rad) {
+            acc += c[rad];
+            rb[rad] = rec;
+            atomicAdd(&sCount[rec], c[rad]);
+            if (acc >= minTiles) { rec = rad - 1; acc = 0; }
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        // offsets in descending-radius order: rbCount[r] becomes the start offset of radius r
+        int off = 0;
+        for (int r = 32; r >= 0; --r) { const int n = sCount[r]; rbCount[r] = off; off += n; }
+        stats[1] = off;
+    }
+}
+
+// Work list: one packed entry per live tile: layer<<24 | slice<<12 | tile.
+__global__ void __launch_bounds__(256)
+fill_list_kernel(const uint8_t* __restrict__ radMap, const int* __restrict__ batchRad, const int* __restrict__ rbOffset,
+                 int* __restrict__ rbCursor, const int nz, const int tiles, uint32_t* __restrict__ list) {
+    const int l = blockIdx.y;
+    const int idx = blockIdx.x * 256 + threadIdx.x;
+    if (idx >= nz * tiles) return;
+    const unsigned r = radMap[(size_t)l * nz * tiles + idx];
+    if (r > 32) return;
+    const int rb = batchRad[l * 34 + r];
+    const int pos = rbOffset[rb] + atomicAdd(rbCursor + rb, 1);
+    list[pos] = ((uint32_t)l << 24) | ((uint32_t)(idx / tiles) << 12) | (uint32_t)(idx % tiles);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// K3b: kernel superposition. out[Y][X] += dose(x,y) e_xy[|X-x|] e_xy[|Y-y|] over the 32x8 sources of a tile with
+// the erf-difference weights of cuh:459-467 and the batch radius RB.
+// Formulation: output-row stationary. Thread q owns output row Y = q-RB of the (8+2RB) x (32+2RB) patch and keeps
+// a sliding window of 2RB+1 column accumulators in registers; all lanes of a warp walk the SAME source at the same
+// time, so the source's horizontal weights e[0..RB] are warp-uniform 128-bit shared-memory broadcasts feeding
+// 2RB+1 FMAs each, and only the vertical weight is lane-specific. Finished columns leave the window into a
+// shared patch that is added to the haloed BEV dose with coalesced reductions.
+struct KsParams {
+    const float* idd; const float* rsig; float* bev;
+    const uint32_t* list; const int* batchRad; const uint8_t* radMap;
+    int Rx, Ry, nz, first, tilesX, tiles;
+};
+
+__host__ __device__ constexpr int ks_str(int rb) { return (((rb + 1 + 3) / 4 * 4) % 8 == 0) ? ((rb + 1 + 3) / 4 * 4 + 4) : ((rb + 1 + 3) / 4 * 4); }
+__host__ __device__ constexpr int ks_smem_floats(int rb) { return 256 * ks_str(rb) + 256 + (8 + 2 * rb) * (32 + 2 * rb + 1); }
+
+template <int NT, int RB>
+__device__ __forceinline__ void ks_tile(const KsParams& p, const int l, const int kk, const int tile, float* smem) {
+    constexpr int STR = ks_str(RB);
+    constexpr int NR = 8 + 2 * RB, NC = 32 + 2 * RB, NCP = NC + 1, W = 2 * RB + 1;
+    float* sE = smem;                  // [256][STR]
+    float* sD = smem + 256 * STR;      // [256]
+    float* sO = sD + 256;              // [NR][NCP]
+    const int tid = threadIdx.x;
+    const int tx = tile % p.tilesX, ty = tile / p.tilesX;
+    const int R = p.Rx * p.Ry;
+    const size_t src0 = ((size_t)l * p.nz + kk) * R + (size_t)(ty * 8) * p.Rx + tx * 32;
+    for (int s = tid; s < 256; s += NT) {
+        const size_t gi = src0 + (size_t)(s >> 5) * p.Rx + (s & 31);
+        const float dose = p.idd[gi];
+        const float r = p.rsig[gi];
+        sD[s] = dose;
+        float erfNew = erff(r * 0.5f), erfOld = -erfNew;       // cuh:459-467
+        float e[STR];
+#pragma unroll
+        for (int i = 0; i < STR; ++i) {
+            if (i <= RB) {
+                e[i] = 0.5f * (erfNew - erfOld);
+                erfOld = erfNew;
+                erfNew = erff(r * (float(i) + 1.5f));
+            } else e[i] = 0.0f;
+        }
+#pragma unroll
+        for (int i = 0; i < STR; i += 4) *reinterpret_cast<float4*>(sE + s * STR + i) = make_float4(e[i], e[i + 1], e[i + 2], e[i + 3]);
+    }
+    __syncthreads();
+    if (tid < NR) {
+        const int q = tid;
+        float win[W];
+#pragma unroll
+        for (int j = 0; j < W; ++j) win[j] = 0.0f;
+        float* orow = sO + q * NCP;
+        for (int x = 0; x < 32; ++x) {
+#pragma unroll
+            for (int y = 0; y < 8; ++y) {
+                const int s = y * 32 + x;
+                const int dyv = abs(q - RB - y);
+                const float ey = sE[s * STR + min(dyv, RB)];
+                const float hy = (dyv <= RB) ? sD[s] * ey : 0.0f;
+                float ex[STR];
+#pragma unroll
+                for (int i = 0; i < STR; i += 4) {
+                    const float4 v = *reinterpret_cast<const float4*>(sE + s * STR + i);
+                    ex[i] = v.x; ex[i + 1] = v.y; ex[i + 2] = v.z; ex[i + 3] = v.w;
+                }
+#pragma unroll
+                for (int j = 0; j < W; ++j) win[j] = fmaf(hy, ex[(j < RB) ? (RB - j) : (j - RB)], win[j]);
+            }
+            orow[x] = win[0];
+#pragma unroll
+            for (int j = 0; j + 1 < W; ++j) win[j] = win[j + 1];
+            win[W - 1] = 0.0f;
+        }
+#pragma unroll
+        for (int j = 0; j + 1 < W; ++j) orow[32 + j] = win[j];
+    }
+    __syncthreads();
+    const int pitch = p.Rx + 64;
+    float* out = p.bev + ((size_t)(kk + p.first) * (p.Ry + 64) + (ty * 8 + 32 - RB)) * pitch + tx * 32 + 32 - RB;
+    for (int i = tid; i < NR * NC; i += NT) {
+        const int rr = i / NC, cc = i - rr * NC;
+        const float v = sO[rr * NCP + cc];
+        if (v != 0.0f) atomicAdd(out + (size_t)rr * pitch + cc, v);
+    }
+    __syncthreads();
+}
+
+template <int NT, int RLO, int RHI>
+__global__ void __launch_bounds__(NT)
+ks_kernel(const KsParams p, const int* __restrict__ rbOffset, const int* __restrict__ stats, int* __restrict__ workCounter) {
+    extern __shared__ __align__(16) float smem[];
+    __shared__ int sItem;
+    // list is ordered by descending radius: this launch covers radii [RLO, RHI]
+    const int start = rbOffset[RHI];
+    const int end = (RLO == 0) ? stats[1] : rbOffset[RLO - 1];
+    for (;;) {
+        if (threadIdx.x == 0) sItem = start + atomicAdd(workCounter, 1);
+        __syncthreads();
+        const int item = sItem;
+        __syncthreads();
+        if (item >= end) break;
+        const uint32_t e = p.list[item];
+        const int l = e >> 24, kk = (e >> 12) & 0xfff, tile = e & 0xfff;
+        const int rad = p.radMap[((size_t)l * p.nz + kk) * p.tiles + tile];
+        const int rb = p.batchRad[l * 34 + rad];
+        switch (rb) {
+#define RTD_KS_CASE(N) case N: if (N >= RLO && N <= RHI) ks_tile<NT, (N >= RLO && N <= RHI) ? N : RLO>(p, l, kk, tile, smem); break;
+            RTD_KS_CASE(0) RTD_KS_CASE(1) RTD_KS_CASE(2) RTD_KS_CASE(3) RTD_KS_CASE(4) RTD_KS_CASE(5) RTD_KS_CASE(6) RTD_KS_CASE(7)
+            RTD_KS_CASE(8) RTD_KS_CASE(9) RTD_KS_CASE(10) RTD_KS_CASE(11) RTD_KS_CASE(12) RTD_KS_CASE(13) RTD_KS_CASE(14) RTD_KS_CASE(15)
+            RTD_KS_CASE(16) RTD_KS_CASE(17) RTD_KS_CASE(18) RTD_KS_CASE(19) RTD_KS_CASE(20) RTD_KS_CASE(21) RTD_KS_CASE(22) RTD_KS_CASE(23)
+            RTD_KS_CASE(24) RTD_KS_CASE(25) RTD_KS_CASE(26) RTD_KS_CASE(27) RTD_KS_CASE(28) RTD_KS_CASE(29) RTD_KS_CASE(30) RTD_KS_CASE(31)
+            RTD_KS_CASE(32)
+#undef RTD_KS_CASE
+            default: break;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// K4: BEV dose -> dose grid, gather with trilinear interpolation straight from the linear haloed BEV volume
+// (no copy into a cudaArray, cu:1107-1141). The texture unit's filter is reproduced: sample at c-0.5, weights
+// quantised to 8 fractional bits, texels outside [first, zEnd) x [0,H) x [0,W) read as 0 (border mode).
+struct GridParams {
+    TransferParams t;
+    int minX, minY, minZ, maxX, maxY, maxZ;   // inclusive bbox in dose indices
+    int nx, ny, nz;                           // dose dims
+    int W, H, first, zEnd;                    // BEV dims (haloed) and valid slice range [first, zEnd)
+};
+
+__device__ __forceinline__ float tex_frac(float f) {   // 9-bit fixed point weight (8 fractional bits)
+    return floorf(f * 256.0f + 0.5f) * (1.0f / 256.0f);
+}
+
+__device__ __forceinline__ float bev_fetch(const float* __restrict__ bev, const GridParams& g, int x, int y, int z) {
+    if ((unsigned)x >= (unsigned)g.W || (unsigned)y >= (unsigned)g.H || z < 0 || z >= g.zEnd - g.first) return 0.0f;
+    return bev[((size_t)(z + g.first) * g.H + y) * g.W + x];
+}
+
+__global__ void __launch_bounds__(256)
+bev_to_grid_kernel(const float* __restrict__ bev, float* __restrict__ dose, const GridParams g) {
+    const int x = g.minX + blockIdx.x * 32 + (threadIdx.x & 31);
+    const int y = g.minY + blockIdx.y * 8 + (threadIdx.x >> 5);
+    if (x >= g.nx || y >= g.ny) return;
+    // init(i,j) (transfer_param_struct_div3.cu:22-25)
+    const float fi = i2f(x), fj = i2f(y);
+    const float sx = f_add(f_fma(g.t.coefIdxI.x, fi, f_mul(g.t.coefIdxJ.x, fj)), g.t.coefOffset.x);
+    const float sy = f_add(f_fma(g.t.coefIdxI.y, fi, f_mul(g.t.coefIdxJ.y, fj)), g.t.coefOffset.y);
+    const float sz = f_add(f_fma(g.t.coefIdxI.z, fi, f_mul(g.t.coefIdxJ.z, fj)), g.t.coefOffset.z);
+    float* res = dose + ((size_t)g.minZ * g.ny + y) * g.nx + x;
+    const size_t zs = (size_t)g.nx * g.ny;
+    for (int z = g.minZ; z <= g.maxZ; ++z, res += zs) {
+        // getFanIdx(k) (cu:27-34) + HALF, then the texture's own -0.5
+        const float fk = i2f(z);
+        const float rx = f_fma(g.t.inc.x, fk, sx), ry = f_fma(g.t.inc.y, fk, sy), rz = f_fma(g.t.inc.z, fk, sz);
+        const float mx = f_add(f_div(rz, f_sub(g.t.normDistX, rz)), 1.0f);
+        const float my = f_add(f_div(rz, f_sub(g.t.normDistY, rz)), 1.0f);
+        const float cx = f_add(f_fma(rx, mx, g.t.globalOffset.x), 0.5f) - 0.5f;
+        const float cy = f_add(f_fma(ry, my, g.t.globalOffset.y), 0.5f) - 0.5f;
+        const float cz = f_add(f_add(rz, g.t.globalOffset.z), 0.5f) - 0.5f;
+        const float flx = floorf(cx), fly = floorf(cy), flz = floorf(cz);
+        const int ix = (int)flx, iy = (int)fly, iz = (int)flz;
+        if (ix < -1 || iy < -1 || iz < -1 || ix >= g.W || iy >= g.H || iz >= g.zEnd - g.first) continue;
+        const float a = tex_frac(cx - flx), b = tex_frac(cy - fly), c = tex_frac(cz - flz);
+        const float v000 = bev_fetch(bev, g, ix, iy, iz), v100 = bev_fetch(bev, g, ix + 1, iy, iz);
+        const float v010 = bev_fetch(bev, g, ix, iy + 1, iz), v110 = bev_fetch(bev, g, ix + 1, iy + 1, iz);
+        const float v001 = bev_fetch(bev, g, ix, iy, iz + 1), v101 = bev_fetch(bev, g, ix + 1, iy, iz + 1);
+        const float v011 = bev_fetch(bev, g, ix, iy + 1, iz + 1), v111 = bev_fetch(bev, g, ix + 1, iy + 1, iz + 1);
+        const float oa = 1.0f - a, ob = 1.0f - b, oc = 1.0f - c;
+        const float v = oc * (ob * (oa * v000 + a * v100) + b * (oa * v010 + a * v110)) +
+                        c * (ob * (oa * v001 + a * v101) + b * (oa * v011 + a * v111));
+        if (v > 0.0f) *res += v;
+    }
+}
+
+}  // namespace rtd

@@ -1,0 +1,587 @@
+// librtdose.so: C ABI (include/rtdose.h) + host orchestration of the dose path.
+// Replaces cudaWrapperProtons() (/root/reference/src/kernel_wrapper.cu:381-1369) with a context that owns all
+// device memory (no per-beam cudaMalloc/cudaFree after the first call), issues every kernel on one stream and
+// synchronises with the host twice per PLAN (the reference blocks ~3 times per energy layer, cu:916-976).
+#include <cstdio>
+#include <cstring>
+#include <cmath>
+#include <string>
+#include <vector>
+#include <algorithm>
+#include "../../include/rtdose.h"
+#include "kernels.cuh"
+
+using namespace rtd;
+
+namespace {
+
+struct DevBuf {
+    void* p = nullptr; size_t cap = 0;
+    cudaError_t ensure(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) { cudaError_t e = cudaFree(p); if (e != cudaSuccess) return e; p = nullptr; cap = 0; }
+        size_t want = bytes + bytes / 8;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e != cudaSuccess) return e;
+        cap = want; return cudaSuccess;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+    template <typename T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+struct PinBuf {
+    void* p = nullptr; size_t cap = 0;
+    cudaError_t ensure(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFreeHost(p);
+        p = nullptr; cap = 0;
+        cudaError_t e = cudaMallocHost(&p, bytes + bytes / 8 + 64);
+        if (e != cudaSuccess) return e;
+        cap = bytes + bytes / 8 + 64; return cudaSuccess;
+    }
+    void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+    template <typename T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+struct TexArr {
+    cudaArray_t arr = nullptr; cudaTextureObject_t tex = 0;
+    void release() { if (tex) cudaDestroyTextureObject(tex); if (arr) cudaFreeArray(arr); tex = 0; arr = nullptr; }
+};
+
+struct BeamWs {
+    // geometry / host results
+    RayGrid grid; int S = 0, L = 0, R = 0, sx = 0, sy = 0;
+    float dist[2]; Affine gtii, gtdi;
+    int bfi = 0, bfo = 0, Zg = 0, nz = 0; bool live = false;
+    float entryZ = 0;
+    std::vector<LayerParams> layers; std::vector<float> entrySig;   // [2L]
+    rtd_beam_report rep; std::vector<rtd_layer_report> lrep;
+    // device
+    DevBuf density, wepl, firstIn, firstOut, weplMin, scalars, spotW, sigmas, rayW, layerDev, idd, rsig, rowMin,
+           firstPassive, lfp, hist, batchRad, rbOffset, rbCursor, stats, work, radMap, list, bev;
+    PinBuf hTrace;   // [2 ints][S floats]
+    PinBuf hStage;   // staging for sigmas + LayerParams uploads and weights
+    PinBuf hOut;     // lfp[L], hist[L*34], batchRad[L*34], stats[4]
+    void release() {
+        DevBuf* all[] = {&density, &wepl, &firstIn, &firstOut, &weplMin, &scalars, &spotW, &sigmas, &rayW, &layerDev, &idd, &rsig,
+                         &rowMin, &firstPassive, &lfp, &hist, &batchRad, &rbOffset, &rbCursor, &stats, &work, &radMap, &list, &bev};
+        for (DevBuf* b : all) b->release();
+        hTrace.release(); hStage.release(); hOut.release();
+    }
+};
+
+}  // namespace
+
+struct rtd_ctx {
+    int device = 0; cudaStream_t stream = nullptr;
+    std::string err;
+    bool haveLuts = false, haveCt = false, haveDose = false;
+    // LUTs (host copies of the small vectors the host logic needs)
+    std::vector<float> energies, peakDepths, scaleFacts;
+    int nEnergySamples = 0, nEnergies = 0; float densScale = 0, spScale = 0, rrlScale = 0;
+    TexArr iddTex, densTex, spTex, rrlTex, ctTex;
+    int ctDims[3] = {0, 0, 0}, doseDims[3] = {0, 0, 0};
+    DevBuf dose;
+    std::vector<BeamWs*> ws;
+    int nBeamsLast = 0;
+    std::vector<cudaEvent_t> events;
+    int smCount = 148;
+    int ksBlocksA = 0, ksBlocksB = 0, ksBlocksC = 0;
+    rtd_opts optsLast;
+};
+
+namespace {
+
+constexpr int KS_NT_A = 64, KS_NT_B = 96, KS_NT_C = 128;
+constexpr size_t KS_SMEM_A = ks_smem_floats(8) * 4, KS_SMEM_B = ks_smem_floats(16) * 4, KS_SMEM_C = ks_smem_floats(32) * 4;
+
+rtd_status fail(rtd_ctx* c, rtd_status s, const std::string& msg) { if (c) c->err = msg; return s; }
+
+#define RTD_CUDA(call)                                                                                           \
+    do {                                                                                                         \
+        cudaError_t e_ = (call);                                                                                 \
+        if (e_ != cudaSuccess) {                                                                                 \
+            char b_[512]; snprintf(b_, sizeof b_, "cudaAssert: %s %s, line: %d", cudaGetErrorString(e_), __FILE__, __LINE__); \
+            return fail(ctx, RTD_ERR_CUDA, b_);                                                                  \
+        }                                                                                                        \
+    } while (0)
+
+cudaError_t makeTexture(TexArr& t, cudaTextureAddressMode mode) {
+    cudaResourceDesc r; memset(&r, 0, sizeof r);
+    r.resType = cudaResourceTypeArray; r.res.array.array = t.arr;
+    cudaTextureDesc d; memset(&d, 0, sizeof d);
+    d.readMode = cudaReadModeElementType; d.normalizedCoords = 0; d.filterMode = cudaFilterModeLinear;
+    d.addressMode[0] = d.addressMode[1] = d.addressMode[2] = mode;
+    return cudaCreateTextureObject(&t.tex, &r, &d, nullptr);
+}
+
+cudaError_t upload1D(TexArr& t, const float* v, int n, cudaStream_t s) {
+    t.release();
+    cudaChannelFormatDesc fd = cudaCreateChannelDesc<float>();
+    cudaError_t e = cudaMallocArray(&t.arr, &fd, n);
+    if (e != cudaSuccess) return e;
+    e = cudaMemcpy2DToArrayAsync(t.arr, 0, 0, v, size_t(n) * 4, size_t(n) * 4, 1, cudaMemcpyHostToDevice, s);
+    if (e != cudaSuccess) return e;
+    return makeTexture(t, cudaAddressModeClamp);
+}
+
+cudaEvent_t ev(rtd_ctx* ctx, size_t i) {
+    while (ctx->events.size() <= i) { cudaEvent_t e; cudaEventCreate(&e); ctx->events.push_back(e); }
+    return ctx->events[i];
+}
+
+rtd_status setCtCommon(rtd_ctx* ctx, const float* src, int nx, int ny, int nz, cudaMemcpyKind kind) {
+    if (!ctx) return RTD_ERR_INVALID;
+    if (!src || nx <= 0 || ny <= 0 || nz <= 0) return fail(ctx, RTD_ERR_INVALID, "rtd_set_ct: null pointer or non-positive dims");
+    RTD_CUDA(cudaSetDevice(ctx->device));
+    if (!ctx->ctTex.arr || ctx->ctDims[0] != nx || ctx->ctDims[1] != ny || ctx->ctDims[2] != nz) {
+        RTD_CUDA(cudaStreamSynchronize(ctx->stream));
+        ctx->ctTex.release();
+        cudaChannelFormatDesc fd = cudaCreateChannelDesc<float>();
+        RTD_CUDA(cudaMalloc3DArray(&ctx->ctTex.arr, &fd, make_cudaExtent(nx, ny, nz)));
+        RTD_CUDA(makeTexture(ctx->ctTex, cudaAddressModeBorder));
+        ctx->ctDims[0] = nx; ctx->ctDims[1] = ny; ctx->ctDims[2] = nz;
+    }
+    cudaMemcpy3DParms cp; memset(&cp, 0, sizeof cp);
+    cp.srcPtr = make_cudaPitchedPtr((void*)src, size_t(nx) * 4, nx, ny);
+    cp.dstArray = ctx->ctTex.arr; cp.extent = make_cudaExtent(nx, ny, nz); cp.kind = kind;
+    RTD_CUDA(cudaMemcpy3DAsync(&cp, ctx->stream));
+    RTD_CUDA(cudaStreamSynchronize(ctx->stream));
+    ctx->haveCt = true;
+    return RTD_OK;
+}
+
+// Everything that can be done for a beam before any device result is known (cu:612-663, 766-790).
+rtd_status beamPhaseA(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opts& o, int& launches) {
+    if (b.nLayers <= 0 || b.sx <= 0 || b.sy <= 0 || !b.weights || !b.energies || !b.sigmas)
+        return fail(ctx, RTD_ERR_INVALID, "Empty list");   // findMax on an empty vector, vector_find.h:22-25
+    if (b.steps == 0 || b.steps > 4095) return fail(ctx, RTD_ERR_INVALID, "beam.steps must be in [1, 4095]");
+    if (b.nLayers > 255) return fail(ctx, RTD_ERR_INVALID, "at most 255 energy layers per beam");
+    float mx = b.sigmas[0], my = b.sigmas[1];
+    for (int l = 1; l < b.nLayers; ++l) { mx = std::max(mx, b.sigmas[2 * l]); my = std::max(my, b.sigmas[2 * l + 1]); }
+    w.grid = makeRayGrid(b.spotDelta, b.spotOffset, b.sx, b.sy, b.raySpacing, mx, my, o.convSigmaCutoff);
+    if (w.grid.dimX <= 0 || w.grid.dimY <= 0) return fail(ctx, RTD_ERR_INVALID, "empty ray grid");
+    w.S = (int)b.steps; w.L = b.nLayers; w.R = w.grid.dimX * w.grid.dimY; w.sx = b.sx; w.sy = b.sy;
+    if ((w.grid.dimX / 32) * (w.grid.dimY / 8) > 4095) return fail(ctx, RTD_ERR_INVALID, "ray grid has more than 4095 tiles");
+    w.dist[0] = b.sourceDist[0]; w.dist[1] = b.sourceDist[1];
+    w.gtii.m = m3(b.gantryToImIdxM); w.gtii.v = v3(b.gantryToImIdxV[0], b.gantryToImIdxV[1], b.gantryToImIdxV[2]);
+    w.gtdi.m = m3(b.gantryToDoseIdxM); w.gtdi.v = v3(b.gantryToDoseIdxV[0], b.gantryToDoseIdxV[1], b.gantryToDoseIdxV[2]);
+    const size_t RS = size_t(w.R) * w.S;
+    RTD_CUDA(w.density.ensure(RS * 4)); RTD_CUDA(w.wepl.ensure(RS * 4));
+    RTD_CUDA(w.firstIn.ensure(size_t(w.R) * 4)); RTD_CUDA(w.firstOut.ensure(size_t(w.R) * 4));
+    RTD_CUDA(w.weplMin.ensure(size_t(w.S) * 4 + 8)); RTD_CUDA(w.hTrace.ensure(size_t(w.S) * 4 + 8));
+    const size_t nW = size_t(b.sx) * b.sy * b.nLayers;
+    RTD_CUDA(w.spotW.ensure(nW * 4)); RTD_CUDA(w.hStage.ensure(nW * 4 + size_t(w.L) * (8 + sizeof(LayerParams))));
+    memcpy(w.hStage.p, b.weights, nW * 4);
+    RTD_CUDA(cudaMemcpyAsync(w.spotW.p, w.hStage.p, nW * 4, cudaMemcpyHostToDevice, ctx->stream));
+    const TraceParams tp = makeTraceParams(ctx->densScale, ctx->spScale, b.steps, w.grid.rayIdxToGantry, w.dist, w.gtii);
+    // weplMin buffer layout: [0]=beamFirstInside, [1]=beamFirstOutside (ints), [2..] weplMin floats
+    int* sc = w.weplMin.as<int>();
+    trace_bev_kernel<<<w.R / 32, TR_THREADS, 0, ctx->stream>>>(tp, ctx->ctTex.tex, ctx->densTex.tex, ctx->spTex.tex,
+        w.density.as<float>(), w.wepl.as<float>(), w.firstIn.as<int>(), w.firstOut.as<int>(), w.grid.dimX, w.R);
+    slice_reduce_kernel<<<w.S, 256, 0, ctx->stream>>>(w.wepl.as<float>(), w.firstIn.as<int>(), w.firstOut.as<int>(), w.R,
+        w.weplMin.as<float>() + 2, sc, sc + 1);
+    launches += 2;
+    RTD_CUDA(cudaGetLastError());
+    RTD_CUDA(cudaMemcpyAsync(w.hTrace.p, w.weplMin.p, size_t(w.S) * 4 + 8, cudaMemcpyDeviceToHost, ctx->stream));
+    return RTD_OK;
+}
+
+// Host logic that needs the tracer's reductions (cu:792-849, 922-925) + all remaining launches of the beam.
+rtd_status beamPhaseB(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opts& o, float* dDose, int& launches,
+                      cudaEvent_t* evs /*6 events: conv, idd, radius, superp, transfer, end*/) {
+    const int* sc = w.hTrace.as<int>();
+    const float* weplMin = w.hTrace.as<float>() + 2;
+    w.bfi = sc[0]; w.bfo = sc[1];
+    const float rayResZ = w.grid.rayIdxToGantry.delta.z, rayOffZ = w.grid.rayIdxToGantry.offset.z;
+    w.entryZ = float(w.bfi) * rayResZ + rayOffZ;
+    float maxEnergy = b.energies[0];
+    for (int l = 1; l < w.L; ++l) maxEnergy = std::max(maxEnergy, b.energies[l]);
+    const float* E = ctx->energies.data(); const int nE = ctx->nEnergies;
+    const float maxEnergyIdx = findDecimalOrdered(E, nE, maxEnergy);
+    const float maxPeakDepth = vectorInterpolate(ctx->peakDepths.data(), nE, maxEnergyIdx);
+    const int firstPastCutoffAll = findFirstLargerOrdered(weplMin, w.S, o.bpDepthCutoff * maxPeakDepth);
+    w.Zg = std::min(firstPastCutoffAll, w.bfo);
+    w.nz = w.Zg - w.bfi;
+    w.live = w.nz > 0;
+    w.layers.resize(w.L); w.entrySig.resize(2 * size_t(w.L));
+    w.lrep.assign(w.L, rtd_layer_report());
+    memset(&w.rep, 0, sizeof w.rep);
+    w.rep.lSteps = w.grid.lSteps; w.rep.bSteps = w.grid.bSteps; w.rep.rSteps = w.grid.rSteps; w.rep.tSteps = w.grid.tSteps;
+    w.rep.rayDimX = w.grid.dimX; w.rep.rayDimY = w.grid.dimY; w.rep.steps = w.S; w.rep.nLayers = w.L;
+    w.rep.beamFirstInside = w.bfi; w.rep.beamFirstOutside = w.bfo; w.rep.beamFirstGuaranteedPassive = w.Zg; w.rep.entryZ = w.entryZ;
+    for (int l = 0; l < w.L; ++l) {
+        LayerParams& lp = w.layers[l];
+        lp.energyIdx = findDecimalOrdered(E, nE, b.energies[l]);
+        lp.energyScale = vectorInterpolate(ctx->scaleFacts.data(), nE, lp.energyIdx);
+        lp.peakDepth = vectorInterpolate(ctx->peakDepths.data(), nE, lp.energyIdx);
+        float ca, cb; sigmaSqAirCoefsHost(lp.peakDepth, true, ca, cb);
+        const float sxg = b.sigmas[2 * l], syg = b.sigmas[2 * l + 1], z = w.entryZ;
+        w.entrySig[2 * l] = sqrtf(ca * z * z + cb * z + sxg * sxg);
+        w.entrySig[2 * l + 1] = sqrtf(ca * z * z + cb * z + syg * syg);
+        const unsigned localAfterLast = (unsigned)findFirstLargerOrdered(weplMin, w.S, o.bpDepthCutoff * lp.peakDepth);
+        lp.afterLast = (int)std::min(localAfterLast, (unsigned)w.Zg);
+        rtd_layer_report& lr = w.lrep[l];
+        lr.energyIdx = lp.energyIdx; lr.energyScaleFact = lp.energyScale; lr.peakDepth = lp.peakDepth;
+        lr.entrySigmaX = w.entrySig[2 * l]; lr.entrySigmaY = w.entrySig[2 * l + 1]; lr.afterLastStep = lp.afterLast;
+    }
+    if (!w.live) return RTD_OK;   // the beam never enters the patient: nothing to add
+
+    const int Rx = w.grid.dimX, Ry = w.grid.dimY, R = w.R, L = w.L, nz = w.nz;
+    const int tilesX = Rx / 32, tilesY = Ry / 8, tiles = tilesX * tilesY;
+    const size_t LnzR = size_t(L) * nz * R;
+    RTD_CUDA(w.sigmas.ensure(size_t(L) * 8)); RTD_CUDA(w.layerDev.ensure(size_t(L) * sizeof(LayerParams)));
+    RTD_CUDA(w.rayW.ensure(size_t(L) * R * 4));
+    RTD_CUDA(w.idd.ensure(LnzR * 4)); RTD_CUDA(w.rsig.ensure(LnzR * 4));
+    RTD_CUDA(w.rowMin.ensure(size_t(L) * nz * Ry * tilesX * 4));
+    RTD_CUDA(w.firstPassive.ensure(size_t(L) * R * 4));
+    // one zero-initialised control block: lfp[L] | hist[L*34] | rbCursor[33] | stats[4] | work[4]
+    const size_t ctlInts = size_t(L) + size_t(L) * 34 + 33 + 4 + 4;
+    RTD_CUDA(w.lfp.ensure(ctlInts * 4));
+    RTD_CUDA(w.batchRad.ensure(size_t(L) * 34 * 4)); RTD_CUDA(w.rbOffset.ensure(33 * 4));
+    RTD_CUDA(w.radMap.ensure(size_t(L) * nz * tiles)); RTD_CUDA(w.list.ensure(size_t(L) * nz * tiles * 4));
+    const size_t bevN = size_t(w.Zg) * (Ry + 64) * (Rx + 64);
+    RTD_CUDA(w.bev.ensure(bevN * 4));
+    RTD_CUDA(w.hOut.ensure((ctlInts + size_t(L) * 34) * 4));
+    int* dLfp = w.lfp.as<int>(); int* dHist = dLfp + L; int* dCursor = dHist + size_t(L) * 34; int* dStats = dCursor + 33; int* dWork = dStats + 4;
+
+    // staging area after the weights: sigmas then layer params
+    const size_t nW = size_t(w.sx) * w.sy * L;
+    char* st = w.hStage.as<char>() + nW * 4;
+    memcpy(st, w.entrySig.data(), size_t(L) * 8);
+    memcpy(st + size_t(L) * 8, w.layers.data(), size_t(L) * sizeof(LayerParams));
+    RTD_CUDA(cudaMemcpyAsync(w.sigmas.p, st, size_t(L) * 8, cudaMemcpyHostToDevice, ctx->stream));
+    RTD_CUDA(cudaMemcpyAsync(w.layerDev.p, st + size_t(L) * 8, size_t(L) * sizeof(LayerParams), cudaMemcpyHostToDevice, ctx->stream));
+    RTD_CUDA(cudaMemsetAsync(w.lfp.p, 0, ctlInts * 4, ctx->stream));
+    RTD_CUDA(cudaMemsetAsync(w.bev.p, 0, bevN * 4, ctx->stream));
+    RTD_CUDA(cudaEventRecord(evs[0], ctx->stream));
+
+    // K3a (cu:849-854)
+    ConvParams cp;
+    cp.inW = w.sx; cp.inH = w.sy; cp.outW = Rx; cp.outH = Ry;
+    const float pxMultX = 1.0f - w.entryZ / w.dist[0], pxMultY = 1.0f - w.entryZ / w.dist[1];
+    const V3 rayD = w.grid.rayIdxToGantry.delta, rayO = w.grid.rayIdxToGantry.offset;
+    cp.pixelSpX = rayD.x * pxMultX; cp.pixelSpY = rayD.y * pxMultY;
+    cp.deltaX = b.spotDelta[0] / rayD.x; cp.deltaY = b.spotDelta[1] / rayD.y;
+    cp.offX = (b.spotOffset[0] - rayO.x) / rayD.x; cp.offY = (b.spotOffset[1] - rayO.y) / rayD.y;
+    cp.cutoff = o.convSigmaCutoff;
+    spot_to_ray_kernel<<<dim3(Rx / 32, L), 256, size_t(w.sy) * 32 * 4, ctx->stream>>>(w.spotW.as<float>(), w.sigmas.as<float2>(), w.rayW.as<float>(), cp);
+    RTD_CUDA(cudaEventRecord(evs[1], ctx->stream));
+
+    // K2
+    IddParams q;
+    q.g = makeFillGeom(w.grid.rayIdxToGantry, w.dist);
+    q.rrlScale = ctx->rrlScale; q.bpCutoff = o.bpDepthCutoff; q.rayWeightCutoff = o.rayWeightCutoff;
+    q.first = w.bfi; q.nz = nz; q.Rx = Rx; q.Ry = Ry; q.nozzle = 1;
+    idd_sigma_kernel<<<dim3(tilesX, tilesY, L), 256, 0, ctx->stream>>>(w.density.as<float>(), w.wepl.as<float>(), w.rayW.as<float>(),
+        w.firstIn.as<int>(), w.firstOut.as<int>(), w.layerDev.as<LayerParams>(), q, ctx->iddTex.tex, ctx->rrlTex.tex,
+        w.idd.as<float>(), w.rsig.as<float>(), w.rowMin.as<float>(), w.firstPassive.as<int>(), dLfp);
+    RTD_CUDA(cudaEventRecord(evs[2], ctx->stream));
+
+    // tile radii, batching, work list
+    const int gx = (nz * tiles + 255) / 256;
+    tile_radius_kernel<<<dim3(gx, L), 256, 0, ctx->stream>>>(w.rowMin.as<float>(), dLfp, w.bfi, nz, Rx, Ry, o.ksSigmaCutoff, w.radMap.as<uint8_t>(), dHist);
+    batch_kernel<<<1, 64, 0, ctx->stream>>>(dHist, L, o.minTilesInBatch, w.batchRad.as<int>(), w.rbOffset.as<int>(), dStats);
+    fill_list_kernel<<<dim3(gx, L), 256, 0, ctx->stream>>>(w.radMap.as<uint8_t>(), w.batchRad.as<int>(), w.rbOffset.as<int>(), dCursor, nz, tiles, w.list.as<uint32_t>());
+    RTD_CUDA(cudaEventRecord(evs[3], ctx->stream));
+
+    // K3b: three radius classes, heavy first
+    KsParams kp;
+    kp.idd = w.idd.as<float>(); kp.rsig = w.rsig.as<float>(); kp.bev = w.bev.as<float>(); kp.list = w.list.as<uint32_t>();
+    kp.batchRad = w.batchRad.as<int>(); kp.radMap = w.radMap.as<uint8_t>();
+    kp.Rx = Rx; kp.Ry = Ry; kp.nz = nz; kp.first = w.bfi; kp.tilesX = tilesX; kp.tiles = tiles;
+    ks_kernel<KS_NT_C, 17, 32><<<ctx->ksBlocksC, KS_NT_C, KS_SMEM_C, ctx->stream>>>(kp, w.rbOffset.as<int>(), dStats, dWork + 0);
+    ks_kernel<KS_NT_B, 9, 16><<<ctx->ksBlocksB, KS_NT_B, KS_SMEM_B, ctx->stream>>>(kp, w.rbOffset.as<int>(), dStats, dWork + 1);
+    ks_kernel<KS_NT_A, 0, 8><<<ctx->ksBlocksA, KS_NT_A, KS_SMEM_A, ctx->stream>>>(kp, w.rbOffset.as<int>(), dStats, dWork + 2);
+    RTD_CUDA(cudaEventRecord(evs[4], ctx->stream));
+
+    // K4 (cu:1185-1218); the z-range uses Zg instead of beamFirstCalculatedPassive: a superset box that only adds
+    // voxels whose interpolated BEV dose is exactly 0, so the result is identical and no host sync is needed here.
+    const float xv[2] = {-float(RTD_MAX_SUPERP_R), float(Rx + RTD_MAX_SUPERP_R - 1)};
+    const float yv[2] = {-float(RTD_MAX_SUPERP_R), float(Ry + RTD_MAX_SUPERP_R - 1)};
+    const float zv[2] = {float(w.bfi), float(w.Zg - 1)};
+    V3 mx = v3(-1.f, -1.f, -1.f), mn = v3(100000.f, 100000.f, 100000.f);
+    for (int k = 0; k < 2; ++k) for (int j = 0; j < 2; ++j) for (int i = 0; i < 2; ++i) {
+        const V3 p = fromFan(w.grid.rayIdxToGantry, w.dist, w.gtdi, v3(xv[i], yv[j], zv[k]));
+        mx.x = std::max(mx.x, p.x); mx.y = std::max(mx.y, p.y); mx.z = std::max(mx.z, p.z);
+        mn.x = std::min(mn.x, p.x); mn.y = std::min(mn.y, p.y); mn.z = std::min(mn.z, p.z);
+    }
+    GridParams gp;
+    gp.t = makeTransferParams(w.grid.rayIdxToGantry, w.dist, w.gtdi, v3(float(RTD_MAX_SUPERP_R), float(RTD_MAX_SUPERP_R), -float(w.bfi)));
+    gp.minX = std::max((int(std::floor(mn.x)) / 32) * 32, 0); gp.minY = std::max(int(std::floor(mn.y)), 0); gp.minZ = std::max(int(std::floor(mn.z)), 0);
+    gp.maxX = std::min(int(std::ceil(mx.x)), ctx->doseDims[0] - 1); gp.maxY = std::min(int(std::ceil(mx.y)), ctx->doseDims[1] - 1);
+    gp.maxZ = std::min(int(std::ceil(mx.z)), ctx->doseDims[2] - 1);
+    gp.nx = ctx->doseDims[0]; gp.ny = ctx->doseDims[1]; gp.nz = ctx->doseDims[2];
+    gp.W = Rx + 64; gp.H = Ry + 64; gp.first = w.bfi; gp.zEnd = w.Zg;
+    if (gp.maxX >= gp.minX && gp.maxY >= gp.minY && gp.maxZ >= gp.minZ) {
+        dim3 g((gp.maxX - gp.minX + 32) / 32, (gp.maxY - gp.minY + 8) / 8);
+        bev_to_grid_kernel<<<g, 256, 0, ctx->stream>>>(w.bev.as<float>(), dDose, gp);
+        launches += 1;
+    }
+    launches += 8;
+    RTD_CUDA(cudaGetLastError());
+    RTD_CUDA(cudaEventRecord(evs[5], ctx->stream));
+    // results for the reports: control block + batch radii
+    RTD_CUDA(cudaMemcpyAsync(w.hOut.p, w.lfp.p, ctlInts * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    RTD_CUDA(cudaMemcpyAsync(w.hOut.as<int>() + ctlInts, w.batchRad.p, size_t(L) * 34 * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    return RTD_OK;
+}
+
+// After the final sync: integer reports (cu:955-957, 1185-1210) and the metric counters.
+bool beamFinish(rtd_ctx* ctx, BeamWs& w, int64_t& updates, int64_t& taps) {
+    if (!w.live) return true;
+    const int L = w.L;
+    const size_t ctlInts = size_t(L) + size_t(L) * 34 + 33 + 4 + 4;
+    const int* lfp = w.hOut.as<int>(); const int* hist = lfp + L; const int* stats = hist + size_t(L) * 34 + 33;
+    const int* brad = w.hOut.as<int>() + ctlInts;
+    int fcp = 0; int64_t u = 0, t = 0;
+    for (int l = 0; l < L; ++l) {
+        rtd_layer_report& lr = w.lrep[l];
+        lr.layerFirstPassive = lfp[l];
+        fcp = std::max(fcp, lfp[l]);
+        const int nLive = std::min(std::max(lfp[l] - w.bfi, 0), w.nz);
+        u += int64_t(w.R) * nLive;
+        for (int i = 0; i < 34; ++i) {
+            lr.radiusHist[i] = hist[l * 34 + i]; lr.batchRadius[i] = brad[l * 34 + i];
+            if (i <= 32) { const int64_t rb = brad[l * 34 + i]; t += int64_t(hist[l * 34 + i]) * 256 * (2 * rb + 1) * (2 * rb + 1); }
+        }
+    }
+    w.rep.beamFirstCalculatedPassive = fcp; w.rep.updates = u;
+    updates += u; taps += t;
+    const int Rx = w.grid.dimX, Ry = w.grid.dimY;
+    const float xv[2] = {-float(RTD_MAX_SUPERP_R), float(Rx + RTD_MAX_SUPERP_R - 1)};
+    const float yv[2] = {-float(RTD_MAX_SUPERP_R), float(Ry + RTD_MAX_SUPERP_R - 1)};
+    const float zv[2] = {float(w.bfi), float(fcp - 1)};
+    V3 mx = v3(-1.f, -1.f, -1.f), mn = v3(100000.f, 100000.f, 100000.f);
+    for (int k = 0; k < 2; ++k) for (int j = 0; j < 2; ++j) for (int i = 0; i < 2; ++i) {
+        const V3 p = fromFan(w.grid.rayIdxToGantry, w.dist, w.gtdi, v3(xv[i], yv[j], zv[k]));
+        mx.x = std::max(mx.x, p.x); mx.y = std::max(mx.y, p.y); mx.z = std::max(mx.z, p.z);
+        mn.x = std::min(mn.x, p.x); mn.y = std::min(mn.y, p.y); mn.z = std::min(mn.z, p.z);
+    }
+    w.rep.bboxMin[0] = std::max((int(std::floor(mn.x)) / 32) * 32, 0); w.rep.bboxMin[1] = std::max(int(std::floor(mn.y)), 0); w.rep.bboxMin[2] = std::max(int(std::floor(mn.z)), 0);
+    w.rep.bboxMax[0] = std::min(int(std::ceil(mx.x)), ctx->doseDims[0] - 1); w.rep.bboxMax[1] = std::min(int(std::ceil(mx.y)), ctx->doseDims[1] - 1);
+    w.rep.bboxMax[2] = std::min(int(std::ceil(mx.z)), ctx->doseDims[2] - 1);
+    return stats[0] == 0;
+}
+
+rtd_status doseCore(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* dDose, const rtd_opts& o, rtd_timing* tm,
+                    cudaEvent_t evBegin, cudaEvent_t evEnd) {
+    int launches = 0;
+    while ((int)ctx->ws.size() < nBeams) ctx->ws.push_back(new BeamWs());
+    ctx->nBeamsLast = nBeams; ctx->optsLast = o;
+    RTD_CUDA(cudaEventRecord(evBegin, ctx->stream));
+    for (int b = 0; b < nBeams; ++b) {
+        rtd_status s = beamPhaseA(ctx, beams[b], *ctx->ws[b], o, launches);
+        if (s != RTD_OK) return s;
+    }
+    cudaEvent_t evTraceEnd = ev(ctx, 2);
+    RTD_CUDA(cudaEventRecord(evTraceEnd, ctx->stream));
+    RTD_CUDA(cudaStreamSynchronize(ctx->stream));                         // host sync 1 of 2
+    for (int b = 0; b < nBeams; ++b) {
+        cudaEvent_t evs[6];
+        for (int i = 0; i < 6; ++i) evs[i] = ev(ctx, 8 + size_t(b) * 6 + i);
+        rtd_status s = beamPhaseB(ctx, beams[b], *ctx->ws[b], o, dDose, launches, evs);
+        if (s != RTD_OK) return s;
+    }
+    RTD_CUDA(cudaEventRecord(evEnd, ctx->stream));
+    RTD_CUDA(cudaStreamSynchronize(ctx->stream));                         // host sync 2 of 2
+    int64_t updates = 0, taps = 0; bool ok = true;
+    for (int b = 0; b < nBeams; ++b) ok = beamFinish(ctx, *ctx->ws[b], updates, taps) && ok;
+    if (tm) {
+        memset(tm, 0, sizeof *tm);
+        tm->updates = updates; tm->ksTaps = taps; tm->kernelLaunches = launches; tm->hostSyncs = 2;
+        float ms = 0;
+        cudaEventElapsedTime(&ms, evBegin, evTraceEnd); tm->msTrace = ms;
+        cudaEvent_t prev = evTraceEnd;
+        for (int b = 0; b < nBeams; ++b) {
+            if (!ctx->ws[b]->live) continue;
+            cudaEvent_t* e = &ctx->events[8 + size_t(b) * 6];
+            cudaEventElapsedTime(&ms, prev, e[0]); tm->msSetup += ms;
+            cudaEventElapsedTime(&ms, e[0], e[1]); tm->msConv += ms;
+            cudaEventElapsedTime(&ms, e[1], e[2]); tm->msIddSigma += ms;
+            cudaEventElapsedTime(&ms, e[2], e[3]); tm->msRadius += ms;
+            cudaEventElapsedTime(&ms, e[3], e[4]); tm->msSuperp += ms;
+            cudaEventElapsedTime(&ms, e[4], e[5]); tm->msTransfer += ms;
+            prev = e[5];
+        }
+        cudaEventElapsedTime(&ms, evBegin, evEnd); tm->msTotal = ms;
+    }
+    if (!ok) return fail(ctx, RTD_ERR_RADIUS, "Found larger than allowed kernel superposition radius");
+    return RTD_OK;
+}
+
+}  // namespace
+
+// =========================================================================================================
+extern "C" {
+
+const char* rtd_version(void) { return "rtdose-b200 0.1 (sm_100a)"; }
+
+void rtd_default_opts(rtd_opts* o) {
+    if (!o) return;
+    memset(o, 0, sizeof *o);
+    o->bpDepthCutoff = 1.05f; o->convSigmaCutoff = 3.0f; o->ksSigmaCutoff = 3.0f; o->rayWeightCutoff = 1.0f;
+    o->minTilesInBatch = 16; o->keepIntermediates = 1;
+}
+
+rtd_status rtd_create(rtd_ctx** out, int device) {
+    if (!out) return RTD_ERR_INVALID;
+    *out = nullptr;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) return RTD_ERR_NO_DEVICE;   // no CPU fallback by design
+    if (device < 0 || device >= n) return RTD_ERR_INVALID;
+    if (cudaSetDevice(device) != cudaSuccess) return RTD_ERR_CUDA;
+    rtd_ctx* ctx = new rtd_ctx();
+    ctx->device = device;
+    if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return RTD_ERR_CUDA; }
+    cudaDeviceGetAttribute(&ctx->smCount, cudaDevAttrMultiProcessorCount, device);
+    rtd_default_opts(&ctx->optsLast);
+    cudaFuncSetAttribute(ks_kernel<KS_NT_C, 17, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)KS_SMEM_C);
+    cudaFuncSetAttribute(ks_kernel<KS_NT_B, 9, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)KS_SMEM_B);
+    cudaFuncSetAttribute(ks_kernel<KS_NT_A, 0, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)KS_SMEM_A);
+    int occ = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ks_kernel<KS_NT_C, 17, 32>, KS_NT_C, KS_SMEM_C); ctx->ksBlocksC = std::max(occ, 1) * ctx->smCount;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ks_kernel<KS_NT_B, 9, 16>, KS_NT_B, KS_SMEM_B); ctx->ksBlocksB = std::max(occ, 1) * ctx->smCount;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ks_kernel<KS_NT_A, 0, 8>, KS_NT_A, KS_SMEM_A); ctx->ksBlocksA = std::max(occ, 1) * ctx->smCount;
+    if (cudaGetLastError() != cudaSuccess) { cudaStreamDestroy(ctx->stream); delete ctx; return RTD_ERR_CUDA; }
+    *out = ctx;
+    return RTD_OK;
+}
+
+void rtd_destroy(rtd_ctx* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    for (BeamWs* w : ctx->ws) { w->release(); delete w; }
+    ctx->iddTex.release(); ctx->densTex.release(); ctx->spTex.release(); ctx->rrlTex.release(); ctx->ctTex.release();
+    ctx->dose.release();
+    for (cudaEvent_t e : ctx->events) cudaEventDestroy(e);
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+const char* rtd_last_error(const rtd_ctx* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+
+void* rtd_stream(rtd_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+
+rtd_status rtd_set_luts(rtd_ctx* ctx, const rtd_luts* l) {
+    if (!ctx) return RTD_ERR_INVALID;
+    if (!l || l->nEnergies < 2 || l->nEnergySamples < 2 || !l->energiesPerU || !l->peakDepths || !l->scaleFacts || !l->ciddMatrix ||
+        l->nDensitySamples < 1 || !l->densityVector || l->nSpSamples < 1 || !l->spVector || l->nRRlSamples < 1 || !l->rRlVector)
+        return fail(ctx, RTD_ERR_INVALID, "rtd_set_luts: incomplete LUT set");
+    RTD_CUDA(cudaSetDevice(ctx->device));
+    RTD_CUDA(cudaStreamSynchronize(ctx->stream));
+    ctx->nEnergies = l->nEnergies; ctx->nEnergySamples = l->nEnergySamples;
+    ctx->energies.assign(l->energiesPerU, l->energiesPerU + l->nEnergies);
+    ctx->peakDepths.assign(l->peakDepths, l->peakDepths + l->nEnergies);
+    ctx->scaleFacts.assign(l->scaleFacts, l->scaleFacts + l->nEnergies);
+    ctx->densScale = l->densityScaleFact; ctx->spScale = l->spScaleFact; ctx->rrlScale = l->rRlScaleFact;
+    ctx->iddTex.release();
+    cudaChannelFormatDesc fd = cudaCreateChannelDesc<float>();
+    RTD_CUDA(cudaMallocArray(&ctx->iddTex.arr, &fd, l->nEnergySamples, l->nEnergies));
+    RTD_CUDA(cudaMemcpy2DToArrayAsync(ctx->iddTex.arr, 0, 0, l->ciddMatrix, size_t(l->nEnergySamples) * 4, size_t(l->nEnergySamples) * 4,
+                                      l->nEnergies, cudaMemcpyHostToDevice, ctx->stream));
+    RTD_CUDA(makeTexture(ctx->iddTex, cudaAddressModeClamp));
+    RTD_CUDA(upload1D(ctx->densTex, l->densityVector, l->nDensitySamples, ctx->stream));
+    RTD_CUDA(upload1D(ctx->spTex, l->spVector, l->nSpSamples, ctx->stream));
+    RTD_CUDA(upload1D(ctx->rrlTex, l->rRlVector, l->nRRlSamples, ctx->stream));
+    RTD_CUDA(cudaStreamSynchronize(ctx->stream));
+    ctx->haveLuts = true;
+    return RTD_OK;
+}
+
+rtd_status rtd_set_ct(rtd_ctx* ctx, const float* hu, int nx, int ny, int nz) { return setCtCommon(ctx, hu, nx, ny, nz, cudaMemcpyHostToDevice); }
+rtd_status rtd_set_ct_device(rtd_ctx* ctx, const float* hu, int nx, int ny, int nz) { return setCtCommon(ctx, hu, nx, ny, nz, cudaMemcpyDeviceToDevice); }
+
+rtd_status rtd_set_dose_grid(rtd_ctx* ctx, int nx, int ny, int nz) {
+    if (!ctx) return RTD_ERR_INVALID;
+    if (nx <= 0 || ny <= 0 || nz <= 0) return fail(ctx, RTD_ERR_INVALID, "rtd_set_dose_grid: non-positive dims");
+    ctx->doseDims[0] = nx; ctx->doseDims[1] = ny; ctx->doseDims[2] = nz; ctx->haveDose = true;
+    return RTD_OK;
+}
+
+static rtd_status checkReady(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, const void* dose) {
+    if (!ctx) return RTD_ERR_INVALID;
+    if (!ctx->haveLuts || !ctx->haveCt || !ctx->haveDose) return fail(ctx, RTD_ERR_STATE, "rtd_dose: LUTs, CT and dose grid must be set first");
+    if (nBeams < 0 || (nBeams > 0 && !beams) || !dose) return fail(ctx, RTD_ERR_INVALID, "rtd_dose: bad beams / dose pointer");
+    return RTD_OK;
+}
+
+rtd_status rtd_dose_device(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* dDose, const rtd_opts* opts, rtd_timing* tm) {
+    rtd_status s = checkReady(ctx, beams, nBeams, dDose);
+    if (s != RTD_OK) return s;
+    RTD_CUDA(cudaSetDevice(ctx->device));
+    rtd_opts o; if (opts) o = *opts; else rtd_default_opts(&o);
+    return doseCore(ctx, beams, nBeams, dDose, o, tm, ev(ctx, 0), ev(ctx, 1));
+}
+
+rtd_status rtd_dose(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* dose, const rtd_opts* opts, rtd_timing* tm) {
+    rtd_status s = checkReady(ctx, beams, nBeams, dose);
+    if (s != RTD_OK) return s;
+    RTD_CUDA(cudaSetDevice(ctx->device));
+    rtd_opts o; if (opts) o = *opts; else rtd_default_opts(&o);
+    const size_t n = size_t(ctx->doseDims[0]) * ctx->doseDims[1] * ctx->doseDims[2];
+    RTD_CUDA(ctx->dose.ensure(n * 4));
+    cudaEvent_t e0 = ev(ctx, 3), e1 = ev(ctx, 4), e2 = ev(ctx, 5);
+    RTD_CUDA(cudaEventRecord(e0, ctx->stream));
+    RTD_CUDA(cudaMemcpyAsync(ctx->dose.p, dose, n * 4, cudaMemcpyHostToDevice, ctx->stream));   // accumulate semantics, cu:542
+    s = doseCore(ctx, beams, nBeams, ctx->dose.as<float>(), o, tm, ev(ctx, 0), ev(ctx, 1));
+    if (s != RTD_OK) return s;
+    RTD_CUDA(cudaEventRecord(e1, ctx->stream));
+    RTD_CUDA(cudaMemcpyAsync(dose, ctx->dose.p, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    RTD_CUDA(cudaEventRecord(e2, ctx->stream));
+    RTD_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (tm) {
+        float ms = 0;
+        cudaEventElapsedTime(&ms, e0, ev(ctx, 0)); tm->msUpload = ms;
+        cudaEventElapsedTime(&ms, e1, e2); tm->msDownload = ms;
+        cudaEventElapsedTime(&ms, e0, e2); tm->msTotal = ms;
+        tm->hostSyncs += 1;
+    }
+    return RTD_OK;
+}
+
+rtd_status rtd_get_beam_report(const rtd_ctx* ctx, int beamNo, rtd_beam_report* out) {
+    if (!ctx || !out || beamNo < 0 || beamNo >= ctx->nBeamsLast) return RTD_ERR_INVALID;
+    *out = ctx->ws[beamNo]->rep;
+    return RTD_OK;
+}
+
+rtd_status rtd_get_layer_report(const rtd_ctx* ctx, int beamNo, int layerNo, rtd_layer_report* out) {
+    if (!ctx || !out || beamNo < 0 || beamNo >= ctx->nBeamsLast) return RTD_ERR_INVALID;
+    const BeamWs& w = *ctx->ws[beamNo];
+    if (layerNo < 0 || layerNo >= (int)w.lrep.size()) return RTD_ERR_INVALID;
+    *out = w.lrep[layerNo];
+    return RTD_OK;
+}
+
+rtd_status rtd_debug_fetch(rtd_ctx* ctx, int beamNo, rtd_fetch_what what, int layerNo, void* dst, size_t dstBytes) {
+    if (!ctx || !dst || beamNo < 0 || beamNo >= ctx->nBeamsLast) return RTD_ERR_INVALID;
+    BeamWs& w = *ctx->ws[beamNo];
+    const size_t R = w.R, S = w.S, L = w.L, nz = w.nz > 0 ? w.nz : 0;
+    const size_t tiles = size_t(w.grid.dimX / 32) * (w.grid.dimY / 8);
+    const void* src = nullptr; size_t bytes = 0;
+    const bool perLayer = (what == RTD_FETCH_IDD || what == RTD_FETCH_RSIGMA || what == RTD_FETCH_FIRST_PASSIVE || what == RTD_FETCH_TILE_RADIUS);
+    if (perLayer && (layerNo < 0 || layerNo >= (int)L)) return fail(ctx, RTD_ERR_INVALID, "rtd_debug_fetch: bad layer");
+    if ((perLayer || what == RTD_FETCH_BEV_DOSE || what == RTD_FETCH_RAY_WEIGHTS) && !w.live) return fail(ctx, RTD_ERR_STATE, "rtd_debug_fetch: beam has no live steps");
+    switch (what) {
+        case RTD_FETCH_DENSITY: src = w.density.p; bytes = R * S * 4; break;
+        case RTD_FETCH_WEPL: src = w.wepl.p; bytes = R * S * 4; break;
+        case RTD_FETCH_FIRST_INSIDE: src = w.firstIn.p; bytes = R * 4; break;
+        case RTD_FETCH_FIRST_OUTSIDE: src = w.firstOut.p; bytes = R * 4; break;
+        case RTD_FETCH_WEPL_MIN: src = w.weplMin.as<float>() + 2; bytes = S * 4; break;
+        case RTD_FETCH_RAY_WEIGHTS: src = w.rayW.p; bytes = L * R * 4; break;
+        case RTD_FETCH_IDD: src = w.idd.as<float>() + size_t(layerNo) * nz * R; bytes = nz * R * 4; break;
+        case RTD_FETCH_RSIGMA: src = w.rsig.as<float>() + size_t(layerNo) * nz * R; bytes = nz * R * 4; break;
+        case RTD_FETCH_FIRST_PASSIVE: src = w.firstPassive.as<int>() + size_t(layerNo) * R; bytes = R * 4; break;
+        case RTD_FETCH_BEV_DOSE: src = w.bev.p; bytes = size_t(w.Zg) * (w.grid.dimY + 64) * (w.grid.dimX + 64) * 4; break;
+        case RTD_FETCH_TILE_RADIUS: src = w.radMap.as<uint8_t>() + size_t(layerNo) * nz * tiles; bytes = nz * tiles; break;
+        default: return fail(ctx, RTD_ERR_INVALID, "rtd_debug_fetch: unknown item");
+    }
+    if (dstBytes < bytes) return fail(ctx, RTD_ERR_INVALID, "rtd_debug_fetch: destination too small");
+    RTD_CUDA(cudaSetDevice(ctx->device));
+    RTD_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    RTD_CUDA(cudaStreamSynchronize(ctx->stream));
+    return RTD_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,279 @@
+"""ctypes binding of librtdose.so (include/rtdose.h) and the Python mirror of the reference's host interface.
+
+``cuda_wrapper_protons(im_vol, dose_vol, beams, idd_data)`` has the argument meaning of the reference's
+``cudaWrapperProtons`` (/root/reference/src/kernel_wrapper.cuh:161): CT volume, dose volume accumulated in
+place, list of BeamSettings-shaped beams, EnergyStruct. There is NO CPU fallback: importing works without a
+GPU (so the symbol table can be checked), creating a context without one raises ``RtdError``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import List, Optional, Sequence
+
+import numpy as np
+
+from .cases import Beam
+from .energy_reader import EnergyStruct
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "librtdose.so")
+
+HIST_BINS = 34
+STATUS = {0: "RTD_OK", 1: "RTD_ERR_INVALID", 2: "RTD_ERR_CUDA", 3: "RTD_ERR_RADIUS", 4: "RTD_ERR_STATE", 5: "RTD_ERR_NO_DEVICE"}
+FETCH = dict(density=0, wepl=1, first_inside=2, first_outside=3, wepl_min=4, ray_weights=5, idd=6, rsigma=7,
+             first_passive=8, bev_dose=9, tile_radius=10)
+
+_fp = C.POINTER(C.c_float)
+
+
+class RtdLuts(C.Structure):
+    _fields_ = [("nEnergySamples", C.c_int), ("nEnergies", C.c_int), ("energiesPerU", _fp), ("peakDepths", _fp),
+                ("scaleFacts", _fp), ("ciddMatrix", _fp),
+                ("nDensitySamples", C.c_int), ("densityScaleFact", C.c_float), ("densityVector", _fp),
+                ("nSpSamples", C.c_int), ("spScaleFact", C.c_float), ("spVector", _fp),
+                ("nRRlSamples", C.c_int), ("rRlScaleFact", C.c_float), ("rRlVector", _fp)]
+
+
+class RtdBeam(C.Structure):
+    _fields_ = [("weights", _fp), ("sx", C.c_int), ("sy", C.c_int), ("nLayers", C.c_int), ("energies", _fp), ("sigmas", _fp),
+                ("raySpacing", C.c_float * 2), ("steps", C.c_uint), ("sourceDist", C.c_float * 2),
+                ("spotDelta", C.c_float * 3), ("spotOffset", C.c_float * 3),
+                ("gantryToImIdxM", C.c_float * 9), ("gantryToImIdxV", C.c_float * 3),
+                ("gantryToDoseIdxM", C.c_float * 9), ("gantryToDoseIdxV", C.c_float * 3)]
+
+
+class RtdOpts(C.Structure):
+    _fields_ = [("bpDepthCutoff", C.c_float), ("convSigmaCutoff", C.c_float), ("ksSigmaCutoff", C.c_float),
+                ("rayWeightCutoff", C.c_float), ("minTilesInBatch", C.c_int), ("keepIntermediates", C.c_int),
+                ("reserved", C.c_int * 4)]
+
+
+class RtdTiming(C.Structure):
+    _fields_ = [("msTotal", C.c_float), ("msUpload", C.c_float), ("msTrace", C.c_float), ("msSetup", C.c_float),
+                ("msConv", C.c_float), ("msIddSigma", C.c_float), ("msRadius", C.c_float), ("msSuperp", C.c_float),
+                ("msTransfer", C.c_float), ("msDownload", C.c_float), ("updates", C.c_int64), ("ksTaps", C.c_int64),
+                ("kernelLaunches", C.c_int), ("hostSyncs", C.c_int)]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+class RtdBeamReport(C.Structure):
+    _fields_ = [("lSteps", C.c_int), ("bSteps", C.c_int), ("rSteps", C.c_int), ("tSteps", C.c_int),
+                ("rayDimX", C.c_int), ("rayDimY", C.c_int), ("steps", C.c_int), ("nLayers", C.c_int),
+                ("beamFirstInside", C.c_int), ("beamFirstOutside", C.c_int), ("beamFirstGuaranteedPassive", C.c_int),
+                ("beamFirstCalculatedPassive", C.c_int), ("bboxMin", C.c_int * 3), ("bboxMax", C.c_int * 3),
+                ("entryZ", C.c_float), ("updates", C.c_int64)]
+
+    def as_dict(self):
+        d = {k: getattr(self, k) for k, _ in self._fields_}
+        d["bboxMin"] = list(self.bboxMin); d["bboxMax"] = list(self.bboxMax)
+        return d
+
+
+class RtdLayerReport(C.Structure):
+    _fields_ = [("energyIdx", C.c_float), ("energyScaleFact", C.c_float), ("peakDepth", C.c_float),
+                ("entrySigmaX", C.c_float), ("entrySigmaY", C.c_float), ("afterLastStep", C.c_int),
+                ("layerFirstPassive", C.c_int), ("radiusHist", C.c_int * HIST_BINS), ("batchRadius", C.c_int * HIST_BINS)]
+
+    def as_dict(self):
+        d = {k: getattr(self, k) for k, _ in self._fields_}
+        d["radiusHist"] = list(self.radiusHist); d["batchRadius"] = list(self.batchRadius)
+        return d
+
+
+class RtdError(RuntimeError):
+    def __init__(self, status: int, msg: str):
+        super().__init__(f"{STATUS.get(status, status)}: {msg}")
+        self.status = status
+
+
+EXPORTS = ["rtd_default_opts", "rtd_create", "rtd_destroy", "rtd_last_error", "rtd_version", "rtd_set_luts", "rtd_set_ct",
+           "rtd_set_ct_device", "rtd_set_dose_grid", "rtd_dose", "rtd_dose_device", "rtd_get_beam_report",
+           "rtd_get_layer_report", "rtd_debug_fetch", "rtd_stream"]
+
+_lib = None
+
+
+def load_library() -> C.CDLL:
+    """Load librtdose.so; fails loudly if the CUDA extension has not been built (no fallback path exists)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(f"{LIB_PATH} not built: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                          f"or `make -C raytracedicom_b200/csrc`. The dose path has no CPU fallback.")
+    lib = C.CDLL(LIB_PATH)
+    vp = C.c_void_p
+    lib.rtd_default_opts.argtypes = [C.POINTER(RtdOpts)]; lib.rtd_default_opts.restype = None
+    lib.rtd_create.argtypes = [C.POINTER(vp), C.c_int]; lib.rtd_create.restype = C.c_int
+    lib.rtd_destroy.argtypes = [vp]; lib.rtd_destroy.restype = None
+    lib.rtd_last_error.argtypes = [vp]; lib.rtd_last_error.restype = C.c_char_p
+    lib.rtd_version.argtypes = []; lib.rtd_version.restype = C.c_char_p
+    lib.rtd_set_luts.argtypes = [vp, C.POINTER(RtdLuts)]; lib.rtd_set_luts.restype = C.c_int
+    lib.rtd_set_ct.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int]; lib.rtd_set_ct.restype = C.c_int
+    lib.rtd_set_ct_device.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int]; lib.rtd_set_ct_device.restype = C.c_int
+    lib.rtd_set_dose_grid.argtypes = [vp, C.c_int, C.c_int, C.c_int]; lib.rtd_set_dose_grid.restype = C.c_int
+    lib.rtd_dose.argtypes = [vp, C.POINTER(RtdBeam), C.c_int, vp, C.POINTER(RtdOpts), C.POINTER(RtdTiming)]; lib.rtd_dose.restype = C.c_int
+    lib.rtd_dose_device.argtypes = lib.rtd_dose.argtypes; lib.rtd_dose_device.restype = C.c_int
+    lib.rtd_get_beam_report.argtypes = [vp, C.c_int, C.POINTER(RtdBeamReport)]; lib.rtd_get_beam_report.restype = C.c_int
+    lib.rtd_get_layer_report.argtypes = [vp, C.c_int, C.c_int, C.POINTER(RtdLayerReport)]; lib.rtd_get_layer_report.restype = C.c_int
+    lib.rtd_debug_fetch.argtypes = [vp, C.c_int, C.c_int, C.c_int, vp, C.c_size_t]; lib.rtd_debug_fetch.restype = C.c_int
+    lib.rtd_stream.argtypes = [vp]; lib.rtd_stream.restype = vp
+    _lib = lib
+    return lib
+
+
+def _f32(a) -> np.ndarray:
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _ptr(a: np.ndarray):
+    return a.ctypes.data_as(_fp)
+
+
+def pack_beams(beams: Sequence[Beam]):
+    """Beam list -> (ctypes array of rtd_beam, keep-alive list)."""
+    arr = (RtdBeam * max(len(beams), 1))()
+    keep = []
+    for i, b in enumerate(beams):
+        w, e, s = _f32(b.weights), _f32(b.energies), _f32(b.sigmas)
+        keep += [w, e, s]
+        rb = arr[i]
+        rb.weights, rb.energies, rb.sigmas = _ptr(w), _ptr(e), _ptr(s)
+        rb.nLayers, rb.sy, rb.sx = w.shape
+        rb.raySpacing = (C.c_float * 2)(*b.ray_spacing)
+        rb.steps = int(b.steps)
+        rb.sourceDist = (C.c_float * 2)(*b.source_dist)
+        rb.spotDelta = (C.c_float * 3)(*b.spot_delta)
+        rb.spotOffset = (C.c_float * 3)(*b.spot_offset)
+        rb.gantryToImIdxM = (C.c_float * 9)(*_f32(b.gantry_to_im_m).ravel())
+        rb.gantryToImIdxV = (C.c_float * 3)(*_f32(b.gantry_to_im_v).ravel())
+        rb.gantryToDoseIdxM = (C.c_float * 9)(*_f32(b.gantry_to_dose_m).ravel())
+        rb.gantryToDoseIdxV = (C.c_float * 3)(*_f32(b.gantry_to_dose_v).ravel())
+    return arr, keep
+
+
+class DoseEngine:
+    """One context per GPU. Mirrors the life cycle inside cudaWrapperProtons: LUT upload, CT upload, per-plan dose."""
+
+    def __init__(self, device: int = 0):
+        self.lib = load_library()
+        self._h = C.c_void_p()
+        st = self.lib.rtd_create(C.byref(self._h), int(device))
+        if st != 0:
+            self._h = C.c_void_p()
+            raise RtdError(st, "rtd_create failed (a CUDA device is required; there is no CPU fallback)")
+        self.device = device
+        self.opts = RtdOpts()
+        self.lib.rtd_default_opts(C.byref(self.opts))
+        self.timing = RtdTiming()
+        self._keep = []
+        self.dose_dims = None
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            self.lib.rtd_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _check(self, st: int):
+        if st != 0:
+            raise RtdError(st, self.lib.rtd_last_error(self._h).decode())
+
+    def set_luts(self, e: EnergyStruct):
+        e.validate()
+        arrs = [_f32(e.energiesPerU), _f32(e.peakDepths), _f32(e.scaleFacts), _f32(e.ciddMatrix), _f32(e.densityVector),
+                _f32(e.spVector), _f32(e.rRlVector)]
+        l = RtdLuts(e.nEnergySamples, e.nEnergies, _ptr(arrs[0]), _ptr(arrs[1]), _ptr(arrs[2]), _ptr(arrs[3]),
+                    e.nDensitySamples, e.densityScaleFact, _ptr(arrs[4]), e.nSpSamples, e.spScaleFact, _ptr(arrs[5]),
+                    e.nRRlSamples, e.rRlScaleFact, _ptr(arrs[6]))
+        self._check(self.lib.rtd_set_luts(self._h, C.byref(l)))
+
+    def set_ct(self, ct: np.ndarray):
+        """ct: float32 [nz][ny][nx] HU+1000 (host)."""
+        ct = _f32(ct)
+        nz, ny, nx = ct.shape
+        self._check(self.lib.rtd_set_ct(self._h, ct.ctypes.data, nx, ny, nz))
+
+    def set_ct_ptr(self, ptr: int, nx: int, ny: int, nz: int, device: bool):
+        fn = self.lib.rtd_set_ct_device if device else self.lib.rtd_set_ct
+        self._check(fn(self._h, C.c_void_p(ptr), nx, ny, nz))
+
+    def set_dose_grid(self, nx: int, ny: int, nz: int):
+        self.dose_dims = (nx, ny, nz)
+        self._check(self.lib.rtd_set_dose_grid(self._h, nx, ny, nz))
+
+    def dose(self, beams: Sequence[Beam], dose: np.ndarray) -> RtdTiming:
+        """Accumulate the plan's dose onto the HOST array ``dose`` ([nz][ny][nx] float32, modified in place)."""
+        if dose.dtype != np.float32 or not dose.flags["C_CONTIGUOUS"]:
+            raise ValueError("dose must be a C-contiguous float32 array")
+        arr, keep = pack_beams(beams)
+        self._check(self.lib.rtd_dose(self._h, arr, len(beams), dose.ctypes.data, C.byref(self.opts), C.byref(self.timing)))
+        return self.timing
+
+    def dose_ptr(self, packed, n_beams: int, ptr: int, device: bool) -> RtdTiming:
+        fn = self.lib.rtd_dose_device if device else self.lib.rtd_dose
+        self._check(fn(self._h, packed, n_beams, C.c_void_p(ptr), C.byref(self.opts), C.byref(self.timing)))
+        return self.timing
+
+    def beam_report(self, beam_no: int) -> dict:
+        r = RtdBeamReport()
+        self._check(self.lib.rtd_get_beam_report(self._h, beam_no, C.byref(r)))
+        return r.as_dict()
+
+    def layer_report(self, beam_no: int, layer_no: int) -> dict:
+        r = RtdLayerReport()
+        self._check(self.lib.rtd_get_layer_report(self._h, beam_no, layer_no, C.byref(r)))
+        return r.as_dict()
+
+    def fetch(self, beam_no: int, what: str, layer: int = 0) -> np.ndarray:
+        rep = self.beam_report(beam_no)
+        rx, ry, s, L = rep["rayDimX"], rep["rayDimY"], rep["steps"], rep["nLayers"]
+        nz = rep["beamFirstGuaranteedPassive"] - rep["beamFirstInside"]
+        shapes = dict(density=((s, ry, rx), np.float32), wepl=((s, ry, rx), np.float32), first_inside=((ry, rx), np.int32),
+                      first_outside=((ry, rx), np.int32), wepl_min=((s,), np.float32), ray_weights=((L, ry, rx), np.float32),
+                      idd=((nz, ry, rx), np.float32), rsigma=((nz, ry, rx), np.float32), first_passive=((ry, rx), np.int32),
+                      bev_dose=((rep["beamFirstGuaranteedPassive"], ry + 64, rx + 64), np.float32),
+                      tile_radius=((nz, ry // 8, rx // 32), np.uint8))
+        shape, dt = shapes[what]
+        out = np.empty(shape, dt)
+        self._check(self.lib.rtd_debug_fetch(self._h, beam_no, FETCH[what], layer, out.ctypes.data, out.nbytes))
+        return out
+
+    @property
+    def stream(self) -> int:
+        return int(self.lib.rtd_stream(self._h) or 0)
+
+
+def cuda_wrapper_protons(im_vol: np.ndarray, dose_vol: np.ndarray, beams: List[Beam], idd_data: EnergyStruct,
+                         out_stream=None, device: int = 0, engine: Optional[DoseEngine] = None) -> RtdTiming:
+    """Python mirror of ``cudaWrapperProtons(imVol, doseVol, beams, iddData, outStream)`` (kernel_wrapper.cuh:161).
+
+    ``dose_vol`` is accumulated in place. Unlike the reference nothing is deleted and the device is not reset."""
+    own = engine is None
+    eng = engine or DoseEngine(device)
+    try:
+        eng.set_luts(idd_data)
+        eng.set_ct(im_vol)
+        nz, ny, nx = dose_vol.shape
+        eng.set_dose_grid(nx, ny, nz)
+        t = eng.dose(beams, dose_vol)
+        if out_stream is not None:
+            out_stream.write(f"    Total global execution time (excluding GPU initialisation): {t.msTotal} ms.\n\n")
+        return t
+    finally:
+        if own:
+            eng.close()
