@@ -1,0 +1,694 @@
+/*
+ * rtd_oracle.c - CPU restatement of the reference's proton dose path.  TEST INFRASTRUCTURE ONLY.
+ *
+ * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may load this
+ * file's shared object (oracle/librtd_oracle.so).  The product (raytracedicom_b200/librtdose.so) never does.
+ *
+ * Parity status: PINNED against outputs of the reference itself.  The reference ships no tests or golden
+ * vectors, so the pin is tests/golden/golden_mini.npz: every intermediate of the reference's own
+ * kernels (rebuilt unmodified for sm_100 by oracle/ref_harness, run on a B200 by tools/gpu_compare.py).
+ * Integer outputs of this restatement match those dumps exactly; float outputs match to the tolerances written
+ * in tests/test_oracle_golden.py (the reference is built with -use_fast_math: div.approx, sqrt.approx,
+ * lg2/ex2.approx cannot be reproduced bit-for-bit on a CPU).
+ *
+ * Every function cites the reference lines it follows (paths relative to /root/reference/src).
+ * Build: gcc -O2 -std=c99 -ffp-contract=off -fopenmp -fPIC -shared rtd_oracle.c -o librtd_oracle.so -lm
+ *        (-ffp-contract=off: fused multiply-adds appear only where written as fmaf(), which is where the
+ *        reference's compiled device code contracts them.)
+ */
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+#define ORC_MAX_R 32 /* maxSuperpR  kernel_wrapper.cuh:26 */
+#define ORC_TX 32    /* superpTileX kernel_wrapper.cuh:27 */
+#define ORC_TY 8     /* superpTileY kernel_wrapper.cuh:28 */
+#define ORC_BINS 34
+
+typedef struct { float x, y, z; } f3;
+static f3 F3(float x, float y, float z) { f3 r; r.x = x; r.y = y; r.z = z; return r; }
+static f3 f3add(f3 a, f3 b) { return F3(a.x + b.x, a.y + b.y, a.z + b.z); }
+static f3 f3sub(f3 a, f3 b) { return F3(a.x - b.x, a.y - b.y, a.z - b.z); }
+static f3 f3mul(f3 a, f3 b) { return F3(a.x * b.x, a.y * b.y, a.z * b.z); }
+static f3 f3scale(f3 a, float s) { return F3(a.x * s, a.y * s, a.z * s); }
+static f3 f3divs(f3 a, float s) { return F3(a.x / s, a.y / s, a.z / s); }
+static float f3dot(f3 a, f3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+
+/* Same field order as the reference's EnergyStruct (energy_struct.h:13-38), as plain pointers. */
+typedef struct {
+    int nEnergySamples, nEnergies;
+    const float *energiesPerU, *peakDepths, *scaleFacts, *ciddMatrix;
+    int nDensitySamples; float densityScaleFact; const float* densityVector;
+    int nSpSamples; float spScaleFact; const float* spVector;
+    int nRRlSamples; float rRlScaleFact; const float* rRlVector;
+} orc_luts;
+
+/* Same content as BeamSettings (beam_settings.h:101-109). */
+typedef struct {
+    const float* weights; int sx, sy, nLayers;
+    const float* energies; const float* sigmas;
+    float raySpacing[2]; unsigned steps; float sourceDist[2];
+    float spotDelta[3], spotOffset[3];
+    float imM[9], imV[3], doseM[9], doseV[3];
+} orc_beam;
+
+/* Run-time copies of the compile-time flags (CMakeLists.txt:36-79). */
+typedef struct { float bpDepthCutoff, convSigmaCutoff, ksSigmaCutoff, rayWeightCutoff; int minTilesInBatch; int texFracMode; } orc_opts;
+
+/* Everything the reference computes for one beam; arrays are malloc'ed here and released by orc_free_result. */
+typedef struct {
+    int lSteps, bSteps, rSteps, tSteps, Rx, Ry, S, L;
+    int bfi, bfo, Zg, fcp;
+    int bboxMin[3], bboxMax[3];
+    float entryZ;
+    long long updates, ksTaps;
+    float *density, *wepl;           /* [S][Ry][Rx] */
+    int *firstInside, *firstOutside; /* [Ry][Rx] */
+    float* weplMin;                  /* [S] */
+    float* rayWeights;               /* [L][Ry][Rx] */
+    float *idd, *rsig;               /* [S][Ry][Rx] of layer keepLayer (as the reference leaves them after that layer) */
+    int* firstPassive;               /* [L][Ry][Rx] */
+    float* layerF;                   /* [L][5]: energyIdx, scale, peak, entrySigX, entrySigY */
+    int* layerI;                     /* [L][2]: afterLast, layerFirstPassive */
+    int* hist;                       /* [L][34] */
+    int* batchRad;                   /* [L][34] */
+    float* bev;                      /* [Zg][Ry+64][Rx+64] */
+    int keepLayer;
+    int radiusError;
+} orc_result;
+
+void orc_default_opts(orc_opts* o) {
+    o->bpDepthCutoff = 1.05f; o->convSigmaCutoff = 3.0f; o->ksSigmaCutoff = 3.0f; o->rayWeightCutoff = 1.0f;
+    o->minTilesInBatch = 16; o->texFracMode = 0;
+}
+
+void orc_free_result(orc_result* r) {
+    free(r->density); free(r->wepl); free(r->firstInside); free(r->firstOutside); free(r->weplMin); free(r->rayWeights);
+    free(r->idd); free(r->rsig); free(r->firstPassive); free(r->layerF); free(r->layerI); free(r->hist); free(r->batchRad); free(r->bev);
+    memset(r, 0, sizeof *r);
+}
+
+/* ---------------------------------------------------------------------------------------------------------
+ * 3x3 matrix / affine / index transforms (matrix_3x3.cu:20-53, float3_affine_transform.cu:16-24,
+ * float3_idx_transform.cu:17-21) */
+typedef struct { f3 r0, r1, r2; } m33;
+static m33 m33from(const float* p) { m33 m; m.r0 = F3(p[0], p[1], p[2]); m.r1 = F3(p[3], p[4], p[5]); m.r2 = F3(p[6], p[7], p[8]); return m; }
+static m33 m33transpose(m33 m) { m33 t; t.r0 = F3(m.r0.x, m.r1.x, m.r2.x); t.r1 = F3(m.r0.y, m.r1.y, m.r2.y); t.r2 = F3(m.r0.z, m.r1.z, m.r2.z); return t; }
+static f3 m33apply(m33 m, f3 a) { return F3(f3dot(m.r0, a), f3dot(m.r1, a), f3dot(m.r2, a)); }
+static float m33det(m33 m) {
+    return (m.r0.x * (m.r1.y * m.r2.z - m.r1.z * m.r2.y) - m.r0.y * (m.r1.x * m.r2.z - m.r1.z * m.r2.x) + m.r0.z * (m.r1.x * m.r2.y - m.r1.y * m.r2.x));
+}
+/* matrix_3x3.cu:48-53: adjugate times float(1./det) through the implicit diagonal-matrix constructor (H14) */
+static m33 m33inverse(m33 m) {
+    const float s = (float)(1. / m33det(m));
+    f3 a0 = F3(m.r1.y * m.r2.z - m.r1.z * m.r2.y, m.r0.z * m.r2.y - m.r0.y * m.r2.z, m.r0.y * m.r1.z - m.r0.z * m.r1.y);
+    f3 a1 = F3(m.r1.z * m.r2.x - m.r1.x * m.r2.z, m.r0.x * m.r2.z - m.r0.z * m.r2.x, m.r0.z * m.r1.x - m.r0.x * m.r1.z);
+    f3 a2 = F3(m.r1.x * m.r2.y - m.r1.y * m.r2.x, m.r0.y * m.r2.x - m.r0.x * m.r2.y, m.r0.x * m.r1.y - m.r0.y * m.r1.x);
+    f3 c0 = F3(s, 0.f, 0.f), c1 = F3(0.f, s, 0.f), c2 = F3(0.f, 0.f, s);
+    m33 r;
+    r.r0 = F3(f3dot(a0, c0), f3dot(a0, c1), f3dot(a0, c2));
+    r.r1 = F3(f3dot(a1, c0), f3dot(a1, c1), f3dot(a1, c2));
+    r.r2 = F3(f3dot(a2, c0), f3dot(a2, c1), f3dot(a2, c2));
+    return r;
+}
+typedef struct { m33 m; f3 v; } affine;
+static f3 affine_apply(affine a, f3 p) { return f3add(m33apply(a.m, p), a.v); }
+static affine affine_inverse(affine a) { affine r; r.m = m33inverse(a.m); r.v = m33apply(m33inverse(a.m), f3scale(a.v, -1.f)); return r; }
+typedef struct { f3 delta, offset; } idxt;
+
+/* Float3FromFanTransform::transformPoint, float3_from_fan_transform.cu:37-42 */
+static f3 from_fan(idxt t, const float dist[2], affine g, f3 fanIdx) {
+    f3 p = f3add(f3mul(fanIdx, t.delta), t.offset);
+    p.x *= 1.0f - p.z / dist[0];
+    p.y *= 1.0f - p.z / dist[1];
+    return affine_apply(g, p);
+}
+
+/* ---------------------------------------------------------------------------------------------------------
+ * ordered-list helpers (vector_find.h:62-145, vector_interpolate.h:19-30) */
+static int find_first_larger_ordered(const float* list, int n, float value) {
+    int upper = n - 1, lower = 0;
+    if (list[n - 1] <= value) return upper;
+    if (list[0] > value) return 0;
+    while (upper - lower > 1) { int pivot = (upper + lower) / 2; if (list[pivot] <= value) lower = pivot; else upper = pivot; }
+    return lower + 1;
+}
+static int find_last_smaller_or_eq(const float* list, int n, float value) {
+    int upper = n - 1, lower = 0;
+    if (list[n - 1] <= value) return upper;
+    if (list[0] > value) return -1;
+    while (upper - lower > 1) { int pivot = (upper + lower) / 2; if (list[pivot] <= value) lower = pivot; else upper = pivot; }
+    return lower;
+}
+float orc_find_decimal_ordered(const float* list, int n, float value) {
+    if (value >= list[n - 1]) return (float)(n - 1);
+    if (value < list[0]) return 0.0f;
+    unsigned f = (unsigned)find_last_smaller_or_eq(list, n, value);
+    float corr = (value - list[f]) / (list[f + 1] - list[f]);
+    return (float)f + corr;
+}
+float orc_vector_interpolate(const float* list, int n, float idx) {
+    if (idx <= 0.0f) return list[0];
+    if (idx >= (float)(n - 1)) return list[n - 1];
+    float ip; float dec = modff(idx, &ip);
+    unsigned f = (unsigned)ip;
+    float corr = (list[f + 1] - list[f]) * dec;
+    return list[f] + corr;
+}
+static int round_to(int v, int m) { return ((v + m - 1) / m) * m; } /* kernel_wrapper.cu:45-48 */
+
+/* ---------------------------------------------------------------------------------------------------------
+ * Software model of the CUDA texture unit as the reference configures it (kernel_wrapper.cu:431-434, 459-460,
+ * 482, 503, 524, 1132-1134): unnormalised coordinates, cudaFilterModeLinear, element read mode; 1-D / 2-D LUTs
+ * clamp, CT and BEV dose use border (0).
+ * The filter arithmetic below was FITTED to the B200's texture unit with tools/texprobe (ramp, product and
+ * random-texel probes, 400k-1.8M fetches per mode; summary in profiles/r01_texture_filter_model.md) and
+ * reproduces every probed fetch to 1 ulp:
+ *   - per axis q = floor((c - 0.5) * 256 + 0.5): texel i = q >> 8, fraction a = q & 255 (8 fractional bits);
+ *   - the 2 / 4 / 8 blend weights are INTEGERS summing to 256, split hierarchically z -> x -> y:
+ *       Wz = a_z | 256 - a_z;  x1 = floor(Wz a_x / 256 + 1/2), x0 = Wz - x1;
+ *       w(x1,y1) = floor(x1 a_y / 256 + 1/2);  w(x0,y1) = ceil(x0 a_y / 256 - 1/2);  y0 weights = remainders;
+ *   - result = sum(w T) / 256 accumulated wider than fp32, rounded once.
+ * texFracMode 0 = this model; 1 = separable weights with truncated fraction; 2 = separable, exact fraction
+ * (the latter two exist to show in tests that the pin against the golden vectors discriminates). */
+static int g_tex_mode = 0;
+static int clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
+static void tex_split(float c, int* i, int* a, float* fr) {
+    const float xb = c - 0.5f;
+    if (g_tex_mode == 0) {
+        float q = floorf(xb * 256.0f + 0.5f);
+        if (q < -1.0e6f) q = -1.0e6f; if (q > 1.0e8f) q = 1.0e8f; /* far outside any texture: keeps the int conversion defined */
+        const int qi = (int)q;
+        *i = qi >> 8; *a = qi & 255; *fr = (float)(*a) * (1.0f / 256.0f);
+    } else {
+        float fl = floorf(xb);
+        if (fl < -1.0e6f) fl = -1.0e6f; if (fl > 1.0e8f) fl = 1.0e8f;
+        *i = (int)fl; *fr = xb - floorf(xb);
+        if (g_tex_mode == 1) *fr = floorf(*fr * 256.0f) * (1.0f / 256.0f);
+        *a = 0;
+    }
+}
+static int rup(int p) { return (p + 128) >> 8; }   /* floor(p/256 + 1/2) */
+static int rdn(int p) { return (p + 127) >> 8; }   /* ceil(p/256 - 1/2)  */
+
+static float tex1d_clamp(const float* t, int n, float c) {
+    int i, a; float f; tex_split(c, &i, &a, &f);
+    const double t0 = t[clampi(i, 0, n - 1)], t1 = t[clampi(i + 1, 0, n - 1)];
+    return (float)((1.0 - (double)f) * t0 + (double)f * t1);
+}
+static float tex2d_clamp(const float* t, int w, int h, float cx, float cy) {
+    int i, j, a, b; float fa, fb; tex_split(cx, &i, &a, &fa); tex_split(cy, &j, &b, &fb);
+    const int i0 = clampi(i, 0, w - 1), i1 = clampi(i + 1, 0, w - 1), j0 = clampi(j, 0, h - 1), j1 = clampi(j + 1, 0, h - 1);
+    const double t00 = t[(size_t)j0 * w + i0], t10 = t[(size_t)j0 * w + i1], t01 = t[(size_t)j1 * w + i0], t11 = t[(size_t)j1 * w + i1];
+    if (g_tex_mode == 0) {
+        const int x1 = a, x0 = 256 - a;
+        const int w11 = rup(x1 * b), w01 = rdn(x0 * b);
+        return (float)(((x0 - w01) * t00 + (x1 - w11) * t10 + w01 * t01 + w11 * t11) * (1.0 / 256.0));
+    }
+    return (float)((1.0 - fb) * ((1.0 - fa) * t00 + fa * t10) + fb * ((1.0 - fa) * t01 + fa * t11));
+}
+static double vox_border(const float* t, int w, int h, int d, int x, int y, int z) {
+    if (x < 0 || y < 0 || z < 0 || x >= w || y >= h || z >= d) return 0.0;
+    return t[((size_t)z * h + y) * w + x];
+}
+static float tex3d_border(const float* t, int w, int h, int d, float cx, float cy, float cz) {
+    int x, y, z, a, b, c; float fa, fb, fc;
+    tex_split(cx, &x, &a, &fa); tex_split(cy, &y, &b, &fb); tex_split(cz, &z, &c, &fc);
+    if (x < -1 || y < -1 || z < -1 || x >= w || y >= h || z >= d) return 0.0f;
+    if (g_tex_mode == 0) {
+        double acc = 0.0;
+        for (int dz = 0; dz < 2; ++dz) {
+            const int Wz = dz ? c : 256 - c;
+            if (Wz == 0) continue;
+            const int x1 = rup(Wz * a), x0 = Wz - x1;
+            const int w11 = rup(x1 * b), w01 = rdn(x0 * b);
+            acc += (x0 - w01) * vox_border(t, w, h, d, x, y, z + dz) + (x1 - w11) * vox_border(t, w, h, d, x + 1, y, z + dz) +
+                   w01 * vox_border(t, w, h, d, x, y + 1, z + dz) + w11 * vox_border(t, w, h, d, x + 1, y + 1, z + dz);
+        }
+        return (float)(acc * (1.0 / 256.0));
+    }
+    const double oa = 1.0 - fa, ob = 1.0 - fb, oc = 1.0 - fc;
+    return (float)(oc * (ob * (oa * vox_border(t, w, h, d, x, y, z) + fa * vox_border(t, w, h, d, x + 1, y, z)) +
+                         fb * (oa * vox_border(t, w, h, d, x, y + 1, z) + fa * vox_border(t, w, h, d, x + 1, y + 1, z))) +
+                   fc * (ob * (oa * vox_border(t, w, h, d, x, y, z + 1) + fa * vox_border(t, w, h, d, x + 1, y, z + 1)) +
+                         fb * (oa * vox_border(t, w, h, d, x, y + 1, z + 1) + fa * vox_border(t, w, h, d, x + 1, y + 1, z + 1))));
+}
+
+/* ---------------------------------------------------------------------------------------------------------
+ * Stage 1: fan-beam density / WEPL tracer.
+ * DensityAndSpTracerParams ctor density_and_sp_tracer_params.cu:19-30; getStart :15, getInc :17, stepLen :32-36;
+ * kernel fillBevDensityAndSp kernel_wrapper.cu:130-187. */
+typedef struct { f3 coefOffset, coefIdxI, coefIdxJ, transl, corner, delta; float distX, distY; } trace_params;
+
+static trace_params make_trace_params(idxt fitf, const float dist[2], affine gtii) {
+    trace_params p; p.distX = dist[0]; p.distY = dist[1]; p.corner = fitf.offset; p.delta = fitf.delta;
+    const m33 t = m33transpose(gtii.m);
+    p.coefOffset = f3sub(f3sub(t.r2, f3divs(f3scale(t.r0, p.corner.x), p.distX)), f3divs(f3scale(t.r1, p.corner.y), p.distY));
+    p.coefIdxI = f3scale(t.r0, p.delta.x);
+    p.coefIdxJ = f3scale(t.r1, p.delta.y);
+    p.transl = f3add(f3add(f3add(gtii.v, f3scale(t.r2, p.corner.z)), f3scale(f3scale(t.r0, p.corner.x), 1.0f - p.corner.z / p.distX)),
+                     f3scale(f3scale(t.r1, p.corner.y), 1.0f - p.corner.z / p.distY));
+    return p;
+}
+
+static void stage_trace(const orc_luts* lut, const float* ct, int nx, int ny, int nz, const trace_params* p, int Rx, int Ry, int S,
+                        float* density, float* wepl, int* firstInside, int* firstOutside) {
+    const size_t R = (size_t)Rx * Ry;
+    const float s1 = 1.0f - p->corner.z / p->distX, s2 = 1.0f - p->corner.z / p->distY;
+#pragma omp parallel for schedule(static)
+    for (int ray = 0; ray < (int)R; ++ray) {
+        const int ix = ray % Rx, iy = ray / Rx;
+        const float fi = (float)ix, fj = (float)iy;
+        /* getStart + HALF (cu:142); the device code contracts a*b+c*d into one fma */
+        float px = (p->transl.x + fmaf(p->coefIdxI.x * fi, s1, (p->coefIdxJ.x * fj) * s2)) + 0.5f;
+        float py = (p->transl.y + fmaf(p->coefIdxI.y * fi, s1, (p->coefIdxJ.y * fj) * s2)) + 0.5f;
+        float pz = (fmaf(p->coefIdxI.z * fi, s1, (p->coefIdxJ.z * fj) * s2) + p->transl.z) + 0.5f;
+        /* getInc (cu:143) */
+        const float dx = ((p->coefOffset.x - (p->coefIdxI.x * fi) / p->distX) - (p->coefIdxJ.x * fj) / p->distY) * p->delta.z;
+        const float dy = ((p->coefOffset.y - (p->coefIdxI.y * fi) / p->distX) - (p->coefIdxJ.y * fj) / p->distY) * p->delta.z;
+        const float dz = ((p->coefOffset.z - (p->coefIdxI.z * fi) / p->distX) - (p->coefIdxJ.z * fj) / p->distY) * p->delta.z;
+        /* stepLen (cu:144) */
+        const float ddx = fmaf(p->delta.x, fi, p->corner.x) / p->distX, ddy = fmaf(p->delta.y, fj, p->corner.y) / p->distY;
+        const float stepLen = fabsf(p->delta.z) * sqrtf(fmaf(ddy, ddy, fmaf(ddx, ddx, 1.0f)));
+        float cumSp = 0.0f, cumHu = 0.0f;
+        int before = -1, last = -1;
+        size_t idx = (size_t)ray;
+        for (int i = 0; i < S; ++i) {
+            const float hu = tex3d_border(ct, nx, ny, nz, px, py, pz);
+            cumHu += hu;
+            density[idx] = tex1d_clamp(lut->densityVector, lut->nDensitySamples, fmaf(hu, lut->densityScaleFact, 0.5f));
+            cumSp = fmaf(stepLen, tex1d_clamp(lut->spVector, lut->nSpSamples, fmaf(hu, lut->spScaleFact, 0.5f)), cumSp);
+            if (cumHu < 150.0f) before = i;
+            if (hu > 150.0f) last = i;
+            wepl[idx] = cumSp;
+            idx += R;
+            px += dx; py += dy; pz += dz; /* accumulated, not recomputed (cu:183) */
+        }
+        firstInside[ray] = before + 1;
+        firstOutside[ray] = last + 1;
+    }
+}
+
+/* sliceMinVar / sliceMaxVar (kernel_wrapper.cuh:173-244; launches kernel_wrapper.cu:781-790) */
+static void stage_reduce(const float* wepl, const int* firstInside, const int* firstOutside, int R, int S, int* bfi, int* bfo, float* weplMin) {
+    int a = firstInside[0], b = firstOutside[0];
+    for (int i = 1; i < R; ++i) { if (firstInside[i] < a) a = firstInside[i]; if (firstOutside[i] > b) b = firstOutside[i]; }
+    *bfi = a; *bfo = b;
+#pragma omp parallel for schedule(static)
+    for (int k = 0; k < S; ++k) {
+        const float* row = wepl + (size_t)k * R;
+        float m = row[0];
+        for (int i = 1; i < R; ++i) if (row[i] < m) m = row[i];
+        weplMin[k] = m;
+    }
+}
+
+/* ---------------------------------------------------------------------------------------------------------
+ * Stage 3a: spot weights -> ray weights (gpu_convolution_2d.cu:16-71; host part :61-71, kernel_wrapper.cu:849-854) */
+static float conv_weight(float dist, float rSig) { /* gpu_convolution_2d.cu:28 */
+    return (erff(rSig * (dist + 0.5f)) - erff(rSig * (dist - 0.5f))) * 0.5f;
+}
+static void conv_axis(const float* in, int inN, int inStride, float* out, int outN, int outStride, float sigma, float pixelSp,
+                      float off, float delta, float cutoff) {
+    const float sigEff = sigma / pixelSp;
+    const float rSig = (1.0f / sqrtf(2.0f)) / sigEff;
+    const float lim = fmaf(sigEff, cutoff, 0.5f);
+    for (int o = 0; o < outN; ++o) {
+        const float fo = (float)o;
+        int ci = (int)ceilf(((fo - lim) - off) / delta);
+        float res = 0.0f;
+        float dist = fmaf(delta, (float)ci, off) - fo;
+        while (dist < lim) {
+            if (ci >= 0 && ci < inN) res = fmaf(in[(size_t)ci * inStride], conv_weight(dist, rSig), res);
+            ++ci;
+            dist = fmaf(delta, (float)ci, off) - fo;
+        }
+        out[(size_t)o * outStride] = res;
+    }
+}
+static void stage_conv(const orc_beam* b, const float* entrySig /*[L][2]*/, idxt ray, float pxMultX, float pxMultY, int Rx, int Ry,
+                       float cutoff, float* rayW) {
+    const int Sx = b->sx, Sy = b->sy, L = b->nLayers;
+    const float deltaX = b->spotDelta[0] / ray.delta.x, deltaY = b->spotDelta[1] / ray.delta.y;
+    const float offX = (b->spotOffset[0] - ray.offset.x) / ray.delta.x, offY = (b->spotOffset[1] - ray.offset.y) / ray.delta.y;
+    const float pixX = ray.delta.x * pxMultX, pixY = ray.delta.y * pxMultY;
+#pragma omp parallel for schedule(static)
+    for (int l = 0; l < L; ++l) {
+        float* interm = (float*)malloc((size_t)Sy * Rx * sizeof(float));
+        for (int y = 0; y < Sy; ++y) /* x pass :16-35 */
+            conv_axis(b->weights + ((size_t)l * Sy + y) * Sx, Sx, 1, interm + (size_t)y * Rx, Rx, 1, entrySig[2 * l], pixX, offX, deltaX, cutoff);
+        for (int x = 0; x < Rx; ++x) /* y pass :37-59 */
+            conv_axis(interm + x, Sy, Rx, rayW + (size_t)l * Rx * Ry + x, Ry, Rx, entrySig[2 * l + 1], pixY, offY, deltaY, cutoff);
+        free(interm);
+    }
+}
+
+/* ---------------------------------------------------------------------------------------------------------
+ * Stage 2: integrated depth dose + lateral sigma of one energy layer.
+ * FillIddAndSigmaParams ctor fill_idd_and_sigma_params.cu:12-26, initStepAndAirDiv :28-40, voxelWidth :42-46,
+ * stepVol :72, sigmaSqAirCoefs :74-83; kernel fillIddAndSigma kernel_wrapper.cu:189-379 (NUCLEAR_CORR off,
+ * DOSE_TO_WATER on, nozzle on). */
+typedef struct { f3 corner, delta; float distX, distY, volConst, volLin, volSq; } fill_geom;
+
+static fill_geom make_fill_geom(idxt fitf, const float dist[2]) {
+    fill_geom g; g.corner = fitf.offset; g.delta = fitf.delta; g.distX = dist[0]; g.distY = dist[1];
+    const f3 c = g.corner, d = g.delta;
+    const float a = fabsf(d.x * d.y * d.z);
+    g.volConst = a * (1.0f - c.z / g.distX - c.z / g.distY + (c.z * c.z + d.z * d.z / 12.0f) / (g.distX * g.distY));
+    g.volLin = a * d.z * (-1.0f / g.distX - 1.0f / g.distY + 2.0f * c.z / (g.distX * g.distY));
+    g.volSq = a * d.z * d.z / (g.distX * g.distY);
+    return g;
+}
+
+typedef struct { float energyIdx, energyScale, peakDepth; int afterLast; } layer_params;
+
+static void stage_idd_sigma(const orc_luts* lut, const fill_geom* g, const layer_params* lp, const orc_opts* o, int first, int Rx, int Ry,
+                            const float* density, const float* wepl, const float* rayW /*[R] of this layer*/, const int* firstInside,
+                            const int* firstOutside, float* idd, float* rsig, int* firstPassive) {
+    const int R = Rx * Ry;
+    const float INF = INFINITY;
+    /* initStepAndAirDiv (cu:223), relStepLenSq = 1 */
+    const float ca = 0.00270f / (lp->peakDepth + -4.50f), cb = -4.39f / (lp->peakDepth + -3.86f);
+    const float dzs = g->delta.z;
+    const float airQuad = dzs * (ca * dzs);
+    const float airLin = fmaf(cb, dzs, g->corner.z * ((ca + ca) * dzs));
+    const float stepLength = fabsf(dzs);
+    const float thr = lp->peakDepth * o->bpDepthCutoff;
+#pragma omp parallel for schedule(static)
+    for (int ray = 0; ray < R; ++ray) {
+        const int firstIn = firstInside[ray];
+        unsigned afterLast = (unsigned)(firstOutside[ray] < lp->afterLast ? firstOutside[ray] : lp->afterLast); /* cu:207 */
+        const float rayWeight = rayW[ray];
+        int live = 1;
+        if (rayWeight < o->rayWeightCutoff || afterLast < (unsigned)first) { live = 0; afterLast = 0; }     /* cu:208-213 */
+        float incScat = 0.0f, incinc = 0.0f;
+        float incDiv = fmaf(airQuad, fmaf((float)(unsigned)first, 2.0f, -1.0f), airLin);                    /* cu:250 */
+        float sigmaSq = -incDiv;
+        float res = 0.0f, rs = 0.0f, wOld = 0.0f, dOld = 0.0f;
+        size_t idx = (size_t)first * R + ray;
+        for (unsigned k = (unsigned)first; k < (unsigned)lp->afterLast; ++k) {
+            if (live) {
+                const float w = wepl[idx];
+                const float d = tex2d_clamp(lut->ciddMatrix, lut->nEnergySamples, lut->nEnergies, fmaf(w, lp->energyScale, 0.5f), lp->energyIdx + 0.5f);
+                const float rho = density[idx];
+                if (w < lp->peakDepth) {
+                    /* __powf(x, y) = exp2(y * log2(x)) */
+                    const float resE = exp2f(log2f(lp->peakDepth - (wOld + w) * 0.5f) * 0.5649718f);
+                    const float e1 = fmaf(resE, 8.639415f, 938.3f);
+                    const float betaP = e1 - 880406.875f / e1;                                              /* 938.3^2 folded by the compiler */
+                    const float rRl = rho * tex1d_clamp(lut->rRlVector, lut->nRRlSamples, fmaf(rho, lut->rRlScaleFact, 0.5f));
+                    const float t1 = (198.81f / (betaP * betaP)) * stepLength;
+                    const float thetaSq = rRl * t1;
+                    sigmaSq = sigmaSq + (incScat + incDiv);
+                    incinc = fmaf(stepLength, stepLength * fmaf(rRl, t1, thetaSq), incinc);                 /* 2*thetaSq*len*len */
+                    incScat = incScat + incinc;
+                    incDiv = fmaf(airQuad, 2.0f, incDiv);
+                } else {
+                    sigmaSq = fmaf((incScat + incDiv) * -1.5f, rho, sigmaSq);                               /* cu:297 */
+                }
+                const float fk = (float)k;
+                const float zk = fmaf(g->delta.z, fk, g->corner.z);
+                const float vwx = g->delta.x * (1.0f - zk / g->distX), vwy = g->delta.y * (1.0f - zk / g->distY);
+                rs = ((vwx + vwy) * 0.5f) / ((sqrtf(sigmaSq) + 0.21f) * 1.41421356f);                      /* cu:307 */
+                const int within = !(w > thr);
+                live = within && (k != afterLast);                                                          /* cu:309-312 */
+                afterLast = within ? afterLast : k;
+                const float vol = fmaf(g->volSq, (float)(k * k), fmaf(g->volLin, fk, g->volConst));
+                const float mass = (w - wOld) * vol;
+                if (mass > 1e-2f) res = (rayWeight * (d - dOld)) / mass;                                    /* else keeps the previous value (H9) */
+                wOld = w; dOld = d;
+            }
+            if (!live || (int)k < firstIn - 1) { res = 0.0f; rs = INF; }                                    /* cu:361-370 */
+            idd[idx] = res;
+            rsig[idx] = rs;
+            idx += R;
+        }
+        firstPassive[ray] = (int)afterLast;
+    }
+}
+
+/* ---------------------------------------------------------------------------------------------------------
+ * Stage 3b: tile radii, batching, kernel superposition.
+ * tileRadCalc kernel_wrapper.cuh:256-313 (radius :303); host batching kernel_wrapper.cu:966-976;
+ * kernelSuperposition<rad> kernel_wrapper.cuh:432-489. */
+static int tile_radius(const float* rsig, int Rx, int tx, int ty, float ksCutoff) {
+    float m = rsig[(size_t)(ty * ORC_TY) * Rx + tx * ORC_TX];
+    for (int y = 0; y < ORC_TY; ++y)
+        for (int x = 0; x < ORC_TX; ++x) { const float v = rsig[(size_t)(ty * ORC_TY + y) * Rx + tx * ORC_TX + x]; if (v < m) m = v; }
+    const float q = ksCutoff / (sqrtf(2.0f) * m) + 0.5f;
+    int rad = (q >= 2147483648.0f) ? 0x7fffffff : (int)q; /* cvt.rzi saturates */
+    if (!(q == q)) rad = 0;                               /* NaN converts to 0 on the device */
+    return rad < ORC_MAX_R + 1 ? rad : ORC_MAX_R + 1;
+}
+
+static void batch_radii(const int* ctr /*[34]*/, int minTiles, int* applied /*[34]: radius applied to tiles of own radius r*/) {
+    int layerMax = 0;
+    for (int i = 0; i < ORC_BINS; ++i) { applied[i] = i; if (ctr[i] > 0) layerMax = i; }
+    if (layerMax > ORC_MAX_R) layerMax = ORC_MAX_R;
+    int rec = layerMax, acc = 0;
+    for (int rad = layerMax; rad > 0; --rad) {
+        acc += ctr[rad];
+        applied[rad] = rec;
+        if (acc >= minTiles) { rec = rad - 1; acc = 0; }
+    }
+}
+
+static void superpose_tile(const float* idd, const float* rsig, int Rx, int tx, int ty, int rb, float* out /* slice, pitch Rx+64 */) {
+    const int pitch = Rx + 2 * ORC_MAX_R;
+    int any = 0;
+    for (int y = 0; y < ORC_TY && !any; ++y)
+        for (int x = 0; x < ORC_TX; ++x) if (idd[(size_t)(ty * ORC_TY + y) * Rx + tx * ORC_TX + x] > 0.0f) { any = 1; break; }
+    if (!any) return; /* __syncthreads_or(dose > 0), cuh:456 */
+    const int NC = ORC_TX + 2 * rb, NR = ORC_TY + 2 * rb;
+    float tile[(ORC_TX + 2 * ORC_MAX_R) * (ORC_TY + 2 * ORC_MAX_R)];
+    memset(tile, 0, sizeof(float) * NC * NR);
+    float e[ORC_MAX_R + 1];
+    for (int y = 0; y < ORC_TY; ++y)
+        for (int x = 0; x < ORC_TX; ++x) {
+            const size_t gi = (size_t)(ty * ORC_TY + y) * Rx + tx * ORC_TX + x;
+            const float dose = idd[gi], r = rsig[gi];
+            float erfNew = erff(r * 0.5f), erfOld = -erfNew;               /* cuh:459-467 */
+            for (int i = 0; i <= rb; ++i) { e[i] = 0.5f * (erfNew - erfOld); erfOld = erfNew; erfNew = erff(r * ((float)i + 1.5f)); }
+            for (int i = 0; i < 2 * rb + 1; ++i) {
+                const float hy = dose * e[abs(rb - i)];
+                float* trow = tile + (size_t)(y + i) * NC + x;
+                for (int j = 0; j < 2 * rb + 1; ++j) trow[j] += hy * e[abs(rb - j)];
+            }
+        }
+    for (int r = 0; r < NR; ++r) {
+        float* orow = out + (size_t)(ty * ORC_TY + ORC_MAX_R - rb + r) * pitch + tx * ORC_TX + ORC_MAX_R - rb;
+        for (int c = 0; c < NC; ++c) orow[c] += tile[(size_t)r * NC + c];
+    }
+}
+
+/* ---------------------------------------------------------------------------------------------------------
+ * Stage 4: BEV dose -> dose grid.  TransferParamStructDiv3 transfer_param_struct_div3.cu:9-34,
+ * invertAndShift float3_from_fan_transform.cu:27-30, kernel primTransfDiv kernel_wrapper.cu:69-97,
+ * bounding box kernel_wrapper.cu:1185-1210. */
+typedef struct { f3 globalOffset, coefOffset, coefIdxI, coefIdxJ, inc; float normDistX, normDistY; } transfer_params;
+
+static transfer_params make_transfer_params(idxt fitf, const float dist[2], affine gtdi, f3 shift) {
+    idxt inv; /* Float3IdxTransform::inverse + shiftOffset */
+    inv.delta = F3(1.0f / fitf.delta.x, 1.0f / fitf.delta.y, 1.0f / fitf.delta.z);
+    inv.offset = F3(-fitf.offset.x / fitf.delta.x, -fitf.offset.y / fitf.delta.y, -fitf.offset.z / fitf.delta.z);
+    inv.offset = f3add(inv.offset, shift);
+    const affine iitg = affine_inverse(gtdi);
+    const m33 t = m33transpose(iitg.m);
+    transfer_params p;
+    p.coefIdxI = f3mul(t.r0, inv.delta);
+    p.coefIdxJ = f3mul(t.r1, inv.delta);
+    p.coefOffset = f3mul(iitg.v, inv.delta);
+    p.globalOffset = inv.offset;
+    p.inc = f3mul(t.r2, inv.delta);
+    p.normDistX = inv.delta.z * dist[0];
+    p.normDistY = inv.delta.z * dist[1];
+    return p;
+}
+
+static void stage_transfer(const transfer_params* t, const float* bevSub, int W, int H, int D, const int mn[3], const int mx[3],
+                           int nx, int ny, int nz, float* dose) {
+    (void)nz;
+    const int x1 = mn[0] + round_to(mx[0] - mn[0] + 1, 32), y1 = mn[1] + round_to(mx[1] - mn[1] + 1, 8); /* launch shape cu:1211-1212 */
+#pragma omp parallel for schedule(static)
+    for (int y = mn[1]; y < y1; ++y) {
+        if (y >= ny) continue;
+        for (int x = mn[0]; x < x1 && x < nx; ++x) {
+            const float fi = (float)x, fj = (float)y;
+            const float sx = fmaf(t->coefIdxI.x, fi, t->coefIdxJ.x * fj) + t->coefOffset.x;   /* init(i,j) */
+            const float sy = fmaf(t->coefIdxI.y, fi, t->coefIdxJ.y * fj) + t->coefOffset.y;
+            const float sz = fmaf(t->coefIdxI.z, fi, t->coefIdxJ.z * fj) + t->coefOffset.z;
+            for (int z = mn[2]; z <= mx[2]; ++z) {
+                const float fk = (float)z;                                                     /* getFanIdx(k) */
+                const float rx = fmaf(t->inc.x, fk, sx), ry = fmaf(t->inc.y, fk, sy), rz = fmaf(t->inc.z, fk, sz);
+                const float mxs = rz / (t->normDistX - rz) + 1.0f, mys = rz / (t->normDistY - rz) + 1.0f;
+                const float cx = fmaf(rx, mxs, t->globalOffset.x) + 0.5f, cy = fmaf(ry, mys, t->globalOffset.y) + 0.5f;
+                const float cz = (rz + t->globalOffset.z) + 0.5f;
+                const float v = tex3d_border(bevSub, W, H, D, cx, cy, cz);
+                if (v > 0.0f) dose[((size_t)z * ny + y) * nx + x] += v;
+            }
+        }
+    }
+}
+
+/* ---------------------------------------------------------------------------------------------------------
+ * One beam of cudaWrapperProtons (kernel_wrapper.cu:601-1281).  dose is accumulated (cu:91-93).
+ * keepLayer: the layer whose idd / rsig arrays are returned (-1: none).  stopAfter: 0 = full beam, 1 = stop
+ * after the tracer + reductions, 2 = after the pre-convolution, 3 = after the layer loop (no transfer).
+ * Returns 0, or 3 when a tile needs a radius > 32 (the reference throws, cu:965), or 1 on bad input. */
+int orc_beam_dose(const orc_luts* lut, const float* ct, int nx, int ny, int nz, const orc_beam* b, int dnx, int dny, int dnz,
+                  float* dose, const orc_opts* opts, int keepLayer, int stopAfter, orc_result* r) {
+    orc_opts o; if (opts) o = *opts; else orc_default_opts(&o);
+    g_tex_mode = o.texFracMode;
+    memset(r, 0, sizeof *r);
+    r->keepLayer = keepLayer;
+    const int L = b->nLayers;
+    if (L <= 0 || b->sx <= 0 || b->sy <= 0 || b->steps == 0) return 1;
+    /* ray grid, cu:612-663 */
+    float maxSigX = b->sigmas[0], maxSigY = b->sigmas[1];
+    for (int l = 1; l < L; ++l) { if (b->sigmas[2 * l] > maxSigX) maxSigX = b->sigmas[2 * l]; if (b->sigmas[2 * l + 1] > maxSigY) maxSigY = b->sigmas[2 * l + 1]; }
+    const f3 res = F3(b->raySpacing[0], b->raySpacing[1], b->spotDelta[2]);
+    const float cc = o.convSigmaCutoff;
+    r->lSteps = (int)ceilf((b->spotOffset[0] - (cc * maxSigX + 0.5f * res.x)) / res.x);
+    r->bSteps = (int)ceilf((b->spotOffset[1] - (cc * maxSigY + 0.5f * res.y)) / res.y);
+    r->rSteps = (int)floorf((((unsigned)b->sx - 1) * b->spotDelta[0] + b->spotOffset[0] + (cc * maxSigX + 0.5f * res.x)) / res.x);
+    r->tSteps = (int)floorf((((unsigned)b->sy - 1) * b->spotDelta[1] + b->spotOffset[1] + (cc * maxSigY + 0.5f * res.y)) / res.y);
+    idxt ray; ray.delta = res; ray.offset = F3(res.x * r->lSteps, res.y * r->bSteps, b->spotOffset[2]);
+    const int Rx = round_to(r->rSteps - r->lSteps + 1, ORC_TX), Ry = round_to(r->tSteps - r->bSteps + 1, ORC_TY);
+    const int S = (int)b->steps, R = Rx * Ry;
+    r->Rx = Rx; r->Ry = Ry; r->S = S; r->L = L;
+    if (Rx <= 0 || Ry <= 0) return 1;
+    affine gtii, gtdi;
+    gtii.m = m33from(b->imM); gtii.v = F3(b->imV[0], b->imV[1], b->imV[2]);
+    gtdi.m = m33from(b->doseM); gtdi.v = F3(b->doseV[0], b->doseV[1], b->doseV[2]);
+
+    /* stage 1 + reductions, cu:766-790 */
+    const size_t RS = (size_t)R * S;
+    r->density = (float*)malloc(RS * 4); r->wepl = (float*)malloc(RS * 4);
+    r->firstInside = (int*)malloc((size_t)R * 4); r->firstOutside = (int*)malloc((size_t)R * 4);
+    r->weplMin = (float*)malloc((size_t)S * 4);
+    const trace_params tp = make_trace_params(ray, b->sourceDist, gtii);
+    stage_trace(lut, ct, nx, ny, nz, &tp, Rx, Ry, S, r->density, r->wepl, r->firstInside, r->firstOutside);
+    stage_reduce(r->wepl, r->firstInside, r->firstOutside, R, S, &r->bfi, &r->bfo, r->weplMin);
+    r->entryZ = (float)r->bfi * res.z + ray.offset.z;
+    if (stopAfter == 1) return 0;
+
+    /* cu:792-849 */
+    float maxEnergy = b->energies[0];
+    for (int l = 1; l < L; ++l) if (b->energies[l] > maxEnergy) maxEnergy = b->energies[l];
+    const int nE = lut->nEnergies;
+    const float maxPeak = orc_vector_interpolate(lut->peakDepths, nE, orc_find_decimal_ordered(lut->energiesPerU, nE, maxEnergy));
+    const int pastAll = find_first_larger_ordered(r->weplMin, S, o.bpDepthCutoff * maxPeak);
+    r->Zg = pastAll < r->bfo ? pastAll : r->bfo;
+    r->layerF = (float*)calloc((size_t)L * 5, 4); r->layerI = (int*)calloc((size_t)L * 2, 4);
+    r->hist = (int*)calloc((size_t)L * ORC_BINS, 4); r->batchRad = (int*)calloc((size_t)L * ORC_BINS, 4);
+    layer_params* lp = (layer_params*)malloc(sizeof(layer_params) * L);
+    float* entrySig = (float*)malloc((size_t)L * 8);
+    for (int l = 0; l < L; ++l) {
+        lp[l].energyIdx = orc_find_decimal_ordered(lut->energiesPerU, nE, b->energies[l]);
+        lp[l].energyScale = orc_vector_interpolate(lut->scaleFacts, nE, lp[l].energyIdx);
+        lp[l].peakDepth = orc_vector_interpolate(lut->peakDepths, nE, lp[l].energyIdx);
+        const float ca = 0.00270f / (lp[l].peakDepth - 4.50f), cb = -4.39f / (lp[l].peakDepth - 3.86f), z = r->entryZ;
+        const float sxg = b->sigmas[2 * l], syg = b->sigmas[2 * l + 1];
+        entrySig[2 * l] = sqrtf(ca * z * z + cb * z + sxg * sxg);          /* cu:840-841 */
+        entrySig[2 * l + 1] = sqrtf(ca * z * z + cb * z + syg * syg);
+        const unsigned la = (unsigned)find_first_larger_ordered(r->weplMin, S, o.bpDepthCutoff * lp[l].peakDepth);
+        lp[l].afterLast = (int)(la < (unsigned)r->Zg ? la : (unsigned)r->Zg); /* cu:923-924 */
+        float* lf = r->layerF + 5 * l;
+        lf[0] = lp[l].energyIdx; lf[1] = lp[l].energyScale; lf[2] = lp[l].peakDepth; lf[3] = entrySig[2 * l]; lf[4] = entrySig[2 * l + 1];
+        r->layerI[2 * l] = lp[l].afterLast;
+    }
+    int rc = 0;
+    if (r->Zg <= r->bfi) { free(lp); free(entrySig); return 0; } /* beam never enters the patient */
+
+    /* stage 3a, cu:849-854 */
+    r->rayWeights = (float*)malloc((size_t)L * R * 4);
+    stage_conv(b, entrySig, ray, 1.0f - r->entryZ / b->sourceDist[0], 1.0f - r->entryZ / b->sourceDist[1], Rx, Ry, o.convSigmaCutoff, r->rayWeights);
+    if (stopAfter == 2) { free(lp); free(entrySig); return 0; }
+
+    /* layer loop, cu:916-1100 */
+    const int W = Rx + 2 * ORC_MAX_R, H = Ry + 2 * ORC_MAX_R, tilesX = Rx / ORC_TX, tilesY = Ry / ORC_TY;
+    r->bev = (float*)calloc((size_t)r->Zg * W * H, 4);
+    r->firstPassive = (int*)malloc((size_t)L * R * 4);
+    float* idd = (float*)calloc(RS, 4); float* rsig = (float*)calloc(RS, 4);
+    if (keepLayer >= 0 && keepLayer < L) { r->idd = (float*)calloc(RS, 4); r->rsig = (float*)calloc(RS, 4); }
+    const fill_geom fg = make_fill_geom(ray, b->sourceDist);
+    for (int l = 0; l < L && rc == 0; ++l) {
+        int* fp = r->firstPassive + (size_t)l * R;
+        stage_idd_sigma(lut, &fg, &lp[l], &o, r->bfi, Rx, Ry, r->density, r->wepl, r->rayWeights + (size_t)l * R, r->firstInside, r->firstOutside, idd, rsig, fp);
+        int lfp = fp[0];
+        for (int i = 1; i < R; ++i) if (fp[i] > lfp) lfp = fp[i];
+        r->layerI[2 * l + 1] = lfp;
+        if (lfp > r->fcp) r->fcp = lfp;
+        if (l == keepLayer) { memcpy(r->idd, idd, RS * 4); memcpy(r->rsig, rsig, RS * 4); }
+        const int nLive = lfp - r->bfi;
+        if (nLive <= 0) { for (int i = 0; i < ORC_BINS; ++i) r->batchRad[l * ORC_BINS + i] = i; continue; }
+        unsigned char* rad = (unsigned char*)malloc((size_t)nLive * tilesX * tilesY);
+        int* ctr = r->hist + l * ORC_BINS;
+        for (int kk = 0; kk < nLive; ++kk)
+            for (int ty = 0; ty < tilesY; ++ty)
+                for (int tx = 0; tx < tilesX; ++tx) {
+                    const int rr = tile_radius(rsig + (size_t)(kk + r->bfi) * R, Rx, tx, ty, o.ksSigmaCutoff);
+                    rad[((size_t)kk * tilesY + ty) * tilesX + tx] = (unsigned char)rr;
+                    ctr[rr] += 1;
+                }
+        r->updates += (long long)R * nLive;
+        int* applied = r->batchRad + l * ORC_BINS;
+        batch_radii(ctr, o.minTilesInBatch, applied);
+        if (ctr[ORC_MAX_R + 1] > 0) { rc = 3; r->radiusError = 1; free(rad); break; }
+        long long taps = 0;
+#pragma omp parallel for schedule(dynamic, 1) reduction(+ : taps)
+        for (int kk = 0; kk < nLive; ++kk) {
+            const size_t k = (size_t)(kk + r->bfi);
+            for (int ty = 0; ty < tilesY; ++ty)
+                for (int tx = 0; tx < tilesX; ++tx) {
+                    const int rb = applied[rad[((size_t)kk * tilesY + ty) * tilesX + tx]];
+                    taps += 256LL * (2 * rb + 1) * (2 * rb + 1);
+                    superpose_tile(idd + k * R, rsig + k * R, Rx, tx, ty, rb, r->bev + k * W * H);
+                }
+        }
+        r->ksTaps += taps;
+        free(rad);
+    }
+    free(idd); free(rsig); free(lp); free(entrySig);
+    if (rc != 0 || stopAfter == 3) return rc;
+
+    /* stage 4, cu:1107-1218 */
+    if (r->fcp <= r->bfi) return 0;
+    const float xv[2] = {-(float)ORC_MAX_R, (float)(Rx + ORC_MAX_R - 1)}, yv[2] = {-(float)ORC_MAX_R, (float)(Ry + ORC_MAX_R - 1)};
+    const float zv[2] = {(float)r->bfi, (float)(r->fcp - 1)};
+    f3 mx = F3(-1.f, -1.f, -1.f), mn = F3(100000.f, 100000.f, 100000.f);
+    for (int k = 0; k < 2; ++k) for (int j = 0; j < 2; ++j) for (int i = 0; i < 2; ++i) {
+        const f3 p = from_fan(ray, b->sourceDist, gtdi, F3(xv[i], yv[j], zv[k]));
+        if (p.x > mx.x) mx.x = p.x; if (p.y > mx.y) mx.y = p.y; if (p.z > mx.z) mx.z = p.z;
+        if (p.x < mn.x) mn.x = p.x; if (p.y < mn.y) mn.y = p.y; if (p.z < mn.z) mn.z = p.z;
+    }
+    int a;
+    a = ((int)floorf(mn.x) / 32) * 32; r->bboxMin[0] = a > 0 ? a : 0;
+    a = (int)floorf(mn.y); r->bboxMin[1] = a > 0 ? a : 0;
+    a = (int)floorf(mn.z); r->bboxMin[2] = a > 0 ? a : 0;
+    a = (int)ceilf(mx.x); r->bboxMax[0] = a < dnx - 1 ? a : dnx - 1;
+    a = (int)ceilf(mx.y); r->bboxMax[1] = a < dny - 1 ? a : dny - 1;
+    a = (int)ceilf(mx.z); r->bboxMax[2] = a < dnz - 1 ? a : dnz - 1;
+    if (dose && r->bboxMax[0] >= r->bboxMin[0] && r->bboxMax[1] >= r->bboxMin[1] && r->bboxMax[2] >= r->bboxMin[2]) {
+        const transfer_params tpar = make_transfer_params(ray, b->sourceDist, gtdi, F3((float)ORC_MAX_R, (float)ORC_MAX_R, -(float)r->bfi));
+        stage_transfer(&tpar, r->bev + (size_t)r->bfi * W * H, W, H, r->fcp - r->bfi, r->bboxMin, r->bboxMax, dnx, dny, dnz, dose);
+    }
+    return 0;
+}
+
+/* Whole plan = cudaWrapperProtons' beam loop (cu:601): beams are independent until the final sum. */
+int orc_plan_dose(const orc_luts* lut, const float* ct, int nx, int ny, int nz, const orc_beam* beams, int nBeams, int dnx, int dny, int dnz,
+                  float* dose, const orc_opts* opts, long long* updates, long long* taps) {
+    long long u = 0, t = 0;
+    for (int i = 0; i < nBeams; ++i) {
+        orc_result r;
+        const int rc = orc_beam_dose(lut, ct, nx, ny, nz, &beams[i], dnx, dny, dnz, dose, opts, -1, 0, &r);
+        u += r.updates; t += r.ksTaps;
+        orc_free_result(&r);
+        if (rc) return rc;
+    }
+    if (updates) *updates = u;
+    if (taps) *taps = t;
+    return 0;
+}
