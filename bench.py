@@ -1,0 +1,332 @@
+#!/usr/bin/env python
+"""Benchmark of the proton dose path (BASELINE.json: plan dose-calc ms & spot-voxel updates/s).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c3] [--impl ours|reference]
+  torchrun --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...      (one rank per GPU, NCCL)
+
+A "step" = one whole-plan dose calculation (all beams, all energy layers) of the named synthetic workload.
+  value  : spot-voxel updates/s with CT and LUTs already resident in HBM (device dose buffer zeroed, all kernels,
+           partial-dose reduce over NCCL when N > 1), timed with CUDA events on the engine's stream, max over ranks.
+  e2e    : the same metric through the reference-facing host call (rtd_dose == cudaWrapperProtons' coverage):
+           H2D CT from pinned host memory + H2D dose-in + all beams + D2H dose, every step.
+  roofline / cpu_baseline: see DESIGN.md "Measurement".
+Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "spot-voxel updates/s (plan dose calculation)"
+UNIT = "updates/s"
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)", float(d.get("sm_max_mhz", 1965.0))
+    return 6650.0, "fallback (B200_PROFILING.md)", 1965.0
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag = index, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                r = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.index)],
+                                   capture_output=True, text=True, timeout=5)
+                if r.returncode == 0 and r.stdout.strip():
+                    self.rows.append([x.strip() for x in r.stdout.strip().splitlines()[0].split(",")])
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def summary(self):
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        sm = [float(r[0]) for r in self.rows if r[0].replace(".", "").isdigit()]
+        reasons = []
+        for i, name in enumerate(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")):
+            if any(r[3 + i].lower().startswith("active") for r in self.rows if len(r) > 3 + i):
+                reasons.append(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": float(self.rows[0][1]) if self.rows[0][1].replace(".", "").isdigit() else None,
+                "reasons": reasons, "samples": len(self.rows)}
+
+
+def cpu_baseline_port(case, budget_s=20.0):
+    """CPU restatement (oracle/, test infrastructure) timed on the host cores on a bounded sample of the workload:
+    whole beams of the plan, one after the other, until the time budget is used (at least one beam)."""
+    from oracle import pyoracle
+    from raytracedicom_b200 import cases
+    cores = os.cpu_count() or 1
+    pyoracle.lib()
+    upd, dt, nb = 0, 0.0, 0
+    dose = np.zeros((case.dose_dims[2], case.dose_dims[1], case.dose_dims[0]), np.float32)
+    for b in case.beams:
+        t0 = time.perf_counter()
+        r = pyoracle.run_beam(cases.Case("sample", case.ct, [b], case.luts), 0, dose=dose)
+        dt += time.perf_counter() - t0
+        upd += r["updates"]; nb += 1
+        if dt * (nb + 1) / nb > budget_s * 1.5:
+            break
+    return {"value": upd / dt, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"beams [0,{nb}) of {len(case.beams)} of workload {case.name}, all energy layers: {upd} updates in {dt:.2f} s "
+                      f"(oracle/rtd_oracle.c, OpenMP, {cores} threads; tracer + pre-convolution + IDD/sigma + superposition + transfer)"}
+
+
+def run_reference(args, case, rank, world):
+    """Reference arm: the UNMODIFIED reference (sources compiled in place from /root/reference into oracle/_ref by
+    oracle/ref_harness/Makefile, sm_100) through its own entry point cudaWrapperProtons on this workload, one process
+    per step (it ends with cudaDeviceReset).  Its own 'Total global execution time' covers H2D CT + LUTs, all beams,
+    D2H dose and frees, i.e. an end-to-end figure.  It is single-GPU: rank 0 alone runs it."""
+    if rank != 0:
+        return None
+    import tempfile
+    exe = os.path.join(ROOT, "oracle", "_ref", "ref_dose")
+    line = {"impl": "reference", "metric": METRIC, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": case.name, "ct_dims": list(case.ct_dims), "beams": len(case.beams),
+                       "layers": int(sum(b.n_layers for b in case.beams))}}
+    from oracle import pyoracle
+    cpu = cpu_baseline_port(case)
+    line["cpu_baseline"] = cpu
+    have_gpu = False
+    try:
+        import torch
+        have_gpu = torch.cuda.is_available()
+    except Exception:
+        pass
+    if os.path.exists(exe) and have_gpu:
+        # U from the oracle-independent integer outputs is identical for both engines; take it from one run of ours
+        from raytracedicom_b200.engine import DoseEngine
+        nx, ny, nz = case.dose_dims
+        with DoseEngine(0) as eng:
+            eng.set_luts(case.luts); eng.set_ct(case.ct); eng.set_dose_grid(nx, ny, nz)
+            U = eng.dose(case.beams, np.zeros((nz, ny, nx), np.float32)).updates
+        tmp = tempfile.mkdtemp(prefix="rtdref_")
+        cpath = os.path.join(tmp, "case.rtdcase"); case.write(cpath)
+        times = []
+        for i in range(args.warmup + args.steps):
+            r = subprocess.run([exe, cpath, os.path.join(tmp, "dose.f32")], capture_output=True, text=True, timeout=600)
+            ms = None
+            for ln in r.stdout.splitlines():
+                if ln.startswith("REF_TIMING"):
+                    ms = float(ln.split("total_ms=")[1].split()[0])
+            if r.returncode != 0 or ms is None or ms <= 0:
+                line["unavailable_gpu_reference"] = (r.stderr or r.stdout)[-300:]
+                break
+            if i >= args.warmup:
+                times.append(ms)
+        if times:
+            ms = sum(times) / len(times)
+            line.update({"value": U / (ms * 1e-3), "ms_per_step": ms, "reference_kind": "reference rebuilt for sm_100 from /root/reference (oracle/_ref/ref_dose), "
+                         "its own total timer: H2D CT+LUTs, all beams, D2H dose, frees; 1 GPU",
+                         "e2e": {"value": U / (ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(case.ct.nbytes * 2), "d2h_bytes_per_step": int(case.ct.nbytes)},
+                         "updates_per_step": int(U), "gpu_launches": None})
+            return line
+    # no rebuilt reference or no GPU: the CPU port is the reference arm
+    line.update({"value": cpu["value"], "ms_per_step": None, "reference_kind": "CPU restatement (oracle port); rebuilt reference or GPU not available",
+                 "e2e": {"value": cpu["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})
+    return line
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c3", help="c3 (default: 512x512x200 CT, 3 fields), c1a, c2, c4, c5, mini")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
+
+    from raytracedicom_b200 import cases
+    case = cases.make_case(args.workload)
+
+    if args.impl == "reference":
+        line = run_reference(args, case, rank, world)
+        if rank == 0:
+            print(json.dumps(line), flush=True)
+        return 0
+
+    import torch
+    import torch.distributed as dist
+    from raytracedicom_b200 import sharding
+    from raytracedicom_b200.engine import DoseEngine, pack_beams
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device - the dose path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+
+    eng = DoseEngine(local)
+    stream = torch.cuda.ExternalStream(eng.stream, device=dev)
+    nx, ny, nz = case.dose_dims
+    cnx, cny, cnz = case.ct_dims
+    eng.set_luts(case.luts)
+    eng.set_dose_grid(nx, ny, nz)
+    ct_host = torch.from_numpy(case.ct).pin_memory()
+    ct_dev = ct_host.to(dev)
+    torch.cuda.synchronize()
+    eng.set_ct_ptr(ct_dev.data_ptr(), cnx, cny, cnz, device=True)
+    parts = sharding.partition(case.beams, case.luts, world)
+    mine = sharding.shard_beams(case.beams, parts[rank])
+    packed, keep = pack_beams(mine)
+    dose_dev = torch.zeros((nz, ny, nx), dtype=torch.float32, device=dev)
+    dose_host = torch.zeros((nz, ny, nx), dtype=torch.float32).pin_memory()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
+
+    def step_device():
+        with torch.cuda.stream(stream):
+            dose_dev.zero_()
+            t = eng.dose_ptr(packed, len(mine), dose_dev.data_ptr(), device=True)
+            sharding.reduce_dose(dose_dev, dst=0)
+        return t
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step_device()
+    barrier()
+    sampler = ClockSampler(local); sampler.start()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    stage = {}
+    t_wall0 = time.perf_counter()
+    for i in range(args.steps):
+        with torch.cuda.stream(stream):
+            flush.fill_(i & 0xFF)                     # L2 flush between timed iterations (outside the event pair)
+            evs[i][0].record(stream)
+        tm = step_device()
+        with torch.cuda.stream(stream):
+            evs[i][1].record(stream)
+        for k, v in tm.as_dict().items():
+            stage[k] = stage.get(k, 0.0) + v
+    barrier()
+    t_wall = time.perf_counter() - t_wall0
+    sampler.stop_flag = True; sampler.join(timeout=2)
+    ms_local = sum(a.elapsed_time(b) for a, b in evs) / args.steps
+    upd_local = torch.tensor([int(stage["updates"] / args.steps), int(stage["ksTaps"] / args.steps)], dtype=torch.int64, device=dev)
+    ms_t = torch.tensor([ms_local], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(ms_t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(upd_local, op=dist.ReduceOp.SUM)
+    ms_step = float(ms_t.item()); U = int(upd_local[0].item()); taps = int(upd_local[1].item())
+    checksum = float(dose_dev.double().sum().item()) if rank == 0 else 0.0
+    dmax = float(dose_dev.max().item()) if rank == 0 else 0.0
+
+    # ---- end-to-end through the host-facing call, host buffers, copies inside the timed region ----
+    e2e = None
+    if not args.no_e2e:
+        def step_e2e():
+            if world == 1:
+                eng.set_ct_ptr(ct_host.data_ptr(), cnx, cny, cnz, device=False)                 # H2D CT (pinned)
+                eng.dose_ptr(packed, len(mine), dose_host.data_ptr(), device=False)            # H2D dose-in, beams, D2H dose
+            else:
+                eng.set_ct_ptr(ct_host.data_ptr(), cnx, cny, cnz, device=False)
+                with torch.cuda.stream(stream):
+                    if rank == 0:
+                        dose_dev.copy_(dose_host, non_blocking=True)                              # caller's dose content (accumulate semantics)
+                    else:
+                        dose_dev.zero_()
+                    eng.dose_ptr(packed, len(mine), dose_dev.data_ptr(), device=True)
+                    sharding.reduce_dose(dose_dev, dst=0)
+                    if rank == 0:
+                        dose_host.copy_(dose_dev, non_blocking=True)
+                stream.synchronize()
+        n_e2e = max(3, min(args.steps, 10))
+        for _ in range(2):
+            dose_host.zero_(); step_e2e()
+        tt = []
+        for _ in range(n_e2e):
+            dose_host.zero_()
+            barrier(); t0 = time.perf_counter(); step_e2e(); barrier(); tt.append(time.perf_counter() - t0)
+        e_ms = torch.tensor([1e3 * sum(tt) / len(tt)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(e_ms, op=dist.ReduceOp.MAX)
+        wbytes = sum(int(np.prod(b.weights.shape[1:])) * ((b.layer_end - b.layer_begin) or b.n_layers) * 4 for b in mine)
+        e2e = {"value": U / (float(e_ms.item()) * 1e-3), "unit": UNIT, "ms_per_plan": float(e_ms.item()),
+               "h2d_bytes_per_step": int(ct_host.numel() * 4 + (dose_host.numel() * 4 if rank == 0 else 0) + wbytes),
+               "d2h_bytes_per_step": int(dose_host.numel() * 4),
+               "timing": "host wall clock between barriers around the host call (rtd_set_ct + rtd_dose), max over ranks",
+               "dose_checksum_matches_device_run": None}
+        if rank == 0:
+            cs = float(dose_host.double().sum().item())
+            e2e["dose_checksum_matches_device_run"] = bool(abs(cs - checksum) <= 1e-5 * abs(checksum))
+        eng.set_ct_ptr(ct_dev.data_ptr(), cnx, cny, cnz, device=True)
+
+    if rank == 0:
+        peak, peak_src, sm_max = load_peaks()
+        reps = [eng.beam_report(b) for b in range(len(mine))]
+        live = [r for r in reps if r["beamFirstCalculatedPassive"] > r["beamFirstInside"]]
+        ks_launches = max(1, 3 * len(live))
+        ks_ms = stage["msSuperp"] / args.steps
+        u_rank0 = sum(r["updates"] for r in reps)
+        bev_bytes = sum(4 * (r["rayDimX"] + 64) * (r["rayDimY"] + 64) * (r["beamFirstCalculatedPassive"] - r["beamFirstInside"]) for r in live)
+        ks_alg = 8 * u_rank0 + bev_bytes          # read idd + rSigmaEff once per update, write the haloed BEV dose once
+        taps0 = stage["ksTaps"] / args.steps
+        achieved = ks_alg / (ks_ms * 1e-3) / 1e9 if ks_ms > 0 else 0.0
+        fp32_peak = 148 * 128 * 2 * sm_max * 1e6 / 1e12
+        # whole-plan algorithmic bytes
+        plan_bytes = 4 * nx * ny * nz
+        for b, r in zip(mine, reps):
+            R = r["rayDimX"] * r["rayDimY"]
+            box = max(0, r["bboxMax"][0] - r["bboxMin"][0] + 1) * max(0, r["bboxMax"][1] - r["bboxMin"][1] + 1) * max(0, r["bboxMax"][2] - r["bboxMin"][2] + 1)
+            plan_bytes += 4 * box + 8 * R * r["steps"] + 8 * r["updates"] + 8 * (r["rayDimX"] + 64) * (r["rayDimY"] + 64) * max(0, r["beamFirstCalculatedPassive"] - r["beamFirstInside"]) + 8 * box
+        line = {"metric": METRIC, "value": U / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": case.name, "ct_dims": list(case.ct_dims), "beams": len(case.beams), "layers": int(sum(b.n_layers for b in case.beams)),
+                           "spots": int(sum(b.weights.size for b in case.beams)), "updates_per_plan": U, "ks_taps_per_plan": taps,
+                           "sharding": f"(beam, layer-range) work items, LPT over {world} rank(s); partial dose grids summed by NCCL reduce" if world > 1 else "single GPU",
+                           "l2": "256 MiB buffer written between timed iterations (L2 flush); CT 4*%d B and BEV arrays exceed L2" % (nx * ny * nz)},
+                "plan_ms": ms_step, "updates_per_step": U,
+                "stage_ms_rank0": {k: stage[k] / args.steps for k in ("msTrace", "msSetup", "msConv", "msIddSigma", "msRadius", "msSuperp", "msTransfer", "msTotal")},
+                "gpu_launches": int(stage["kernelLaunches"]), "host_syncs_per_plan": int(stage["hostSyncs"] / args.steps),
+                "dose_max": dmax, "dose_checksum": checksum,
+                "roofline": {"kernel": "ks_kernel (kernel superposition, 3 radius-class launches per beam)", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                             "frac": achieved / peak, "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": ks_alg / ks_launches,
+                             "avg_launch_ms": ks_ms / ks_launches, "launches_per_plan_rank0": ks_launches,
+                             "fp32": {"achieved_tflops": 2 * taps0 / (ks_ms * 1e-3) / 1e12 if ks_ms > 0 else 0.0, "peak_tflops": fp32_peak,
+                                      "frac": (2 * taps0 / (ks_ms * 1e-3) / 1e12) / fp32_peak if ks_ms > 0 else 0.0,
+                                      "note": "superposition is FMA-bound: 2 x taps / kernel time vs 148 SM x 128 FMA/clk x sm_max_mhz"}},
+                "plan_roofline": {"algorithmic_bytes": plan_bytes, "achieved_gbs": plan_bytes / (ms_step * 1e-3) / 1e9, "frac_of_hbm_peak": plan_bytes / (ms_step * 1e-3) / 1e9 / peak,
+                                  "note": "rank 0's share of the plan over the whole step" if world > 1 else "whole plan"},
+                "clocks": sampler.summary(), "wall_s_timed_region": t_wall}
+        if e2e:
+            line["e2e"] = e2e
+        if not args.no_cpu_baseline and world == 1:
+            line["cpu_baseline"] = cpu_baseline_port(case)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    eng.close()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

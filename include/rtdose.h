@@ -72,6 +72,10 @@ typedef struct {
     float spotOffset[3];         /* spotIdxToGantry offset (z: start plane) */
     float gantryToImIdxM[9];  float gantryToImIdxV[3];     /* row-major 3x3 + translation */
     float gantryToDoseIdxM[9]; float gantryToDoseIdxV[3];
+    /* Layer shard: compute only energy layers [layerBegin, layerEnd) of this beam (0,0 = all). The ray grid, the
+     * tracer and every cut-off still come from the WHOLE beam, so the doses of disjoint shards add up to the dose
+     * of the whole beam (multi-GPU work items). Not part of the reference's BeamSettings. */
+    int layerBegin, layerEnd;
 } rtd_beam;
 
 /* Run-time equivalents of the reference's compile-time flags (reference: CMakeLists.txt:36-79). */

@@ -32,7 +32,8 @@ class OrcBeam(C.Structure):
     _fields_ = [("weights", _fp), ("sx", C.c_int), ("sy", C.c_int), ("nLayers", C.c_int), ("energies", _fp), ("sigmas", _fp),
                 ("raySpacing", C.c_float * 2), ("steps", C.c_uint), ("sourceDist", C.c_float * 2),
                 ("spotDelta", C.c_float * 3), ("spotOffset", C.c_float * 3),
-                ("imM", C.c_float * 9), ("imV", C.c_float * 3), ("doseM", C.c_float * 9), ("doseV", C.c_float * 3)]
+                ("imM", C.c_float * 9), ("imV", C.c_float * 3), ("doseM", C.c_float * 9), ("doseV", C.c_float * 3),
+                ("layerBegin", C.c_int), ("layerEnd", C.c_int)]
 
 
 class OrcOpts(C.Structure):
@@ -110,6 +111,7 @@ def pack_beam(b):
     ob.imV = (C.c_float * 3)(*_f32(b.gantry_to_im_v).ravel())
     ob.doseM = (C.c_float * 9)(*_f32(b.gantry_to_dose_m).ravel())
     ob.doseV = (C.c_float * 3)(*_f32(b.gantry_to_dose_v).ravel())
+    ob.layerBegin, ob.layerEnd = getattr(b, "layer_begin", 0), getattr(b, "layer_end", 0)
     return ob, [w, e, s]
 
 

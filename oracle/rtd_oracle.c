@@ -51,6 +51,7 @@ typedef struct {
     float raySpacing[2]; unsigned steps; float sourceDist[2];
     float spotDelta[3], spotOffset[3];
     float imM[9], imV[3], doseM[9], doseV[3];
+    int layerBegin, layerEnd; /* test-only shard [begin,end) of the layer loop cu:916 (0,0 = all); geometry stays the whole beam's */
 } orc_beam;
 
 /* Run-time copies of the compile-time flags (CMakeLists.txt:36-79). */
@@ -613,7 +614,9 @@ int orc_beam_dose(const orc_luts* lut, const float* ct, int nx, int ny, int nz, 
     float* idd = (float*)calloc(RS, 4); float* rsig = (float*)calloc(RS, 4);
     if (keepLayer >= 0 && keepLayer < L) { r->idd = (float*)calloc(RS, 4); r->rsig = (float*)calloc(RS, 4); }
     const fill_geom fg = make_fill_geom(ray, b->sourceDist);
-    for (int l = 0; l < L && rc == 0; ++l) {
+    const int l0 = (b->layerBegin == 0 && b->layerEnd == 0) ? 0 : b->layerBegin, l1 = (b->layerBegin == 0 && b->layerEnd == 0) ? L : b->layerEnd;
+    memset(r->firstPassive, 0, (size_t)L * R * 4);
+    for (int l = l0; l < l1 && rc == 0; ++l) {
         int* fp = r->firstPassive + (size_t)l * R;
         stage_idd_sigma(lut, &fg, &lp[l], &o, r->bfi, Rx, Ry, r->density, r->wepl, r->rayWeights + (size_t)l * R, r->firstInside, r->firstOutside, idd, rsig, fp);
         int lfp = fp[0];

@@ -52,6 +52,8 @@ class Beam:
     gantry_to_im_v: np.ndarray = field(default_factory=lambda: np.zeros(3, np.float32))
     gantry_to_dose_m: np.ndarray = None
     gantry_to_dose_v: np.ndarray = None
+    layer_begin: int = 0          # layer shard [layer_begin, layer_end) (0,0 = all); rtd_beam.layerBegin/End
+    layer_end: int = 0
 
     def __post_init__(self):
         self.weights = np.ascontiguousarray(self.weights, np.float32)
@@ -71,6 +73,12 @@ class Beam:
     @property
     def n_layers(self) -> int:
         return self.weights.shape[0]
+
+    def shard(self, lo: int, hi: int) -> "Beam":
+        """Same beam (same ray grid, tracer and cut-offs) restricted to energy layers [lo, hi): the multi-GPU work
+        item of SURVEY.md 8e. The doses of disjoint shards add up to the dose of the whole beam."""
+        return Beam(self.weights, self.energies, self.sigmas, self.ray_spacing, self.steps, self.source_dist, self.spot_delta,
+                    self.spot_offset, self.gantry_to_im_m, self.gantry_to_im_v, self.gantry_to_dose_m, self.gantry_to_dose_v, lo, hi)
 
     def layer_slice(self, lo: int, hi: int) -> "Beam":
         """Sub-beam holding energy layers [lo, hi) - dose is linear in layers."""

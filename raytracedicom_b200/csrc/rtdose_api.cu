@@ -50,6 +50,7 @@ struct TexArr {
 struct BeamWs {
     // geometry / host results
     RayGrid grid; int S = 0, L = 0, R = 0, sx = 0, sy = 0;
+    int l0 = 0, Lc = 0;   // computed layer range [l0, l0+Lc) of the beam's L layers (rtd_beam.layerBegin/End)
     float dist[2]; Affine gtii, gtdi;
     int bfi = 0, bfo = 0, Zg = 0, nz = 0; bool live = false;
     float entryZ = 0;
@@ -161,6 +162,11 @@ rtd_status beamPhaseA(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opts
     w.grid = makeRayGrid(b.spotDelta, b.spotOffset, b.sx, b.sy, b.raySpacing, mx, my, o.convSigmaCutoff);
     if (w.grid.dimX <= 0 || w.grid.dimY <= 0) return fail(ctx, RTD_ERR_INVALID, "empty ray grid");
     w.S = (int)b.steps; w.L = b.nLayers; w.R = w.grid.dimX * w.grid.dimY; w.sx = b.sx; w.sy = b.sy;
+    if (b.layerBegin == 0 && b.layerEnd == 0) { w.l0 = 0; w.Lc = b.nLayers; }
+    else {
+        if (b.layerBegin < 0 || b.layerEnd > b.nLayers || b.layerBegin >= b.layerEnd) return fail(ctx, RTD_ERR_INVALID, "beam.layerBegin/layerEnd out of range");
+        w.l0 = b.layerBegin; w.Lc = b.layerEnd - b.layerBegin;
+    }
     if ((w.grid.dimX / 32) * (w.grid.dimY / 8) > 4095) return fail(ctx, RTD_ERR_INVALID, "ray grid has more than 4095 tiles");
     w.dist[0] = b.sourceDist[0]; w.dist[1] = b.sourceDist[1];
     w.gtii.m = m3(b.gantryToImIdxM); w.gtii.v = v3(b.gantryToImIdxV[0], b.gantryToImIdxV[1], b.gantryToImIdxV[2]);
@@ -169,9 +175,9 @@ rtd_status beamPhaseA(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opts
     RTD_CUDA(w.density.ensure(RS * 4)); RTD_CUDA(w.wepl.ensure(RS * 4));
     RTD_CUDA(w.firstIn.ensure(size_t(w.R) * 4)); RTD_CUDA(w.firstOut.ensure(size_t(w.R) * 4));
     RTD_CUDA(w.weplMin.ensure(size_t(w.S) * 4 + 8)); RTD_CUDA(w.hTrace.ensure(size_t(w.S) * 4 + 8));
-    const size_t nW = size_t(b.sx) * b.sy * b.nLayers;
-    RTD_CUDA(w.spotW.ensure(nW * 4)); RTD_CUDA(w.hStage.ensure(nW * 4 + size_t(w.L) * (8 + sizeof(LayerParams))));
-    memcpy(w.hStage.p, b.weights, nW * 4);
+    const size_t nW = size_t(b.sx) * b.sy * w.Lc;
+    RTD_CUDA(w.spotW.ensure(nW * 4)); RTD_CUDA(w.hStage.ensure(nW * 4 + size_t(w.Lc) * (8 + sizeof(LayerParams))));
+    memcpy(w.hStage.p, b.weights + size_t(b.sx) * b.sy * w.l0, nW * 4);
     RTD_CUDA(cudaMemcpyAsync(w.spotW.p, w.hStage.p, nW * 4, cudaMemcpyHostToDevice, ctx->stream));
     const TraceParams tp = makeTraceParams(ctx->densScale, ctx->spScale, b.steps, w.grid.rayIdxToGantry, w.dist, w.gtii);
     // weplMin buffer layout: [0]=beamFirstInside, [1]=beamFirstOutside (ints), [2..] weplMin floats
@@ -203,30 +209,31 @@ rtd_status beamPhaseB(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opts
     w.Zg = std::min(firstPastCutoffAll, w.bfo);
     w.nz = w.Zg - w.bfi;
     w.live = w.nz > 0;
-    w.layers.resize(w.L); w.entrySig.resize(2 * size_t(w.L));
+    w.layers.resize(w.Lc); w.entrySig.resize(2 * size_t(w.Lc));
     w.lrep.assign(w.L, rtd_layer_report());
     memset(&w.rep, 0, sizeof w.rep);
     w.rep.lSteps = w.grid.lSteps; w.rep.bSteps = w.grid.bSteps; w.rep.rSteps = w.grid.rSteps; w.rep.tSteps = w.grid.tSteps;
     w.rep.rayDimX = w.grid.dimX; w.rep.rayDimY = w.grid.dimY; w.rep.steps = w.S; w.rep.nLayers = w.L;
     w.rep.beamFirstInside = w.bfi; w.rep.beamFirstOutside = w.bfo; w.rep.beamFirstGuaranteedPassive = w.Zg; w.rep.entryZ = w.entryZ;
-    for (int l = 0; l < w.L; ++l) {
+    for (int l = 0; l < w.Lc; ++l) {
+        const int al = w.l0 + l;   // absolute layer number in the beam
         LayerParams& lp = w.layers[l];
-        lp.energyIdx = findDecimalOrdered(E, nE, b.energies[l]);
+        lp.energyIdx = findDecimalOrdered(E, nE, b.energies[al]);
         lp.energyScale = vectorInterpolate(ctx->scaleFacts.data(), nE, lp.energyIdx);
         lp.peakDepth = vectorInterpolate(ctx->peakDepths.data(), nE, lp.energyIdx);
         float ca, cb; sigmaSqAirCoefsHost(lp.peakDepth, true, ca, cb);
-        const float sxg = b.sigmas[2 * l], syg = b.sigmas[2 * l + 1], z = w.entryZ;
+        const float sxg = b.sigmas[2 * al], syg = b.sigmas[2 * al + 1], z = w.entryZ;
         w.entrySig[2 * l] = sqrtf(ca * z * z + cb * z + sxg * sxg);
         w.entrySig[2 * l + 1] = sqrtf(ca * z * z + cb * z + syg * syg);
         const unsigned localAfterLast = (unsigned)findFirstLargerOrdered(weplMin, w.S, o.bpDepthCutoff * lp.peakDepth);
         lp.afterLast = (int)std::min(localAfterLast, (unsigned)w.Zg);
-        rtd_layer_report& lr = w.lrep[l];
+        rtd_layer_report& lr = w.lrep[al];
         lr.energyIdx = lp.energyIdx; lr.energyScaleFact = lp.energyScale; lr.peakDepth = lp.peakDepth;
         lr.entrySigmaX = w.entrySig[2 * l]; lr.entrySigmaY = w.entrySig[2 * l + 1]; lr.afterLastStep = lp.afterLast;
     }
     if (!w.live) return RTD_OK;   // the beam never enters the patient: nothing to add
 
-    const int Rx = w.grid.dimX, Ry = w.grid.dimY, R = w.R, L = w.L, nz = w.nz;
+    const int Rx = w.grid.dimX, Ry = w.grid.dimY, R = w.R, L = w.Lc, nz = w.nz;
     const int tilesX = Rx / 32, tilesY = Ry / 8, tiles = tilesX * tilesY;
     const size_t LnzR = size_t(L) * nz * R;
     RTD_CUDA(w.sigmas.ensure(size_t(L) * 8)); RTD_CUDA(w.layerDev.ensure(size_t(L) * sizeof(LayerParams)));
@@ -245,7 +252,7 @@ rtd_status beamPhaseB(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opts
     int* dLfp = w.lfp.as<int>(); int* dHist = dLfp + L; int* dCursor = dHist + size_t(L) * 34; int* dStats = dCursor + 33; int* dWork = dStats + 4;
 
     // staging area after the weights: sigmas then layer params
-    const size_t nW = size_t(w.sx) * w.sy * L;
+    const size_t nW = size_t(w.sx) * w.sy * L;   // L = computed layers
     char* st = w.hStage.as<char>() + nW * 4;
     memcpy(st, w.entrySig.data(), size_t(L) * 8);
     memcpy(st + size_t(L) * 8, w.layers.data(), size_t(L) * sizeof(LayerParams));
@@ -329,13 +336,13 @@ rtd_status beamPhaseB(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opts
 // After the final sync: integer reports (cu:955-957, 1185-1210) and the metric counters.
 bool beamFinish(rtd_ctx* ctx, BeamWs& w, int64_t& updates, int64_t& taps) {
     if (!w.live) return true;
-    const int L = w.L;
+    const int L = w.Lc;
     const size_t ctlInts = size_t(L) + size_t(L) * 34 + 33 + 4 + 4;
     const int* lfp = w.hOut.as<int>(); const int* hist = lfp + L; const int* stats = hist + size_t(L) * 34 + 33;
     const int* brad = w.hOut.as<int>() + ctlInts;
     int fcp = 0; int64_t u = 0, t = 0;
     for (int l = 0; l < L; ++l) {
-        rtd_layer_report& lr = w.lrep[l];
+        rtd_layer_report& lr = w.lrep[w.l0 + l];
         lr.layerFirstPassive = lfp[l];
         fcp = std::max(fcp, lfp[l]);
         const int nLive = std::min(std::max(lfp[l] - w.bfi, 0), w.nz);
@@ -561,7 +568,8 @@ rtd_status rtd_debug_fetch(rtd_ctx* ctx, int beamNo, rtd_fetch_what what, int la
     const size_t tiles = size_t(w.grid.dimX / 32) * (w.grid.dimY / 8);
     const void* src = nullptr; size_t bytes = 0;
     const bool perLayer = (what == RTD_FETCH_IDD || what == RTD_FETCH_RSIGMA || what == RTD_FETCH_FIRST_PASSIVE || what == RTD_FETCH_TILE_RADIUS);
-    if (perLayer && (layerNo < 0 || layerNo >= (int)L)) return fail(ctx, RTD_ERR_INVALID, "rtd_debug_fetch: bad layer");
+    if (perLayer && (layerNo < w.l0 || layerNo >= w.l0 + w.Lc)) return fail(ctx, RTD_ERR_INVALID, "rtd_debug_fetch: bad layer");
+    layerNo -= w.l0;
     if ((perLayer || what == RTD_FETCH_BEV_DOSE || what == RTD_FETCH_RAY_WEIGHTS) && !w.live) return fail(ctx, RTD_ERR_STATE, "rtd_debug_fetch: beam has no live steps");
     switch (what) {
         case RTD_FETCH_DENSITY: src = w.density.p; bytes = R * S * 4; break;
@@ -569,7 +577,7 @@ rtd_status rtd_debug_fetch(rtd_ctx* ctx, int beamNo, rtd_fetch_what what, int la
         case RTD_FETCH_FIRST_INSIDE: src = w.firstIn.p; bytes = R * 4; break;
         case RTD_FETCH_FIRST_OUTSIDE: src = w.firstOut.p; bytes = R * 4; break;
         case RTD_FETCH_WEPL_MIN: src = w.weplMin.as<float>() + 2; bytes = S * 4; break;
-        case RTD_FETCH_RAY_WEIGHTS: src = w.rayW.p; bytes = L * R * 4; break;
+        case RTD_FETCH_RAY_WEIGHTS: src = w.rayW.p; bytes = size_t(w.Lc) * R * 4; break;
         case RTD_FETCH_IDD: src = w.idd.as<float>() + size_t(layerNo) * nz * R; bytes = nz * R * 4; break;
         case RTD_FETCH_RSIGMA: src = w.rsig.as<float>() + size_t(layerNo) * nz * R; bytes = nz * R * 4; break;
         case RTD_FETCH_FIRST_PASSIVE: src = w.firstPassive.as<int>() + size_t(layerNo) * R; bytes = R * 4; break;

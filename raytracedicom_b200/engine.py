@@ -40,7 +40,8 @@ class RtdBeam(C.Structure):
                 ("raySpacing", C.c_float * 2), ("steps", C.c_uint), ("sourceDist", C.c_float * 2),
                 ("spotDelta", C.c_float * 3), ("spotOffset", C.c_float * 3),
                 ("gantryToImIdxM", C.c_float * 9), ("gantryToImIdxV", C.c_float * 3),
-                ("gantryToDoseIdxM", C.c_float * 9), ("gantryToDoseIdxV", C.c_float * 3)]
+                ("gantryToDoseIdxM", C.c_float * 9), ("gantryToDoseIdxV", C.c_float * 3),
+                ("layerBegin", C.c_int), ("layerEnd", C.c_int)]
 
 
 class RtdOpts(C.Structure):
@@ -152,6 +153,7 @@ def pack_beams(beams: Sequence[Beam]):
         rb.gantryToImIdxV = (C.c_float * 3)(*_f32(b.gantry_to_im_v).ravel())
         rb.gantryToDoseIdxM = (C.c_float * 9)(*_f32(b.gantry_to_dose_m).ravel())
         rb.gantryToDoseIdxV = (C.c_float * 3)(*_f32(b.gantry_to_dose_v).ravel())
+        rb.layerBegin, rb.layerEnd = getattr(b, "layer_begin", 0), getattr(b, "layer_end", 0)
     return arr, keep
 
 
