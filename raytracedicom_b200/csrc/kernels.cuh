@@ -400,6 +400,7 @@ fill_list_kernel(const uint8_t* __restrict__ radMap, const int* __restrict__ bat
     const unsigned r = radMap[(size_t)l * nz * tiles + idx];
     if (r > 32) return;
     const int rb = batchRad[l * 34 + r];
+    if (rb <= 16) return;   // radii <= 16 are enumerated directly by ks2_kernel (ks2.cuh); the list only feeds ks_kernel<.,17,32>
     const int pos = rbOffset[rb] + atomicAdd(rbCursor + rb, 1);
     list[pos] = ((uint32_t)l << 24) | ((uint32_t)(idx / tiles) << 12) | (uint32_t)(idx % tiles);
 }

@@ -1,0 +1,191 @@
+// K3b (second generation): kernel superposition, layer-fused and warp-autonomous.
+//
+// Reference: kernelSuperposition<rad> (/root/reference/src/kernel_wrapper.cuh:432-489) is launched per layer and per
+// radius batch; every tile does (2r+1)^2 volatile shared-memory read-modify-writes per voxel with a block barrier per
+// row offset and then (32+2r)(8+2r) global float atomics.  Here:
+//   * work item = (depth slice kk, 32x8 tile); ONE WARP owns the item and loops over ALL energy layers of the beam,
+//     accumulating them into a warp-private shared-memory patch, so the haloed BEV dose receives one global reduction
+//     per item instead of one per (item, layer): ~L times fewer global atomics, and no block barriers at all;
+//   * lane x owns the source column x of the tile.  The erf-difference weights of its 8 voxels (same recurrence as
+//     cuh:459-467, same libdevice erff) go through a warp-private table so that the hot loop is a SMALL rolled loop
+//     over the column offset j (instruction-cache resident) with the row weights e[y][|i|] held in registers:
+//     per j the lane accumulates a whole output column (P+2RB rows) in registers - P(2RB+1) FMAs, no memory traffic -
+//     and adds it to the patch columns x+j and x-j (the horizontal weight is symmetric: +j and -j share the FMAs);
+//   * the radius applied to a tile is still the reference's BATCH radius (cuh:443-448 vs 459-473).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace rtd {
+
+struct Ks2Params {
+    const float* idd; const float* rsig; float* bev;
+    const int* batchRad;            // [L][34] radius applied to a tile of own radius r
+    const uint8_t* radMap;          // [L][nz][tiles] own radius, 255 = not live
+    const int* layerFirstPassive;   // [L]
+    int L, Rx, Ry, nz, first, tilesX, tiles;
+};
+
+constexpr int KS2_MAXRB = 16;       // larger batch radii go through the block-wide ks_kernel<.,17,32>
+constexpr int KS2_MAXL = 256;
+
+__host__ __device__ constexpr int ks2_rows_per_pass(int rb) { return rb <= 8 ? 8 : 4; }
+// per-warp shared memory (floats): patch + weight table + layer list
+__host__ __device__ constexpr int ks2_patch_floats(int rbmax) { return (8 + 2 * rbmax) * (32 + 2 * rbmax); }
+__host__ __device__ constexpr int ks2_table_floats(int rbmax) { return 8 * (rbmax + 1) * 32; }
+__host__ __device__ constexpr int ks2_warp_floats(int rbmax) { return ks2_patch_floats(rbmax) + ks2_table_floats(rbmax) + KS2_MAXL / 2; }
+
+// One pass over P source rows [y0, y0+P) of the tile with batch radius RB.
+//   tab : table rows of this pass, tab[(y*(RB+1) + i)*32 + lane] = e_y[i]
+//   dP  : dose of the lane's P voxels
+//   org : patch element that receives (row y0 - RB, column x - RB) of this tile's footprint for lane 0
+template <int RB, int P>
+__device__ __forceinline__ void ks2_pass(const float* __restrict__ tab, const float (&dP)[P], float* __restrict__ org, const int pitch,
+                                         const int lane) {
+    constexpr int W = 2 * RB + 1, NRP = P + 2 * RB;
+    float e[P][RB + 1];
+#pragma unroll
+    for (int y = 0; y < P; ++y)
+#pragma unroll
+        for (int i = 0; i <= RB; ++i) e[y][i] = tab[(y * (RB + 1) + i) * 32 + lane];
+#pragma unroll 1
+    for (int j = 0; j <= RB; ++j) {
+        float acc[NRP];
+#pragma unroll
+        for (int Y = 0; Y < NRP; ++Y) acc[Y] = 0.0f;
+#pragma unroll
+        for (int y = 0; y < P; ++y) {
+            const float g = dP[y] * tab[(y * (RB + 1) + j) * 32 + lane];
+#pragma unroll
+            for (int i = 0; i < W; ++i) acc[y + i] = fmaf(g, e[y][(i < RB) ? (RB - i) : (i - RB)], acc[y + i]);
+        }
+        float* c0 = org + lane + RB + j;
+#pragma unroll
+        for (int Y = 0; Y < NRP; ++Y) c0[Y * pitch] += acc[Y];
+        __syncwarp();
+        if (j > 0) {
+            float* c1 = org + lane + RB - j;
+#pragma unroll
+            for (int Y = 0; Y < NRP; ++Y) c1[Y * pitch] += acc[Y];
+            __syncwarp();
+        }
+    }
+}
+
+template <int RB>
+__device__ __forceinline__ void ks2_tile(const float* __restrict__ tab, const float (&d)[8], float* __restrict__ org, const int pitch, const int lane) {
+    constexpr int P = ks2_rows_per_pass(RB);
+    if (P == 8) {
+        ks2_pass<RB, 8>(tab, d, org, pitch, lane);
+    } else {
+#pragma unroll
+        for (int p = 0; p < 8 / P; ++p) {
+            float dP[P];
+#pragma unroll
+            for (int y = 0; y < P; ++y) dP[y] = d[p * P + y];
+            ks2_pass<RB, P>(tab + p * P * (RB + 1) * 32, dP, org + p * P * pitch, pitch, lane);
+        }
+    }
+}
+
+// RBMAX: 8 -> items whose largest applied radius (among radii <= 16) is <= 8; 16 -> items with 9..16.
+template <int RBMAX, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32)
+ks2_kernel(const Ks2Params p, int* __restrict__ workCounter) {
+    constexpr int RBMIN = (RBMAX == 8) ? 0 : 9;
+    constexpr int PITCH = 32 + 2 * RBMAX;
+    extern __shared__ __align__(16) float smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float* patch = smem + (size_t)warp * ks2_warp_floats(RBMAX);
+    float* tab = patch + ks2_patch_floats(RBMAX);
+    uint16_t* llist = reinterpret_cast<uint16_t*>(tab + ks2_table_floats(RBMAX));   // [KS2_MAXL] layer | rb << 8
+    const int nItems = p.nz * p.tiles;
+    const int R = p.Rx * p.Ry;
+    const int bevPitch = p.Rx + 64;
+    for (;;) {
+        int it = 0;
+        if (lane == 0) it = atomicAdd(workCounter, 1);
+        it = __shfl_sync(0xffffffffu, it, 0);
+        if (it >= nItems) break;
+        const int idx = nItems - 1 - it;            // deepest slices (largest radii) first
+        const int kk = idx / p.tiles, tile = idx - kk * p.tiles;
+        // compact list of the layers that are live at this (slice, tile), with their applied radius
+        int imax = -1, n = 0;
+        for (int l0 = 0; l0 < p.L; l0 += 32) {
+            const int l = l0 + lane;
+            int rb = -1;
+            if (l < p.L && kk < p.layerFirstPassive[l] - p.first) {
+                const unsigned own = p.radMap[((size_t)l * p.nz + kk) * p.tiles + tile];
+                if (own <= 32u) { rb = p.batchRad[l * 34 + own]; if (rb > KS2_MAXRB) rb = -1; }
+            }
+            const unsigned m = __ballot_sync(0xffffffffu, rb >= 0);
+            if (rb >= 0) llist[n + __popc(m & ((1u << lane) - 1u))] = (uint16_t)(l | (rb << 8));
+            n += __popc(m);
+            imax = max(imax, rb);
+        }
+        imax = __reduce_max_sync(0xffffffffu, imax);
+        if (imax < RBMIN || imax > RBMAX) continue;
+        const int nr = 8 + 2 * imax, nc = 32 + 2 * imax;
+        for (int i = lane; i < nr * PITCH; i += 32) patch[i] = 0.0f;
+        __syncwarp();
+        const int tx = tile % p.tilesX, ty = tile / p.tilesX;
+        const size_t tileOff = (size_t)kk * R + (size_t)(ty * 8) * p.Rx + tx * 32 + lane;
+        const size_t layerStride = (size_t)p.nz * R;
+        // software pipeline: the next layer's 16 loads are in flight while the current layer is processed
+        float dn[8], rn[8];
+        {
+            const size_t src = (size_t)(llist[0] & 0xff) * layerStride + tileOff;
+#pragma unroll
+            for (int y = 0; y < 8; ++y) { dn[y] = __ldg(p.idd + src + (size_t)y * p.Rx); rn[y] = __ldg(p.rsig + src + (size_t)y * p.Rx); }
+        }
+        for (int q = 0; q < n; ++q) {
+            const int rb = llist[q] >> 8;
+            float d[8], r[8];
+#pragma unroll
+            for (int y = 0; y < 8; ++y) { d[y] = dn[y]; r[y] = rn[y]; }
+            if (q + 1 < n) {
+                const size_t src = (size_t)(llist[q + 1] & 0xff) * layerStride + tileOff;
+#pragma unroll
+                for (int y = 0; y < 8; ++y) { dn[y] = __ldg(p.idd + src + (size_t)y * p.Rx); rn[y] = __ldg(p.rsig + src + (size_t)y * p.Rx); }
+            }
+            bool any = false;
+#pragma unroll
+            for (int y = 0; y < 8; ++y) any |= d[y] > 0.0f;
+            if (!__any_sync(0xffffffffu, any)) continue;      // __syncthreads_or(dose > 0), cuh:456
+            // erf-difference weights (cuh:459-467) -> table
+#pragma unroll
+            for (int y = 0; y < 8; ++y) {
+                float erfNew = erff(r[y] * 0.5f), erfOld = -erfNew;
+                float* t = tab + (y * (rb + 1)) * 32 + lane;
+#pragma unroll 1
+                for (int i = 0; i <= rb; ++i) {
+                    t[i * 32] = 0.5f * (erfNew - erfOld);
+                    erfOld = erfNew;
+                    erfNew = erff(r[y] * ((float)i + 1.5f));
+                }
+            }
+            __syncwarp();
+            float* org = patch + (imax - rb) * PITCH + (imax - rb);
+            switch (rb) {
+#define RTD_KS2_CASE(N) case N: if (N <= RBMAX) ks2_tile<(N <= RBMAX) ? N : 0>(tab, d, org, PITCH, lane); break;
+                RTD_KS2_CASE(0) RTD_KS2_CASE(1) RTD_KS2_CASE(2) RTD_KS2_CASE(3) RTD_KS2_CASE(4) RTD_KS2_CASE(5) RTD_KS2_CASE(6)
+                RTD_KS2_CASE(7) RTD_KS2_CASE(8) RTD_KS2_CASE(9) RTD_KS2_CASE(10) RTD_KS2_CASE(11) RTD_KS2_CASE(12) RTD_KS2_CASE(13)
+                RTD_KS2_CASE(14) RTD_KS2_CASE(15) RTD_KS2_CASE(16)
+#undef RTD_KS2_CASE
+                default: break;
+            }
+            __syncwarp();
+        }
+        // one reduction of the whole patch into the haloed BEV dose (z index = absolute step, 32-px halo)
+        float* out = p.bev + ((size_t)(kk + p.first) * (p.Ry + 64) + (ty * 8 + 32 - imax)) * bevPitch + tx * 32 + 32 - imax;
+        for (int rr = 0; rr < nr; ++rr) {
+            for (int cc = lane; cc < nc; cc += 32) {
+                const float v = patch[rr * PITCH + cc];
+                if (v != 0.0f) atomicAdd(out + (size_t)rr * bevPitch + cc, v);
+            }
+        }
+        __syncwarp();
+    }
+}
+
+}  // namespace rtd

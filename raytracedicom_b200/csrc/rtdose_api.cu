@@ -10,6 +10,7 @@
 #include <algorithm>
 #include "../../include/rtdose.h"
 #include "kernels.cuh"
+#include "ks2.cuh"
 
 using namespace rtd;
 
@@ -86,13 +87,15 @@ struct rtd_ctx {
     int nBeamsLast = 0;
     std::vector<cudaEvent_t> events;
     int smCount = 148;
-    int ksBlocksA = 0, ksBlocksB = 0, ksBlocksC = 0;
+    int ksBlocksA = 0, ksBlocksB = 0, ksBlocksC = 0, ks2Blocks8 = 0, ks2Blocks16 = 0;
     rtd_opts optsLast;
 };
 
 namespace {
 
 constexpr int KS_NT_A = 64, KS_NT_B = 96, KS_NT_C = 128;
+constexpr int KS2_WARPS_8 = 15, KS2_WARPS_16 = 8;   // warps per CTA: as many as the per-warp shared memory allows on one SM
+constexpr size_t KS2_SMEM_8 = size_t(KS2_WARPS_8) * ks2_warp_floats(8) * 4, KS2_SMEM_16 = size_t(KS2_WARPS_16) * ks2_warp_floats(16) * 4;
 constexpr size_t KS_SMEM_A = ks_smem_floats(8) * 4, KS_SMEM_B = ks_smem_floats(16) * 4, KS_SMEM_C = ks_smem_floats(32) * 4;
 
 rtd_status fail(rtd_ctx* c, rtd_status s, const std::string& msg) { if (c) c->err = msg; return s; }
@@ -291,14 +294,18 @@ rtd_status beamPhaseB(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opts
     fill_list_kernel<<<dim3(gx, L), 256, 0, ctx->stream>>>(w.radMap.as<uint8_t>(), w.batchRad.as<int>(), w.rbOffset.as<int>(), dCursor, nz, tiles, w.list.as<uint32_t>());
     RTD_CUDA(cudaEventRecord(evs[3], ctx->stream));
 
-    // K3b: three radius classes, heavy first
+    // K3b: radii 17..32 (rare) through the block-wide kernel and its work list; radii <= 16 through the layer-fused
+    // warp-autonomous kernel (ks2.cuh), one launch per patch-size class
     KsParams kp;
     kp.idd = w.idd.as<float>(); kp.rsig = w.rsig.as<float>(); kp.bev = w.bev.as<float>(); kp.list = w.list.as<uint32_t>();
     kp.batchRad = w.batchRad.as<int>(); kp.radMap = w.radMap.as<uint8_t>();
     kp.Rx = Rx; kp.Ry = Ry; kp.nz = nz; kp.first = w.bfi; kp.tilesX = tilesX; kp.tiles = tiles;
     ks_kernel<KS_NT_C, 17, 32><<<ctx->ksBlocksC, KS_NT_C, KS_SMEM_C, ctx->stream>>>(kp, w.rbOffset.as<int>(), dStats, dWork + 0);
-    ks_kernel<KS_NT_B, 9, 16><<<ctx->ksBlocksB, KS_NT_B, KS_SMEM_B, ctx->stream>>>(kp, w.rbOffset.as<int>(), dStats, dWork + 1);
-    ks_kernel<KS_NT_A, 0, 8><<<ctx->ksBlocksA, KS_NT_A, KS_SMEM_A, ctx->stream>>>(kp, w.rbOffset.as<int>(), dStats, dWork + 2);
+    Ks2Params k2;
+    k2.idd = kp.idd; k2.rsig = kp.rsig; k2.bev = kp.bev; k2.batchRad = kp.batchRad; k2.radMap = kp.radMap; k2.layerFirstPassive = dLfp;
+    k2.L = L; k2.Rx = Rx; k2.Ry = Ry; k2.nz = nz; k2.first = w.bfi; k2.tilesX = tilesX; k2.tiles = tiles;
+    ks2_kernel<16, KS2_WARPS_16><<<ctx->ks2Blocks16, KS2_WARPS_16 * 32, KS2_SMEM_16, ctx->stream>>>(k2, dWork + 1);
+    ks2_kernel<8, KS2_WARPS_8><<<ctx->ks2Blocks8, KS2_WARPS_8 * 32, KS2_SMEM_8, ctx->stream>>>(k2, dWork + 2);
     RTD_CUDA(cudaEventRecord(evs[4], ctx->stream));
 
     // K4 (cu:1185-1218); the z-range uses Zg instead of beamFirstCalculatedPassive: a superset box that only adds
@@ -443,12 +450,12 @@ rtd_status rtd_create(rtd_ctx** out, int device) {
     cudaDeviceGetAttribute(&ctx->smCount, cudaDevAttrMultiProcessorCount, device);
     rtd_default_opts(&ctx->optsLast);
     cudaFuncSetAttribute(ks_kernel<KS_NT_C, 17, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)KS_SMEM_C);
-    cudaFuncSetAttribute(ks_kernel<KS_NT_B, 9, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)KS_SMEM_B);
-    cudaFuncSetAttribute(ks_kernel<KS_NT_A, 0, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)KS_SMEM_A);
+    cudaFuncSetAttribute(ks2_kernel<16, KS2_WARPS_16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)KS2_SMEM_16);
+    cudaFuncSetAttribute(ks2_kernel<8, KS2_WARPS_8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)KS2_SMEM_8);
     int occ = 0;
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ks_kernel<KS_NT_C, 17, 32>, KS_NT_C, KS_SMEM_C); ctx->ksBlocksC = std::max(occ, 1) * ctx->smCount;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ks_kernel<KS_NT_B, 9, 16>, KS_NT_B, KS_SMEM_B); ctx->ksBlocksB = std::max(occ, 1) * ctx->smCount;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ks_kernel<KS_NT_A, 0, 8>, KS_NT_A, KS_SMEM_A); ctx->ksBlocksA = std::max(occ, 1) * ctx->smCount;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ks2_kernel<16, KS2_WARPS_16>, KS2_WARPS_16 * 32, KS2_SMEM_16); ctx->ks2Blocks16 = std::max(occ, 1) * ctx->smCount;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ks2_kernel<8, KS2_WARPS_8>, KS2_WARPS_8 * 32, KS2_SMEM_8); ctx->ks2Blocks8 = std::max(occ, 1) * ctx->smCount;
     if (cudaGetLastError() != cudaSuccess) { cudaStreamDestroy(ctx->stream); delete ctx; return RTD_ERR_CUDA; }
     *out = ctx;
     return RTD_OK;
