@@ -26,6 +26,23 @@ struct Ks2Params {
     int L, Rx, Ry, nz, first, tilesX, tiles;
 };
 
+// erf(x) for x >= 0 as 1 - 2^(x Q(x)), Q = degree-7 fit of log2(erfc(x))/x on [0,4] (erf(4) rounds to 1 in fp32).
+// Max abs error 1.0e-7 (+ ex2.approx's 2 ulp), i.e. the fp32 resolution of erf near 1; 11 instructions against
+// ~25 for libdevice's two-range erff, which dominated the instruction count of this kernel at small radii.
+// The weights only need erf differences to ~1e-6 of the central weight (BASELINE.json bound: 1e-3 of max dose).
+__device__ __forceinline__ float ks_erf_pos(float x) {
+    x = fminf(x, 4.0f);
+    float q = -4.223215728e-05f;
+    q = fmaf(q, x, 4.191363114e-04f);
+    q = fmaf(q, x, -1.401739311e-03f);
+    q = fmaf(q, x, -9.219333297e-04f);
+    q = fmaf(q, x, 2.838649414e-02f);
+    q = fmaf(q, x, -1.485444903e-01f);
+    q = fmaf(q, x, -9.184023738e-01f);
+    q = fmaf(q, x, -1.627909660e+00f);
+    return 1.0f - exp2f(x * q);
+}
+
 constexpr int KS2_MAXRB = 16;       // larger batch radii go through the block-wide ks_kernel<.,17,32>
 constexpr int KS2_MAXL = 256;
 
@@ -152,16 +169,17 @@ ks2_kernel(const Ks2Params p, int* __restrict__ workCounter) {
 #pragma unroll
             for (int y = 0; y < 8; ++y) any |= d[y] > 0.0f;
             if (!__any_sync(0xffffffffu, any)) continue;      // __syncthreads_or(dose > 0), cuh:456
-            // erf-difference weights (cuh:459-467) -> table
+            // erf-difference weights (cuh:459-467) -> table: e[0] = erf(r/2), e[i] = (erf(r(i+1/2)) - erf(r(i-1/2)))/2
 #pragma unroll
             for (int y = 0; y < 8; ++y) {
-                float erfNew = erff(r[y] * 0.5f), erfOld = -erfNew;
+                float erfOld = ks_erf_pos(r[y] * 0.5f);
                 float* t = tab + (y * (rb + 1)) * 32 + lane;
+                t[0] = erfOld;
 #pragma unroll 1
-                for (int i = 0; i <= rb; ++i) {
+                for (int i = 1; i <= rb; ++i) {
+                    const float erfNew = ks_erf_pos(r[y] * ((float)i + 0.5f));
                     t[i * 32] = 0.5f * (erfNew - erfOld);
                     erfOld = erfNew;
-                    erfNew = erff(r[y] * ((float)i + 1.5f));
                 }
             }
             __syncwarp();
