@@ -139,7 +139,7 @@ typedef enum {
     RTD_FETCH_RSIGMA = 7,        /* float [nz][Ry][Rx] of one layer */
     RTD_FETCH_FIRST_PASSIVE = 8, /* int   [Ry][Rx] of one layer */
     RTD_FETCH_BEV_DOSE = 9,      /* float [Zg][Ry+64][Rx+64] */
-    RTD_FETCH_TILE_RADIUS = 10   /* uint8 [nz][Ry/8][Rx/32] of one layer (own radius, before batching) */
+    RTD_FETCH_TILE_RADIUS = 10   /* uint8 [nz][Ry/8][Rx/32] of one layer (own radius, before batching; 254 = live tile without dose, 255 = not live) */
 } rtd_fetch_what;
 
 void        rtd_default_opts(rtd_opts* o);

@@ -317,8 +317,11 @@ idd_sigma_kernel(const float* __restrict__ density, const float* __restrict__ we
         rs = keep ? rs : inf;
         idd[outIdx] = res;
         rsig[outIdx] = rs;
+        // row minimum of rSigmaEff for the tile radius; its sign carries "some voxel of this row has dose > 0"
+        // (a tile without dose is skipped by the superposition exactly like the reference's __syncthreads_or, cuh:456)
         const float m = warp_min(rs);
-        if (lane == 0) rowMin[rmIdx] = m;
+        const bool anyDose = __any_sync(0xffffffffu, res > 0.0f);
+        if (lane == 0) rowMin[rmIdx] = anyDose ? m : -m;
         inIdx += R; outIdx += R; rmIdx += (size_t)q.Ry * (q.Rx / 32);
     }
     firstPassive[(size_t)l * R + ray] = (int)afterLast;
@@ -344,12 +347,13 @@ tile_radius_kernel(const float* __restrict__ rowMin, const int* __restrict__ lay
         uint8_t r8 = 255;
         if (kk < nLive) {
             const float* p = rowMin + (((size_t)l * nz + kk) * Ry + ty * 8) * tilesX + tx;
-            float m = p[0];
+            float m = fabsf(p[0]);
+            bool anyDose = p[0] > 0.0f;
 #pragma unroll
-            for (int i = 1; i < 8; ++i) { const float v = p[(size_t)i * tilesX]; if (v < m) m = v; }
+            for (int i = 1; i < 8; ++i) { const float v = p[(size_t)i * tilesX]; anyDose |= v > 0.0f; if (fabsf(v) < m) m = fabsf(v); }
             // kernel_wrapper.cuh:303
             const unsigned rad = min((unsigned)f_toint_rz(f_add(f_div(ksCutoff, f_mul(f_sqrt(2.0f), m)), 0.5f)), 33u);
-            r8 = (uint8_t)rad;
+            r8 = anyDose ? (uint8_t)rad : (uint8_t)254;   // 254: live tile (counted in the histogram) that deposits nothing
             atomicAdd(&sHist[rad], 1);
         }
         radMap[((size_t)l * nz + kk) * tiles + t] = r8;
