@@ -228,7 +228,6 @@ def main():
             stage[k] = stage.get(k, 0.0) + v
     barrier()
     t_wall = time.perf_counter() - t_wall0
-    sampler.stop_flag = True; sampler.join(timeout=2)
     ms_local = sum(a.elapsed_time(b) for a, b in evs) / args.steps
     upd_local = torch.tensor([int(stage["updates"] / args.steps), int(stage["ksTaps"] / args.steps)], dtype=torch.int64, device=dev)
     ms_t = torch.tensor([ms_local], dtype=torch.float64, device=dev)
@@ -279,6 +278,7 @@ def main():
             e2e["dose_checksum_matches_device_run"] = bool(abs(cs - checksum) <= 1e-5 * abs(checksum))
         eng.set_ct_ptr(ct_dev.data_ptr(), cnx, cny, cnz, device=True)
 
+    sampler.stop_flag = True; sampler.join(timeout=2)   # sampled over the device-resident and the end-to-end timed regions
     if rank == 0:
         peak, peak_src, sm_max = load_peaks()
         reps = [eng.beam_report(b) for b in range(len(mine))]
