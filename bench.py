@@ -147,6 +147,8 @@ def run_reference(args, case, rank, world):
 
 
 def main():
+    import faulthandler
+    faulthandler.enable()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
@@ -321,11 +323,18 @@ def main():
         if not args.no_cpu_baseline and world == 1:
             line["cpu_baseline"] = cpu_baseline_port(case)
         print(json.dumps(line), flush=True)
+    # tear down in dependency order: torch tensors that were used on the engine's stream must die before the stream does
+    del evs, ms_t, upd_local
+    dose_dev = ct_dev = flush = None
+    torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
-    eng.close()
-    return 0
+    # torch's pinned-memory and device allocators record events on every stream a block was used on when the block is
+    # released, including the engine's stream (ExternalStream): leave the context to process exit instead of destroying
+    # that stream under them.
+    sys.stdout.flush(); sys.stderr.flush()
+    os._exit(0)
 
 
 if __name__ == "__main__":
