@@ -46,7 +46,7 @@ __device__ __forceinline__ float ks_erf_pos(float x) {
 constexpr int KS2_MAXRB = 16;       // larger batch radii go through the block-wide ks_kernel<.,17,32>
 constexpr int KS2_MAXL = 256;
 
-__host__ __device__ constexpr int ks2_rows_per_pass(int rb) { return rb <= 8 ? 8 : 4; }
+__host__ __device__ constexpr int ks2_rows_per_pass(int rb) { return rb <= 16 ? 8 : 4; }
 // per-warp shared memory (floats): patch + weight table + layer list
 __host__ __device__ constexpr int ks2_patch_floats(int rbmax) { return (8 + 2 * rbmax) * (32 + 2 * rbmax); }
 __host__ __device__ constexpr int ks2_table_floats(int rbmax) { return 8 * (rbmax + 1) * 32; }
