@@ -231,6 +231,23 @@ def main():
     barrier()
     t_wall = time.perf_counter() - t_wall0
     ms_local = sum(a.elapsed_time(b) for a, b in evs) / args.steps
+    # stage timings / roofline: a few extra steps with the beams serialised on one stream, so that the library's stage
+    # events bracket each kernel alone (with concurrent beams the stages of different beams overlap in time)
+    conc_stage = dict(stage)
+    eng.opts.serialBeams = 1
+    stage = {}
+    n_serial = 3
+    step_device()
+    for _ in range(n_serial):
+        with torch.cuda.stream(stream):
+            flush.fill_(1)
+        tm = step_device()
+        for k, v in tm.as_dict().items():
+            stage[k] = stage.get(k, 0.0) + v
+    eng.opts.serialBeams = 0
+    for k in stage:
+        stage[k] = stage[k] * args.steps / n_serial      # same normalisation as the timed loop below
+    torch.cuda.synchronize()
     upd_local = torch.tensor([int(stage["updates"] / args.steps), int(stage["ksTaps"] / args.steps)], dtype=torch.int64, device=dev)
     ms_t = torch.tensor([ms_local], dtype=torch.float64, device=dev)
     if world > 1:
@@ -307,7 +324,9 @@ def main():
                            "l2": "256 MiB buffer written between timed iterations (L2 flush); CT 4*%d B and BEV arrays exceed L2" % (nx * ny * nz)},
                 "plan_ms": ms_step, "updates_per_step": U,
                 "stage_ms_rank0": {k: stage[k] / args.steps for k in ("msTrace", "msSetup", "msConv", "msIddSigma", "msRadius", "msSuperp", "msTransfer", "msTotal")},
-                "gpu_launches": int(stage["kernelLaunches"]), "host_syncs_per_plan": int(stage["hostSyncs"] / args.steps),
+                "stage_note": "stage_ms_rank0 and roofline come from 3 extra steps with opts.serialBeams=1 (stages bracketed alone); the timed steps run one stream per beam",
+                "serial_beams_plan_ms": stage["msTotal"] / args.steps,
+                "gpu_launches": int(conc_stage["kernelLaunches"]), "host_syncs_per_plan": int(stage["hostSyncs"] / args.steps),
                 "dose_max": dmax, "dose_checksum": checksum,
                 "roofline": {"kernel": "ks_kernel (kernel superposition, 3 radius-class launches per beam)", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                              "frac": achieved / peak, "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": ks_alg / ks_launches,

@@ -86,10 +86,13 @@ typedef struct {
     float rayWeightCutoff;   /* RAY_WEIGHT_CUTOFF 1.0  */
     int   minTilesInBatch;   /* 16, src/kernel_wrapper.cuh:29 */
     int   keepIntermediates; /* 1: keep per-beam BEV arrays of every layer for rtd_debug_fetch */
-    int   reserved[4];
+    int   serialBeams;       /* 1: run the beams one after the other on one stream (stage timings then do not overlap);
+                                0 (default): one stream per beam, transfers into the dose grid serialised in beam order */
+    int   reserved[3];
 } rtd_opts;
 
-/* Stage timing of the last rtd_dose* call (CUDA events on the context's stream), the counterpart of the
+/* Stage timing of the last rtd_dose* call (CUDA events; with concurrent beams the per-stage figures are sums over the
+ * beams' streams and overlap in time, so they can exceed msTotal), the counterpart of the
  * reference's FINE_GRAINED_TIMING report (src/kernel_wrapper.cu:1291-1311). */
 typedef struct {
     float msTotal;       /* first event -> last event of the call */

@@ -86,6 +86,7 @@ struct rtd_ctx {
     std::vector<BeamWs*> ws;
     int nBeamsLast = 0;
     std::vector<cudaEvent_t> events;
+    std::vector<cudaStream_t> bstreams;   // per-beam streams (concurrent beams)
     int smCount = 148;
     int ksBlocksA = 0, ksBlocksB = 0, ksBlocksC = 0, ks2Blocks8 = 0, ks2Blocks16 = 0;
     rtd_opts optsLast;
@@ -155,7 +156,7 @@ rtd_status setCtCommon(rtd_ctx* ctx, const float* src, int nx, int ny, int nz, c
 }
 
 // Everything that can be done for a beam before any device result is known (cu:612-663, 766-790).
-rtd_status beamPhaseA(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opts& o, int& launches) {
+rtd_status beamPhaseA(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opts& o, int& launches, cudaStream_t st) {
     if (b.nLayers <= 0 || b.sx <= 0 || b.sy <= 0 || !b.weights || !b.energies || !b.sigmas)
         return fail(ctx, RTD_ERR_INVALID, "Empty list");   // findMax on an empty vector, vector_find.h:22-25
     if (b.steps == 0 || b.steps > 4095) return fail(ctx, RTD_ERR_INVALID, "beam.steps must be in [1, 4095]");
@@ -181,23 +182,23 @@ rtd_status beamPhaseA(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opts
     const size_t nW = size_t(b.sx) * b.sy * w.Lc;
     RTD_CUDA(w.spotW.ensure(nW * 4)); RTD_CUDA(w.hStage.ensure(nW * 4 + size_t(w.Lc) * (8 + sizeof(LayerParams))));
     memcpy(w.hStage.p, b.weights + size_t(b.sx) * b.sy * w.l0, nW * 4);
-    RTD_CUDA(cudaMemcpyAsync(w.spotW.p, w.hStage.p, nW * 4, cudaMemcpyHostToDevice, ctx->stream));
+    RTD_CUDA(cudaMemcpyAsync(w.spotW.p, w.hStage.p, nW * 4, cudaMemcpyHostToDevice, st));
     const TraceParams tp = makeTraceParams(ctx->densScale, ctx->spScale, b.steps, w.grid.rayIdxToGantry, w.dist, w.gtii);
     // weplMin buffer layout: [0]=beamFirstInside, [1]=beamFirstOutside (ints), [2..] weplMin floats
     int* sc = w.weplMin.as<int>();
-    trace_bev_kernel<<<w.R / 32, TR_THREADS, 0, ctx->stream>>>(tp, ctx->ctTex.tex, ctx->densTex.tex, ctx->spTex.tex,
+    trace_bev_kernel<<<w.R / 32, TR_THREADS, 0, st>>>(tp, ctx->ctTex.tex, ctx->densTex.tex, ctx->spTex.tex,
         w.density.as<float>(), w.wepl.as<float>(), w.firstIn.as<int>(), w.firstOut.as<int>(), w.grid.dimX, w.R);
-    slice_reduce_kernel<<<w.S, 256, 0, ctx->stream>>>(w.wepl.as<float>(), w.firstIn.as<int>(), w.firstOut.as<int>(), w.R,
+    slice_reduce_kernel<<<w.S, 256, 0, st>>>(w.wepl.as<float>(), w.firstIn.as<int>(), w.firstOut.as<int>(), w.R,
         w.weplMin.as<float>() + 2, sc, sc + 1);
     launches += 2;
     RTD_CUDA(cudaGetLastError());
-    RTD_CUDA(cudaMemcpyAsync(w.hTrace.p, w.weplMin.p, size_t(w.S) * 4 + 8, cudaMemcpyDeviceToHost, ctx->stream));
+    RTD_CUDA(cudaMemcpyAsync(w.hTrace.p, w.weplMin.p, size_t(w.S) * 4 + 8, cudaMemcpyDeviceToHost, st));
     return RTD_OK;
 }
 
 // Host logic that needs the tracer's reductions (cu:792-849, 922-925) + all remaining launches of the beam.
 rtd_status beamPhaseB(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opts& o, float* dDose, int& launches,
-                      cudaEvent_t* evs /*6 events: conv, idd, radius, superp, transfer, end*/) {
+                      cudaEvent_t* evs /*6 events: conv, idd, radius, superp, transfer, end*/, cudaStream_t strm) {
     const int* sc = w.hTrace.as<int>();
     const float* weplMin = w.hTrace.as<float>() + 2;
     w.bfi = sc[0]; w.bfo = sc[1];
@@ -259,11 +260,11 @@ rtd_status beamPhaseB(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opts
     char* st = w.hStage.as<char>() + nW * 4;
     memcpy(st, w.entrySig.data(), size_t(L) * 8);
     memcpy(st + size_t(L) * 8, w.layers.data(), size_t(L) * sizeof(LayerParams));
-    RTD_CUDA(cudaMemcpyAsync(w.sigmas.p, st, size_t(L) * 8, cudaMemcpyHostToDevice, ctx->stream));
-    RTD_CUDA(cudaMemcpyAsync(w.layerDev.p, st + size_t(L) * 8, size_t(L) * sizeof(LayerParams), cudaMemcpyHostToDevice, ctx->stream));
-    RTD_CUDA(cudaMemsetAsync(w.lfp.p, 0, ctlInts * 4, ctx->stream));
-    RTD_CUDA(cudaMemsetAsync(w.bev.p, 0, bevN * 4, ctx->stream));
-    RTD_CUDA(cudaEventRecord(evs[0], ctx->stream));
+    RTD_CUDA(cudaMemcpyAsync(w.sigmas.p, st, size_t(L) * 8, cudaMemcpyHostToDevice, strm));
+    RTD_CUDA(cudaMemcpyAsync(w.layerDev.p, st + size_t(L) * 8, size_t(L) * sizeof(LayerParams), cudaMemcpyHostToDevice, strm));
+    RTD_CUDA(cudaMemsetAsync(w.lfp.p, 0, ctlInts * 4, strm));
+    RTD_CUDA(cudaMemsetAsync(w.bev.p, 0, bevN * 4, strm));
+    RTD_CUDA(cudaEventRecord(evs[0], strm));
 
     // K3a (cu:849-854)
     ConvParams cp;
@@ -274,25 +275,25 @@ rtd_status beamPhaseB(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opts
     cp.deltaX = b.spotDelta[0] / rayD.x; cp.deltaY = b.spotDelta[1] / rayD.y;
     cp.offX = (b.spotOffset[0] - rayO.x) / rayD.x; cp.offY = (b.spotOffset[1] - rayO.y) / rayD.y;
     cp.cutoff = o.convSigmaCutoff;
-    spot_to_ray_kernel<<<dim3(Rx / 32, L), 256, size_t(w.sy) * 32 * 4, ctx->stream>>>(w.spotW.as<float>(), w.sigmas.as<float2>(), w.rayW.as<float>(), cp);
-    RTD_CUDA(cudaEventRecord(evs[1], ctx->stream));
+    spot_to_ray_kernel<<<dim3(Rx / 32, L), 256, size_t(w.sy) * 32 * 4, strm>>>(w.spotW.as<float>(), w.sigmas.as<float2>(), w.rayW.as<float>(), cp);
+    RTD_CUDA(cudaEventRecord(evs[1], strm));
 
     // K2
     IddParams q;
     q.g = makeFillGeom(w.grid.rayIdxToGantry, w.dist);
     q.rrlScale = ctx->rrlScale; q.bpCutoff = o.bpDepthCutoff; q.rayWeightCutoff = o.rayWeightCutoff;
     q.first = w.bfi; q.nz = nz; q.Rx = Rx; q.Ry = Ry; q.nozzle = 1;
-    idd_sigma_kernel<<<dim3(tilesX, tilesY, L), 256, 0, ctx->stream>>>(w.density.as<float>(), w.wepl.as<float>(), w.rayW.as<float>(),
+    idd_sigma_kernel<<<dim3(tilesX, tilesY, L), 256, 0, strm>>>(w.density.as<float>(), w.wepl.as<float>(), w.rayW.as<float>(),
         w.firstIn.as<int>(), w.firstOut.as<int>(), w.layerDev.as<LayerParams>(), q, ctx->iddTex.tex, ctx->rrlTex.tex,
         w.idd.as<float>(), w.rsig.as<float>(), w.rowMin.as<float>(), w.firstPassive.as<int>(), dLfp);
-    RTD_CUDA(cudaEventRecord(evs[2], ctx->stream));
+    RTD_CUDA(cudaEventRecord(evs[2], strm));
 
     // tile radii, batching, work list
     const int gx = (nz * tiles + 255) / 256;
-    tile_radius_kernel<<<dim3(gx, L), 256, 0, ctx->stream>>>(w.rowMin.as<float>(), dLfp, w.bfi, nz, Rx, Ry, o.ksSigmaCutoff, w.radMap.as<uint8_t>(), dHist);
-    batch_kernel<<<1, 64, 0, ctx->stream>>>(dHist, L, o.minTilesInBatch, w.batchRad.as<int>(), w.rbOffset.as<int>(), dStats);
-    fill_list_kernel<<<dim3(gx, L), 256, 0, ctx->stream>>>(w.radMap.as<uint8_t>(), w.batchRad.as<int>(), w.rbOffset.as<int>(), dCursor, nz, tiles, w.list.as<uint32_t>());
-    RTD_CUDA(cudaEventRecord(evs[3], ctx->stream));
+    tile_radius_kernel<<<dim3(gx, L), 256, 0, strm>>>(w.rowMin.as<float>(), dLfp, w.bfi, nz, Rx, Ry, o.ksSigmaCutoff, w.radMap.as<uint8_t>(), dHist);
+    batch_kernel<<<1, 64, 0, strm>>>(dHist, L, o.minTilesInBatch, w.batchRad.as<int>(), w.rbOffset.as<int>(), dStats);
+    fill_list_kernel<<<dim3(gx, L), 256, 0, strm>>>(w.radMap.as<uint8_t>(), w.batchRad.as<int>(), w.rbOffset.as<int>(), dCursor, nz, tiles, w.list.as<uint32_t>());
+    RTD_CUDA(cudaEventRecord(evs[3], strm));
 
     // K3b: radii 17..32 (rare) through the block-wide kernel and its work list; radii <= 16 through the layer-fused
     // warp-autonomous kernel (ks2.cuh), one launch per patch-size class
@@ -300,13 +301,13 @@ rtd_status beamPhaseB(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opts
     kp.idd = w.idd.as<float>(); kp.rsig = w.rsig.as<float>(); kp.bev = w.bev.as<float>(); kp.list = w.list.as<uint32_t>();
     kp.batchRad = w.batchRad.as<int>(); kp.radMap = w.radMap.as<uint8_t>();
     kp.Rx = Rx; kp.Ry = Ry; kp.nz = nz; kp.first = w.bfi; kp.tilesX = tilesX; kp.tiles = tiles;
-    ks_kernel<KS_NT_C, 17, 32><<<ctx->ksBlocksC, KS_NT_C, KS_SMEM_C, ctx->stream>>>(kp, w.rbOffset.as<int>(), dStats, dWork + 0);
+    ks_kernel<KS_NT_C, 17, 32><<<ctx->ksBlocksC, KS_NT_C, KS_SMEM_C, strm>>>(kp, w.rbOffset.as<int>(), dStats, dWork + 0);
     Ks2Params k2;
     k2.idd = kp.idd; k2.rsig = kp.rsig; k2.bev = kp.bev; k2.batchRad = kp.batchRad; k2.radMap = kp.radMap; k2.layerFirstPassive = dLfp;
     k2.L = L; k2.Rx = Rx; k2.Ry = Ry; k2.nz = nz; k2.first = w.bfi; k2.tilesX = tilesX; k2.tiles = tiles;
-    ks2_kernel<16, KS2_WARPS_16><<<ctx->ks2Blocks16, KS2_WARPS_16 * 32, KS2_SMEM_16, ctx->stream>>>(k2, dWork + 1);
-    ks2_kernel<8, KS2_WARPS_8><<<ctx->ks2Blocks8, KS2_WARPS_8 * 32, KS2_SMEM_8, ctx->stream>>>(k2, dWork + 2);
-    RTD_CUDA(cudaEventRecord(evs[4], ctx->stream));
+    ks2_kernel<16, KS2_WARPS_16><<<ctx->ks2Blocks16, KS2_WARPS_16 * 32, KS2_SMEM_16, strm>>>(k2, dWork + 1);
+    ks2_kernel<8, KS2_WARPS_8><<<ctx->ks2Blocks8, KS2_WARPS_8 * 32, KS2_SMEM_8, strm>>>(k2, dWork + 2);
+    RTD_CUDA(cudaEventRecord(evs[4], strm));
 
     // K4 (cu:1185-1218); the z-range uses Zg instead of beamFirstCalculatedPassive: a superset box that only adds
     // voxels whose interpolated BEV dose is exactly 0, so the result is identical and no host sync is needed here.
@@ -319,6 +320,9 @@ rtd_status beamPhaseB(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opts
         mx.x = std::max(mx.x, p.x); mx.y = std::max(mx.y, p.y); mx.z = std::max(mx.z, p.z);
         mn.x = std::min(mn.x, p.x); mn.y = std::min(mn.y, p.y); mn.z = std::min(mn.z, p.z);
     }
+    // the dose grid is shared by all beams: transfers are serialised on the context's main stream, in beam order,
+    // each one waiting for its own beam's superposition
+    RTD_CUDA(cudaStreamWaitEvent(ctx->stream, evs[4], 0));
     GridParams gp;
     gp.t = makeTransferParams(w.grid.rayIdxToGantry, w.dist, w.gtdi, v3(float(RTD_MAX_SUPERP_R), float(RTD_MAX_SUPERP_R), -float(w.bfi)));
     gp.minX = std::max((int(std::floor(mn.x)) / 32) * 32, 0); gp.minY = std::max(int(std::floor(mn.y)), 0); gp.minZ = std::max(int(std::floor(mn.z)), 0);
@@ -335,8 +339,8 @@ rtd_status beamPhaseB(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opts
     RTD_CUDA(cudaGetLastError());
     RTD_CUDA(cudaEventRecord(evs[5], ctx->stream));
     // results for the reports: control block + batch radii
-    RTD_CUDA(cudaMemcpyAsync(w.hOut.p, w.lfp.p, ctlInts * 4, cudaMemcpyDeviceToHost, ctx->stream));
-    RTD_CUDA(cudaMemcpyAsync(w.hOut.as<int>() + ctlInts, w.batchRad.p, size_t(L) * 34 * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    RTD_CUDA(cudaMemcpyAsync(w.hOut.p, w.lfp.p, ctlInts * 4, cudaMemcpyDeviceToHost, strm));
+    RTD_CUDA(cudaMemcpyAsync(w.hOut.as<int>() + ctlInts, w.batchRad.p, size_t(L) * 34 * 4, cudaMemcpyDeviceToHost, strm));
     return RTD_OK;
 }
 
@@ -383,18 +387,32 @@ rtd_status doseCore(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* dDos
     while ((int)ctx->ws.size() < nBeams) ctx->ws.push_back(new BeamWs());
     ctx->nBeamsLast = nBeams; ctx->optsLast = o;
     RTD_CUDA(cudaEventRecord(evBegin, ctx->stream));
+    // Beams are independent until the transfer into the shared dose grid: unless opts.serialBeams is set every beam runs
+    // on its own stream so that the latency-bound stages (tracer, IDD/sigma depth scans) of different beams overlap.
+    const bool serial = o.serialBeams != 0 || nBeams == 1;
+    auto beamStream = [&](int b) -> cudaStream_t {
+        if (serial) return ctx->stream;
+        const size_t i = size_t(b) % 8;
+        while (ctx->bstreams.size() <= i) { cudaStream_t s_; cudaStreamCreateWithFlags(&s_, cudaStreamNonBlocking); ctx->bstreams.push_back(s_); }
+        return ctx->bstreams[i];
+    };
     for (int b = 0; b < nBeams; ++b) {
-        rtd_status s = beamPhaseA(ctx, beams[b], *ctx->ws[b], o, launches);
+        cudaStream_t st = beamStream(b);
+        if (st != ctx->stream) RTD_CUDA(cudaStreamWaitEvent(st, evBegin, 0));
+        rtd_status s = beamPhaseA(ctx, beams[b], *ctx->ws[b], o, launches, st);
         if (s != RTD_OK) return s;
+        if (st != ctx->stream) { cudaEvent_t e = ev(ctx, 8 + size_t(b) * 8 + 6); RTD_CUDA(cudaEventRecord(e, st)); RTD_CUDA(cudaStreamWaitEvent(ctx->stream, e, 0)); }
     }
     cudaEvent_t evTraceEnd = ev(ctx, 2);
     RTD_CUDA(cudaEventRecord(evTraceEnd, ctx->stream));
-    RTD_CUDA(cudaStreamSynchronize(ctx->stream));                         // host sync 1 of 2
+    RTD_CUDA(cudaStreamSynchronize(ctx->stream));                         // host sync 1 of 2 (covers every beam stream)
     for (int b = 0; b < nBeams; ++b) {
         cudaEvent_t evs[6];
-        for (int i = 0; i < 6; ++i) evs[i] = ev(ctx, 8 + size_t(b) * 6 + i);
-        rtd_status s = beamPhaseB(ctx, beams[b], *ctx->ws[b], o, dDose, launches, evs);
+        for (int i = 0; i < 6; ++i) evs[i] = ev(ctx, 8 + size_t(b) * 8 + i);
+        cudaStream_t st = beamStream(b);
+        rtd_status s = beamPhaseB(ctx, beams[b], *ctx->ws[b], o, dDose, launches, evs, st);
         if (s != RTD_OK) return s;
+        if (st != ctx->stream) { cudaEvent_t e = ev(ctx, 8 + size_t(b) * 8 + 7); RTD_CUDA(cudaEventRecord(e, st)); RTD_CUDA(cudaStreamWaitEvent(ctx->stream, e, 0)); }
     }
     RTD_CUDA(cudaEventRecord(evEnd, ctx->stream));
     RTD_CUDA(cudaStreamSynchronize(ctx->stream));                         // host sync 2 of 2
@@ -408,14 +426,14 @@ rtd_status doseCore(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* dDos
         cudaEvent_t prev = evTraceEnd;
         for (int b = 0; b < nBeams; ++b) {
             if (!ctx->ws[b]->live) continue;
-            cudaEvent_t* e = &ctx->events[8 + size_t(b) * 6];
-            cudaEventElapsedTime(&ms, prev, e[0]); tm->msSetup += ms;
+            cudaEvent_t* e = &ctx->events[8 + size_t(b) * 8];
+            cudaEventElapsedTime(&ms, prev, e[0]); tm->msSetup += std::max(ms, 0.0f);
             cudaEventElapsedTime(&ms, e[0], e[1]); tm->msConv += ms;
             cudaEventElapsedTime(&ms, e[1], e[2]); tm->msIddSigma += ms;
             cudaEventElapsedTime(&ms, e[2], e[3]); tm->msRadius += ms;
             cudaEventElapsedTime(&ms, e[3], e[4]); tm->msSuperp += ms;
             cudaEventElapsedTime(&ms, e[4], e[5]); tm->msTransfer += ms;
-            prev = e[5];
+            prev = serial ? e[5] : evTraceEnd;
         }
         cudaEventElapsedTime(&ms, evBegin, evEnd); tm->msTotal = ms;
     }
@@ -469,6 +487,7 @@ void rtd_destroy(rtd_ctx* ctx) {
     ctx->iddTex.release(); ctx->densTex.release(); ctx->spTex.release(); ctx->rrlTex.release(); ctx->ctTex.release();
     ctx->dose.release();
     for (cudaEvent_t e : ctx->events) cudaEventDestroy(e);
+    for (cudaStream_t s_ : ctx->bstreams) { cudaStreamSynchronize(s_); cudaStreamDestroy(s_); }
     cudaStreamDestroy(ctx->stream);
     delete ctx;
 }

@@ -47,7 +47,7 @@ class RtdBeam(C.Structure):
 class RtdOpts(C.Structure):
     _fields_ = [("bpDepthCutoff", C.c_float), ("convSigmaCutoff", C.c_float), ("ksSigmaCutoff", C.c_float),
                 ("rayWeightCutoff", C.c_float), ("minTilesInBatch", C.c_int), ("keepIntermediates", C.c_int),
-                ("reserved", C.c_int * 4)]
+                ("serialBeams", C.c_int), ("reserved", C.c_int * 3)]
 
 
 class RtdTiming(C.Structure):
