@@ -8,7 +8,8 @@ A "step" = one whole-plan dose calculation (all beams, all energy layers) of the
   value  : spot-voxel updates/s with CT and LUTs already resident in HBM (device dose buffer zeroed, all kernels,
            partial-dose reduce over NCCL when N > 1), timed with CUDA events on the engine's stream, max over ranks.
   e2e    : the same metric through the reference-facing host call (rtd_dose == cudaWrapperProtons' coverage):
-           H2D CT from pinned host memory + H2D dose-in + all beams + D2H dose, every step.
+           rtd_plan_dose with pinned HOST CT + HOST dose: H2D of the CT / dose-in sub-volumes the plan touches, all beams,
+           D2H of the dose sub-volumes, every step.
   roofline / cpu_baseline: see DESIGN.md "Measurement".
 Prints ONE JSON line on rank 0.
 """
@@ -261,36 +262,41 @@ def main():
     e2e = None
     if not args.no_e2e:
         def step_e2e():
+            # the call a user of the reference makes: cudaWrapperProtons(imVol, doseVol, beams, ...) == rtd_plan_dose with
+            # HOST CT and HOST dose; the library copies the sub-volumes the plan touches (bytes reported by the library)
             if world == 1:
-                eng.set_ct_ptr(ct_host.data_ptr(), cnx, cny, cnz, device=False)                 # H2D CT (pinned)
-                eng.dose_ptr(packed, len(mine), dose_host.data_ptr(), device=False)            # H2D dose-in, beams, D2H dose
-            else:
-                eng.set_ct_ptr(ct_host.data_ptr(), cnx, cny, cnz, device=False)
-                with torch.cuda.stream(stream):
-                    if rank == 0:
-                        dose_dev.copy_(dose_host, non_blocking=True)                              # caller's dose content (accumulate semantics)
-                    else:
-                        dose_dev.zero_()
-                    eng.dose_ptr(packed, len(mine), dose_dev.data_ptr(), device=True)
-                    sharding.reduce_dose(dose_dev, dst=0)
-                    if rank == 0:
-                        dose_host.copy_(dose_dev, non_blocking=True)
-                stream.synchronize()
+                return eng.plan_dose_ptr(ct_host.data_ptr(), cnx, cny, cnz, packed, len(mine), dose_host.data_ptr())
+            with torch.cuda.stream(stream):
+                if rank == 0:
+                    dose_dev.copy_(dose_host, non_blocking=True)                              # caller's dose content (accumulate semantics)
+                else:
+                    dose_dev.zero_()
+                t = eng.plan_dose_ptr(ct_host.data_ptr(), cnx, cny, cnz, packed, len(mine), dose_dev.data_ptr(), device=True)
+                sharding.reduce_dose(dose_dev, dst=0)
+                if rank == 0:
+                    dose_host.copy_(dose_dev, non_blocking=True)
+            stream.synchronize()
+            return t
         n_e2e = max(3, min(args.steps, 10))
         for _ in range(2):
             dose_host.zero_(); step_e2e()
         tt = []
         for _ in range(n_e2e):
             dose_host.zero_()
-            barrier(); t0 = time.perf_counter(); step_e2e(); barrier(); tt.append(time.perf_counter() - t0)
+            barrier(); t0 = time.perf_counter(); te = step_e2e(); barrier(); tt.append(time.perf_counter() - t0)
         e_ms = torch.tensor([1e3 * sum(tt) / len(tt)], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(e_ms, op=dist.ReduceOp.MAX)
-        wbytes = sum(int(np.prod(b.weights.shape[1:])) * ((b.layer_end - b.layer_begin) or b.n_layers) * 4 for b in mine)
+        io = torch.tensor([int(te.h2dBytes) + (dose_host.numel() * 4 if (world > 1 and rank == 0) else 0),
+                           int(te.d2hBytes) + (dose_host.numel() * 4 if (world > 1 and rank == 0) else 0)], dtype=torch.int64, device=dev)
+        if world > 1:
+            dist.all_reduce(io, op=dist.ReduceOp.SUM)
         e2e = {"value": U / (float(e_ms.item()) * 1e-3), "unit": UNIT, "ms_per_plan": float(e_ms.item()),
-               "h2d_bytes_per_step": int(ct_host.numel() * 4 + (dose_host.numel() * 4 if rank == 0 else 0) + wbytes),
-               "d2h_bytes_per_step": int(dose_host.numel() * 4),
-               "timing": "host wall clock between barriers around the host call (rtd_set_ct + rtd_dose), max over ranks",
+               "h2d_bytes_per_step": int(io[0].item()), "d2h_bytes_per_step": int(io[1].item()),
+               "dense_bytes": {"h2d": int(ct_host.numel() * 4 + dose_host.numel() * 4), "d2h": int(dose_host.numel() * 4),
+                               "note": "what the reference moves: whole CT + whole dose grid up, whole dose grid down"},
+               "timing": "host wall clock between barriers around the host call rtd_plan_dose (HOST CT + HOST dose in, dose out; the "
+                         "library copies only the CT / dose sub-volumes the plan touches), max over ranks",
                "dose_checksum_matches_device_run": None}
         if rank == 0:
             cs = float(dose_host.double().sum().item())

@@ -109,6 +109,8 @@ typedef struct {
     int64_t ksTaps;      /* sum over updates of (2*rb+1)^2, rb = batch radius */
     int     kernelLaunches;
     int     hostSyncs;
+    int64_t h2dBytes;    /* bytes copied host->device inside the call (CT sub-volumes, dose-in sub-volumes, weights, parameters) */
+    int64_t d2hBytes;    /* bytes copied device->host inside the call (dose sub-volumes, reductions, reports) */
 } rtd_timing;
 
 typedef struct {
@@ -167,6 +169,22 @@ rtd_status rtd_dose(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* dose
  * context's stream has been synchronised. */
 rtd_status rtd_dose_device(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* dDoseInOut,
                            const rtd_opts* opts, rtd_timing* timing);
+
+/* The one-call equivalent of cudaWrapperProtons (src/kernel_wrapper.cu:381-1369): HOST CT + HOST dose, accumulated in
+ * place. Where the reference uploads the whole CT (cu:420-451) and the whole dose grid (cu:542) and downloads the whole
+ * dose grid (cu:1357), this call moves only the sub-volumes the plan can touch: the CT boxes that enclose every
+ * tracer sample of each beam (the fan frustum cut into depth segments) before the tracers, and the dose boxes that
+ * enclose each beam's haloed BEV volume (kernel_wrapper.cu:1185-1210) - uploaded while the beams compute, downloaded
+ * after the last transfer. Voxels outside those boxes are never read or written by any kernel, so the result equals
+ * rtd_set_ct + rtd_dose. After this call the context's CT is only PARTIALLY resident: rtd_dose / rtd_dose_device
+ * return RTD_ERR_STATE until rtd_set_ct* is called again. Pinned (cudaHostRegister'ed, like HostPinnedImage3D,
+ * src/host_image_3d.cuh:24) host buffers make the copies asynchronous. Dose dims come from rtd_set_dose_grid. */
+rtd_status rtd_plan_dose(rtd_ctx* ctx, const float* ctHuPlus1000, int nx, int ny, int nz, const rtd_beam* beams, int nBeams,
+                         float* doseInOut, const rtd_opts* opts, rtd_timing* timing);
+/* Same CT handling (HOST CT, sub-volumes only) with a DEVICE dose buffer: a rank of a multi-GPU plan computes its work
+ * items into its partial dose grid, which is then reduced over NCCL by the caller. */
+rtd_status rtd_plan_dose_device(rtd_ctx* ctx, const float* ctHuPlus1000, int nx, int ny, int nz, const rtd_beam* beams, int nBeams,
+                                float* dDoseInOut, const rtd_opts* opts, rtd_timing* timing);
 
 /* Integer/index outputs of the last call (the reference's bit-exact quantities). */
 rtd_status rtd_get_beam_report(const rtd_ctx* ctx, int beamNo, rtd_beam_report* out);

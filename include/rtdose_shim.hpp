@@ -76,7 +76,6 @@ void cudaWrapperProtons(Image* const imVol, Image* const doseVol, std::vector<Be
     ctx.check(rtd_set_luts(ctx.c, &l));
 
     const auto id = imVol->getDims();
-    ctx.check(rtd_set_ct(ctx.c, imVol->getImData(), (int)id.x, (int)id.y, (int)id.z));
     const auto dd = doseVol->getDims();
     ctx.check(rtd_set_dose_grid(ctx.c, (int)dd.x, (int)dd.y, (int)dd.z));
 
@@ -105,7 +104,9 @@ void cudaWrapperProtons(Image* const imVol, Image* const doseVol, std::vector<Be
     }
 
     rtd_timing tm;
-    const rtd_status s = rtd_dose(ctx.c, rb.data(), (int)rb.size(), doseVol->getImData(), &so.opts, &tm);
+    // one call: CT and dose sub-volumes travel inside (the reference uploads / downloads both volumes whole, cu:420-451, 542, 1357)
+    const rtd_status s = rtd_plan_dose(ctx.c, imVol->getImData(), (int)id.x, (int)id.y, (int)id.z, rb.data(), (int)rb.size(),
+                                       doseVol->getImData(), &so.opts, &tm);
     if (s == RTD_ERR_RADIUS) throw std::runtime_error("Found larger than allowed kernel superposition radius");   // cu:965
     ctx.check(s);
     if (so.timing) *so.timing = tm;

@@ -48,6 +48,16 @@ struct TexArr {
     void release() { if (tex) cudaDestroyTextureObject(tex); if (arr) cudaFreeArray(arr); tex = 0; arr = nullptr; }
 };
 
+struct Box { int lo[3], hi[3]; };   // inclusive voxel box (x, y, z)
+inline bool boxInside(const Box& a, const Box& b) {   // a inside b
+    for (int d = 0; d < 3; ++d) if (a.lo[d] < b.lo[d] || a.hi[d] > b.hi[d]) return false;
+    return true;
+}
+inline int64_t boxVoxels(const Box& b) { return int64_t(b.hi[0] - b.lo[0] + 1) * (b.hi[1] - b.lo[1] + 1) * (b.hi[2] - b.lo[2] + 1); }
+
+// Host buffers of a one-call plan (rtd_plan_dose / rtd_dose): only the sub-volumes the plan touches are moved.
+struct HostIo { const float* ct = nullptr; float* dose = nullptr; int64_t h2d = 0, d2h = 0; };
+
 struct BeamWs {
     // geometry / host results
     RayGrid grid; int S = 0, L = 0, R = 0, sx = 0, sy = 0;
@@ -55,6 +65,7 @@ struct BeamWs {
     float dist[2]; Affine gtii, gtdi;
     int bfi = 0, bfo = 0, Zg = 0, nz = 0; bool live = false;
     float entryZ = 0;
+    GridParams gp; bool doTransfer = false; dim3 gpGrid;
     std::vector<LayerParams> layers; std::vector<float> entrySig;   // [2L]
     rtd_beam_report rep; std::vector<rtd_layer_report> lrep;
     // device
@@ -75,6 +86,9 @@ struct BeamWs {
 
 struct rtd_ctx {
     int device = 0; cudaStream_t stream = nullptr;
+    cudaStream_t cstream = nullptr;       // copy stream of the one-call host path (CT / dose-in sub-volumes)
+    bool ctPartial = false;               // the CT array holds only the sub-volumes of the last rtd_plan_dose
+    std::vector<Box> ctBoxes, doseBoxes;  // sub-volumes moved by the current call
     std::string err;
     bool haveLuts = false, haveCt = false, haveDose = false;
     // LUTs (host copies of the small vectors the host logic needs)
@@ -134,29 +148,142 @@ cudaEvent_t ev(rtd_ctx* ctx, size_t i) {
     return ctx->events[i];
 }
 
-rtd_status setCtCommon(rtd_ctx* ctx, const float* src, int nx, int ny, int nz, cudaMemcpyKind kind) {
-    if (!ctx) return RTD_ERR_INVALID;
-    if (!src || nx <= 0 || ny <= 0 || nz <= 0) return fail(ctx, RTD_ERR_INVALID, "rtd_set_ct: null pointer or non-positive dims");
-    RTD_CUDA(cudaSetDevice(ctx->device));
+rtd_status ensureCtArray(rtd_ctx* ctx, int nx, int ny, int nz) {
     if (!ctx->ctTex.arr || ctx->ctDims[0] != nx || ctx->ctDims[1] != ny || ctx->ctDims[2] != nz) {
         RTD_CUDA(cudaStreamSynchronize(ctx->stream));
         ctx->ctTex.release();
+        ctx->haveCt = false;
         cudaChannelFormatDesc fd = cudaCreateChannelDesc<float>();
         RTD_CUDA(cudaMalloc3DArray(&ctx->ctTex.arr, &fd, make_cudaExtent(nx, ny, nz)));
         RTD_CUDA(makeTexture(ctx->ctTex, cudaAddressModeBorder));
         ctx->ctDims[0] = nx; ctx->ctDims[1] = ny; ctx->ctDims[2] = nz;
     }
+    return RTD_OK;
+}
+
+rtd_status setCtCommon(rtd_ctx* ctx, const float* src, int nx, int ny, int nz, cudaMemcpyKind kind) {
+    if (!ctx) return RTD_ERR_INVALID;
+    if (!src || nx <= 0 || ny <= 0 || nz <= 0) return fail(ctx, RTD_ERR_INVALID, "rtd_set_ct: null pointer or non-positive dims");
+    RTD_CUDA(cudaSetDevice(ctx->device));
+    rtd_status s = ensureCtArray(ctx, nx, ny, nz);
+    if (s != RTD_OK) return s;
     cudaMemcpy3DParms cp; memset(&cp, 0, sizeof cp);
     cp.srcPtr = make_cudaPitchedPtr((void*)src, size_t(nx) * 4, nx, ny);
     cp.dstArray = ctx->ctTex.arr; cp.extent = make_cudaExtent(nx, ny, nz); cp.kind = kind;
     RTD_CUDA(cudaMemcpy3DAsync(&cp, ctx->stream));
     RTD_CUDA(cudaStreamSynchronize(ctx->stream));
-    ctx->haveCt = true;
+    ctx->haveCt = true; ctx->ctPartial = false;
     return RTD_OK;
 }
 
+// ---- sub-volume transfers of the one-call host path -------------------------------------------------------
+// Queues a box unless an already queued box contains it (beams overlap around the isocentre).
+void addBox(std::vector<Box>& v, Box b, const int dims[3]) {
+    for (int d = 0; d < 3; ++d) { b.lo[d] = std::max(b.lo[d], 0); b.hi[d] = std::min(b.hi[d], dims[d] - 1); if (b.lo[d] > b.hi[d]) return; }
+    // full rows when most of a row is needed anyway: one contiguous run per row / slice for the copy engine
+    if (int64_t(b.hi[0] - b.lo[0] + 1) * 4 >= int64_t(dims[0]) * 3) { b.lo[0] = 0; b.hi[0] = dims[0] - 1; }
+    for (const Box& o : v) if (boxInside(b, o)) return;
+    v.push_back(b);
+}
+
+// CT boxes that enclose every texel the tracer of this beam can fetch (trace_bev_kernel: pos = start(i,j) + 1/2 + k inc(i,j),
+// density_and_sp_tracer_params.cu:15-17; linear filtering reads floor(pos - 1/2) and the texel after it). start and inc
+// are affine in i and in j, so pos is affine in each of i, j, k separately and its extremes over a box of (i, j, k) are
+// attained at the 8 corners. The frustum is cut into depth segments so that oblique beams do not drag their whole
+// axis-aligned bounding box along.
+void ctBoxesOfBeam(const TraceParams& p, int Rx, int Ry, int S, const int dims[3], std::vector<Box>& out) {
+    const double s1 = 1.0 - double(p.corner.z) / double(p.distX), s2 = 1.0 - double(p.corner.z) / double(p.distY);
+    auto start = [&](int i, int j, double r[3]) {
+        const double I[3] = {p.coefIdxI.x, p.coefIdxI.y, p.coefIdxI.z}, J[3] = {p.coefIdxJ.x, p.coefIdxJ.y, p.coefIdxJ.z}, T[3] = {p.transl.x, p.transl.y, p.transl.z};
+        for (int d = 0; d < 3; ++d) r[d] = T[d] + I[d] * i * s1 + J[d] * j * s2;
+    };
+    auto inc = [&](int i, int j, double r[3]) {
+        const double I[3] = {p.coefIdxI.x, p.coefIdxI.y, p.coefIdxI.z}, J[3] = {p.coefIdxJ.x, p.coefIdxJ.y, p.coefIdxJ.z}, O[3] = {p.coefOffset.x, p.coefOffset.y, p.coefOffset.z};
+        for (int d = 0; d < 3; ++d) r[d] = (O[d] - I[d] * i / double(p.distX) - J[d] * j / double(p.distY)) * double(p.delta.z);
+    };
+    const int segLen = 48;
+    for (int k0 = 0; k0 < S; k0 += segLen) {
+        const int k1 = std::min(k0 + segLen, S - 1);   // segments share their end planes
+        double mn[3] = {1e30, 1e30, 1e30}, mx[3] = {-1e30, -1e30, -1e30};
+        for (int c = 0; c < 8; ++c) {
+            const int i = (c & 1) ? Rx - 1 : 0, j = (c & 2) ? Ry - 1 : 0, k = (c & 4) ? k1 : k0;
+            double st[3], in[3]; start(i, j, st); inc(i, j, in);
+            for (int d = 0; d < 3; ++d) { const double v = st[d] + k * in[d]; mn[d] = std::min(mn[d], v); mx[d] = std::max(mx[d], v); }
+        }
+        Box b; bool finite = true;
+        for (int d = 0; d < 3; ++d) {
+            if (!(std::fabs(mn[d]) < 1e9 && std::fabs(mx[d]) < 1e9)) { finite = false; break; }
+            b.lo[d] = int(std::floor(mn[d])) - 2; b.hi[d] = int(std::floor(mx[d])) + 3;   // texel pair + fp32 accumulation slack
+        }
+        if (!finite) { b.lo[0] = b.lo[1] = b.lo[2] = 0; b.hi[0] = dims[0] - 1; b.hi[1] = dims[1] - 1; b.hi[2] = dims[2] - 1; }
+        addBox(out, b, dims);
+    }
+}
+
+// Dose boxes that enclose every voxel bev_to_grid_kernel can modify for this beam: voxels whose fan index lies within
+// one texel of the haloed BEV volume [-32, Rx+32) x [-32, Ry+32) x [bfi, Zg) (trilinear, border 0), clipped to the
+// kernel's own coverage. fromFan is affine in each fan index separately -> corners suffice.
+void doseBoxesOfBeam(const BeamWs& w, const int dims[3], std::vector<Box>& out) {
+    const GridParams& g = w.gp;
+    Box cover;
+    cover.lo[0] = g.minX; cover.hi[0] = std::min(g.minX + int(w.gpGrid.x) * 32 - 1, g.nx - 1);
+    cover.lo[1] = g.minY; cover.hi[1] = std::min(g.minY + int(w.gpGrid.y) * 8 - 1, g.ny - 1);
+    cover.lo[2] = g.minZ; cover.hi[2] = g.maxZ;
+    const int Rx = w.grid.dimX, Ry = w.grid.dimY;
+    const int segLen = 48;
+    for (int k0 = w.bfi; k0 < w.Zg; k0 += segLen) {
+        const int k1 = std::min(k0 + segLen, w.Zg - 1);
+        float mn[3] = {1e30f, 1e30f, 1e30f}, mx[3] = {-1e30f, -1e30f, -1e30f};
+        for (int c = 0; c < 8; ++c) {
+            const V3 f = v3((c & 1) ? float(Rx + RTD_MAX_SUPERP_R) : -float(RTD_MAX_SUPERP_R + 1), (c & 2) ? float(Ry + RTD_MAX_SUPERP_R) : -float(RTD_MAX_SUPERP_R + 1),
+                            (c & 4) ? float(k1 + 1) : float(k0 - 1));
+            const V3 q = fromFan(w.grid.rayIdxToGantry, w.dist, w.gtdi, f);
+            const float v[3] = {q.x, q.y, q.z};
+            for (int d = 0; d < 3; ++d) { mn[d] = std::min(mn[d], v[d]); mx[d] = std::max(mx[d], v[d]); }
+        }
+        Box b; bool finite = true;
+        for (int d = 0; d < 3; ++d) {
+            if (!(std::fabs(mn[d]) < 1e9f && std::fabs(mx[d]) < 1e9f)) { finite = false; break; }
+            b.lo[d] = std::max(int(std::floor(mn[d])) - 1, cover.lo[d]); b.hi[d] = std::min(int(std::ceil(mx[d])) + 1, cover.hi[d]);
+        }
+        if (!finite) b = cover;
+        addBox(out, b, dims);
+    }
+}
+
+// Sub-volume copies: the host / linear-device side is addressed by offsetting the base pointer (positions stay 0), so only
+// the array side uses cudaPos, in elements.
+cudaError_t copyCtBox(rtd_ctx* ctx, const float* host, const Box& b, cudaStream_t st) {
+    const size_t nx = ctx->ctDims[0], ny = ctx->ctDims[1];
+    const size_t w = b.hi[0] - b.lo[0] + 1, h = b.hi[1] - b.lo[1] + 1, d = b.hi[2] - b.lo[2] + 1;
+    const float* src = host + (size_t(b.lo[2]) * ny + b.lo[1]) * nx + b.lo[0];
+    cudaMemcpy3DParms cp; memset(&cp, 0, sizeof cp);
+    cp.srcPtr = make_cudaPitchedPtr((void*)src, nx * 4, w, ny);
+    cp.dstArray = ctx->ctTex.arr; cp.dstPos = make_cudaPos(b.lo[0], b.lo[1], b.lo[2]);
+    cp.extent = make_cudaExtent(w, h, d);          // an array takes part: extent in elements
+    cp.kind = cudaMemcpyHostToDevice;
+    return cudaMemcpy3DAsync(&cp, st);
+}
+
+cudaError_t copyDoseBox(rtd_ctx* ctx, float* host, float* dev, const Box& b, bool toDevice, cudaStream_t st) {
+    const size_t nx = ctx->doseDims[0], ny = ctx->doseDims[1];
+    const size_t w = b.hi[0] - b.lo[0] + 1, h = b.hi[1] - b.lo[1] + 1, d = b.hi[2] - b.lo[2] + 1;
+    const size_t off = (size_t(b.lo[2]) * ny + b.lo[1]) * nx + b.lo[0];
+    if (w == nx && h == ny) {   // whole slices: one linear copy
+        return toDevice ? cudaMemcpyAsync(dev + off, host + off, d * ny * nx * 4, cudaMemcpyHostToDevice, st)
+                        : cudaMemcpyAsync(host + off, dev + off, d * ny * nx * 4, cudaMemcpyDeviceToHost, st);
+    }
+    cudaMemcpy3DParms cp; memset(&cp, 0, sizeof cp);
+    const cudaPitchedPtr hp = make_cudaPitchedPtr((void*)(host + off), nx * 4, w * 4, ny);
+    const cudaPitchedPtr dp = make_cudaPitchedPtr((void*)(dev + off), nx * 4, w * 4, ny);
+    cp.srcPtr = toDevice ? hp : dp; cp.dstPtr = toDevice ? dp : hp;
+    cp.extent = make_cudaExtent(w * 4, h, d);      // no array: width in bytes
+    cp.kind = toDevice ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost;
+    return cudaMemcpy3DAsync(&cp, st);
+}
+
 // Everything that can be done for a beam before any device result is known (cu:612-663, 766-790).
-rtd_status beamPhaseA(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opts& o, int& launches, cudaStream_t st) {
+rtd_status beamPhaseA(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opts& o, int& launches, cudaStream_t st, HostIo* io, cudaEvent_t evCt) {
     if (b.nLayers <= 0 || b.sx <= 0 || b.sy <= 0 || !b.weights || !b.energies || !b.sigmas)
         return fail(ctx, RTD_ERR_INVALID, "Empty list");   // findMax on an empty vector, vector_find.h:22-25
     if (b.steps == 0 || b.steps > 4095) return fail(ctx, RTD_ERR_INVALID, "beam.steps must be in [1, 4095]");
@@ -184,6 +311,18 @@ rtd_status beamPhaseA(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opts
     memcpy(w.hStage.p, b.weights + size_t(b.sx) * b.sy * w.l0, nW * 4);
     RTD_CUDA(cudaMemcpyAsync(w.spotW.p, w.hStage.p, nW * 4, cudaMemcpyHostToDevice, st));
     const TraceParams tp = makeTraceParams(ctx->densScale, ctx->spScale, b.steps, w.grid.rayIdxToGantry, w.dist, w.gtii);
+    if (io && io->ct) {
+        // one-call host path: upload the CT sub-volumes this beam's tracer samples (copy stream), then let the beam's stream go
+        const size_t n0 = ctx->ctBoxes.size();
+        ctBoxesOfBeam(tp, w.grid.dimX, w.grid.dimY, w.S, ctx->ctDims, ctx->ctBoxes);
+        for (size_t i = n0; i < ctx->ctBoxes.size(); ++i) {
+            RTD_CUDA(copyCtBox(ctx, io->ct, ctx->ctBoxes[i], ctx->cstream));
+            io->h2d += boxVoxels(ctx->ctBoxes[i]) * 4;
+        }
+        RTD_CUDA(cudaEventRecord(evCt, ctx->cstream));
+        RTD_CUDA(cudaStreamWaitEvent(st, evCt, 0));
+    }
+    if (io) io->h2d += int64_t(nW) * 4;
     // weplMin buffer layout: [0]=beamFirstInside, [1]=beamFirstOutside (ints), [2..] weplMin floats
     int* sc = w.weplMin.as<int>();
     trace_bev_kernel<<<w.R / 32, TR_THREADS, 0, st>>>(tp, ctx->ctTex.tex, ctx->densTex.tex, ctx->spTex.tex,
@@ -193,12 +332,12 @@ rtd_status beamPhaseA(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opts
     launches += 2;
     RTD_CUDA(cudaGetLastError());
     RTD_CUDA(cudaMemcpyAsync(w.hTrace.p, w.weplMin.p, size_t(w.S) * 4 + 8, cudaMemcpyDeviceToHost, st));
+    if (io) io->d2h += int64_t(w.S) * 4 + 8;
     return RTD_OK;
 }
 
 // Host logic that needs the tracer's reductions (cu:792-849, 922-925) + all remaining launches of the beam.
-rtd_status beamPhaseB(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opts& o, float* dDose, int& launches,
-                      cudaEvent_t* evs /*6 events: conv, idd, radius, superp, transfer, end*/, cudaStream_t strm) {
+rtd_status beamPhaseB1(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opts& o) {
     const int* sc = w.hTrace.as<int>();
     const float* weplMin = w.hTrace.as<float>() + 2;
     w.bfi = sc[0]; w.bfo = sc[1];
@@ -235,8 +374,40 @@ rtd_status beamPhaseB(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opts
         lr.energyIdx = lp.energyIdx; lr.energyScaleFact = lp.energyScale; lr.peakDepth = lp.peakDepth;
         lr.entrySigmaX = w.entrySig[2 * l]; lr.entrySigmaY = w.entrySig[2 * l + 1]; lr.afterLastStep = lp.afterLast;
     }
+    w.doTransfer = false;
     if (!w.live) return RTD_OK;   // the beam never enters the patient: nothing to add
 
+    // K4 box (cu:1185-1218); the z-range uses Zg instead of beamFirstCalculatedPassive: a superset box that only adds
+    // voxels whose interpolated BEV dose is exactly 0, so the result is identical and no host sync is needed here.
+    const int Rx = w.grid.dimX, Ry = w.grid.dimY;
+    const float xv[2] = {-float(RTD_MAX_SUPERP_R), float(Rx + RTD_MAX_SUPERP_R - 1)};
+    const float yv[2] = {-float(RTD_MAX_SUPERP_R), float(Ry + RTD_MAX_SUPERP_R - 1)};
+    const float zv[2] = {float(w.bfi), float(w.Zg - 1)};
+    V3 mx = v3(-1.f, -1.f, -1.f), mn = v3(100000.f, 100000.f, 100000.f);
+    for (int k = 0; k < 2; ++k) for (int j = 0; j < 2; ++j) for (int i = 0; i < 2; ++i) {
+        const V3 p = fromFan(w.grid.rayIdxToGantry, w.dist, w.gtdi, v3(xv[i], yv[j], zv[k]));
+        mx.x = std::max(mx.x, p.x); mx.y = std::max(mx.y, p.y); mx.z = std::max(mx.z, p.z);
+        mn.x = std::min(mn.x, p.x); mn.y = std::min(mn.y, p.y); mn.z = std::min(mn.z, p.z);
+    }
+    GridParams& gp = w.gp;
+    gp.t = makeTransferParams(w.grid.rayIdxToGantry, w.dist, w.gtdi, v3(float(RTD_MAX_SUPERP_R), float(RTD_MAX_SUPERP_R), -float(w.bfi)));
+    gp.minX = std::max((int(std::floor(mn.x)) / 32) * 32, 0); gp.minY = std::max(int(std::floor(mn.y)), 0); gp.minZ = std::max(int(std::floor(mn.z)), 0);
+    gp.maxX = std::min(int(std::ceil(mx.x)), ctx->doseDims[0] - 1); gp.maxY = std::min(int(std::ceil(mx.y)), ctx->doseDims[1] - 1);
+    gp.maxZ = std::min(int(std::ceil(mx.z)), ctx->doseDims[2] - 1);
+    gp.nx = ctx->doseDims[0]; gp.ny = ctx->doseDims[1]; gp.nz = ctx->doseDims[2];
+    gp.W = Rx + 64; gp.H = Ry + 64; gp.first = w.bfi; gp.zEnd = w.Zg;
+    if (gp.maxX >= gp.minX && gp.maxY >= gp.minY && gp.maxZ >= gp.minZ) {
+        w.doTransfer = true;
+        w.gpGrid = dim3((gp.maxX - gp.minX + 32) / 32, (gp.maxY - gp.minY + 8) / 8);
+    }
+    return RTD_OK;
+}
+
+// All remaining launches of the beam.
+rtd_status beamPhaseB2(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opts& o, float* dDose, int& launches,
+                       cudaEvent_t* evs /*6 events: conv, idd, radius, superp, transfer, end*/, cudaStream_t strm, HostIo* io,
+                       cudaEvent_t evDoseIn, bool& doseInWaited) {
+    if (!w.live) return RTD_OK;
     const int Rx = w.grid.dimX, Ry = w.grid.dimY, R = w.R, L = w.Lc, nz = w.nz;
     const int tilesX = Rx / 32, tilesY = Ry / 8, tiles = tilesX * tilesY;
     const size_t LnzR = size_t(L) * nz * R;
@@ -309,30 +480,12 @@ rtd_status beamPhaseB(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opts
     ks2_kernel<8, KS2_WARPS_8><<<ctx->ks2Blocks8, KS2_WARPS_8 * 32, KS2_SMEM_8, strm>>>(k2, dWork + 2);
     RTD_CUDA(cudaEventRecord(evs[4], strm));
 
-    // K4 (cu:1185-1218); the z-range uses Zg instead of beamFirstCalculatedPassive: a superset box that only adds
-    // voxels whose interpolated BEV dose is exactly 0, so the result is identical and no host sync is needed here.
-    const float xv[2] = {-float(RTD_MAX_SUPERP_R), float(Rx + RTD_MAX_SUPERP_R - 1)};
-    const float yv[2] = {-float(RTD_MAX_SUPERP_R), float(Ry + RTD_MAX_SUPERP_R - 1)};
-    const float zv[2] = {float(w.bfi), float(w.Zg - 1)};
-    V3 mx = v3(-1.f, -1.f, -1.f), mn = v3(100000.f, 100000.f, 100000.f);
-    for (int k = 0; k < 2; ++k) for (int j = 0; j < 2; ++j) for (int i = 0; i < 2; ++i) {
-        const V3 p = fromFan(w.grid.rayIdxToGantry, w.dist, w.gtdi, v3(xv[i], yv[j], zv[k]));
-        mx.x = std::max(mx.x, p.x); mx.y = std::max(mx.y, p.y); mx.z = std::max(mx.z, p.z);
-        mn.x = std::min(mn.x, p.x); mn.y = std::min(mn.y, p.y); mn.z = std::min(mn.z, p.z);
-    }
-    // the dose grid is shared by all beams: transfers are serialised on the context's main stream, in beam order,
-    // each one waiting for its own beam's superposition
+    // K4: the dose grid is shared by all beams: transfers are serialised on the context's main stream, in beam order,
+    // each one waiting for its own beam's superposition (and, on the one-call host path, for the dose-in sub-volumes)
     RTD_CUDA(cudaStreamWaitEvent(ctx->stream, evs[4], 0));
-    GridParams gp;
-    gp.t = makeTransferParams(w.grid.rayIdxToGantry, w.dist, w.gtdi, v3(float(RTD_MAX_SUPERP_R), float(RTD_MAX_SUPERP_R), -float(w.bfi)));
-    gp.minX = std::max((int(std::floor(mn.x)) / 32) * 32, 0); gp.minY = std::max(int(std::floor(mn.y)), 0); gp.minZ = std::max(int(std::floor(mn.z)), 0);
-    gp.maxX = std::min(int(std::ceil(mx.x)), ctx->doseDims[0] - 1); gp.maxY = std::min(int(std::ceil(mx.y)), ctx->doseDims[1] - 1);
-    gp.maxZ = std::min(int(std::ceil(mx.z)), ctx->doseDims[2] - 1);
-    gp.nx = ctx->doseDims[0]; gp.ny = ctx->doseDims[1]; gp.nz = ctx->doseDims[2];
-    gp.W = Rx + 64; gp.H = Ry + 64; gp.first = w.bfi; gp.zEnd = w.Zg;
-    if (gp.maxX >= gp.minX && gp.maxY >= gp.minY && gp.maxZ >= gp.minZ) {
-        dim3 g((gp.maxX - gp.minX + 32) / 32, (gp.maxY - gp.minY + 8) / 8);
-        bev_to_grid_kernel<<<g, 256, 0, ctx->stream>>>(w.bev.as<float>(), dDose, gp);
+    if (w.doTransfer) {
+        if (io && io->dose && !doseInWaited) { RTD_CUDA(cudaStreamWaitEvent(ctx->stream, evDoseIn, 0)); doseInWaited = true; }
+        bev_to_grid_kernel<<<w.gpGrid, 256, 0, ctx->stream>>>(w.bev.as<float>(), dDose, w.gp);
         launches += 1;
     }
     launches += 8;
@@ -341,6 +494,7 @@ rtd_status beamPhaseB(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opts
     // results for the reports: control block + batch radii
     RTD_CUDA(cudaMemcpyAsync(w.hOut.p, w.lfp.p, ctlInts * 4, cudaMemcpyDeviceToHost, strm));
     RTD_CUDA(cudaMemcpyAsync(w.hOut.as<int>() + ctlInts, w.batchRad.p, size_t(L) * 34 * 4, cudaMemcpyDeviceToHost, strm));
+    if (io) { io->h2d += int64_t(L) * (8 + sizeof(LayerParams)); io->d2h += int64_t(ctlInts + size_t(L) * 34) * 4; }
     return RTD_OK;
 }
 
@@ -381,12 +535,17 @@ bool beamFinish(rtd_ctx* ctx, BeamWs& w, int64_t& updates, int64_t& taps) {
     return stats[0] == 0;
 }
 
+constexpr size_t EV_BEAM0 = 8, EV_PER_BEAM = 10;   // events 0..7 are per call; per beam: 0..5 stages, 6 traced, 7 done, 8 CT boxes uploaded
+cudaEvent_t evBeam(rtd_ctx* ctx, int b, int i) { return ev(ctx, EV_BEAM0 + size_t(b) * EV_PER_BEAM + i); }
+
 rtd_status doseCore(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* dDose, const rtd_opts& o, rtd_timing* tm,
-                    cudaEvent_t evBegin, cudaEvent_t evEnd) {
+                    cudaEvent_t evBegin, cudaEvent_t evEnd, HostIo* io) {
     int launches = 0;
     while ((int)ctx->ws.size() < nBeams) ctx->ws.push_back(new BeamWs());
     ctx->nBeamsLast = nBeams; ctx->optsLast = o;
+    ctx->ctBoxes.clear(); ctx->doseBoxes.clear();
     RTD_CUDA(cudaEventRecord(evBegin, ctx->stream));
+    if (io) RTD_CUDA(cudaStreamWaitEvent(ctx->cstream, evBegin, 0));
     // Beams are independent until the transfer into the shared dose grid: unless opts.serialBeams is set every beam runs
     // on its own stream so that the latency-bound stages (tracer, IDD/sigma depth scans) of different beams overlap.
     const bool serial = o.serialBeams != 0 || nBeams == 1;
@@ -399,20 +558,39 @@ rtd_status doseCore(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* dDos
     for (int b = 0; b < nBeams; ++b) {
         cudaStream_t st = beamStream(b);
         if (st != ctx->stream) RTD_CUDA(cudaStreamWaitEvent(st, evBegin, 0));
-        rtd_status s = beamPhaseA(ctx, beams[b], *ctx->ws[b], o, launches, st);
+        rtd_status s = beamPhaseA(ctx, beams[b], *ctx->ws[b], o, launches, st, io, evBeam(ctx, b, 8));
         if (s != RTD_OK) return s;
-        if (st != ctx->stream) { cudaEvent_t e = ev(ctx, 8 + size_t(b) * 8 + 6); RTD_CUDA(cudaEventRecord(e, st)); RTD_CUDA(cudaStreamWaitEvent(ctx->stream, e, 0)); }
+        if (st != ctx->stream) { cudaEvent_t e = evBeam(ctx, b, 6); RTD_CUDA(cudaEventRecord(e, st)); RTD_CUDA(cudaStreamWaitEvent(ctx->stream, e, 0)); }
     }
     cudaEvent_t evTraceEnd = ev(ctx, 2);
     RTD_CUDA(cudaEventRecord(evTraceEnd, ctx->stream));
     RTD_CUDA(cudaStreamSynchronize(ctx->stream));                         // host sync 1 of 2 (covers every beam stream)
     for (int b = 0; b < nBeams; ++b) {
-        cudaEvent_t evs[6];
-        for (int i = 0; i < 6; ++i) evs[i] = ev(ctx, 8 + size_t(b) * 8 + i);
-        cudaStream_t st = beamStream(b);
-        rtd_status s = beamPhaseB(ctx, beams[b], *ctx->ws[b], o, dDose, launches, evs, st);
+        rtd_status s = beamPhaseB1(ctx, beams[b], *ctx->ws[b], o);
         if (s != RTD_OK) return s;
-        if (st != ctx->stream) { cudaEvent_t e = ev(ctx, 8 + size_t(b) * 8 + 7); RTD_CUDA(cudaEventRecord(e, st)); RTD_CUDA(cudaStreamWaitEvent(ctx->stream, e, 0)); }
+    }
+    cudaEvent_t evDoseIn = ev(ctx, 6);
+    if (io && io->dose) {
+        // dose-in sub-volumes (accumulate semantics, cu:542) on the copy stream while the beams compute; every box is
+        // uploaded before the first transfer, so overlapping boxes of different beams are harmless
+        for (int b = 0; b < nBeams; ++b) if (ctx->ws[b]->doTransfer) doseBoxesOfBeam(*ctx->ws[b], ctx->doseDims, ctx->doseBoxes);
+        for (const Box& bx : ctx->doseBoxes) { RTD_CUDA(copyDoseBox(ctx, io->dose, dDose, bx, true, ctx->cstream)); io->h2d += boxVoxels(bx) * 4; }
+        RTD_CUDA(cudaEventRecord(evDoseIn, ctx->cstream));
+    }
+    bool doseInWaited = false;
+    for (int b = 0; b < nBeams; ++b) {
+        cudaEvent_t evs[6];
+        for (int i = 0; i < 6; ++i) evs[i] = evBeam(ctx, b, i);
+        cudaStream_t st = beamStream(b);
+        rtd_status s = beamPhaseB2(ctx, beams[b], *ctx->ws[b], o, dDose, launches, evs, st, io, evDoseIn, doseInWaited);
+        if (s != RTD_OK) return s;
+        if (st != ctx->stream) { cudaEvent_t e = evBeam(ctx, b, 7); RTD_CUDA(cudaEventRecord(e, st)); RTD_CUDA(cudaStreamWaitEvent(ctx->stream, e, 0)); }
+    }
+    cudaEvent_t evXferEnd = ev(ctx, 7);
+    RTD_CUDA(cudaEventRecord(evXferEnd, ctx->stream));
+    if (io && io->dose) {
+        if (!doseInWaited) RTD_CUDA(cudaStreamWaitEvent(ctx->stream, evDoseIn, 0));
+        for (const Box& bx : ctx->doseBoxes) { RTD_CUDA(copyDoseBox(ctx, io->dose, dDose, bx, false, ctx->stream)); io->d2h += boxVoxels(bx) * 4; }
     }
     RTD_CUDA(cudaEventRecord(evEnd, ctx->stream));
     RTD_CUDA(cudaStreamSynchronize(ctx->stream));                         // host sync 2 of 2
@@ -426,7 +604,8 @@ rtd_status doseCore(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* dDos
         cudaEvent_t prev = evTraceEnd;
         for (int b = 0; b < nBeams; ++b) {
             if (!ctx->ws[b]->live) continue;
-            cudaEvent_t* e = &ctx->events[8 + size_t(b) * 8];
+            cudaEvent_t e[6];
+            for (int i = 0; i < 6; ++i) e[i] = evBeam(ctx, b, i);
             cudaEventElapsedTime(&ms, prev, e[0]); tm->msSetup += std::max(ms, 0.0f);
             cudaEventElapsedTime(&ms, e[0], e[1]); tm->msConv += ms;
             cudaEventElapsedTime(&ms, e[1], e[2]); tm->msIddSigma += ms;
@@ -436,6 +615,11 @@ rtd_status doseCore(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* dDos
             prev = serial ? e[5] : evTraceEnd;
         }
         cudaEventElapsedTime(&ms, evBegin, evEnd); tm->msTotal = ms;
+        if (io) {
+            if (io->ct && nBeams > 0) { cudaEventElapsedTime(&ms, evBegin, evBeam(ctx, nBeams - 1, 8)); tm->msUpload = ms; }
+            if (io->dose) { cudaEventElapsedTime(&ms, evXferEnd, evEnd); tm->msDownload = ms; }
+            tm->h2dBytes = io->h2d; tm->d2hBytes = io->d2h;
+        }
     }
     if (!ok) return fail(ctx, RTD_ERR_RADIUS, "Found larger than allowed kernel superposition radius");
     return RTD_OK;
@@ -465,6 +649,7 @@ rtd_status rtd_create(rtd_ctx** out, int device) {
     rtd_ctx* ctx = new rtd_ctx();
     ctx->device = device;
     if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return RTD_ERR_CUDA; }
+    if (cudaStreamCreateWithFlags(&ctx->cstream, cudaStreamNonBlocking) != cudaSuccess) { cudaStreamDestroy(ctx->stream); delete ctx; return RTD_ERR_CUDA; }
     cudaDeviceGetAttribute(&ctx->smCount, cudaDevAttrMultiProcessorCount, device);
     rtd_default_opts(&ctx->optsLast);
     cudaFuncSetAttribute(ks_kernel<KS_NT_C, 17, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)KS_SMEM_C);
@@ -488,6 +673,7 @@ void rtd_destroy(rtd_ctx* ctx) {
     ctx->dose.release();
     for (cudaEvent_t e : ctx->events) cudaEventDestroy(e);
     for (cudaStream_t s_ : ctx->bstreams) { cudaStreamSynchronize(s_); cudaStreamDestroy(s_); }
+    cudaStreamSynchronize(ctx->cstream); cudaStreamDestroy(ctx->cstream);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -535,6 +721,7 @@ rtd_status rtd_set_dose_grid(rtd_ctx* ctx, int nx, int ny, int nz) {
 static rtd_status checkReady(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, const void* dose) {
     if (!ctx) return RTD_ERR_INVALID;
     if (!ctx->haveLuts || !ctx->haveCt || !ctx->haveDose) return fail(ctx, RTD_ERR_STATE, "rtd_dose: LUTs, CT and dose grid must be set first");
+    if (ctx->ctPartial) return fail(ctx, RTD_ERR_STATE, "rtd_dose: the CT is only partially resident after rtd_plan_dose; call rtd_set_ct again");
     if (nBeams < 0 || (nBeams > 0 && !beams) || !dose) return fail(ctx, RTD_ERR_INVALID, "rtd_dose: bad beams / dose pointer");
     return RTD_OK;
 }
@@ -544,33 +731,50 @@ rtd_status rtd_dose_device(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, floa
     if (s != RTD_OK) return s;
     RTD_CUDA(cudaSetDevice(ctx->device));
     rtd_opts o; if (opts) o = *opts; else rtd_default_opts(&o);
-    return doseCore(ctx, beams, nBeams, dDose, o, tm, ev(ctx, 0), ev(ctx, 1));
+    return doseCore(ctx, beams, nBeams, dDose, o, tm, ev(ctx, 0), ev(ctx, 1), nullptr);
+}
+
+// Host dose buffer: only the sub-volumes the beams can modify travel (see rtd_plan_dose in rtdose.h).
+static rtd_status doseHost(rtd_ctx* ctx, const float* ct, const rtd_beam* beams, int nBeams, float* dose, float* dDose, const rtd_opts* opts, rtd_timing* tm) {
+    rtd_opts o; if (opts) o = *opts; else rtd_default_opts(&o);
+    HostIo io; io.ct = ct; io.dose = dose;
+    if (dose) {
+        const size_t n = size_t(ctx->doseDims[0]) * ctx->doseDims[1] * ctx->doseDims[2];
+        RTD_CUDA(ctx->dose.ensure(n * 4));
+        dDose = ctx->dose.as<float>();
+    }
+    rtd_status s = doseCore(ctx, beams, nBeams, dDose, o, tm, ev(ctx, 0), ev(ctx, 1), &io);
+    if (s != RTD_OK) { cudaStreamSynchronize(ctx->cstream); cudaStreamSynchronize(ctx->stream); }
+    return s;
 }
 
 rtd_status rtd_dose(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* dose, const rtd_opts* opts, rtd_timing* tm) {
     rtd_status s = checkReady(ctx, beams, nBeams, dose);
     if (s != RTD_OK) return s;
     RTD_CUDA(cudaSetDevice(ctx->device));
-    rtd_opts o; if (opts) o = *opts; else rtd_default_opts(&o);
-    const size_t n = size_t(ctx->doseDims[0]) * ctx->doseDims[1] * ctx->doseDims[2];
-    RTD_CUDA(ctx->dose.ensure(n * 4));
-    cudaEvent_t e0 = ev(ctx, 3), e1 = ev(ctx, 4), e2 = ev(ctx, 5);
-    RTD_CUDA(cudaEventRecord(e0, ctx->stream));
-    RTD_CUDA(cudaMemcpyAsync(ctx->dose.p, dose, n * 4, cudaMemcpyHostToDevice, ctx->stream));   // accumulate semantics, cu:542
-    s = doseCore(ctx, beams, nBeams, ctx->dose.as<float>(), o, tm, ev(ctx, 0), ev(ctx, 1));
+    return doseHost(ctx, nullptr, beams, nBeams, dose, nullptr, opts, tm);
+}
+
+static rtd_status planDose(rtd_ctx* ctx, const float* ct, int nx, int ny, int nz, const rtd_beam* beams, int nBeams, float* dose, float* dDose,
+                           const rtd_opts* opts, rtd_timing* tm) {
+    if (!ctx) return RTD_ERR_INVALID;
+    if (!ct || nx <= 0 || ny <= 0 || nz <= 0) return fail(ctx, RTD_ERR_INVALID, "rtd_plan_dose: null CT pointer or non-positive dims");
+    if (!ctx->haveLuts || !ctx->haveDose) return fail(ctx, RTD_ERR_STATE, "rtd_plan_dose: LUTs and dose grid must be set first");
+    if (nBeams < 0 || (nBeams > 0 && !beams) || (!dose && !dDose)) return fail(ctx, RTD_ERR_INVALID, "rtd_plan_dose: bad beams / dose pointer");
+    RTD_CUDA(cudaSetDevice(ctx->device));
+    rtd_status s = ensureCtArray(ctx, nx, ny, nz);
     if (s != RTD_OK) return s;
-    RTD_CUDA(cudaEventRecord(e1, ctx->stream));
-    RTD_CUDA(cudaMemcpyAsync(dose, ctx->dose.p, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
-    RTD_CUDA(cudaEventRecord(e2, ctx->stream));
-    RTD_CUDA(cudaStreamSynchronize(ctx->stream));
-    if (tm) {
-        float ms = 0;
-        cudaEventElapsedTime(&ms, e0, ev(ctx, 0)); tm->msUpload = ms;
-        cudaEventElapsedTime(&ms, e1, e2); tm->msDownload = ms;
-        cudaEventElapsedTime(&ms, e0, e2); tm->msTotal = ms;
-        tm->hostSyncs += 1;
-    }
-    return RTD_OK;
+    ctx->haveCt = true; ctx->ctPartial = true;
+    return doseHost(ctx, ct, beams, nBeams, dose, dDose, opts, tm);
+}
+
+rtd_status rtd_plan_dose(rtd_ctx* ctx, const float* ct, int nx, int ny, int nz, const rtd_beam* beams, int nBeams, float* dose,
+                         const rtd_opts* opts, rtd_timing* tm) {
+    return planDose(ctx, ct, nx, ny, nz, beams, nBeams, dose, nullptr, opts, tm);
+}
+rtd_status rtd_plan_dose_device(rtd_ctx* ctx, const float* ct, int nx, int ny, int nz, const rtd_beam* beams, int nBeams, float* dDose,
+                                const rtd_opts* opts, rtd_timing* tm) {
+    return planDose(ctx, ct, nx, ny, nz, beams, nBeams, nullptr, dDose, opts, tm);
 }
 
 rtd_status rtd_get_beam_report(const rtd_ctx* ctx, int beamNo, rtd_beam_report* out) {

@@ -54,7 +54,7 @@ class RtdTiming(C.Structure):
     _fields_ = [("msTotal", C.c_float), ("msUpload", C.c_float), ("msTrace", C.c_float), ("msSetup", C.c_float),
                 ("msConv", C.c_float), ("msIddSigma", C.c_float), ("msRadius", C.c_float), ("msSuperp", C.c_float),
                 ("msTransfer", C.c_float), ("msDownload", C.c_float), ("updates", C.c_int64), ("ksTaps", C.c_int64),
-                ("kernelLaunches", C.c_int), ("hostSyncs", C.c_int)]
+                ("kernelLaunches", C.c_int), ("hostSyncs", C.c_int), ("h2dBytes", C.c_int64), ("d2hBytes", C.c_int64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -91,7 +91,7 @@ class RtdError(RuntimeError):
 
 
 EXPORTS = ["rtd_default_opts", "rtd_create", "rtd_destroy", "rtd_last_error", "rtd_version", "rtd_set_luts", "rtd_set_ct",
-           "rtd_set_ct_device", "rtd_set_dose_grid", "rtd_dose", "rtd_dose_device", "rtd_get_beam_report",
+           "rtd_set_ct_device", "rtd_set_dose_grid", "rtd_dose", "rtd_dose_device", "rtd_plan_dose", "rtd_plan_dose_device", "rtd_get_beam_report",
            "rtd_get_layer_report", "rtd_debug_fetch", "rtd_stream"]
 
 _lib = None
@@ -118,6 +118,9 @@ def load_library() -> C.CDLL:
     lib.rtd_set_dose_grid.argtypes = [vp, C.c_int, C.c_int, C.c_int]; lib.rtd_set_dose_grid.restype = C.c_int
     lib.rtd_dose.argtypes = [vp, C.POINTER(RtdBeam), C.c_int, vp, C.POINTER(RtdOpts), C.POINTER(RtdTiming)]; lib.rtd_dose.restype = C.c_int
     lib.rtd_dose_device.argtypes = lib.rtd_dose.argtypes; lib.rtd_dose_device.restype = C.c_int
+    lib.rtd_plan_dose.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.POINTER(RtdBeam), C.c_int, vp, C.POINTER(RtdOpts), C.POINTER(RtdTiming)]
+    lib.rtd_plan_dose.restype = C.c_int
+    lib.rtd_plan_dose_device.argtypes = lib.rtd_plan_dose.argtypes; lib.rtd_plan_dose_device.restype = C.c_int
     lib.rtd_get_beam_report.argtypes = [vp, C.c_int, C.POINTER(RtdBeamReport)]; lib.rtd_get_beam_report.restype = C.c_int
     lib.rtd_get_layer_report.argtypes = [vp, C.c_int, C.c_int, C.POINTER(RtdLayerReport)]; lib.rtd_get_layer_report.restype = C.c_int
     lib.rtd_debug_fetch.argtypes = [vp, C.c_int, C.c_int, C.c_int, vp, C.c_size_t]; lib.rtd_debug_fetch.restype = C.c_int
@@ -231,6 +234,24 @@ class DoseEngine:
         self._check(fn(self._h, packed, n_beams, C.c_void_p(ptr), C.byref(self.opts), C.byref(self.timing)))
         return self.timing
 
+    def plan_dose(self, ct: np.ndarray, beams: Sequence[Beam], dose: np.ndarray) -> RtdTiming:
+        """One-call equivalent of cudaWrapperProtons: HOST CT ([nz][ny][nx] float32 HU+1000) and HOST dose (accumulated
+        in place); only the sub-volumes the plan touches are copied (rtd_plan_dose). Needs set_luts + set_dose_grid."""
+        if dose.dtype != np.float32 or not dose.flags["C_CONTIGUOUS"]:
+            raise ValueError("dose must be a C-contiguous float32 array")
+        ct = _f32(ct)
+        nz, ny, nx = ct.shape
+        arr, keep = pack_beams(beams)
+        self._check(self.lib.rtd_plan_dose(self._h, ct.ctypes.data, nx, ny, nz, arr, len(beams), dose.ctypes.data,
+                                           C.byref(self.opts), C.byref(self.timing)))
+        return self.timing
+
+    def plan_dose_ptr(self, ct_ptr: int, nx: int, ny: int, nz: int, packed, n_beams: int, dose_ptr: int, device: bool = False) -> RtdTiming:
+        fn = self.lib.rtd_plan_dose_device if device else self.lib.rtd_plan_dose
+        self._check(fn(self._h, C.c_void_p(ct_ptr), nx, ny, nz, packed, n_beams, C.c_void_p(dose_ptr),
+                                           C.byref(self.opts), C.byref(self.timing)))
+        return self.timing
+
     def beam_report(self, beam_no: int) -> dict:
         r = RtdBeamReport()
         self._check(self.lib.rtd_get_beam_report(self._h, beam_no, C.byref(r)))
@@ -269,10 +290,9 @@ def cuda_wrapper_protons(im_vol: np.ndarray, dose_vol: np.ndarray, beams: List[B
     eng = engine or DoseEngine(device)
     try:
         eng.set_luts(idd_data)
-        eng.set_ct(im_vol)
         nz, ny, nx = dose_vol.shape
         eng.set_dose_grid(nx, ny, nz)
-        t = eng.dose(beams, dose_vol)
+        t = eng.plan_dose(im_vol, beams, dose_vol)
         if out_stream is not None:
             out_stream.write(f"    Total global execution time (excluding GPU initialisation): {t.msTotal} ms.\n\n")
         return t

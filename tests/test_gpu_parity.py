@@ -215,3 +215,55 @@ def test_edge_cases(eng, mini_case):
     # the context stays usable after an error
     d, _ = run_case(eng, mini_case)
     assert d.max() > 0
+
+
+@pytest.mark.parametrize("name", ["mini", "c2", "c3"])
+def test_one_call_host_path_moves_sub_volumes_only_and_matches(eng, name):
+    """rtd_plan_dose (the cudaWrapperProtons-shaped call) uploads only the CT boxes the tracers sample and moves only the
+    dose boxes the transfers touch. Against the dense path (whole CT resident, device dose buffer): tracer outputs
+    bit-identical, the same set of voxels modified, dose equal up to fp32 atomic order. The device CT array and the
+    context's dose buffer are poisoned with NaN first so that any texel / voxel outside the boxes would show."""
+    import torch
+    case = cases.make_case(name) if name != "mini" else cases.make_case("mini")
+    nx, ny, nz = case.dose_dims
+    rng = np.random.default_rng(5)
+    din = (rng.random((nz, ny, nx), dtype=np.float32) * 1.0e-7).astype(np.float32)
+    eng.set_luts(case.luts); eng.set_dose_grid(nx, ny, nz)
+    # dense path
+    eng.set_ct(case.ct)
+    packed, keep = engine.pack_beams(case.beams)
+    d = torch.from_numpy(din).to("cuda:0")
+    eng.dose_ptr(packed, len(case.beams), d.data_ptr(), device=True)
+    dense_acc = d.cpu().numpy()
+    d.zero_()
+    eng.dose_ptr(packed, len(case.beams), d.data_ptr(), device=True)
+    dense = d.cpu().numpy()
+    wepl = [eng.fetch(b, "wepl") for b in range(len(case.beams))]
+    fin = [eng.fetch(b, "first_inside") for b in range(len(case.beams))]
+    # poison: NaN CT resident, NaN left behind in the context's dose buffer by a first one-call run
+    nan_dose = np.full((nz, ny, nx), np.nan, np.float32)
+    eng.plan_dose(case.ct, case.beams, nan_dose)
+    eng.set_ct(np.full_like(case.ct, np.nan))
+    # one-call path, beam by beam (accumulating) and then the whole plan
+    step = din.copy()
+    for b in case.beams:
+        t = eng.plan_dose(case.ct, [b], step)
+        assert 0 < t.h2dBytes and 0 < t.d2hBytes
+    whole = np.zeros_like(din)
+    t = eng.plan_dose(case.ct, case.beams, whole)
+    for b in range(len(case.beams)):
+        assert bits_equal(eng.fetch(b, "wepl"), wepl[b])
+        assert np.array_equal(eng.fetch(b, "first_inside"), fin[b])
+    assert np.isfinite(whole).all() and np.isfinite(step).all()
+    assert np.array_equal(whole != 0, dense != 0)          # exactly the same voxels receive dose
+    assert rel_to_max(whole, dense)[0] <= 2e-6
+    assert rel_to_max(step, dense_acc)[0] <= 5e-6
+    untouched = dense == 0
+    assert np.array_equal(step[untouched], din[untouched])   # the caller's content survives where no beam adds dose
+    # fewer bytes than the dense host path, which moves 2 volumes up and 1 down
+    if name == "c3":
+        assert t.h2dBytes < 0.6 * 2 * din.nbytes and t.d2hBytes < 0.6 * din.nbytes
+    # a partially resident CT must not be reused silently
+    with pytest.raises(engine.RtdError) as ei:
+        eng.dose(case.beams, whole)
+    assert ei.value.status == 4
