@@ -88,7 +88,9 @@ typedef struct {
     int   keepIntermediates; /* 1: keep per-beam BEV arrays of every layer for rtd_debug_fetch */
     int   serialBeams;       /* 1: run the beams one after the other on one stream (stage timings then do not overlap);
                                 0 (default): one stream per beam, transfers into the dose grid serialised in beam order */
-    int   reserved[3];
+    int   noZeroCopyDose;    /* 0 (default): a PINNED host dose grid is accumulated in place by the transfer kernels (only voxels
+                                that receive dose cross PCIe); 1: always stage dose sub-volumes through device memory */
+    int   reserved[2];
 } rtd_opts;
 
 /* Stage timing of the last rtd_dose* call (CUDA events; with concurrent beams the per-stage figures are sums over the
@@ -111,6 +113,7 @@ typedef struct {
     int     hostSyncs;
     int64_t h2dBytes;    /* bytes copied host->device inside the call (CT sub-volumes, dose-in sub-volumes, weights, parameters) */
     int64_t d2hBytes;    /* bytes copied device->host inside the call (dose sub-volumes, reductions, reports) */
+    int64_t doseVoxelsModified;   /* dose-grid voxels that received dose (summed over beams) */
 } rtd_timing;
 
 typedef struct {

@@ -559,10 +559,12 @@ __device__ __forceinline__ float bev_plane(const float* __restrict__ pl, const G
 }
 
 __global__ void __launch_bounds__(256)
-bev_to_grid_kernel(const float* __restrict__ bev, float* __restrict__ dose, const GridParams g) {
+bev_to_grid_kernel(const float* __restrict__ bev, float* __restrict__ dose, const GridParams g, unsigned long long* __restrict__ modified) {
     const int x = g.minX + blockIdx.x * 32 + (threadIdx.x & 31);
     const int y = g.minY + blockIdx.y * 8 + (threadIdx.x >> 5);
-    if (x >= g.nx || y >= g.ny) return;
+    if (y >= g.ny) return;               // warp-uniform (a warp is one row of 32 x)
+    const bool inside = x < g.nx;
+    unsigned nMod = 0;
     // init(i,j) (transfer_param_struct_div3.cu:22-25)
     const float fi = i2f(x), fj = i2f(y);
     const float sx = f_add(f_fma(g.t.coefIdxI.x, fi, f_mul(g.t.coefIdxJ.x, fj)), g.t.coefOffset.x);
@@ -573,7 +575,7 @@ bev_to_grid_kernel(const float* __restrict__ bev, float* __restrict__ dose, cons
     const size_t plane = (size_t)g.W * g.H;
     const int D = g.zEnd - g.first;
     const float* base = bev + (size_t)g.first * plane;
-    for (int z = g.minZ; z <= g.maxZ; ++z, res += zs) {
+    for (int z = inside ? g.minZ : g.maxZ + 1; z <= g.maxZ; ++z, res += zs) {
         // getFanIdx(k) (cu:27-34) + HALF
         const float fk = i2f(z);
         const float rx = f_fma(g.t.inc.x, fk, sx), ry = f_fma(g.t.inc.y, fk, sy), rz = f_fma(g.t.inc.z, fk, sz);
@@ -591,7 +593,12 @@ bev_to_grid_kernel(const float* __restrict__ bev, float* __restrict__ dose, cons
         if ((unsigned)iz < (unsigned)D && c != 256) acc = bev_plane(base + (size_t)iz * plane, g, ix, iy, a, b, 256 - c);
         if ((unsigned)(iz + 1) < (unsigned)D && c != 0) acc += bev_plane(base + (size_t)(iz + 1) * plane, g, ix, iy, a, b, c);
         const float v = acc * (1.0f / 256.0f);
-        if (v > 0.0f) *res += v;
+        if (v > 0.0f) { *res += v; ++nMod; }
+    }
+    // voxels modified by this launch (the bytes a host-resident dose grid exchanges over PCIe): one atomic per warp
+    if (modified) {
+        nMod = __reduce_add_sync(0xffffffffu, nMod);
+        if ((threadIdx.x & 31) == 0 && nMod) atomicAdd(modified, (unsigned long long)nMod);
     }
 }
 

@@ -56,7 +56,7 @@ inline bool boxInside(const Box& a, const Box& b) {   // a inside b
 inline int64_t boxVoxels(const Box& b) { return int64_t(b.hi[0] - b.lo[0] + 1) * (b.hi[1] - b.lo[1] + 1) * (b.hi[2] - b.lo[2] + 1); }
 
 // Host buffers of a one-call plan (rtd_plan_dose / rtd_dose): only the sub-volumes the plan touches are moved.
-struct HostIo { const float* ct = nullptr; float* dose = nullptr; int64_t h2d = 0, d2h = 0; };
+struct HostIo { const float* ct = nullptr; float* dose = nullptr; bool zeroCopy = false; int64_t h2d = 0, d2h = 0; };
 
 struct BeamWs {
     // geometry / host results
@@ -89,6 +89,7 @@ struct rtd_ctx {
     cudaStream_t cstream = nullptr;       // copy stream of the one-call host path (CT / dose-in sub-volumes)
     bool ctPartial = false;               // the CT array holds only the sub-volumes of the last rtd_plan_dose
     std::vector<Box> ctBoxes, doseBoxes;  // sub-volumes moved by the current call
+    DevBuf xferCount; PinBuf hXferCount;  // dose voxels modified by the transfers of the current call
     std::string err;
     bool haveLuts = false, haveCt = false, haveDose = false;
     // LUTs (host copies of the small vectors the host logic needs)
@@ -484,8 +485,8 @@ rtd_status beamPhaseB2(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opt
     // each one waiting for its own beam's superposition (and, on the one-call host path, for the dose-in sub-volumes)
     RTD_CUDA(cudaStreamWaitEvent(ctx->stream, evs[4], 0));
     if (w.doTransfer) {
-        if (io && io->dose && !doseInWaited) { RTD_CUDA(cudaStreamWaitEvent(ctx->stream, evDoseIn, 0)); doseInWaited = true; }
-        bev_to_grid_kernel<<<w.gpGrid, 256, 0, ctx->stream>>>(w.bev.as<float>(), dDose, w.gp);
+        if (io && io->dose && !io->zeroCopy && !doseInWaited) { RTD_CUDA(cudaStreamWaitEvent(ctx->stream, evDoseIn, 0)); doseInWaited = true; }
+        bev_to_grid_kernel<<<w.gpGrid, 256, 0, ctx->stream>>>(w.bev.as<float>(), dDose, w.gp, ctx->xferCount.as<unsigned long long>());
         launches += 1;
     }
     launches += 8;
@@ -544,7 +545,9 @@ rtd_status doseCore(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* dDos
     while ((int)ctx->ws.size() < nBeams) ctx->ws.push_back(new BeamWs());
     ctx->nBeamsLast = nBeams; ctx->optsLast = o;
     ctx->ctBoxes.clear(); ctx->doseBoxes.clear();
+    RTD_CUDA(ctx->xferCount.ensure(8)); RTD_CUDA(ctx->hXferCount.ensure(8));
     RTD_CUDA(cudaEventRecord(evBegin, ctx->stream));
+    RTD_CUDA(cudaMemsetAsync(ctx->xferCount.p, 0, 8, ctx->stream));
     if (io) RTD_CUDA(cudaStreamWaitEvent(ctx->cstream, evBegin, 0));
     // Beams are independent until the transfer into the shared dose grid: unless opts.serialBeams is set every beam runs
     // on its own stream so that the latency-bound stages (tracer, IDD/sigma depth scans) of different beams overlap.
@@ -570,7 +573,7 @@ rtd_status doseCore(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* dDos
         if (s != RTD_OK) return s;
     }
     cudaEvent_t evDoseIn = ev(ctx, 6);
-    if (io && io->dose) {
+    if (io && io->dose && !io->zeroCopy) {
         // dose-in sub-volumes (accumulate semantics, cu:542) on the copy stream while the beams compute; every box is
         // uploaded before the first transfer, so overlapping boxes of different beams are harmless
         for (int b = 0; b < nBeams; ++b) if (ctx->ws[b]->doTransfer) doseBoxesOfBeam(*ctx->ws[b], ctx->doseDims, ctx->doseBoxes);
@@ -588,7 +591,8 @@ rtd_status doseCore(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* dDos
     }
     cudaEvent_t evXferEnd = ev(ctx, 7);
     RTD_CUDA(cudaEventRecord(evXferEnd, ctx->stream));
-    if (io && io->dose) {
+    RTD_CUDA(cudaMemcpyAsync(ctx->hXferCount.p, ctx->xferCount.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    if (io && io->dose && !io->zeroCopy) {
         if (!doseInWaited) RTD_CUDA(cudaStreamWaitEvent(ctx->stream, evDoseIn, 0));
         for (const Box& bx : ctx->doseBoxes) { RTD_CUDA(copyDoseBox(ctx, io->dose, dDose, bx, false, ctx->stream)); io->d2h += boxVoxels(bx) * 4; }
     }
@@ -596,6 +600,8 @@ rtd_status doseCore(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* dDos
     RTD_CUDA(cudaStreamSynchronize(ctx->stream));                         // host sync 2 of 2
     int64_t updates = 0, taps = 0; bool ok = true;
     for (int b = 0; b < nBeams; ++b) ok = beamFinish(ctx, *ctx->ws[b], updates, taps) && ok;
+    const int64_t modified = (int64_t)*ctx->hXferCount.as<unsigned long long>();
+    if (io && io->dose && io->zeroCopy) { io->h2d += modified * 4; io->d2h += modified * 4; }   // the transfers read-modify-write the caller's pinned grid in place
     if (tm) {
         memset(tm, 0, sizeof *tm);
         tm->updates = updates; tm->ksTaps = taps; tm->kernelLaunches = launches; tm->hostSyncs = 2;
@@ -620,6 +626,7 @@ rtd_status doseCore(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* dDos
             if (io->dose) { cudaEventElapsedTime(&ms, evXferEnd, evEnd); tm->msDownload = ms; }
             tm->h2dBytes = io->h2d; tm->d2hBytes = io->d2h;
         }
+        tm->doseVoxelsModified = modified;
     }
     if (!ok) return fail(ctx, RTD_ERR_RADIUS, "Found larger than allowed kernel superposition radius");
     return RTD_OK;
@@ -670,7 +677,7 @@ void rtd_destroy(rtd_ctx* ctx) {
     cudaStreamSynchronize(ctx->stream);
     for (BeamWs* w : ctx->ws) { w->release(); delete w; }
     ctx->iddTex.release(); ctx->densTex.release(); ctx->spTex.release(); ctx->rrlTex.release(); ctx->ctTex.release();
-    ctx->dose.release();
+    ctx->dose.release(); ctx->xferCount.release(); ctx->hXferCount.release();
     for (cudaEvent_t e : ctx->events) cudaEventDestroy(e);
     for (cudaStream_t s_ : ctx->bstreams) { cudaStreamSynchronize(s_); cudaStreamDestroy(s_); }
     cudaStreamSynchronize(ctx->cstream); cudaStreamDestroy(ctx->cstream);
@@ -740,8 +747,20 @@ static rtd_status doseHost(rtd_ctx* ctx, const float* ct, const rtd_beam* beams,
     HostIo io; io.ct = ct; io.dose = dose;
     if (dose) {
         const size_t n = size_t(ctx->doseDims[0]) * ctx->doseDims[1] * ctx->doseDims[2];
-        RTD_CUDA(ctx->dose.ensure(n * 4));
-        dDose = ctx->dose.as<float>();
+        // Pinned (cudaHostAlloc / cudaHostRegister, as HostPinnedImage3D does, host_image_3d.cuh:24) dose grids are
+        // accumulated IN PLACE over PCIe by the transfer kernels: only voxels that receive dose are read and written,
+        // in the reference's summation order ((dose + beam0) + beam1 ...). Pageable grids go through sub-volume copies.
+        float* mapped = nullptr;
+        if (!o.noZeroCopyDose) {
+            cudaPointerAttributes a0, a1;
+            if (cudaPointerGetAttributes(&a0, dose) == cudaSuccess && cudaPointerGetAttributes(&a1, dose + (n - 1)) == cudaSuccess &&
+                a0.type == cudaMemoryTypeHost && a1.type == cudaMemoryTypeHost && a0.devicePointer &&
+                (char*)a1.devicePointer - (char*)a0.devicePointer == (ptrdiff_t)((n - 1) * 4))
+                mapped = (float*)a0.devicePointer;
+            cudaGetLastError();
+        }
+        if (mapped) { io.zeroCopy = true; dDose = mapped; }
+        else { RTD_CUDA(ctx->dose.ensure(n * 4)); dDose = ctx->dose.as<float>(); }
     }
     rtd_status s = doseCore(ctx, beams, nBeams, dDose, o, tm, ev(ctx, 0), ev(ctx, 1), &io);
     if (s != RTD_OK) { cudaStreamSynchronize(ctx->cstream); cudaStreamSynchronize(ctx->stream); }

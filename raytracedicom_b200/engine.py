@@ -47,14 +47,15 @@ class RtdBeam(C.Structure):
 class RtdOpts(C.Structure):
     _fields_ = [("bpDepthCutoff", C.c_float), ("convSigmaCutoff", C.c_float), ("ksSigmaCutoff", C.c_float),
                 ("rayWeightCutoff", C.c_float), ("minTilesInBatch", C.c_int), ("keepIntermediates", C.c_int),
-                ("serialBeams", C.c_int), ("reserved", C.c_int * 3)]
+                ("serialBeams", C.c_int), ("noZeroCopyDose", C.c_int), ("reserved", C.c_int * 2)]
 
 
 class RtdTiming(C.Structure):
     _fields_ = [("msTotal", C.c_float), ("msUpload", C.c_float), ("msTrace", C.c_float), ("msSetup", C.c_float),
                 ("msConv", C.c_float), ("msIddSigma", C.c_float), ("msRadius", C.c_float), ("msSuperp", C.c_float),
                 ("msTransfer", C.c_float), ("msDownload", C.c_float), ("updates", C.c_int64), ("ksTaps", C.c_int64),
-                ("kernelLaunches", C.c_int), ("hostSyncs", C.c_int), ("h2dBytes", C.c_int64), ("d2hBytes", C.c_int64)]
+                ("kernelLaunches", C.c_int), ("hostSyncs", C.c_int), ("h2dBytes", C.c_int64), ("d2hBytes", C.c_int64),
+                ("doseVoxelsModified", C.c_int64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

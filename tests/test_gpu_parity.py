@@ -217,13 +217,24 @@ def test_edge_cases(eng, mini_case):
     assert d.max() > 0
 
 
+@pytest.mark.parametrize("pinned", [False, True])
 @pytest.mark.parametrize("name", ["mini", "c2", "c3"])
-def test_one_call_host_path_moves_sub_volumes_only_and_matches(eng, name):
+def test_one_call_host_path_moves_sub_volumes_only_and_matches(eng, name, pinned):
     """rtd_plan_dose (the cudaWrapperProtons-shaped call) uploads only the CT boxes the tracers sample and moves only the
     dose boxes the transfers touch. Against the dense path (whole CT resident, device dose buffer): tracer outputs
     bit-identical, the same set of voxels modified, dose equal up to fp32 atomic order. The device CT array and the
-    context's dose buffer are poisoned with NaN first so that any texel / voxel outside the boxes would show."""
+    context's dose buffer are poisoned with NaN first so that any texel / voxel outside the boxes would show.
+    pinned=True: the dose grid is page-locked, so the transfer kernels accumulate it in place over PCIe (no dose copies
+    at all); pinned=False: pageable grid, staged through dose sub-volume copies."""
     import torch
+
+    def host_copy(a):
+        if not pinned:
+            return a.copy()
+        t = torch.from_numpy(a.copy()).pin_memory()
+        keep.append(t)
+        return t.numpy()
+    keep = []
     case = cases.make_case(name) if name != "mini" else cases.make_case("mini")
     nx, ny, nz = case.dose_dims
     rng = np.random.default_rng(5)
@@ -231,7 +242,7 @@ def test_one_call_host_path_moves_sub_volumes_only_and_matches(eng, name):
     eng.set_luts(case.luts); eng.set_dose_grid(nx, ny, nz)
     # dense path
     eng.set_ct(case.ct)
-    packed, keep = engine.pack_beams(case.beams)
+    packed, keep_b = engine.pack_beams(case.beams)
     d = torch.from_numpy(din).to("cuda:0")
     eng.dose_ptr(packed, len(case.beams), d.data_ptr(), device=True)
     dense_acc = d.cpu().numpy()
@@ -242,15 +253,20 @@ def test_one_call_host_path_moves_sub_volumes_only_and_matches(eng, name):
     fin = [eng.fetch(b, "first_inside") for b in range(len(case.beams))]
     # poison: NaN CT resident, NaN left behind in the context's dose buffer by a first one-call run
     nan_dose = np.full((nz, ny, nx), np.nan, np.float32)
-    eng.plan_dose(case.ct, case.beams, nan_dose)
+    eng.opts.noZeroCopyDose = 1
+    try:
+        eng.plan_dose(case.ct, case.beams, nan_dose)
+    finally:
+        eng.opts.noZeroCopyDose = 0
     eng.set_ct(np.full_like(case.ct, np.nan))
     # one-call path, beam by beam (accumulating) and then the whole plan
-    step = din.copy()
+    step = host_copy(din)
     for b in case.beams:
         t = eng.plan_dose(case.ct, [b], step)
         assert 0 < t.h2dBytes and 0 < t.d2hBytes
-    whole = np.zeros_like(din)
+    whole = host_copy(np.zeros_like(din))
     t = eng.plan_dose(case.ct, case.beams, whole)
+    assert t.doseVoxelsModified >= int((dense != 0).sum())
     for b in range(len(case.beams)):
         assert bits_equal(eng.fetch(b, "wepl"), wepl[b])
         assert np.array_equal(eng.fetch(b, "first_inside"), fin[b])
