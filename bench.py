@@ -297,6 +297,8 @@ def main():
                                "note": "what the reference moves: whole CT + whole dose grid up, whole dose grid down"},
                "timing": "host wall clock between barriers around the host call rtd_plan_dose (HOST CT + HOST dose in, dose out; the "
                          "library copies only the CT / dose sub-volumes the plan touches), max over ranks",
+               "library_events_ms": {"total": float(te.msTotal), "ct_upload_done_at": float(te.msUpload), "download": float(te.msDownload)},
+               "host_syncs_per_plan": int(te.hostSyncs), "dose_voxels_modified": int(te.doseVoxelsModified),
                "dose_checksum_matches_device_run": None}
         if rank == 0:
             cs = float(dose_host.double().sum().item())

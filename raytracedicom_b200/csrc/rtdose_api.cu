@@ -558,19 +558,31 @@ rtd_status doseCore(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* dDos
         while (ctx->bstreams.size() <= i) { cudaStream_t s_; cudaStreamCreateWithFlags(&s_, cudaStreamNonBlocking); ctx->bstreams.push_back(s_); }
         return ctx->bstreams[i];
     };
+    // One-call host path with several beams: the CT sub-volumes of beam b+1 upload while beam b computes. The host then
+    // waits for each beam's tracer reductions separately (nBeams + 1 host syncs instead of 2) and issues that beam's
+    // remaining launches at once. Needs a dose grid the transfers can write as soon as they run (device or pinned host).
+    const bool pipelined = io && io->ct && !serial && (io->zeroCopy || !io->dose);
     for (int b = 0; b < nBeams; ++b) {
         cudaStream_t st = beamStream(b);
         if (st != ctx->stream) RTD_CUDA(cudaStreamWaitEvent(st, evBegin, 0));
         rtd_status s = beamPhaseA(ctx, beams[b], *ctx->ws[b], o, launches, st, io, evBeam(ctx, b, 8));
         if (s != RTD_OK) return s;
-        if (st != ctx->stream) { cudaEvent_t e = evBeam(ctx, b, 6); RTD_CUDA(cudaEventRecord(e, st)); RTD_CUDA(cudaStreamWaitEvent(ctx->stream, e, 0)); }
+        cudaEvent_t e = evBeam(ctx, b, 6);
+        RTD_CUDA(cudaEventRecord(e, st));
+        if (st != ctx->stream && !pipelined) RTD_CUDA(cudaStreamWaitEvent(ctx->stream, e, 0));
     }
     cudaEvent_t evTraceEnd = ev(ctx, 2);
-    RTD_CUDA(cudaEventRecord(evTraceEnd, ctx->stream));
-    RTD_CUDA(cudaStreamSynchronize(ctx->stream));                         // host sync 1 of 2 (covers every beam stream)
-    for (int b = 0; b < nBeams; ++b) {
-        rtd_status s = beamPhaseB1(ctx, beams[b], *ctx->ws[b], o);
-        if (s != RTD_OK) return s;
+    int hostSyncs = 2;
+    if (!pipelined) {
+        RTD_CUDA(cudaEventRecord(evTraceEnd, ctx->stream));
+        RTD_CUDA(cudaStreamSynchronize(ctx->stream));                     // host sync 1 of 2 (covers every beam stream)
+        for (int b = 0; b < nBeams; ++b) {
+            rtd_status s = beamPhaseB1(ctx, beams[b], *ctx->ws[b], o);
+            if (s != RTD_OK) return s;
+        }
+    } else {
+        evTraceEnd = evBeam(ctx, nBeams - 1, 6);
+        hostSyncs = nBeams + 1;
     }
     cudaEvent_t evDoseIn = ev(ctx, 6);
     if (io && io->dose && !io->zeroCopy) {
@@ -585,6 +597,11 @@ rtd_status doseCore(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* dDos
         cudaEvent_t evs[6];
         for (int i = 0; i < 6; ++i) evs[i] = evBeam(ctx, b, i);
         cudaStream_t st = beamStream(b);
+        if (pipelined) {
+            RTD_CUDA(cudaEventSynchronize(evBeam(ctx, b, 6)));            // this beam's tracer reductions are on the host
+            rtd_status s1 = beamPhaseB1(ctx, beams[b], *ctx->ws[b], o);
+            if (s1 != RTD_OK) return s1;
+        }
         rtd_status s = beamPhaseB2(ctx, beams[b], *ctx->ws[b], o, dDose, launches, evs, st, io, evDoseIn, doseInWaited);
         if (s != RTD_OK) return s;
         if (st != ctx->stream) { cudaEvent_t e = evBeam(ctx, b, 7); RTD_CUDA(cudaEventRecord(e, st)); RTD_CUDA(cudaStreamWaitEvent(ctx->stream, e, 0)); }
@@ -604,7 +621,7 @@ rtd_status doseCore(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* dDos
     if (io && io->dose && io->zeroCopy) { io->h2d += modified * 4; io->d2h += modified * 4; }   // the transfers read-modify-write the caller's pinned grid in place
     if (tm) {
         memset(tm, 0, sizeof *tm);
-        tm->updates = updates; tm->ksTaps = taps; tm->kernelLaunches = launches; tm->hostSyncs = 2;
+        tm->updates = updates; tm->ksTaps = taps; tm->kernelLaunches = launches; tm->hostSyncs = hostSyncs;
         float ms = 0;
         cudaEventElapsedTime(&ms, evBegin, evTraceEnd); tm->msTrace = ms;
         cudaEvent_t prev = evTraceEnd;
