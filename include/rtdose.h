@@ -90,6 +90,8 @@ typedef struct {
                                 0 (default): one stream per beam, transfers into the dose grid serialised in beam order */
     int   noZeroCopyDose;    /* 0 (default): a PINNED host dose grid is accumulated in place by the transfer kernels (only voxels
                                 that receive dose cross PCIe); 1: always stage dose sub-volumes through device memory */
+    int   noNozzle;          /* 1: the reference's -DNO_NOZZLE build: no in-air spot-size growth (fill_idd_and_sigma_params.cu:76-82) */
+    int   doseToMedium;      /* 1: the reference built with DOSE_TO_WATER off: voxel mass = density x volume (kernel_wrapper.cu:314-318) */
     int   reserved[2];
 } rtd_opts;
 

@@ -38,7 +38,8 @@ class OrcBeam(C.Structure):
 
 class OrcOpts(C.Structure):
     _fields_ = [("bpDepthCutoff", C.c_float), ("convSigmaCutoff", C.c_float), ("ksSigmaCutoff", C.c_float),
-                ("rayWeightCutoff", C.c_float), ("minTilesInBatch", C.c_int), ("texFracMode", C.c_int)]
+                ("rayWeightCutoff", C.c_float), ("minTilesInBatch", C.c_int), ("texFracMode", C.c_int),
+                ("noNozzle", C.c_int), ("doseToMedium", C.c_int)]
 
 
 class OrcResult(C.Structure):

@@ -55,7 +55,9 @@ typedef struct {
 } orc_beam;
 
 /* Run-time copies of the compile-time flags (CMakeLists.txt:36-79). */
-typedef struct { float bpDepthCutoff, convSigmaCutoff, ksSigmaCutoff, rayWeightCutoff; int minTilesInBatch; int texFracMode; } orc_opts;
+typedef struct { float bpDepthCutoff, convSigmaCutoff, ksSigmaCutoff, rayWeightCutoff; int minTilesInBatch; int texFracMode;
+                 int noNozzle;      /* -DNO_NOZZLE (CMakeLists.txt:48-51; fill_idd_and_sigma_params.cu:76-82) */
+                 int doseToMedium;  /* DOSE_TO_WATER off (CMakeLists.txt:40-43; kernel_wrapper.cu:314-318) */ } orc_opts;
 
 /* Everything the reference computes for one beam; arrays are malloc'ed here and released by orc_free_result. */
 typedef struct {
@@ -81,7 +83,7 @@ typedef struct {
 
 void orc_default_opts(orc_opts* o) {
     o->bpDepthCutoff = 1.05f; o->convSigmaCutoff = 3.0f; o->ksSigmaCutoff = 3.0f; o->rayWeightCutoff = 1.0f;
-    o->minTilesInBatch = 16; o->texFracMode = 0;
+    o->minTilesInBatch = 16; o->texFracMode = 0; o->noNozzle = 0; o->doseToMedium = 0;
 }
 
 void orc_free_result(orc_result* r) {
@@ -370,7 +372,7 @@ static void stage_idd_sigma(const orc_luts* lut, const fill_geom* g, const layer
     const int R = Rx * Ry;
     const float INF = INFINITY;
     /* initStepAndAirDiv (cu:223), relStepLenSq = 1 */
-    const float ca = 0.00270f / (lp->peakDepth + -4.50f), cb = -4.39f / (lp->peakDepth + -3.86f);
+    const float ca = o->noNozzle ? 0.0f : 0.00270f / (lp->peakDepth + -4.50f), cb = o->noNozzle ? 0.0f : -4.39f / (lp->peakDepth + -3.86f);
     const float dzs = g->delta.z;
     const float airQuad = dzs * (ca * dzs);
     const float airLin = fmaf(cb, dzs, g->corner.z * ((ca + ca) * dzs));
@@ -416,7 +418,7 @@ static void stage_idd_sigma(const orc_luts* lut, const fill_geom* g, const layer
                 live = within && (k != afterLast);                                                          /* cu:309-312 */
                 afterLast = within ? afterLast : k;
                 const float vol = fmaf(g->volSq, (float)(k * k), fmaf(g->volLin, fk, g->volConst));
-                const float mass = (w - wOld) * vol;
+                const float mass = o->doseToMedium ? rho * vol : (w - wOld) * vol;                          /* cu:314-318 */
                 if (mass > 1e-2f) res = (rayWeight * (d - dOld)) / mass;                                    /* else keeps the previous value (H9) */
                 wOld = w; dOld = d;
             }
@@ -589,7 +591,7 @@ int orc_beam_dose(const orc_luts* lut, const float* ct, int nx, int ny, int nz, 
         lp[l].energyIdx = orc_find_decimal_ordered(lut->energiesPerU, nE, b->energies[l]);
         lp[l].energyScale = orc_vector_interpolate(lut->scaleFacts, nE, lp[l].energyIdx);
         lp[l].peakDepth = orc_vector_interpolate(lut->peakDepths, nE, lp[l].energyIdx);
-        const float ca = 0.00270f / (lp[l].peakDepth - 4.50f), cb = -4.39f / (lp[l].peakDepth - 3.86f), z = r->entryZ;
+        const float ca = o.noNozzle ? 0.0f : 0.00270f / (lp[l].peakDepth - 4.50f), cb = o.noNozzle ? 0.0f : -4.39f / (lp[l].peakDepth - 3.86f), z = r->entryZ;
         const float sxg = b->sigmas[2 * l], syg = b->sigmas[2 * l + 1];
         entrySig[2 * l] = sqrtf(ca * z * z + cb * z + sxg * sxg);          /* cu:840-841 */
         entrySig[2 * l + 1] = sqrtf(ca * z * z + cb * z + syg * syg);

@@ -236,7 +236,8 @@ struct IddParams {
     int first;                // beamFirstInside
     int nz;                   // Zg - first: slices kept per layer
     int Rx, Ry;
-    int nozzle;
+    int nozzle;               // 0 = the reference's -DNO_NOZZLE build (fill_idd_and_sigma_params.cu:76-82)
+    int doseToMedium;         // 1 = the reference built without -DDOSE_TO_WATER (kernel_wrapper.cu:314-318)
 };
 
 __global__ void __launch_bounds__(256)
@@ -308,7 +309,7 @@ idd_sigma_kernel(const float* __restrict__ density, const float* __restrict__ we
             live = within && (k != afterLast);
             afterLast = within ? afterLast : k;
             const float vol = f_fma(q.g.volSq, u2f(k * k), f_fma(q.g.volLin, fk, q.g.volConst));
-            const float mass = f_mul(f_sub(w, wOld), vol);
+            const float mass = q.doseToMedium ? f_mul(rho, vol) : f_mul(f_sub(w, wOld), vol);
             if (mass > 1e-2f) res = f_div(f_mul(rayWeight, f_sub(d, dOld)), mass);
             wOld = w; dOld = d;
         }

@@ -365,7 +365,7 @@ rtd_status beamPhaseB1(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opt
         lp.energyIdx = findDecimalOrdered(E, nE, b.energies[al]);
         lp.energyScale = vectorInterpolate(ctx->scaleFacts.data(), nE, lp.energyIdx);
         lp.peakDepth = vectorInterpolate(ctx->peakDepths.data(), nE, lp.energyIdx);
-        float ca, cb; sigmaSqAirCoefsHost(lp.peakDepth, true, ca, cb);
+        float ca, cb; sigmaSqAirCoefsHost(lp.peakDepth, !o.noNozzle, ca, cb);
         const float sxg = b.sigmas[2 * al], syg = b.sigmas[2 * al + 1], z = w.entryZ;
         w.entrySig[2 * l] = sqrtf(ca * z * z + cb * z + sxg * sxg);
         w.entrySig[2 * l + 1] = sqrtf(ca * z * z + cb * z + syg * syg);
@@ -454,7 +454,7 @@ rtd_status beamPhaseB2(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opt
     IddParams q;
     q.g = makeFillGeom(w.grid.rayIdxToGantry, w.dist);
     q.rrlScale = ctx->rrlScale; q.bpCutoff = o.bpDepthCutoff; q.rayWeightCutoff = o.rayWeightCutoff;
-    q.first = w.bfi; q.nz = nz; q.Rx = Rx; q.Ry = Ry; q.nozzle = 1;
+    q.first = w.bfi; q.nz = nz; q.Rx = Rx; q.Ry = Ry; q.nozzle = o.noNozzle ? 0 : 1; q.doseToMedium = o.doseToMedium ? 1 : 0;
     idd_sigma_kernel<<<dim3(tilesX, tilesY, L), 256, 0, strm>>>(w.density.as<float>(), w.wepl.as<float>(), w.rayW.as<float>(),
         w.firstIn.as<int>(), w.firstOut.as<int>(), w.layerDev.as<LayerParams>(), q, ctx->iddTex.tex, ctx->rrlTex.tex,
         w.idd.as<float>(), w.rsig.as<float>(), w.rowMin.as<float>(), w.firstPassive.as<int>(), dLfp);

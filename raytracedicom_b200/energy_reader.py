@@ -119,3 +119,24 @@ def load_packaged_luts(water_cube_test: bool = False) -> EnergyStruct:
     e.rRlScaleFact = float(z["rRlScaleFact"])
     e.validate()
     return e
+
+
+def write_text_luts(data_path: str, e: EnergyStruct = None, water_cube_test: bool = False) -> None:
+    """Write an EnergyStruct in the reference's text LUT format (the files ``energy_reader`` / the C++ ``energyReader``
+    read; ``data_path`` ends with a separator). float32 values are printed with 9 significant digits, so reading them
+    back reproduces every bit. Lets the DICOM input path of the host driver run where /root/reference/LUTs is absent."""
+    e = e or load_packaged_luts(water_cube_test)
+    os.makedirs(data_path, exist_ok=True)
+
+    def fmt(a):
+        return "\n".join("%.9g" % float(v) for v in np.asarray(a, np.float32).ravel())
+
+    with open(data_path + "proton_cumul_ddd_data.txt", "w") as f:
+        f.write(f"{e.nEnergySamples} {e.nEnergies}\n")
+        for a in (e.energiesPerU, e.peakDepths, e.scaleFacts, e.ciddMatrix):
+            f.write(fmt(a) + "\n")
+    rl = "radiation_length_inc_water.txt" if water_cube_test else "radiation_length.txt"
+    for name, n, s, v in (("density_Schneider2000_adj.txt", e.nDensitySamples, e.densityScaleFact, e.densityVector),
+                          ("HU_to_SP_H&N_adj.txt", e.nSpSamples, e.spScaleFact, e.spVector), (rl, e.nRRlSamples, e.rRlScaleFact, e.rRlVector)):
+        with open(data_path + name, "w") as f:
+            f.write(f"{n} {'%.9g' % float(s)}\n" + fmt(v) + "\n")

@@ -18,7 +18,8 @@ const char* kUsage =
     "  --water_cube_test        the reference's WATER_CUBE_TEST configuration\n"
     "  --case FILE              raw case file (RTDCASE1) instead of DICOM input\n"
     "  --phys_data DIR/         directory of the physics look-up tables\n"
-    "  --timing                 print the stage timing report\n";
+    "  --timing                 print the stage timing report\n"
+    "  --dump_case FILE         write the assembled plan as an RTDCASE1 file and stop (no GPU needed)\n";
 
 void splitList(const std::string& s, std::vector<std::string>& out) {
     std::stringstream ss(s);
@@ -37,6 +38,7 @@ Config::Config(int argc, char** argv) {
         else if (key == "output_directory") output_directory = val;
         else if (key == "case") case_file = val;
         else if (key == "phys_data") phys_data_directory = val;
+        else if (key == "dump_case") dump_case = val;
         else { std::cerr << "Unknown option: " << key << "\n" << kUsage; exit = true; }
     };
     for (int i = 1; i < argc && !exit; ++i) {

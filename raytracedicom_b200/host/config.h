@@ -3,8 +3,8 @@
 #include <string>
 #include <vector>
 // The reference's run-time options (src/config.h:20-32, src/config.cpp:13-51), parsed without CLI11, plus the
-// switches that are compile-time -D flags in the reference (CMakeLists.txt:36-79) and two input modes that stand
-// in for the DICOM readers (ITK/GDCM are not available in this build: SURVEY.md 8f-3).
+// switches that are compile-time -D flags in the reference (CMakeLists.txt:36-79) and two raw input modes beside
+// the DICOM input (--ct_dir / --rtplan / --beams, read by host/dicom_reader.cpp without ITK/GDCM).
 struct Config {
     Config(int argc, char** argv);
     unsigned short gpu_id{0};
@@ -16,5 +16,6 @@ struct Config {
     std::string case_file;            // RTDCASE1 file (raytracedicom_b200/cases.py): raw CT + BeamSettings
     std::string phys_data_directory;  // PHYS_DATA_DIRECTORY
     bool timing{false};               // FINE_GRAINED_TIMING-style stage report
+    std::string dump_case;            // write the assembled plan (CT + BeamSettings + LUTs) as an RTDCASE1 file and stop: no GPU needed
 };
 #endif

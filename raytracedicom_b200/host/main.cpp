@@ -1,8 +1,10 @@
 // Host driver of the B200 dose engine: the role of the reference's main() (src/main.cu:20-252) on top of the C ABI.
 //   rtdose_main --water_cube_test [--phys_data DIR/] [--output_directory DIR]      (reference: -DWATER_CUBE_TEST build)
 //   rtdose_main --case plan.rtdcase [--output_directory DIR]                        (raw CT + BeamSettings, any number of beams)
-// The DICOM input path (--ct_dir / --rtplan) needs ITK/GDCM, which this build does not have; the
-// reference's own DICOM path never loads the plan into the BeamSettings either (src/main.cu:185-188).
+//   rtdose_main --ct_dir DIR --rtplan FILE [--beams A,B] --phys_data DIR/            (the reference's DICOM input, src/main.cu:105-197)
+// The DICOM path reads the CT series and the RT Ion Plan with host/dicom_reader.cpp (no ITK/GDCM/rti) and - unlike the
+// reference, whose main() prints the plan's spots but hands all-zero weights / energies / sigmas to the dose engine
+// (src/main.cu:185-197) and stops at one beam (main.cu:117-120) - maps every requested beam to a BeamSettings.
 #include <algorithm>
 #include <chrono>
 #include <cmath>
@@ -17,6 +19,7 @@
 
 #include "../../include/rtdose_shim.hpp"
 #include "config.h"
+#include "dicom_reader.h"
 #include "energy_reader.h"
 #include "host_types.h"
 
@@ -44,8 +47,68 @@ struct Plan {   // everything main() hands to cudaWrapperProtons, with owned sto
     std::vector<std::vector<float>> weightData;
     std::vector<std::unique_ptr<HostPinnedImage3D<float>>> weightImages;
     std::vector<BeamSettings> beams;
+    std::vector<std::unique_ptr<PlanBeamSettings>> planBeams;
     EnergyStruct luts; bool haveLuts = false;
 };
+
+// DICOM input: CT series + RT Ion Plan -> plan (src/main.cu:105-197 completed).
+void readDicom(const Config& config, Plan& p) {
+    unsigned int N = 0; clock_t t;
+    const Float3AffineTransform imIdxToWorld = itk_reader(config.ct_dir, p.imageData, N, p.dim, t);
+    p.doseDim = p.dim;
+    const std::vector<PlanBeam> all = readIonPlan(config.rtplan);
+    std::vector<std::string> names = config.beams;
+    if (names.empty()) for (const PlanBeam& b : all) names.push_back(b.name);
+    for (size_t i = 0; i < names.size(); ++i) {
+        std::cout << "Loading field " << i << " corresponding to beamname " << names[i] << std::endl;
+        const PlanBeam* pb = nullptr;
+        for (const PlanBeam& b : all) if (b.name == names[i]) pb = &b;
+        if (!pb) throw std::runtime_error("beam " + names[i] + " not found in " + config.rtplan);
+        std::cout << "Angles: " << pb->collimatorAngle << " " << pb->gantryAngle << " " << pb->couchAngle << " deg\n"
+                  << "IsoCenter: " << pb->isocenter.x << " " << pb->isocenter.y << " " << pb->isocenter.z << " mm\n"
+                  << "ImgPixels: " << p.dim.x << " " << p.dim.y << " " << p.dim.z << "\n";
+        size_t nSpots = 0;
+        for (const PlanLayer& l : pb->layers) nSpots += l.x.size();
+        std::cout << "Layers: " << pb->layers.size() << ", spots: " << nSpots << "\n\n";
+        p.planBeams.push_back(beamFromPlan(*pb, imIdxToWorld, p.dim));
+        p.beams.push_back(*p.planBeams.back()->beam);
+    }
+}
+
+// RTDCASE1 writer (layout: oracle/ref_harness/case_io.h; reader: readCaseFile below, raytracedicom_b200/cases.py).
+void writeCaseFile(const std::string& path, Plan& p) {
+    FILE* f = fopen(path.c_str(), "wb");
+    if (!f) throw std::runtime_error("cannot write " + path);
+    auto wr = [&](const void* src, size_t n) { if (n && fwrite(src, 1, n, f) != n) { fclose(f); throw std::runtime_error("write failed: " + path); } };
+    auto wri = [&](int v) { wr(&v, 4); };
+    auto wrf = [&](float v) { wr(&v, 4); };
+    auto wrv = [&](const std::vector<float>& v) { wr(v.data(), v.size() * 4); };
+    wr("RTDCASE1", 8);
+    wri(int(p.dim.x)); wri(int(p.dim.y)); wri(int(p.dim.z)); wrv(p.imageData);
+    wri(int(p.doseDim.x)); wri(int(p.doseDim.y)); wri(int(p.doseDim.z));
+    const EnergyStruct& l = p.luts;
+    wri(l.nEnergySamples); wri(l.nEnergies); wrv(l.energiesPerU); wrv(l.peakDepths); wrv(l.scaleFacts); wrv(l.ciddMatrix);
+    wri(l.nDensitySamples); wrf(l.densityScaleFact); wrv(l.densityVector);
+    wri(l.nSpSamples); wrf(l.spScaleFact); wrv(l.spVector);
+    wri(l.nRRlSamples); wrf(l.rRlScaleFact); wrv(l.rRlVector);
+    wri(int(p.beams.size()));
+    for (BeamSettings& b : p.beams) {
+        const uint3 wd = b.getWeights()->getDims();
+        wri(int(wd.x)); wri(int(wd.y)); wri(int(wd.z)); wri(int(b.getSteps()));
+        wr(b.getWeights()->getImData(), size_t(wd.x) * wd.y * wd.z * 4);
+        wrv(b.getEnergies());
+        for (const float2& s : b.getSpotSigmas()) { wrf(s.x); wrf(s.y); }
+        wrf(b.getRaySpacing().x); wrf(b.getRaySpacing().y); wrf(b.getSourceDist().x); wrf(b.getSourceDist().y);
+        const float3 de = b.getSpotIdxToGantry().getDelta(), of = b.getSpotIdxToGantry().getOffset();
+        wrf(de.x); wrf(de.y); wrf(de.z); wrf(of.x); wrf(of.y); wrf(of.z);
+        for (const Float3AffineTransform& t : {b.getGantryToImIdx(), b.getGantryToDoseIdx()}) {
+            const Matrix3x3 m = t.getMatrix();
+            for (const float3& r : {m.row0(), m.row1(), m.row2()}) { wrf(r.x); wrf(r.y); wrf(r.z); }
+            wrf(t.getOffset().x); wrf(t.getOffset().y); wrf(t.getOffset().z);
+        }
+    }
+    fclose(f);
+}
 
 // The WATER_CUBE_TEST configuration (src/main.cu:39-43, 61-62, 74-99, 192-197).
 void makeWaterCubeTest(Plan& p, const EnergyStruct& ciddData) {
@@ -125,8 +188,18 @@ int main(int argc, char** argv) {
             plan.luts = energyReader(config.phys_data_directory, true);
             plan.haveLuts = true;
             makeWaterCubeTest(plan, plan.luts);
+        } else if (!config.ct_dir.empty() && !config.rtplan.empty()) {
+            if (config.phys_data_directory.empty()) throw std::runtime_error("DICOM input needs --phys_data DIR/ (the reference's PHYS_DATA_DIRECTORY)");
+            plan.luts = energyReader(config.phys_data_directory, false);
+            plan.haveLuts = true;
+            readDicom(config, plan);
         } else {
-            throw std::runtime_error("DICOM input (--ct_dir/--rtplan) needs ITK/GDCM, unavailable in this build; use --case FILE or --water_cube_test");
+            throw std::runtime_error("no input: give --ct_dir DIR --rtplan FILE [--beams ...], --case FILE or --water_cube_test");
+        }
+        if (!config.dump_case.empty()) {
+            writeCaseFile(config.dump_case, plan);
+            std::cout << "Written " << config.dump_case << " (" << plan.beams.size() << " beam(s)); stopping before the dose calculation\n";
+            return 0;
         }
         const double tRead = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
         std::cout << "Read cumulative energy matrix: " << tRead << " seconds.\n\n";

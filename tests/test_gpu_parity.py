@@ -283,3 +283,30 @@ def test_one_call_host_path_moves_sub_volumes_only_and_matches(eng, name, pinned
     with pytest.raises(engine.RtdError) as ei:
         eng.dose(case.beams, whole)
     assert ei.value.status == 4
+
+
+@pytest.mark.parametrize("variant", ["noNozzle", "doseToMedium"])
+def test_build_variants_against_oracle_and_rebuilt_reference(eng, oracle, mini_case, variant, tmp_path):
+    """The reference's CMake options NOZZLE=OFF (-DNO_NOZZLE, fill_idd_and_sigma_params.cu:76-82) and DOSE_TO_WATER=OFF
+    (kernel_wrapper.cu:314-318) as run-time rtd_opts: against the oracle with the same switch, and against the UNMODIFIED
+    reference rebuilt with that option (oracle/_ref/ref_dose_nonozzle, ref_dose_medium) where it is present."""
+    from oracle import pyoracle
+    case = mini_case
+    base, _ = run_case(eng, case)
+    setattr(eng.opts, variant, 1)
+    try:
+        dose, t = run_case(eng, case)
+        rep = eng.beam_report(0)
+    finally:
+        setattr(eng.opts, variant, 0)
+    assert rel_to_max(dose, base)[0] > 1e-3          # the switch changes the physics
+    o = pyoracle.run_beam(case, 0, opts=pyoracle.default_opts(**{variant: 1}))
+    assert rep["updates"] == o["updates"] and rep["beamFirstCalculatedPassive"] == o["beamFirstCalculatedPassive"]
+    assert rel_to_max(dose, o["dose"])[0] <= 2e-4
+    exe = os.path.join(ROOT, "oracle", "_ref", {"noNozzle": "ref_dose_nonozzle", "doseToMedium": "ref_dose_medium"}[variant])
+    if os.path.exists(exe):
+        cpath = str(tmp_path / "case.rtdcase"); case.write(cpath)
+        r = subprocess.run([exe, cpath, str(tmp_path / "dose.f32")], capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stderr[-1000:]
+        ref = np.fromfile(tmp_path / "dose.f32", np.float32).reshape(dose.shape)
+        assert rel_to_max(dose, ref)[0] <= DOSE_TOL_TIGHT
