@@ -310,7 +310,13 @@ def main():
         peak, peak_src, sm_max = load_peaks()
         reps = [eng.beam_report(b) for b in range(len(mine))]
         live = [r for r in reps if r["beamFirstCalculatedPassive"] > r["beamFirstInside"]]
-        ks_launches = max(1, 3 * len(live))
+        # two ks2 launches per live beam do the work (radius classes <= 8 and 9..16); the third launch of the stage
+        # (ks_kernel<17..32>) finds an empty work list on this workload (a few microseconds inside msSuperp)
+        ks_launches = max(1, 2 * len(live))
+        traffic, traffic_src = None, None
+        tp = os.path.join(ROOT, "profiles", "r01_ncu_ks2_traffic.json")
+        if os.path.exists(tp) and case.name.startswith("c3") and world == 1:
+            tj = json.load(open(tp)); traffic = tj["dram_bytes_per_launch"]; traffic_src = tj["source"]
         ks_ms = stage["msSuperp"] / args.steps
         u_rank0 = sum(r["updates"] for r in reps)
         bev_bytes = sum(4 * (r["rayDimX"] + 64) * (r["rayDimY"] + 64) * (r["beamFirstCalculatedPassive"] - r["beamFirstInside"]) for r in live)
@@ -336,8 +342,10 @@ def main():
                 "serial_beams_plan_ms": stage["msTotal"] / args.steps,
                 "gpu_launches": int(conc_stage["kernelLaunches"]), "host_syncs_per_plan": int(stage["hostSyncs"] / args.steps),
                 "dose_max": dmax, "dose_checksum": checksum,
-                "roofline": {"kernel": "ks_kernel (kernel superposition, 3 radius-class launches per beam)", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                             "frac": achieved / peak, "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": ks_alg / ks_launches,
+                "roofline": {"kernel": "ks2_kernel (layer-fused kernel superposition, 2 radius-class launches per beam)", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                             "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
+                             "traffic_note": "DRAM bytes per launch from ncu; below the algorithmic 8 B/update because tiles without dose and layers past their range are skipped before their idd / rSigmaEff are read",
+                             "peak_source": peak_src, "algorithmic_bytes_per_launch": ks_alg / ks_launches,
                              "avg_launch_ms": ks_ms / ks_launches, "launches_per_plan_rank0": ks_launches,
                              "fp32": {"achieved_tflops": 2 * taps0 / (ks_ms * 1e-3) / 1e12 if ks_ms > 0 else 0.0, "peak_tflops": fp32_peak,
                                       "frac": (2 * taps0 / (ks_ms * 1e-3) / 1e12) / fp32_peak if ks_ms > 0 else 0.0,

@@ -202,23 +202,34 @@ void ctBoxesOfBeam(const TraceParams& p, int Rx, int Ry, int S, const int dims[3
         const double I[3] = {p.coefIdxI.x, p.coefIdxI.y, p.coefIdxI.z}, J[3] = {p.coefIdxJ.x, p.coefIdxJ.y, p.coefIdxJ.z}, O[3] = {p.coefOffset.x, p.coefOffset.y, p.coefOffset.z};
         for (int d = 0; d < 3; ++d) r[d] = (O[d] - I[d] * i / double(p.distX) - J[d] * j / double(p.distY)) * double(p.delta.z);
     };
-    const int segLen = 48;
-    for (int k0 = 0; k0 < S; k0 += segLen) {
-        const int k1 = std::min(k0 + segLen, S - 1);   // segments share their end planes
-        double mn[3] = {1e30, 1e30, 1e30}, mx[3] = {-1e30, -1e30, -1e30};
-        for (int c = 0; c < 8; ++c) {
-            const int i = (c & 1) ? Rx - 1 : 0, j = (c & 2) ? Ry - 1 : 0, k = (c & 4) ? k1 : k0;
-            double st[3], in[3]; start(i, j, st); inc(i, j, in);
-            for (int d = 0; d < 3; ++d) { const double v = st[d] + k * in[d]; mn[d] = std::min(mn[d], v); mx[d] = std::max(mx[d], v); }
+    auto boxesFor = [&](int segLen, std::vector<Box>& dst) {
+        for (int k0 = 0; k0 < S; k0 += segLen) {
+            const int k1 = std::min(k0 + segLen, S - 1);   // segments share their end planes
+            double mn[3] = {1e30, 1e30, 1e30}, mx[3] = {-1e30, -1e30, -1e30};
+            for (int c = 0; c < 8; ++c) {
+                const int i = (c & 1) ? Rx - 1 : 0, j = (c & 2) ? Ry - 1 : 0, k = (c & 4) ? k1 : k0;
+                double st[3], in[3]; start(i, j, st); inc(i, j, in);
+                for (int d = 0; d < 3; ++d) { const double v = st[d] + k * in[d]; mn[d] = std::min(mn[d], v); mx[d] = std::max(mx[d], v); }
+            }
+            Box b; bool finite = true;
+            for (int d = 0; d < 3; ++d) {
+                if (!(std::fabs(mn[d]) < 1e9 && std::fabs(mx[d]) < 1e9)) { finite = false; break; }
+                b.lo[d] = int(std::floor(mn[d])) - 2; b.hi[d] = int(std::floor(mx[d])) + 3;   // texel pair + fp32 accumulation slack
+            }
+            if (!finite) { b.lo[0] = b.lo[1] = b.lo[2] = 0; b.hi[0] = dims[0] - 1; b.hi[1] = dims[1] - 1; b.hi[2] = dims[2] - 1; }
+            addBox(dst, b, dims);
         }
-        Box b; bool finite = true;
-        for (int d = 0; d < 3; ++d) {
-            if (!(std::fabs(mn[d]) < 1e9 && std::fabs(mx[d]) < 1e9)) { finite = false; break; }
-            b.lo[d] = int(std::floor(mn[d])) - 2; b.hi[d] = int(std::floor(mx[d])) + 3;   // texel pair + fp32 accumulation slack
-        }
-        if (!finite) { b.lo[0] = b.lo[1] = b.lo[2] = 0; b.hi[0] = dims[0] - 1; b.hi[1] = dims[1] - 1; b.hi[2] = dims[2] - 1; }
-        addBox(out, b, dims);
+    };
+    // segment length: short segments follow an oblique beam closely but pay the slack on every box, long ones drag the
+    // beam's bounding box along; take the candidate that moves the fewest voxels
+    int best = S; int64_t bestVox = -1;
+    for (int segLen : {32, 64, 128, 256, S}) {
+        if (segLen > S) continue;
+        std::vector<Box> tmp; boxesFor(segLen, tmp);
+        int64_t vox = 0; for (const Box& b : tmp) vox += boxVoxels(b);
+        if (bestVox < 0 || vox < bestVox) { bestVox = vox; best = segLen; }
     }
+    boxesFor(best, out);
 }
 
 // Dose boxes that enclose every voxel bev_to_grid_kernel can modify for this beam: voxels whose fan index lies within
