@@ -10,7 +10,8 @@
 //     cuh:459-467, same libdevice erff) go through a warp-private table so that the hot loop is a SMALL rolled loop
 //     over the column offset j (instruction-cache resident) with the row weights e[y][|i|] held in registers:
 //     per j the lane accumulates a whole output column (P+2RB rows) in registers - P(2RB+1) FMAs, no memory traffic -
-//     and adds it to the patch columns x+j and x-j (the horizontal weight is symmetric: +j and -j share the FMAs);
+//     and adds it to the patch columns x+j and x-j (the horizontal weight is symmetric: +j and -j share the FMAs); the
+//     patch is column-major so that this read-modify-write is 128-bit wide (see ks2_col_pitch);
 //   * the radius applied to a tile is still the reference's BATCH radius (cuh:443-448 vs 459-473).
 #pragma once
 #include <cuda_runtime.h>
@@ -46,25 +47,43 @@ __device__ __forceinline__ float ks_erf_pos(float x) {
 constexpr int KS2_MAXRB = 16;       // larger batch radii go through the block-wide ks_kernel<.,17,32>
 constexpr int KS2_MAXL = 256;
 
-__host__ __device__ constexpr int ks2_rows_per_pass(int rb) { return rb <= 16 ? 8 : 4; }
-// per-warp shared memory (floats): patch + weight table + layer list
-__host__ __device__ constexpr int ks2_patch_floats(int rbmax) { return (8 + 2 * rbmax) * (32 + 2 * rbmax); }
+// Warp-private patch, COLUMN-major: patch[X][Y], X = tile column + RBMAX (32 + 2 RBMAX columns), Y = tile row + RBMAX
+// (8 + 2 RBMAX rows, a multiple of 4), column pitch padded so that 128-bit accesses of 8 consecutive lanes (one column
+// each) fall into 8 distinct groups of 4 banks: pitch % 4 == 0 and pitch % 32 in {4, 12, 20, 28}  ->  44 (RBMAX 16), 28 (8).
+// A lane's register-accumulated output column is then added with LDS.128 / STS.128: a quarter of the shared-memory
+// instructions of a row-major patch at the same bank-conflict-free bandwidth.
+// The 4 pad floats at the end of every column hold the item's layer list (8 uint16 entries per column).
+__host__ __device__ constexpr int ks2_rows(int rbmax) { return 8 + 2 * rbmax; }
+__host__ __device__ constexpr int ks2_cols(int rbmax) { return 32 + 2 * rbmax; }
+__host__ __device__ constexpr int ks2_col_pitch(int rbmax) {
+    int p = ks2_rows(rbmax) + 4;
+    while (p % 4 != 0 || (p % 32) % 8 != 4) ++p;
+    return p;
+}
+// per-warp shared memory (floats): patch (with the layer list in its pad) + weight table
+__host__ __device__ constexpr int ks2_patch_floats(int rbmax) { return ks2_cols(rbmax) * ks2_col_pitch(rbmax); }
 __host__ __device__ constexpr int ks2_table_floats(int rbmax) { return 8 * (rbmax + 1) * 32; }
-__host__ __device__ constexpr int ks2_warp_floats(int rbmax) { return ks2_patch_floats(rbmax) + ks2_table_floats(rbmax) + KS2_MAXL / 2; }
+__host__ __device__ constexpr int ks2_warp_floats(int rbmax) { return ks2_patch_floats(rbmax) + ks2_table_floats(rbmax); }
+static_assert(ks2_col_pitch(16) == 44 && ks2_col_pitch(8) == 28, "column pitch");
+static_assert((ks2_col_pitch(16) - ks2_rows(16)) * 2 * ks2_cols(16) >= KS2_MAXL && (ks2_col_pitch(8) - ks2_rows(8)) * 2 * ks2_cols(8) >= KS2_MAXL, "layer list fits the column pads");
 
-// One pass over P source rows [y0, y0+P) of the tile with batch radius RB.
-//   tab : table rows of this pass, tab[(y*(RB+1) + i)*32 + lane] = e_y[i]
-//   dP  : dose of the lane's P voxels
-//   org : patch element that receives (row y0 - RB, column x - RB) of this tile's footprint for lane 0
-template <int RB, int P>
-__device__ __forceinline__ void ks2_pass(const float* __restrict__ tab, const float (&dP)[P], float* __restrict__ org, const int pitch,
-                                         const int lane) {
-    constexpr int W = 2 * RB + 1, NRP = P + 2 * RB;
+// All 8 source rows of the tile with batch radius RB into the patch of a kernel instantiated for radii <= RBMAX.
+//   tab    : tab[(y*(RB+1) + i)*32 + lane] = e_y[i] of the lane's 8 voxels
+//   d      : dose of the lane's 8 voxels
+//   patch  : column-major patch of this warp
+template <int RB, int RBMAX>
+__device__ __forceinline__ void ks2_tile(const float* __restrict__ tab, const float (&d)[8], float* __restrict__ patch, const int lane) {
+    constexpr int P = 8, W = 2 * RB + 1, NRP = P + 2 * RB, PC = ks2_col_pitch(RBMAX);
+    constexpr int Y0 = RBMAX - RB;            // patch row of the first output row (tile row -RB)
+    constexpr int A = Y0 & 3, YS = Y0 - A;    // 128-bit window [YS, YS + 4 NV) around the NRP output rows
+    constexpr int NV = (A + NRP + 3) / 4;
+    static_assert(YS + 4 * NV <= ks2_rows(RBMAX), "window stays inside the column");
     float e[P][RB + 1];
 #pragma unroll
     for (int y = 0; y < P; ++y)
 #pragma unroll
         for (int i = 0; i <= RB; ++i) e[y][i] = tab[(y * (RB + 1) + i) * 32 + lane];
+    float* const col0 = patch + (lane + RBMAX) * PC + YS;     // the lane's own column (offset j = 0)
 #pragma unroll 1
     for (int j = 0; j <= RB; ++j) {
         float acc[NRP];
@@ -72,35 +91,26 @@ __device__ __forceinline__ void ks2_pass(const float* __restrict__ tab, const fl
         for (int Y = 0; Y < NRP; ++Y) acc[Y] = 0.0f;
 #pragma unroll
         for (int y = 0; y < P; ++y) {
-            const float g = dP[y] * tab[(y * (RB + 1) + j) * 32 + lane];
+            const float g = d[y] * tab[(y * (RB + 1) + j) * 32 + lane];
 #pragma unroll
             for (int i = 0; i < W; ++i) acc[y + i] = fmaf(g, e[y][(i < RB) ? (RB - i) : (i - RB)], acc[y + i]);
         }
-        float* c0 = org + lane + RB + j;
+        // the horizontal weight is symmetric: the same output column goes to patch columns x+j and x-j. Within one phase
+        // every lane owns a different column; rows of the window outside the NRP outputs are rewritten unchanged.
 #pragma unroll
-        for (int Y = 0; Y < NRP; ++Y) c0[Y * pitch] += acc[Y];
-        __syncwarp();
-        if (j > 0) {
-            float* c1 = org + lane + RB - j;
+        for (int side = 0; side < 2; ++side) {
+            if (side == 1 && j == 0) break;
+            float4* c = reinterpret_cast<float4*>(side == 0 ? col0 + j * PC : col0 - j * PC);
 #pragma unroll
-            for (int Y = 0; Y < NRP; ++Y) c1[Y * pitch] += acc[Y];
+            for (int q = 0; q < NV; ++q) {
+                float4 v = c[q];
+                if (4 * q + 0 - A >= 0 && 4 * q + 0 - A < NRP) v.x += acc[(4 * q + 0 - A >= 0 && 4 * q + 0 - A < NRP) ? 4 * q + 0 - A : 0];
+                if (4 * q + 1 - A >= 0 && 4 * q + 1 - A < NRP) v.y += acc[(4 * q + 1 - A >= 0 && 4 * q + 1 - A < NRP) ? 4 * q + 1 - A : 0];
+                if (4 * q + 2 - A >= 0 && 4 * q + 2 - A < NRP) v.z += acc[(4 * q + 2 - A >= 0 && 4 * q + 2 - A < NRP) ? 4 * q + 2 - A : 0];
+                if (4 * q + 3 - A >= 0 && 4 * q + 3 - A < NRP) v.w += acc[(4 * q + 3 - A >= 0 && 4 * q + 3 - A < NRP) ? 4 * q + 3 - A : 0];
+                c[q] = v;
+            }
             __syncwarp();
-        }
-    }
-}
-
-template <int RB>
-__device__ __forceinline__ void ks2_tile(const float* __restrict__ tab, const float (&d)[8], float* __restrict__ org, const int pitch, const int lane) {
-    constexpr int P = ks2_rows_per_pass(RB);
-    if (P == 8) {
-        ks2_pass<RB, 8>(tab, d, org, pitch, lane);
-    } else {
-#pragma unroll
-        for (int p = 0; p < 8 / P; ++p) {
-            float dP[P];
-#pragma unroll
-            for (int y = 0; y < P; ++y) dP[y] = d[p * P + y];
-            ks2_pass<RB, P>(tab + p * P * (RB + 1) * 32, dP, org + p * P * pitch, pitch, lane);
         }
     }
 }
@@ -110,12 +120,13 @@ template <int RBMAX, int WARPS>
 __global__ void __launch_bounds__(WARPS * 32)
 ks2_kernel(const Ks2Params p, int* __restrict__ workCounter) {
     constexpr int RBMIN = (RBMAX == 8) ? 0 : 9;
-    constexpr int PITCH = 32 + 2 * RBMAX;
+    constexpr int PC = ks2_col_pitch(RBMAX), ROWS = ks2_rows(RBMAX);
     extern __shared__ __align__(16) float smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     float* patch = smem + (size_t)warp * ks2_warp_floats(RBMAX);
     float* tab = patch + ks2_patch_floats(RBMAX);
-    uint16_t* llist = reinterpret_cast<uint16_t*>(tab + ks2_table_floats(RBMAX));   // [KS2_MAXL] layer | rb << 8
+    // layer list entry q (layer | rb << 8) lives in the pad of patch column q / 8
+    auto llist = [&](int q) -> uint16_t& { return reinterpret_cast<uint16_t*>(patch + (q >> 3) * PC + ROWS)[q & 7]; };
     const int nItems = p.nz * p.tiles;
     const int R = p.Rx * p.Ry;
     const int bevPitch = p.Rx + 64;
@@ -136,14 +147,18 @@ ks2_kernel(const Ks2Params p, int* __restrict__ workCounter) {
                 if (own <= 32u) { rb = p.batchRad[l * 34 + own]; if (rb > KS2_MAXRB) rb = -1; }
             }
             const unsigned m = __ballot_sync(0xffffffffu, rb >= 0);
-            if (rb >= 0) llist[n + __popc(m & ((1u << lane) - 1u))] = (uint16_t)(l | (rb << 8));
+            if (rb >= 0) llist(n + __popc(m & ((1u << lane) - 1u))) = (uint16_t)(l | (rb << 8));
             n += __popc(m);
             imax = max(imax, rb);
         }
         imax = __reduce_max_sync(0xffffffffu, imax);
         if (imax < RBMIN || imax > RBMAX) continue;
-        const int nr = 8 + 2 * imax, nc = 32 + 2 * imax;
-        for (int i = lane; i < nr * PITCH; i += 32) patch[i] = 0.0f;
+        // zero the columns this item can touch (rows 0..ROWS-1 only: the pads hold the layer list)
+        const int nr = 8 + 2 * imax, nc = 32 + 2 * imax, c0 = RBMAX - imax;
+        for (int i = lane; i < nc * (ROWS / 4); i += 32) {
+            const int c = i / (ROWS / 4), q = i - c * (ROWS / 4);
+            reinterpret_cast<float4*>(patch + (c0 + c) * PC)[q] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        }
         __syncwarp();
         const int tx = tile % p.tilesX, ty = tile / p.tilesX;
         const size_t tileOff = (size_t)kk * R + (size_t)(ty * 8) * p.Rx + tx * 32 + lane;
@@ -151,17 +166,17 @@ ks2_kernel(const Ks2Params p, int* __restrict__ workCounter) {
         // software pipeline: the next layer's 16 loads are in flight while the current layer is processed
         float dn[8], rn[8];
         {
-            const size_t src = (size_t)(llist[0] & 0xff) * layerStride + tileOff;
+            const size_t src = (size_t)(llist(0) & 0xff) * layerStride + tileOff;
 #pragma unroll
             for (int y = 0; y < 8; ++y) { dn[y] = __ldg(p.idd + src + (size_t)y * p.Rx); rn[y] = __ldg(p.rsig + src + (size_t)y * p.Rx); }
         }
         for (int q = 0; q < n; ++q) {
-            const int rb = llist[q] >> 8;
+            const int rb = llist(q) >> 8;
             float d[8], r[8];
 #pragma unroll
             for (int y = 0; y < 8; ++y) { d[y] = dn[y]; r[y] = rn[y]; }
             if (q + 1 < n) {
-                const size_t src = (size_t)(llist[q + 1] & 0xff) * layerStride + tileOff;
+                const size_t src = (size_t)(llist(q + 1) & 0xff) * layerStride + tileOff;
 #pragma unroll
                 for (int y = 0; y < 8; ++y) { dn[y] = __ldg(p.idd + src + (size_t)y * p.Rx); rn[y] = __ldg(p.rsig + src + (size_t)y * p.Rx); }
             }
@@ -183,9 +198,8 @@ ks2_kernel(const Ks2Params p, int* __restrict__ workCounter) {
                 }
             }
             __syncwarp();
-            float* org = patch + (imax - rb) * PITCH + (imax - rb);
             switch (rb) {
-#define RTD_KS2_CASE(N) case N: if (N <= RBMAX) ks2_tile<(N <= RBMAX) ? N : 0>(tab, d, org, PITCH, lane); break;
+#define RTD_KS2_CASE(N) case N: if (N <= RBMAX) ks2_tile<(N <= RBMAX) ? N : 0, RBMAX>(tab, d, patch, lane); break;
                 RTD_KS2_CASE(0) RTD_KS2_CASE(1) RTD_KS2_CASE(2) RTD_KS2_CASE(3) RTD_KS2_CASE(4) RTD_KS2_CASE(5) RTD_KS2_CASE(6)
                 RTD_KS2_CASE(7) RTD_KS2_CASE(8) RTD_KS2_CASE(9) RTD_KS2_CASE(10) RTD_KS2_CASE(11) RTD_KS2_CASE(12) RTD_KS2_CASE(13)
                 RTD_KS2_CASE(14) RTD_KS2_CASE(15) RTD_KS2_CASE(16)
@@ -194,11 +208,12 @@ ks2_kernel(const Ks2Params p, int* __restrict__ workCounter) {
             }
             __syncwarp();
         }
-        // one reduction of the whole patch into the haloed BEV dose (z index = absolute step, 32-px halo)
+        // one reduction of the touched part of the patch into the haloed BEV dose (z index = absolute step, 32-px halo):
+        // patch (column c0 + cc, row c0 + rr)  ->  BEV (tile column - imax + cc, tile row - imax + rr)
         float* out = p.bev + ((size_t)(kk + p.first) * (p.Ry + 64) + (ty * 8 + 32 - imax)) * bevPitch + tx * 32 + 32 - imax;
         for (int rr = 0; rr < nr; ++rr) {
             for (int cc = lane; cc < nc; cc += 32) {
-                const float v = patch[rr * PITCH + cc];
+                const float v = patch[(c0 + cc) * PC + c0 + rr];
                 if (v != 0.0f) atomicAdd(out + (size_t)rr * bevPitch + cc, v);
             }
         }
