@@ -185,16 +185,24 @@ ks2_kernel(const Ks2Params p, int* __restrict__ workCounter) {
             for (int y = 0; y < 8; ++y) any |= d[y] > 0.0f;
             if (!__any_sync(0xffffffffu, any)) continue;      // __syncthreads_or(dose > 0), cuh:456
             // erf-difference weights (cuh:459-467) -> table: e[0] = erf(r/2), e[i] = (erf(r(i+1/2)) - erf(r(i-1/2)))/2
+            // the 8 rows advance together so that 8 independent polynomial chains are in flight per lane; the argument
+            // r (i + 1/2) is advanced by repeated addition
+            {
+                float x[8], erfOld[8];
+                float* t = tab + lane;
+                const int rowStride = (rb + 1) * 32;
 #pragma unroll
-            for (int y = 0; y < 8; ++y) {
-                float erfOld = ks_erf_pos(r[y] * 0.5f);
-                float* t = tab + (y * (rb + 1)) * 32 + lane;
-                t[0] = erfOld;
+                for (int y = 0; y < 8; ++y) { x[y] = r[y] * 0.5f; erfOld[y] = ks_erf_pos(x[y]); t[y * rowStride] = erfOld[y]; }
 #pragma unroll 1
                 for (int i = 1; i <= rb; ++i) {
-                    const float erfNew = ks_erf_pos(r[y] * ((float)i + 0.5f));
-                    t[i * 32] = 0.5f * (erfNew - erfOld);
-                    erfOld = erfNew;
+                    t += 32;
+#pragma unroll
+                    for (int y = 0; y < 8; ++y) {
+                        x[y] += r[y];
+                        const float erfNew = ks_erf_pos(x[y]);
+                        t[y * rowStride] = 0.5f * (erfNew - erfOld[y]);
+                        erfOld[y] = erfNew;
+                    }
                 }
             }
             __syncwarp();
