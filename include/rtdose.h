@@ -191,6 +191,12 @@ rtd_status rtd_plan_dose(rtd_ctx* ctx, const float* ctHuPlus1000, int nx, int ny
 rtd_status rtd_plan_dose_device(rtd_ctx* ctx, const float* ctHuPlus1000, int nx, int ny, int nz, const rtd_beam* beams, int nBeams,
                                 float* dDoseInOut, const rtd_opts* opts, rtd_timing* timing);
 
+/* Multi-GPU tail: after the ranks' partial dose grids have been summed on one device (NCCL reduce, issued
+ * by the caller on rtd_stream), add the non-zero voxels of dSrc[0..n) onto the caller's HOST dose grid hostDst[0..n)
+ * (the accumulate semantics of kernel_wrapper.cu:91-93 for the whole plan). A pinned hostDst is updated in place over
+ * PCIe (only voxels that received dose travel); a pageable one is staged. modifiedOut (optional): voxels updated. */
+rtd_status rtd_add_device_to_host(rtd_ctx* ctx, const float* dSrc, float* hostDst, size_t n, int64_t* modifiedOut);
+
 /* Integer/index outputs of the last call (the reference's bit-exact quantities). */
 rtd_status rtd_get_beam_report(const rtd_ctx* ctx, int beamNo, rtd_beam_report* out);
 rtd_status rtd_get_layer_report(const rtd_ctx* ctx, int beamNo, int layerNo, rtd_layer_report* out);

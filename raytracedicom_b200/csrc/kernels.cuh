@@ -280,11 +280,14 @@ idd_sigma_kernel(const float* __restrict__ density, const float* __restrict__ we
     size_t outIdx = (size_t)l * q.nz * R + ray;
     size_t rmIdx = ((size_t)l * q.nz * q.Ry + y) * (q.Rx / 32) + blockIdx.x;
     const int lane = threadIdx.x & 31;
+    // WEPL and density of the next step are requested one iteration ahead (the depth scan is a dependent chain)
+    float wNext = 0.0f, rhoNext = 0.0f;
+    if (live && first < (unsigned)lp.afterLast) { wNext = wepl[inIdx]; rhoNext = density[inIdx]; }
     for (unsigned k = first; k < (unsigned)lp.afterLast; ++k) {
+        const float w = wNext, rho = rhoNext;
+        if (live && k + 1 < (unsigned)lp.afterLast) { wNext = wepl[inIdx + R]; rhoNext = density[inIdx + R]; }
         if (live) {
-            const float w = wepl[inIdx];
             const float d = tex2D<float>(iddTex, f_fma(w, lp.energyScale, 0.5f), f_add(lp.energyIdx, 0.5f));
-            const float rho = density[inIdx];
             if (w < lp.peakDepth) {
                 const float resE = f_ex2(f_mul(f_lg2(f_sub(lp.peakDepth, f_mul(f_add(wOld, w), 0.5f))), 0.5649718f));
                 const float e1 = f_fma(resE, 8.639415f, 938.3f);
@@ -320,7 +323,9 @@ idd_sigma_kernel(const float* __restrict__ density, const float* __restrict__ we
         rsig[outIdx] = rs;
         // row minimum of rSigmaEff for the tile radius; its sign carries "some voxel of this row has dose > 0"
         // (a tile without dose is skipped by the superposition exactly like the reference's __syncthreads_or, cuh:456)
-        const float m = warp_min(rs);
+        // rs is positive or +inf: its bit pattern orders like an unsigned integer -> one REDUX instead of 5 shuffle+min pairs
+        const unsigned rsBits = __float_as_uint(rs);
+        const float m = __any_sync(0xffffffffu, (int)rsBits < 0) ? warp_min(rs) : __uint_as_float(__reduce_min_sync(0xffffffffu, rsBits));
         const bool anyDose = __any_sync(0xffffffffu, res > 0.0f);
         if (lane == 0) rowMin[rmIdx] = anyDose ? m : -m;
         inIdx += R; outIdx += R; rmIdx += (size_t)q.Ry * (q.Rx / 32);
@@ -571,12 +576,15 @@ bev_to_grid_kernel(const float* __restrict__ bev, float* __restrict__ dose, cons
     const float sx = f_add(f_fma(g.t.coefIdxI.x, fi, f_mul(g.t.coefIdxJ.x, fj)), g.t.coefOffset.x);
     const float sy = f_add(f_fma(g.t.coefIdxI.y, fi, f_mul(g.t.coefIdxJ.y, fj)), g.t.coefOffset.y);
     const float sz = f_add(f_fma(g.t.coefIdxI.z, fi, f_mul(g.t.coefIdxJ.z, fj)), g.t.coefOffset.z);
-    float* res = dose + ((size_t)g.minZ * g.ny + y) * g.nx + x;
+    // blockIdx.z splits the z range so that a box of a few hundred (x, y) tiles still fills the machine
+    const int zPer = (g.maxZ - g.minZ + (int)gridDim.z) / (int)gridDim.z;
+    const int zBeg = g.minZ + (int)blockIdx.z * zPer, zEnd = min(zBeg + zPer - 1, g.maxZ);
+    float* res = dose + ((size_t)zBeg * g.ny + y) * g.nx + x;
     const size_t zs = (size_t)g.nx * g.ny;
     const size_t plane = (size_t)g.W * g.H;
     const int D = g.zEnd - g.first;
     const float* base = bev + (size_t)g.first * plane;
-    for (int z = inside ? g.minZ : g.maxZ + 1; z <= g.maxZ; ++z, res += zs) {
+    for (int z = inside ? zBeg : zEnd + 1; z <= zEnd; ++z, res += zs) {
         // getFanIdx(k) (cu:27-34) + HALF
         const float fk = i2f(z);
         const float rx = f_fma(g.t.inc.x, fk, sx), ry = f_fma(g.t.inc.y, fk, sy), rz = f_fma(g.t.inc.z, fk, sz);
@@ -601,6 +609,19 @@ bev_to_grid_kernel(const float* __restrict__ bev, float* __restrict__ dose, cons
         nMod = __reduce_add_sync(0xffffffffu, nMod);
         if ((threadIdx.x & 31) == 0 && nMod) atomicAdd(modified, (unsigned long long)nMod);
     }
+}
+
+// Multi-GPU tail: dst[i] += src[i] where src[i] != 0; dst may be the caller's pinned host grid (mapped pointer), so only
+// voxels that received dose cross PCIe. One warp-aggregated count of the voxels touched.
+__global__ void __launch_bounds__(256)
+add_nonzero_kernel(const float* __restrict__ src, float* __restrict__ dst, const size_t n, unsigned long long* __restrict__ modified) {
+    unsigned nMod = 0;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const float v = src[i];
+        if (v != 0.0f) { dst[i] += v; ++nMod; }
+    }
+    nMod = __reduce_add_sync(0xffffffffu, nMod);
+    if ((threadIdx.x & 31) == 0 && nMod && modified) atomicAdd(modified, (unsigned long long)nMod);
 }
 
 }  // namespace rtd

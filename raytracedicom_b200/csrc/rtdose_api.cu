@@ -411,6 +411,8 @@ rtd_status beamPhaseB1(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opt
     if (gp.maxX >= gp.minX && gp.maxY >= gp.minY && gp.maxZ >= gp.minZ) {
         w.doTransfer = true;
         w.gpGrid = dim3((gp.maxX - gp.minX + 32) / 32, (gp.maxY - gp.minY + 8) / 8);
+        const int tilesXY = int(w.gpGrid.x * w.gpGrid.y), nzBox = gp.maxZ - gp.minZ + 1;
+        w.gpGrid.z = unsigned(std::max(1, std::min({(8 * ctx->smCount + tilesXY - 1) / tilesXY, nzBox, 64})));   // ~8 CTAs per SM
     }
     return RTD_OK;
 }
@@ -822,6 +824,39 @@ rtd_status rtd_plan_dose(rtd_ctx* ctx, const float* ct, int nx, int ny, int nz, 
 rtd_status rtd_plan_dose_device(rtd_ctx* ctx, const float* ct, int nx, int ny, int nz, const rtd_beam* beams, int nBeams, float* dDose,
                                 const rtd_opts* opts, rtd_timing* tm) {
     return planDose(ctx, ct, nx, ny, nz, beams, nBeams, nullptr, dDose, opts, tm);
+}
+
+rtd_status rtd_add_device_to_host(rtd_ctx* ctx, const float* dSrc, float* hostDst, size_t n, int64_t* modifiedOut) {
+    if (!ctx) return RTD_ERR_INVALID;
+    if (!dSrc || !hostDst) return fail(ctx, RTD_ERR_INVALID, "rtd_add_device_to_host: null pointer");
+    RTD_CUDA(cudaSetDevice(ctx->device));
+    if (modifiedOut) *modifiedOut = 0;
+    if (n == 0) return RTD_OK;
+    cudaPointerAttributes a0, a1;
+    float* mapped = nullptr;
+    if (cudaPointerGetAttributes(&a0, hostDst) == cudaSuccess && cudaPointerGetAttributes(&a1, hostDst + (n - 1)) == cudaSuccess &&
+        a0.type == cudaMemoryTypeHost && a1.type == cudaMemoryTypeHost && a0.devicePointer &&
+        (char*)a1.devicePointer - (char*)a0.devicePointer == (ptrdiff_t)((n - 1) * 4))
+        mapped = (float*)a0.devicePointer;
+    cudaGetLastError();
+    if (mapped) {
+        RTD_CUDA(ctx->xferCount.ensure(8)); RTD_CUDA(ctx->hXferCount.ensure(8));
+        RTD_CUDA(cudaMemsetAsync(ctx->xferCount.p, 0, 8, ctx->stream));
+        const int blocks = (int)std::min<size_t>((n + 255) / 256, size_t(ctx->smCount) * 16);
+        add_nonzero_kernel<<<blocks, 256, 0, ctx->stream>>>(dSrc, mapped, n, ctx->xferCount.as<unsigned long long>());
+        RTD_CUDA(cudaGetLastError());
+        RTD_CUDA(cudaMemcpyAsync(ctx->hXferCount.p, ctx->xferCount.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
+        RTD_CUDA(cudaStreamSynchronize(ctx->stream));
+        if (modifiedOut) *modifiedOut = (int64_t)*ctx->hXferCount.as<unsigned long long>();
+    } else {   // pageable destination: stage through host memory
+        std::vector<float> tmp(n);
+        RTD_CUDA(cudaMemcpyAsync(tmp.data(), dSrc, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        RTD_CUDA(cudaStreamSynchronize(ctx->stream));
+        int64_t m = 0;
+        for (size_t i = 0; i < n; ++i) if (tmp[i] != 0.0f) { hostDst[i] += tmp[i]; ++m; }
+        if (modifiedOut) *modifiedOut = m;
+    }
+    return RTD_OK;
 }
 
 rtd_status rtd_get_beam_report(const rtd_ctx* ctx, int beamNo, rtd_beam_report* out) {

@@ -93,7 +93,7 @@ class RtdError(RuntimeError):
 
 
 EXPORTS = ["rtd_default_opts", "rtd_create", "rtd_destroy", "rtd_last_error", "rtd_version", "rtd_set_luts", "rtd_set_ct",
-           "rtd_set_ct_device", "rtd_set_dose_grid", "rtd_dose", "rtd_dose_device", "rtd_plan_dose", "rtd_plan_dose_device", "rtd_get_beam_report",
+           "rtd_set_ct_device", "rtd_set_dose_grid", "rtd_dose", "rtd_dose_device", "rtd_plan_dose", "rtd_plan_dose_device", "rtd_add_device_to_host", "rtd_get_beam_report",
            "rtd_get_layer_report", "rtd_debug_fetch", "rtd_stream"]
 
 _lib = None
@@ -123,6 +123,7 @@ def load_library() -> C.CDLL:
     lib.rtd_plan_dose.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.POINTER(RtdBeam), C.c_int, vp, C.POINTER(RtdOpts), C.POINTER(RtdTiming)]
     lib.rtd_plan_dose.restype = C.c_int
     lib.rtd_plan_dose_device.argtypes = lib.rtd_plan_dose.argtypes; lib.rtd_plan_dose_device.restype = C.c_int
+    lib.rtd_add_device_to_host.argtypes = [vp, vp, vp, C.c_size_t, C.POINTER(C.c_int64)]; lib.rtd_add_device_to_host.restype = C.c_int
     lib.rtd_get_beam_report.argtypes = [vp, C.c_int, C.POINTER(RtdBeamReport)]; lib.rtd_get_beam_report.restype = C.c_int
     lib.rtd_get_layer_report.argtypes = [vp, C.c_int, C.c_int, C.POINTER(RtdLayerReport)]; lib.rtd_get_layer_report.restype = C.c_int
     lib.rtd_debug_fetch.argtypes = [vp, C.c_int, C.c_int, C.c_int, vp, C.c_size_t]; lib.rtd_debug_fetch.restype = C.c_int
@@ -253,6 +254,12 @@ class DoseEngine:
         self._check(fn(self._h, C.c_void_p(ct_ptr), nx, ny, nz, packed, n_beams, C.c_void_p(dose_ptr),
                                            C.byref(self.opts), C.byref(self.timing)))
         return self.timing
+
+    def add_device_to_host(self, d_src_ptr: int, host_dst_ptr: int, n: int) -> int:
+        """host[i] += device[i] where device[i] != 0 (multi-GPU tail, rtd_add_device_to_host); returns the voxels updated."""
+        m = C.c_int64(0)
+        self._check(self.lib.rtd_add_device_to_host(self._h, C.c_void_p(d_src_ptr), C.c_void_p(host_dst_ptr), n, C.byref(m)))
+        return int(m.value)
 
     def beam_report(self, beam_no: int) -> dict:
         r = RtdBeamReport()

@@ -61,3 +61,30 @@ def test_two_rank_sharded_plan_sums_to_whole_plan(tmp_path):
     assert int(r["u"]) == int(r["total_u"])                    # the metric's unit count is shard-invariant
     assert all(n >= 1 for n in r["n_items"])
     assert rel_to_max(r["reduced"], r["whole"])[0] < 1e-6        # fp32 sum order differs between 1 and 2 ranks
+
+
+def test_reduced_dose_slab_contains_every_beam(oracle):
+    """sharding.dose_slab: the z-slab that is zeroed / reduced over NCCL is derived from geometry alone and must contain
+    every voxel any beam can reach - checked with the oracle on two oblique diverging beams in a tall dose grid."""
+    from raytracedicom_b200 import cases, sharding
+    luts = cases.load_packaged_luts()
+    nx, ny, nz = 96, 96, 200
+    ct = np.full((nz, ny, nx), 1000.0, np.float32)
+    beams = []
+    for ang, zc in ((20.0, 70.0), (250.0, 120.0)):
+        m, v = cases.gantry_to_im_idx(ang, (48.0, 48.0, zc), (0.0, 0.0, 0.0), (1.0, 1.0, 1.0))
+        zstart, steps = cases.steps_and_start(m, v, (nx, ny, nz))
+        w = np.full((2, 3, 3), 60.0, np.float32)
+        beams.append(cases.Beam(w, np.array([75.0, 80.0], np.float32), np.full((2, 2), 3.0, np.float32), (1.0, 1.0), steps, (2000.0, 1800.0),
+                                (4.0, 4.0, -1.0), (-4.0, -4.0, zstart), m, v))
+    case = cases.Case("slab", ct, beams, luts)
+    z0, z1 = sharding.dose_slab(case.beams, case.dose_dims)
+    assert 0 < z0 < z1 < nz - 1                       # a real restriction for this plan
+    dose = np.zeros((nz, ny, nx), np.float32)
+    for b in range(2):
+        oracle.run_beam(case, b, dose=dose)
+    zs = np.nonzero(dose.reshape(nz, -1).any(axis=1))[0]
+    assert zs.size > 0 and z0 <= zs.min() and zs.max() <= z1
+    # each beam alone is inside its own slab too, and the plan's slab is the union
+    s0, s1 = sharding.dose_slab(case.beams[:1], case.dose_dims), sharding.dose_slab(case.beams[1:], case.dose_dims)
+    assert (min(s0[0], s1[0]), max(s0[1], s1[1])) == (z0, z1)
