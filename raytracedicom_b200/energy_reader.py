@@ -39,6 +39,10 @@ class EnergyStruct:
     nRRlSamples: int = 0
     rRlScaleFact: float = 0.0
     rRlVector: np.ndarray = field(default_factory=lambda: np.zeros(0, np.float32))
+    # NUCLEAR_CORR builds only (energy_struct.h:33-36): nuclear-halo weight and variance, same shape as ciddMatrix
+    nucWeightMatrix: np.ndarray = field(default_factory=lambda: np.zeros(0, np.float32))
+    nucSqSigmaMatrix: np.ndarray = field(default_factory=lambda: np.zeros(0, np.float32))
+    nuclearCorr: int = 0          # 0 = none, else the model the two matrices belong to (NUCLEAR_MODELS)
 
     def validate(self) -> None:
         if self.nEnergies < 2 or self.nEnergySamples < 2:
@@ -50,8 +54,16 @@ class EnergyStruct:
                         ("spVector", self.nSpSamples), ("rRlVector", self.nRRlSamples)):
             if getattr(self, name).size != n:
                 raise ValueError(f"EnergyStruct: {name} has {getattr(self, name).size} entries, expected {n}")
+        if self.nuclearCorr and (self.nucWeightMatrix.size != self.ciddMatrix.size or self.nucSqSigmaMatrix.size != self.ciddMatrix.size):
+            raise ValueError("EnergyStruct: nuclear matrices must have the shape of ciddMatrix")
         if np.any(np.diff(self.energiesPerU) <= 0):
             raise ValueError("EnergyStruct: energiesPerU must be strictly increasing (vector_find.h:130)")
+
+
+# rtd_opts.nuclearCorr / orc_opts.nuclearCorr: 0 = off (the reference's default build), 1.. = the reference's
+# NUCLEAR_CORR models SOUKUP / FLUKA / GAUSS_FIT (CMakeLists.txt:57-62; the reference numbers them 0 / 1 / 2)
+NUCLEAR_MODELS = {"soukup": 1, "fluka": 2, "gauss_fit": 3}
+NUCLEAR_FILES = {1: "nuclear_weights_and_sigmas_Soukup.txt", 2: "nuclear_weights_and_sigmas_Fluka.txt", 3: "nuclear_weights_and_sigmas_fit.txt"}
 
 
 def _tokens(path: str) -> np.ndarray:
@@ -72,7 +84,7 @@ def _read_1d(path: str):
     return n, scale, t[2:2 + n].astype(np.float32)
 
 
-def energy_reader(data_path: str, water_cube_test: bool = False) -> EnergyStruct:
+def energy_reader(data_path: str, water_cube_test: bool = False, nuclear_corr: int = 0) -> EnergyStruct:
     """Text LUT loader; ``data_path`` must end with a separator exactly like the reference's
     PHYS_DATA_DIRECTORY (energy_reader.cpp:19 concatenates ``dataPath + file``).
 
@@ -94,6 +106,22 @@ def energy_reader(data_path: str, water_cube_test: bool = False) -> EnergyStruct
     e.nSpSamples, e.spScaleFact, e.spVector = _read_1d(data_path + "HU_to_SP_H&N_adj.txt")
     rl = "radiation_length_inc_water.txt" if water_cube_test else "radiation_length.txt"
     e.nRRlSamples, e.rRlScaleFact, e.rRlVector = _read_1d(data_path + rl)
+    if nuclear_corr:
+        # energy_reader.cpp:103-162: same header as the IDD file (checked to 0.01), then the two matrices
+        name = NUCLEAR_FILES[nuclear_corr]
+        t = _tokens(data_path + name)
+        if int(t[0]) != nS or int(t[1]) != nE:
+            raise RuntimeError(f"Number of samples or energies in {name} different from proton_cumul_ddd_data.txt")
+        p = 2
+        for what, ref in (("Energies", e.energiesPerU), ("Peak depths", e.peakDepths), ("Scale facts", e.scaleFacts)):
+            if np.any(np.abs(t[p:p + nE].astype(np.float32) - ref) > 0.01):
+                raise RuntimeError(f"{what} in {name} different from proton_cumul_ddd_data.txt")
+            p += nE
+        if t.size < p + 2 * nE * nS:
+            raise RuntimeError(f"{name}: truncated")
+        e.nucWeightMatrix = t[p:p + nE * nS].astype(np.float32); p += nE * nS
+        e.nucSqSigmaMatrix = t[p:p + nE * nS].astype(np.float32)
+        e.nuclearCorr = nuclear_corr
     e.validate()
     return e
 

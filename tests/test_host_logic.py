@@ -90,3 +90,17 @@ def test_shard_keeps_whole_beam_geometry():
     s = c.beams[0].shard(1, 3)
     assert s.weights is c.beams[0].weights or np.array_equal(s.weights, c.beams[0].weights)
     assert (s.layer_begin, s.layer_end) == (1, 3) and s.n_layers == c.beams[0].n_layers
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference/LUTs"), reason="needs the reference's LUT text files (build container only)")
+def test_energy_reader_loads_the_nuclear_luts_like_the_reference():
+    """energy_reader.cpp:103-162 (NUCLEAR_CORR builds): header checked against the IDD file, then two matrices of the
+    IDD matrix's shape. The dose engine does not consume them: the reference's nuclear path is not functional as shipped
+    (kernel_wrapper.cu:925 passes nucMemStep = 0)."""
+    from raytracedicom_b200 import energy_reader as er
+    base = er.energy_reader("/root/reference/LUTs/")
+    for name, model in er.NUCLEAR_MODELS.items():
+        e = er.energy_reader("/root/reference/LUTs/", nuclear_corr=model)
+        assert e.nuclearCorr == model and e.nucWeightMatrix.shape == base.ciddMatrix.shape == e.nucSqSigmaMatrix.shape
+        assert -0.05 < e.nucWeightMatrix.min() and e.nucWeightMatrix.max() < 1.0 and np.isfinite(e.nucSqSigmaMatrix).all()
+        assert np.array_equal(e.ciddMatrix, base.ciddMatrix)
