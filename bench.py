@@ -158,6 +158,11 @@ def main():
     ap.add_argument("--workload", default="c3", help="c3 (default: 512x512x200 CT, 3 fields), c1a, c2, c4, c5, mini")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--reduce", default="push", choices=["push", "peer", "nccl"],
+                    help="N > 1, how the ranks' partial doses meet in ONE grid on rank 0 (mapped by every rank over CUDA IPC): 'push' = each "
+                         "rank adds the float4 groups of its slab that hold dose with 16-byte vector reductions over NVLink; 'peer' = the "
+                         "transfer kernels themselves add into the mapped grid (scalar reductions, NVLink packet-rate bound); "
+                         "'nccl' = local partial grids + one dense NCCL reduce of the reachable slab")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -203,14 +208,68 @@ def main():
     # N > 1: only the z-slab of the dose grid that the plan's beams can reach (geometry alone, same on every rank) is
     # zeroed and summed over NCCL; the rest of every partial grid stays zero (checked once after the warm-up)
     z0, z1 = (0, nz - 1) if world == 1 else sharding.dose_slab(case.beams, case.dose_dims)
-    slab = dose_dev[z0:z1 + 1]
     e2e_extra = {"mod": 0}
+    # N > 1, --reduce peer: the transfer kernels of every rank accumulate straight into rank 0's grid over NVLink
+    # (rtd_shared_dose_*, opts.atomicDose): the reduce is fused into the kernel that produces the data. Falls back to the
+    # NCCL reduce when the IPC mapping is not available.
+    peer = world > 1 and args.reduce in ("peer", "push")
+    push = args.reduce == "push"
+    shared_ptr, token = 0, torch.zeros(1, dtype=torch.int32, device=dev)
+    if peer:
+        handle = [None]
+        try:
+            if rank == 0:
+                shared_ptr, handle[0] = eng.shared_dose_create(nz * ny * nx)
+        except Exception as ex:          # noqa: BLE001 - reported in the JSON line
+            handle[0] = f"error: {ex}"
+        dist.broadcast_object_list(handle, src=0)
+        ok = torch.ones(1, dtype=torch.int32, device=dev)
+        if isinstance(handle[0], str):
+            ok.zero_()
+        elif rank != 0:
+            try:
+                shared_ptr = eng.shared_dose_open(handle[0])
+            except Exception:            # noqa: BLE001
+                ok.zero_()
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        peer = bool(ok.item())
+    if peer:
+        class _Ext:                       # zero-copy torch view of the shared grid (rank 0 zeroes / reads it through torch)
+            __cuda_array_interface__ = {"shape": (nz, ny, nx), "typestr": "<f4", "data": (shared_ptr, False), "version": 2}
+        if rank == 0:
+            dose_dev = torch.as_tensor(_Ext(), device=dev)
+        # push: only rank 0 writes its grid while pushes of the others may land in it -> its own transfers are atomic too
+        eng.opts.atomicDose = 1 if (not push or rank == 0) else 0
+    push = push and peer
+    slab = dose_dev[z0:z1 + 1]
+    slab_off = z0 * ny * nx * 4
+
+    def dose_target():
+        return shared_ptr if (peer and (rank == 0 or not push)) else dose_dev.data_ptr()
+
+    def before_dose():
+        if not peer or push or rank == 0:
+            slab.zero_()
+        if peer:
+            stream_barrier()                                      # rank 0's grid is zeroed before anything is added into it
+
+    def after_dose():
+        if push and rank != 0:
+            eng.push_dose_to_peer(slab.data_ptr(), shared_ptr + slab_off, slab.numel())
+        if peer:
+            stream_barrier()                                      # every rank's contributions have landed
+        else:
+            sharding.reduce_dose(slab, dst=0)
+
+    def stream_barrier():
+        # orders the streams of all ranks without a host sync: a 4-byte all-reduce on the engine's stream
+        dist.all_reduce(token)
 
     def step_device():
         with torch.cuda.stream(stream):
-            slab.zero_()
-            t = eng.dose_ptr(packed, len(mine), dose_dev.data_ptr(), device=True)
-            sharding.reduce_dose(slab, dst=0)
+            before_dose()
+            t = eng.dose_ptr(packed, len(mine), dose_target(), device=True)
+            after_dose()
         return t
 
     def barrier():
@@ -222,7 +281,7 @@ def main():
     for _ in range(args.warmup):
         step_device()
     barrier()
-    if world > 1 and (bool(dose_dev[:z0].any().item()) or bool(dose_dev[z1 + 1:].any().item())):
+    if world > 1 and (not peer or push or rank == 0) and (bool(dose_dev[:z0].any().item()) or bool(dose_dev[z1 + 1:].any().item())):
         raise SystemExit(f"bench.py: rank {rank} deposited dose outside the reduced slab [{z0}, {z1}]")
     sampler = ClockSampler(local); sampler.start()
     evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
@@ -278,9 +337,9 @@ def main():
             # one NCCL reduce of the reachable slab; rank 0 adds the summed dose onto the caller's pinned host grid in
             # place (rtd_add_device_to_host: only voxels that received dose cross PCIe)
             with torch.cuda.stream(stream):
-                slab.zero_()
-                t = eng.plan_dose_ptr(ct_host.data_ptr(), cnx, cny, cnz, packed, len(mine), dose_dev.data_ptr(), device=True)
-                sharding.reduce_dose(slab, dst=0)
+                before_dose()
+                t = eng.plan_dose_ptr(ct_host.data_ptr(), cnx, cny, cnz, packed, len(mine), dose_target(), device=True)
+                after_dose()
             if rank == 0:
                 e2e_extra["mod"] = eng.add_device_to_host(slab.data_ptr(), dose_host.data_ptr() + z0 * ny * nx * 4, slab.numel())
             else:
@@ -342,7 +401,7 @@ def main():
                 "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": case.name, "ct_dims": list(case.ct_dims), "beams": len(case.beams), "layers": int(sum(b.n_layers for b in case.beams)),
                            "spots": int(sum(b.weights.size for b in case.beams)), "updates_per_plan": U, "ks_taps_per_plan": taps,
-                           "sharding": f"(beam, layer-range) work items, LPT over {world} rank(s); partial dose grids summed by NCCL reduce" if world > 1 else "single GPU",
+                           "sharding": (f"(beam, layer-range) work items, LPT over {world} rank(s); " + ("every rank adds the dose-holding float4 groups of its slab into ONE grid on rank 0 over NVLink (CUDA IPC, red.global.add.v4.f32), no dense collective" if push else "every rank's transfer kernels add into ONE dose grid on rank 0 over NVLink (CUDA IPC, red.global.add.f32), no separate collective" if peer else "partial dose grids (reachable z-slab) summed by one NCCL reduce")) if world > 1 else "single GPU",
                            "l2": "256 MiB buffer written between timed iterations (L2 flush); CT 4*%d B and BEV arrays exceed L2" % (nx * ny * nz)},
                 "plan_ms": ms_step, "updates_per_step": U,
                 "stage_ms_rank0": {k: stage[k] / args.steps for k in ("msTrace", "msSetup", "msConv", "msIddSigma", "msRadius", "msSuperp", "msTransfer", "msTotal")},

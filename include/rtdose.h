@@ -92,7 +92,9 @@ typedef struct {
                                 that receive dose cross PCIe); 1: always stage dose sub-volumes through device memory */
     int   noNozzle;          /* 1: the reference's -DNO_NOZZLE build: no in-air spot-size growth (fill_idd_and_sigma_params.cu:76-82) */
     int   doseToMedium;      /* 1: the reference built with DOSE_TO_WATER off: voxel mass = density x volume (kernel_wrapper.cu:314-318) */
-    int   reserved[2];
+    int   atomicDose;        /* 1: the transfers add with red.global.add.f32: the dose grid may then be ONE buffer shared by all
+                                ranks of a node (rtd_shared_dose_*), written over NVLink - no separate reduce collective */
+    int   reserved[1];
 } rtd_opts;
 
 /* Stage timing of the last rtd_dose* call (CUDA events; with concurrent beams the per-stage figures are sums over the
@@ -190,6 +192,19 @@ rtd_status rtd_plan_dose(rtd_ctx* ctx, const float* ctHuPlus1000, int nx, int ny
  * items into its partial dose grid, which is then reduced over NCCL by the caller. */
 rtd_status rtd_plan_dose_device(rtd_ctx* ctx, const float* ctHuPlus1000, int nx, int ny, int nz, const rtd_beam* beams, int nBeams,
                                 float* dDoseInOut, const rtd_opts* opts, rtd_timing* timing);
+
+/* Multi-GPU without a separate collective ("NVLS / peer stores issued from the transfer kernel"): one rank
+ * creates the plan's dose grid and exports a 64-byte CUDA IPC handle, the other ranks of the node map it, and every rank
+ * runs rtd_dose_device / rtd_plan_dose_device on the mapped pointer with opts.atomicDose = 1: the transfer kernels of all
+ * GPUs accumulate into the one grid with float reductions over NVLink / NVSwitch while they compute. The caller orders
+ * "grid zeroed" before and "all ranks done" after (a stream-ordered barrier). close: owner = 1 frees, 0 unmaps. */
+rtd_status rtd_shared_dose_create(rtd_ctx* ctx, size_t nFloats, float** dPtr, unsigned char* handle64);
+rtd_status rtd_shared_dose_open(rtd_ctx* ctx, const unsigned char* handle64, float** dPtr);
+rtd_status rtd_shared_dose_close(rtd_ctx* ctx, float* dPtr, int owner);
+/* Sparse push of a rank's partial grid onto the shared one (the faster of the two peer variants): adds the
+ * float4 groups of dSrc[0..n) that hold dose onto dPeerDst[0..n) with 16-byte vector reductions over NVLink. Asynchronous
+ * on rtd_stream; several ranks may push concurrently. Both pointers 16-byte aligned. */
+rtd_status rtd_push_dose_to_peer(rtd_ctx* ctx, const float* dSrc, float* dPeerDst, size_t n);
 
 /* Multi-GPU tail: after the ranks' partial dose grids have been summed on one device (NCCL reduce, issued
  * by the caller on rtd_stream), add the non-zero voxels of dSrc[0..n) onto the caller's HOST dose grid hostDst[0..n)

@@ -545,6 +545,7 @@ struct GridParams {
     int minX, minY, minZ, maxX, maxY, maxZ;   // inclusive bbox in dose indices
     int nx, ny, nz;                           // dose dims
     int W, H, first, zEnd;                    // BEV dims (haloed) and valid slice range [first, zEnd)
+    int atomic;                               // 1: red.global.add.f32 (the dose grid is shared by several GPUs over NVLink)
 };
 
 __device__ __forceinline__ int tex_q(float c) {   // fixed-point texel coordinate, 8 fractional bits
@@ -602,7 +603,7 @@ bev_to_grid_kernel(const float* __restrict__ bev, float* __restrict__ dose, cons
         if ((unsigned)iz < (unsigned)D && c != 256) acc = bev_plane(base + (size_t)iz * plane, g, ix, iy, a, b, 256 - c);
         if ((unsigned)(iz + 1) < (unsigned)D && c != 0) acc += bev_plane(base + (size_t)(iz + 1) * plane, g, ix, iy, a, b, c);
         const float v = acc * (1.0f / 256.0f);
-        if (v > 0.0f) { *res += v; ++nMod; }
+        if (v > 0.0f) { if (g.atomic) atomicAdd(res, v); else *res += v; ++nMod; }
     }
     // voxels modified by this launch (the bytes a host-resident dose grid exchanges over PCIe): one atomic per warp
     if (modified) {
@@ -622,6 +623,22 @@ add_nonzero_kernel(const float* __restrict__ src, float* __restrict__ dst, const
     }
     nMod = __reduce_add_sync(0xffffffffu, nMod);
     if ((threadIdx.x & 31) == 0 && nMod && modified) atomicAdd(modified, (unsigned long long)nMod);
+}
+
+// Multi-GPU push (N > 1, --reduce push): a rank's partial dose slab is added onto the plan's ONE dose grid that lives on
+// another GPU of the NVSwitch domain (peer mapping, rtd_shared_dose_open). Only float4 groups holding dose cross NVLink,
+// each as one 16-byte red.global.add.v4.f32 (a warp's 32 groups are 512 contiguous bytes); several ranks may push at
+// once. Needs src and dst 16-byte aligned; the host wrapper checks that and handles the (< 4 float) tail.
+__global__ void __launch_bounds__(256)
+push_nonzero_kernel(const float4* __restrict__ src, float4* __restrict__ dst, const size_t n4) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+        const float4 v = __ldg(src + i);
+        if (v.x != 0.0f || v.y != 0.0f || v.z != 0.0f || v.w != 0.0f) atomicAdd(dst + i, v);
+    }
+}
+__global__ void push_nonzero_tail_kernel(const float* __restrict__ src, float* __restrict__ dst, const int n) {
+    const int i = threadIdx.x;
+    if (i < n && src[i] != 0.0f) atomicAdd(dst + i, src[i]);
 }
 
 }  // namespace rtd

@@ -407,7 +407,7 @@ rtd_status beamPhaseB1(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opt
     gp.maxX = std::min(int(std::ceil(mx.x)), ctx->doseDims[0] - 1); gp.maxY = std::min(int(std::ceil(mx.y)), ctx->doseDims[1] - 1);
     gp.maxZ = std::min(int(std::ceil(mx.z)), ctx->doseDims[2] - 1);
     gp.nx = ctx->doseDims[0]; gp.ny = ctx->doseDims[1]; gp.nz = ctx->doseDims[2];
-    gp.W = Rx + 64; gp.H = Ry + 64; gp.first = w.bfi; gp.zEnd = w.Zg;
+    gp.W = Rx + 64; gp.H = Ry + 64; gp.first = w.bfi; gp.zEnd = w.Zg; gp.atomic = o.atomicDose ? 1 : 0;
     if (gp.maxX >= gp.minX && gp.maxY >= gp.minY && gp.maxZ >= gp.minZ) {
         w.doTransfer = true;
         w.gpGrid = dim3((gp.maxX - gp.minX + 32) / 32, (gp.maxY - gp.minY + 8) / 8);
@@ -826,6 +826,44 @@ rtd_status rtd_plan_dose_device(rtd_ctx* ctx, const float* ct, int nx, int ny, i
     return planDose(ctx, ct, nx, ny, nz, beams, nBeams, nullptr, dDose, opts, tm);
 }
 
+// ---- one dose grid shared by the ranks of a node (CUDA IPC over NVLink / NVSwitch) -------------------------
+rtd_status rtd_shared_dose_create(rtd_ctx* ctx, size_t nFloats, float** dPtr, unsigned char* handle64) {
+    if (!ctx) return RTD_ERR_INVALID;
+    if (!dPtr || !handle64 || nFloats == 0) return fail(ctx, RTD_ERR_INVALID, "rtd_shared_dose_create: bad arguments");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    RTD_CUDA(cudaSetDevice(ctx->device));
+    void* p = nullptr;
+    RTD_CUDA(cudaMalloc(&p, nFloats * 4));
+    cudaIpcMemHandle_t h;
+    cudaError_t e = cudaIpcGetMemHandle(&h, p);
+    if (e != cudaSuccess) { cudaFree(p); char b[256]; snprintf(b, sizeof b, "cudaIpcGetMemHandle: %s", cudaGetErrorString(e)); return fail(ctx, RTD_ERR_CUDA, b); }
+    RTD_CUDA(cudaMemsetAsync(p, 0, nFloats * 4, ctx->stream));
+    RTD_CUDA(cudaStreamSynchronize(ctx->stream));
+    memcpy(handle64, &h, 64);
+    *dPtr = (float*)p;
+    return RTD_OK;
+}
+
+rtd_status rtd_shared_dose_open(rtd_ctx* ctx, const unsigned char* handle64, float** dPtr) {
+    if (!ctx) return RTD_ERR_INVALID;
+    if (!dPtr || !handle64) return fail(ctx, RTD_ERR_INVALID, "rtd_shared_dose_open: bad arguments");
+    RTD_CUDA(cudaSetDevice(ctx->device));
+    cudaIpcMemHandle_t h; memcpy(&h, handle64, 64);
+    void* p = nullptr;
+    RTD_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    *dPtr = (float*)p;
+    return RTD_OK;
+}
+
+rtd_status rtd_shared_dose_close(rtd_ctx* ctx, float* dPtr, int owner) {
+    if (!ctx) return RTD_ERR_INVALID;
+    if (!dPtr) return RTD_OK;
+    RTD_CUDA(cudaSetDevice(ctx->device));
+    RTD_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (owner) RTD_CUDA(cudaFree(dPtr)); else RTD_CUDA(cudaIpcCloseMemHandle(dPtr));
+    return RTD_OK;
+}
+
 rtd_status rtd_add_device_to_host(rtd_ctx* ctx, const float* dSrc, float* hostDst, size_t n, int64_t* modifiedOut) {
     if (!ctx) return RTD_ERR_INVALID;
     if (!dSrc || !hostDst) return fail(ctx, RTD_ERR_INVALID, "rtd_add_device_to_host: null pointer");
@@ -856,6 +894,21 @@ rtd_status rtd_add_device_to_host(rtd_ctx* ctx, const float* dSrc, float* hostDs
         for (size_t i = 0; i < n; ++i) if (tmp[i] != 0.0f) { hostDst[i] += tmp[i]; ++m; }
         if (modifiedOut) *modifiedOut = m;
     }
+    return RTD_OK;
+}
+
+rtd_status rtd_push_dose_to_peer(rtd_ctx* ctx, const float* dSrc, float* dPeerDst, size_t n) {
+    if (!ctx) return RTD_ERR_INVALID;
+    if (!dSrc || !dPeerDst) return fail(ctx, RTD_ERR_INVALID, "rtd_push_dose_to_peer: null pointer");
+    if (((uintptr_t)dSrc | (uintptr_t)dPeerDst) & 15) return fail(ctx, RTD_ERR_INVALID, "rtd_push_dose_to_peer: pointers must be 16-byte aligned");
+    RTD_CUDA(cudaSetDevice(ctx->device));
+    const size_t n4 = n / 4;
+    if (n4) {
+        const int blocks = (int)std::min<size_t>((n4 + 255) / 256, size_t(ctx->smCount) * 16);
+        push_nonzero_kernel<<<blocks, 256, 0, ctx->stream>>>((const float4*)dSrc, (float4*)dPeerDst, n4);
+    }
+    if (n & 3) push_nonzero_tail_kernel<<<1, 32, 0, ctx->stream>>>(dSrc + n4 * 4, dPeerDst + n4 * 4, (int)(n & 3));
+    RTD_CUDA(cudaGetLastError());
     return RTD_OK;
 }
 

@@ -48,7 +48,7 @@ class RtdOpts(C.Structure):
     _fields_ = [("bpDepthCutoff", C.c_float), ("convSigmaCutoff", C.c_float), ("ksSigmaCutoff", C.c_float),
                 ("rayWeightCutoff", C.c_float), ("minTilesInBatch", C.c_int), ("keepIntermediates", C.c_int),
                 ("serialBeams", C.c_int), ("noZeroCopyDose", C.c_int), ("noNozzle", C.c_int), ("doseToMedium", C.c_int),
-                ("reserved", C.c_int * 2)]
+                ("atomicDose", C.c_int), ("reserved", C.c_int * 1)]
 
 
 class RtdTiming(C.Structure):
@@ -93,7 +93,8 @@ class RtdError(RuntimeError):
 
 
 EXPORTS = ["rtd_default_opts", "rtd_create", "rtd_destroy", "rtd_last_error", "rtd_version", "rtd_set_luts", "rtd_set_ct",
-           "rtd_set_ct_device", "rtd_set_dose_grid", "rtd_dose", "rtd_dose_device", "rtd_plan_dose", "rtd_plan_dose_device", "rtd_add_device_to_host", "rtd_get_beam_report",
+           "rtd_set_ct_device", "rtd_set_dose_grid", "rtd_dose", "rtd_dose_device", "rtd_plan_dose", "rtd_plan_dose_device", "rtd_add_device_to_host", "rtd_shared_dose_create", "rtd_shared_dose_open", "rtd_shared_dose_close", "rtd_push_dose_to_peer",
+           "rtd_get_beam_report",
            "rtd_get_layer_report", "rtd_debug_fetch", "rtd_stream"]
 
 _lib = None
@@ -124,6 +125,10 @@ def load_library() -> C.CDLL:
     lib.rtd_plan_dose.restype = C.c_int
     lib.rtd_plan_dose_device.argtypes = lib.rtd_plan_dose.argtypes; lib.rtd_plan_dose_device.restype = C.c_int
     lib.rtd_add_device_to_host.argtypes = [vp, vp, vp, C.c_size_t, C.POINTER(C.c_int64)]; lib.rtd_add_device_to_host.restype = C.c_int
+    lib.rtd_shared_dose_create.argtypes = [vp, C.c_size_t, C.POINTER(vp), C.c_char_p]; lib.rtd_shared_dose_create.restype = C.c_int
+    lib.rtd_shared_dose_open.argtypes = [vp, C.c_char_p, C.POINTER(vp)]; lib.rtd_shared_dose_open.restype = C.c_int
+    lib.rtd_shared_dose_close.argtypes = [vp, vp, C.c_int]; lib.rtd_shared_dose_close.restype = C.c_int
+    lib.rtd_push_dose_to_peer.argtypes = [vp, vp, vp, C.c_size_t]; lib.rtd_push_dose_to_peer.restype = C.c_int
     lib.rtd_get_beam_report.argtypes = [vp, C.c_int, C.POINTER(RtdBeamReport)]; lib.rtd_get_beam_report.restype = C.c_int
     lib.rtd_get_layer_report.argtypes = [vp, C.c_int, C.c_int, C.POINTER(RtdLayerReport)]; lib.rtd_get_layer_report.restype = C.c_int
     lib.rtd_debug_fetch.argtypes = [vp, C.c_int, C.c_int, C.c_int, vp, C.c_size_t]; lib.rtd_debug_fetch.restype = C.c_int
@@ -260,6 +265,24 @@ class DoseEngine:
         m = C.c_int64(0)
         self._check(self.lib.rtd_add_device_to_host(self._h, C.c_void_p(d_src_ptr), C.c_void_p(host_dst_ptr), n, C.byref(m)))
         return int(m.value)
+
+    def shared_dose_create(self, n_floats: int):
+        """(device pointer, 64-byte IPC handle) of a zeroed dose grid other ranks of the node can map (rtd_shared_dose_create)."""
+        p = C.c_void_p(); h = C.create_string_buffer(64)
+        self._check(self.lib.rtd_shared_dose_create(self._h, n_floats, C.byref(p), h))
+        return int(p.value), h.raw
+
+    def shared_dose_open(self, handle: bytes) -> int:
+        p = C.c_void_p()
+        self._check(self.lib.rtd_shared_dose_open(self._h, handle, C.byref(p)))
+        return int(p.value)
+
+    def shared_dose_close(self, ptr: int, owner: bool):
+        self._check(self.lib.rtd_shared_dose_close(self._h, C.c_void_p(ptr), 1 if owner else 0))
+
+    def push_dose_to_peer(self, d_src_ptr: int, d_peer_dst_ptr: int, n: int):
+        """peer[i] += device[i] for the float4 groups holding dose (rtd_push_dose_to_peer); asynchronous on the engine stream."""
+        self._check(self.lib.rtd_push_dose_to_peer(self._h, C.c_void_p(d_src_ptr), C.c_void_p(d_peer_dst_ptr), n))
 
     def beam_report(self, beam_no: int) -> dict:
         r = RtdBeamReport()

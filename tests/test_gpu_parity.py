@@ -310,3 +310,33 @@ def test_build_variants_against_oracle_and_rebuilt_reference(eng, oracle, mini_c
         assert r.returncode == 0, r.stderr[-1000:]
         ref = np.fromfile(tmp_path / "dose.f32", np.float32).reshape(dose.shape)
         assert rel_to_max(dose, ref)[0] <= DOSE_TOL_TIGHT
+
+
+def test_atomic_transfer_and_shared_grid_owner(eng, mini_case):
+    """opts.atomicDose (transfers add with float reductions, so that several GPUs can accumulate into one grid over NVLink)
+    gives the same dose as the plain read-modify-write, also into a grid created by rtd_shared_dose_create; the tail
+    rtd_add_device_to_host adds exactly the non-zero voxels onto a pinned and onto a pageable host grid."""
+    import torch
+    case = mini_case
+    nx, ny, nz = case.dose_dims
+    plain, _ = run_case(eng, case)
+    packed, keep = engine.pack_beams(case.beams)
+    ptr, handle = eng.shared_dose_create(nz * ny * nx)
+    assert len(handle) == 64 and ptr != 0
+    try:
+        eng.opts.atomicDose = 1
+        eng.dose_ptr(packed, len(case.beams), ptr, device=True)
+        eng.dose_ptr(packed, len(case.beams), ptr, device=True)          # accumulates: twice the dose
+    finally:
+        eng.opts.atomicDose = 0
+    for pinned in (True, False):
+        host = torch.full((nz, ny, nx), 0.5, dtype=torch.float32)
+        if pinned:
+            host = host.pin_memory()
+        n = eng.add_device_to_host(ptr, host.data_ptr(), nz * ny * nx)
+        got = host.numpy()
+        assert n == int((plain != 0).sum())
+        assert np.all(got[plain == 0] == 0.5)
+        # the sum 0.5 + dose is rounded at 0.5's ulp (2^-24 relative to 0.5 -> 3e-8 absolute)
+        assert rel_to_max(got.astype(np.float64) - 0.5, 2.0 * plain)[0] <= 1e-5 + 6.0e-8 / float(plain.max())
+    eng.shared_dose_close(ptr, owner=True)
