@@ -322,6 +322,14 @@ def main():
         dist.all_reduce(ms_t, op=dist.ReduceOp.MAX)
         dist.all_reduce(upd_local, op=dist.ReduceOp.SUM)
     ms_step = float(ms_t.item()); U = int(upd_local[0].item()); taps = int(upd_local[1].item())
+    # balance of the sharding: every rank's own stage total of the serialised extra steps (no waiting on the others in it)
+    own_ms = torch.tensor([stage["msTotal"] / args.steps], dtype=torch.float64, device=dev)
+    own_all = [torch.zeros_like(own_ms) for _ in range(world)]
+    if world > 1:
+        dist.all_gather(own_all, own_ms)
+    else:
+        own_all = [own_ms]
+    rank_stage_ms = [round(float(t.item()), 4) for t in own_all]
     checksum = float(dose_dev.double().sum().item()) if rank == 0 else 0.0
     dmax = float(dose_dev.max().item()) if rank == 0 else 0.0
 
@@ -404,6 +412,7 @@ def main():
                            "sharding": (f"(beam, layer-range) work items, LPT over {world} rank(s); " + ("every rank adds the dose-holding float4 groups of its slab into ONE grid on rank 0 over NVLink (CUDA IPC, red.global.add.v4.f32), no dense collective" if push else "every rank's transfer kernels add into ONE dose grid on rank 0 over NVLink (CUDA IPC, red.global.add.f32), no separate collective" if peer else "partial dose grids (reachable z-slab) summed by one NCCL reduce")) if world > 1 else "single GPU",
                            "l2": "256 MiB buffer written between timed iterations (L2 flush); CT 4*%d B and BEV arrays exceed L2" % (nx * ny * nz)},
                 "plan_ms": ms_step, "updates_per_step": U,
+                "stage_total_ms_per_rank": rank_stage_ms, "work_items_per_rank": [len(p) for p in parts],
                 "stage_ms_rank0": {k: stage[k] / args.steps for k in ("msTrace", "msSetup", "msConv", "msIddSigma", "msRadius", "msSuperp", "msTransfer", "msTotal")},
                 "stage_note": "stage_ms_rank0 and roofline come from 3 extra steps with opts.serialBeams=1 (stages bracketed alone); the timed steps run one stream per beam",
                 "serial_beams_plan_ms": stage["msTotal"] / args.steps,

@@ -32,17 +32,31 @@ def layer_cost(beam: Beam, luts) -> np.ndarray:
     return out
 
 
+PIECE_COST_PER_STEP = 150.0   # in layer_cost units: the tracer + transfer + setup a rank repeats for every beam it touches
+                              # (C3 on B200: 0.45 ms for 3 beams of ~300 steps against 1.9e-10 ms per layer_cost unit)
+
+
+def piece_cost(beam: Beam) -> float:
+    """Cost, in ``layer_cost`` units, of the per-beam stages every rank holding ANY layer of the beam runs in full
+    (fan-beam tracer over all steps, spot pre-convolution set-up, BEV -> dose-grid transfer)."""
+    return PIECE_COST_PER_STEP * float(beam.steps)
+
+
 def partition(beams: Sequence[Beam], luts, world_size: int, chunks_per_beam: int = 0) -> List[List[WorkItem]]:
-    """Split every beam into contiguous layer ranges of near-equal cost and assign them to ``world_size`` ranks
-    (LPT greedy). Returns one list of work items per rank; every (beam, layer) appears exactly once."""
+    """Assign every (beam, layer) to exactly one of ``world_size`` ranks as (beam, contiguous layer range) work items.
+
+    Default (``chunks_per_beam`` = 0): the beams' layers are laid end to end and cut into ``world_size`` consecutive
+    runs of near-equal cost (McNaughton's wrap-around rule), where a run pays ``piece_cost`` for every beam it
+    touches. A beam is split only where a cut falls inside it, so a rank repeats the tracer / transfer of as few beams
+    as possible (at most world_size - 1 extra beam pieces in the whole plan).
+    ``chunks_per_beam`` > 0: every beam is split into that many ranges, assigned with an LPT greedy (finer interleaving;
+    used by the tests to force layer splits)."""
     if world_size < 1:
         raise ValueError("world_size must be >= 1")
     if world_size == 1:
         return [[(b, 0, beams[b].n_layers) for b in range(len(beams))]]
-    nb = len(beams)
     if chunks_per_beam <= 0:
-        # enough items for balance, few enough that the per-item tracer recomputation stays small
-        chunks_per_beam = max(1, -(-2 * world_size // max(nb, 1)))
+        return _partition_contiguous(beams, luts, world_size)
     items = []
     for b, beam in enumerate(beams):
         cost = layer_cost(beam, luts)
@@ -68,6 +82,53 @@ def partition(beams: Sequence[Beam], luts, world_size: int, chunks_per_beam: int
     for r in range(world_size):
         out[r].sort()
     return out
+
+
+def _partition_contiguous(beams: Sequence[Beam], luts, world_size: int) -> List[List[WorkItem]]:
+    costs = [layer_cost(b, luts) for b in beams]
+    fixed = [piece_cost(b) for b in beams]
+    n_layers = sum(len(c) for c in costs)
+
+    def fill(target: float) -> List[List[WorkItem]]:
+        """Greedy: a rank takes layers in plan order until its load (layers + one piece_cost per beam touched) reaches
+        ``target``; the cut goes before the layer that overshoots by more than it undershoots. The last rank takes the
+        rest. Ranks left with nothing stay empty."""
+        out: List[List[WorkItem]] = [[] for _ in range(world_size)]
+        r, load = 0, 0.0
+        left = n_layers
+        for b, c in enumerate(costs):
+            lo = 0
+            started = False
+            for l in range(len(c)):
+                add = c[l] + (0.0 if started else fixed[b])
+                ranks_after = world_size - 1 - r
+                over = load + add - target
+                if r < world_size - 1 and load > 0.0 and over > 0.0 and over > target - load and left >= 1:
+                    if started:
+                        out[r].append((b, lo, l))
+                    r, load, lo, started = r + 1, 0.0, l, False
+                    add = c[l] + fixed[b]
+                load += add
+                started = True
+                left -= 1
+                del ranks_after
+            out[r].append((b, lo, len(c)))
+        return out
+
+    def makespan(parts) -> float:
+        return max(sum(costs[b][lo:hi].sum() + fixed[b] for b, lo, hi in items) for items in parts)
+
+    total = sum(float(c.sum()) for c in costs) + sum(fixed)
+    best, best_span = None, np.inf
+    # the pieces created by the cuts add their own fixed cost, so the right target lies a little above total / world:
+    # scan a few and keep the partition with the smallest makespan
+    for k in range(0, 2 * world_size + 1):
+        extra = sum(sorted(fixed, reverse=True)[:1]) * k * 0.5
+        parts = fill((total + extra) / world_size)
+        span = makespan(parts)
+        if span < best_span - 1e-9:
+            best, best_span = parts, span
+    return best
 
 
 def shard_beams(beams: Sequence[Beam], items: Sequence[WorkItem]) -> List[Beam]:
