@@ -32,8 +32,8 @@ def layer_cost(beam: Beam, luts) -> np.ndarray:
     return out
 
 
-PIECE_COST_PER_STEP = 150.0   # in layer_cost units: the tracer + transfer + setup a rank repeats for every beam it touches
-                              # (C3 on B200: 0.45 ms for 3 beams of ~300 steps against 1.9e-10 ms per layer_cost unit)
+PIECE_COST_PER_STEP = 400.0   # in layer_cost units: the tracer + transfer + setup a rank repeats for every beam it touches
+                              # (least-squares fit of the per-rank stage totals of C3 and C4 at N = 2 and 8 on B200: 300 - 530)
 
 
 def piece_cost(beam: Beam) -> float:
