@@ -340,3 +340,22 @@ def test_atomic_transfer_and_shared_grid_owner(eng, mini_case):
         # the sum 0.5 + dose is rounded at 0.5's ulp (2^-24 relative to 0.5 -> 3e-8 absolute)
         assert rel_to_max(got.astype(np.float64) - 0.5, 2.0 * plain)[0] <= 1e-5 + 6.0e-8 / float(plain.max())
     eng.shared_dose_close(ptr, owner=True)
+
+
+def test_push_dose_to_peer_adds_only_dose_holding_groups(eng):
+    """rtd_push_dose_to_peer: dst += src for the float4 groups of src that hold dose (vector reductions; on one GPU the
+    'peer' grid is a local one), tail of n % 4 floats included, misaligned pointers rejected."""
+    import torch
+    n = 4 * 1000 + 3
+    g = torch.Generator().manual_seed(5)
+    src = torch.rand(n, generator=g)
+    src[torch.rand(n, generator=g) < 0.7] = 0.0
+    base = torch.rand(n, generator=g)
+    d_src, d_dst = src.cuda(), base.cuda()
+    eng.push_dose_to_peer(d_src.data_ptr(), d_dst.data_ptr(), n)
+    eng.push_dose_to_peer(d_src.data_ptr(), d_dst.data_ptr(), n)
+    torch.cuda.synchronize()          # device-wide: covers the engine's own stream
+    want = base + src + src
+    assert torch.equal(d_dst.cpu(), want)
+    with pytest.raises(engine.RtdError):
+        eng.push_dose_to_peer(d_src.data_ptr() + 4, d_dst.data_ptr(), 8)
