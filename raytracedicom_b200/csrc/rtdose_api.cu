@@ -468,7 +468,9 @@ rtd_status beamPhaseB2(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opt
     q.g = makeFillGeom(w.grid.rayIdxToGantry, w.dist);
     q.rrlScale = ctx->rrlScale; q.bpCutoff = o.bpDepthCutoff; q.rayWeightCutoff = o.rayWeightCutoff;
     q.first = w.bfi; q.nz = nz; q.Rx = Rx; q.Ry = Ry; q.nozzle = o.noNozzle ? 0 : 1; q.doseToMedium = o.doseToMedium ? 1 : 0;
-    idd_sigma_kernel<<<dim3(tilesX, tilesY, L), 256, 0, strm>>>(w.density.as<float>(), w.wepl.as<float>(), w.rayW.as<float>(),
+    const size_t stepSmem = size_t(nz) * 8;     // per-step voxel width + volume, computed once per CTA
+    if (stepSmem > 48 * 1024) RTD_CUDA(cudaFuncSetAttribute(idd_sigma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stepSmem));
+    idd_sigma_kernel<<<dim3(tilesX, tilesY, L), 256, stepSmem, strm>>>(w.density.as<float>(), w.wepl.as<float>(), w.rayW.as<float>(),
         w.firstIn.as<int>(), w.firstOut.as<int>(), w.layerDev.as<LayerParams>(), q, ctx->iddTex.tex, ctx->rrlTex.tex,
         w.idd.as<float>(), w.rsig.as<float>(), w.rowMin.as<float>(), w.firstPassive.as<int>(), dLfp);
     RTD_CUDA(cudaEventRecord(evs[2], strm));
