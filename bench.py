@@ -91,6 +91,29 @@ def cpu_baseline_port(case, budget_s=20.0):
                       f"(oracle/rtd_oracle.c, OpenMP, {cores} threads; tracer + pre-convolution + IDD/sigma + superposition + transfer)"}
 
 
+def cpu_stage_baseline(case, gpu_stage_ms=None):
+    """"Baseline B" (BASELINE.md 2B): the reference's OWN CPU stage code, src/cpu_convolution_1d.cpp (xConvCpuSparse +
+    yConvCpuSparse, compiled unmodified into oracle/_ref/libref_cpuconv.so), timed on stage K3a (spot weights -> ray weights)
+    of every beam of the workload on this box's host cores: as shipped (1 thread) and with an OpenMP loop over the layers."""
+    from oracle import ref_cpu_stage as rcs
+    if not rcs.available():
+        return {"unavailable": "oracle/_ref/libref_cpuconv.so not built (needs /root/reference at build time)"}
+    try:
+        probs = [rcs.k3a_problem(case, b) for b in range(len(case.beams))]
+        t1 = sum(rcs.run(p, threads=1, repeats=3)[1] for p in probs)
+        tn = sum(rcs.run(p, threads=0, repeats=3)[1] for p in probs)
+        err = max(float(np.abs(rcs.run(p, 0)[0] - p["oracle_ray_weights"]).max() / p["oracle_ray_weights"].max()) for p in probs)
+    except Exception as ex:          # noqa: BLE001 - e.g. non-integer spot pitch: the reference code cannot run the problem
+        return {"unavailable": str(ex)[:200]}
+    out = {"stage": "K3a spot weights -> ray weights, all beams and layers of the workload",
+           "kind": "reference", "code": "src/cpu_convolution_1d.cpp xConvCpuSparse + yConvCpuSparse, g++ -O2",
+           "ms_1_core": 1e3 * t1, "ms_all_cores": 1e3 * tn, "cores": rcs.max_threads(),
+           "max_rel_diff_vs_oracle_stage": err}
+    if gpu_stage_ms is not None:
+        out["gpu_stage_ms"] = gpu_stage_ms
+    return out
+
+
 def run_reference(args, case, rank, world):
     """Reference arm: the UNMODIFIED reference (sources compiled in place from /root/reference into oracle/_ref by
     oracle/ref_harness/Makefile, sm_100) through its own entry point cudaWrapperProtons on this workload, one process
@@ -107,6 +130,7 @@ def run_reference(args, case, rank, world):
     from oracle import pyoracle
     cpu = cpu_baseline_port(case)
     line["cpu_baseline"] = cpu
+    line["cpu_stage_baseline"] = cpu_stage_baseline(case)
     have_gpu = False
     try:
         import torch
@@ -433,6 +457,7 @@ def main():
             line["e2e"] = e2e
         if not args.no_cpu_baseline and world == 1:
             line["cpu_baseline"] = cpu_baseline_port(case)
+            line["cpu_stage_baseline"] = cpu_stage_baseline(case, gpu_stage_ms=stage["msConv"] / args.steps)
         print(json.dumps(line), flush=True)
     # tear down in dependency order: torch tensors that were used on the engine's stream must die before the stream does
     del evs, ms_t, upd_local
