@@ -229,6 +229,7 @@ spot_to_ray_kernel(const float* __restrict__ in, const float2* __restrict__ sigm
 struct LayerParams {          // per-layer constants, kernel_wrapper.cu:829-849, 922-925
     float energyIdx, energyScale, peakDepth;
     int afterLast;
+    int order;                // launch order: grid.z = i runs layer layers[i].order, deepest layers (longest depth scans) first
 };
 struct IddParams {
     FillGeom g;
@@ -247,9 +248,16 @@ idd_sigma_kernel(const float* __restrict__ density, const float* __restrict__ we
                  cudaTextureObject_t iddTex, cudaTextureObject_t rrlTex,
                  float* __restrict__ idd, float* __restrict__ rsig, float* __restrict__ rowMin,
                  int* __restrict__ firstPassive, int* __restrict__ layerFirstPassive) {
-    const int l = blockIdx.z;
-    const int x = blockIdx.x * 32 + (threadIdx.x & 31);
-    const int y = blockIdx.y * 8 + (threadIdx.x >> 5);
+    // CTAs are handed out in grid order and not all of them are resident at once: the layers with the longest depth scan go
+    // first so that the short ones fill the tail instead of the other way round
+    const int l = layers[blockIdx.z].order;
+    // a warp owns a 32-ray row segment; the 8 warps of a CTA own 8 CONSECUTIVE segments in memory order (for Rx = 128: two
+    // full ray rows), so that a CTA's stores of one step form 1 KB runs instead of eight 128 B pieces 4 Rx bytes apart
+    const int tilesX = q.Rx / 32;
+    const int seg = blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int segX = seg % tilesX;
+    const int x = segX * 32 + (threadIdx.x & 31);
+    const int y = min(seg / tilesX, q.Ry - 1);          // Ry is a multiple of 8: segments never run past the grid
     const int R = q.Rx * q.Ry;
     const int ray = y * q.Rx + x;
     const LayerParams lp = layers[l];
@@ -291,24 +299,56 @@ idd_sigma_kernel(const float* __restrict__ density, const float* __restrict__ we
     }
     __syncthreads();
 
-    size_t inIdx = (size_t)first * R + ray;
-    size_t outIdx = (size_t)l * q.nz * R + ray;
-    size_t rmIdx = ((size_t)l * q.nz * q.Ry + y) * (q.Rx / 32) + blockIdx.x;
+    // per-thread base pointers + one 32-bit running offset per array (a slab of one layer / one beam stays far below 2^32
+    // elements): one IMAD.WIDE per access instead of 64-bit index chains
+    const float* const weplP = wepl + (size_t)first * R + ray;
+    const float* const densP = density + (size_t)first * R + ray;
+    float* const iddP = idd + (size_t)l * q.nz * R + ray;
+    float* const rsigP = rsig + (size_t)l * q.nz * R + ray;
+    float* const rowMinP = rowMin + ((size_t)l * q.nz * q.Ry + y) * (q.Rx / 32) + segX;
+    const unsigned rmStride = (unsigned)(q.Ry * (q.Rx / 32));
+    unsigned off = 0, rmOff = 0;
     const int lane = threadIdx.x & 31;
-    // WEPL and density of the next step are requested one iteration ahead (the depth scan is a dependent chain)
-    float wNext = 0.0f, rhoNext = 0.0f;
-    if (live && first < (unsigned)lp.afterLast) { wNext = wepl[inIdx]; rhoNext = density[inIdx]; }
-    for (unsigned k = first; k < (unsigned)lp.afterLast; ++k) {
-        const float w = wNext, rho = rhoNext;
-        if (live && k + 1 < (unsigned)lp.afterLast) { wNext = wepl[inIdx + R]; rhoNext = density[inIdx + R]; }
+    // The depth scan is a dependent chain per ray, and with ~10 warps per scheduler the load -> texture -> arithmetic latency
+    // of one step is what a step costs. Software pipeline over two statically named slots (step s lives in slot s & 1, the
+    // loop is unrolled by two so that no register is rotated at the back edge - a rotating MOV would wait for the request
+    // issued in the same iteration): at step k the slot of step k is copied out and re-used for the WEPL / density request
+    // of step k + 2, and the two LUT fetches of step k + 1 (IDD at its WEPL, 1/X0 at its density) are issued from the other
+    // slot, whose data was requested one iteration earlier. Every result has about one full iteration to arrive.
+    // Coordinates and order of the arithmetic are unchanged.
+    const unsigned last = (unsigned)lp.afterLast;
+    const float eRow = f_add(lp.energyIdx, 0.5f);
+    // The scattering power per unit 1/X0 of a step (t1: residual energy from the mean WEPL of the step, 4 of the step's 7 MUFU
+    // operations) depends on WEPL alone, not on the running sums: it is evaluated one step ahead as well, which leaves
+    // only the short sigma^2 recurrence on the loop-carried chain.
+    auto scatPower = [&](const float wPrev, const float wCur) {
+        const float resE = f_ex2(f_mul(f_lg2(f_sub(lp.peakDepth, f_mul(f_add(wPrev, wCur), 0.5f))), 0.5649718f));
+        const float e1 = f_fma(resE, 8.639415f, 938.3f);
+        const float betaP = f_sub(e1, f_div(880406.875f, e1));
+        return f_mul(f_div(198.81f, f_mul(betaP, betaP)), stepLength);
+    };
+    float wS0 = 0.0f, rhoS0 = 0.0f, dS0 = 0.0f, xS0 = 0.0f, tS0 = 0.0f, wS1 = 0.0f, rhoS1 = 0.0f, dS1 = 0.0f, xS1 = 0.0f, tS1 = 0.0f;
+    if (live && first < last) {
+        wS0 = weplP[0]; rhoS0 = densP[0];
+        if (first + 1 < last) { wS1 = weplP[R]; rhoS1 = densP[R]; }
+        dS0 = tex2D<float>(iddTex, f_fma(wS0, lp.energyScale, 0.5f), eRow);
+        xS0 = tex1D<float>(rrlTex, f_fma(rhoS0, q.rrlScale, 0.5f));
+        tS0 = scatPower(0.0f, wS0);
+    }
+    // one step: (wC, rhoC, dC, xC, tC) = slot of step k, (wN, rhoN, dN, xN, tN) = slot of step k + 1
+    auto step = [&](const unsigned k, float& wC, float& rhoC, const float& dC, const float& xC, const float& tC,
+                    const float& wN, const float& rhoN, float& dN, float& xN, float& tN) {
+        const float w = wC, rho = rhoC;
+        if (live && k + 1 < last) {
+            dN = tex2D<float>(iddTex, f_fma(wN, lp.energyScale, 0.5f), eRow);
+            xN = tex1D<float>(rrlTex, f_fma(rhoN, q.rrlScale, 0.5f));
+            tN = scatPower(w, wN);          // wOld of step k + 1 is this step's WEPL (the ray is live here)
+            if (k + 2 < last) { wC = weplP[off + 2 * R]; rhoC = densP[off + 2 * R]; }
+        }
         if (live) {
-            const float d = tex2D<float>(iddTex, f_fma(w, lp.energyScale, 0.5f), f_add(lp.energyIdx, 0.5f));
             if (w < lp.peakDepth) {
-                const float resE = f_ex2(f_mul(f_lg2(f_sub(lp.peakDepth, f_mul(f_add(wOld, w), 0.5f))), 0.5649718f));
-                const float e1 = f_fma(resE, 8.639415f, 938.3f);
-                const float betaP = f_sub(e1, f_div(880406.875f, e1));
-                const float rRl = f_mul(rho, tex1D<float>(rrlTex, f_fma(rho, q.rrlScale, 0.5f)));
-                const float t1 = f_mul(f_div(198.81f, f_mul(betaP, betaP)), stepLength);
+                const float rRl = f_mul(rho, xC);
+                const float t1 = tC;
                 const float thetaSq = f_mul(rRl, t1);
                 sigmaSq = f_add(sigmaSq, f_add(incScat, incDiv));
                 incinc = f_fma(stepLength, f_mul(stepLength, f_fma(rRl, t1, thetaSq)), incinc);
@@ -323,22 +363,40 @@ idd_sigma_kernel(const float* __restrict__ density, const float* __restrict__ we
             afterLast = within ? afterLast : k;
             const float vol = sStep[q.nz + k - first];
             const float mass = q.doseToMedium ? f_mul(rho, vol) : f_mul(f_sub(w, wOld), vol);
+            const float d = dC;
             if (mass > 1e-2f) res = f_div(f_mul(rayWeight, f_sub(d, dOld)), mass);
             wOld = w; dOld = d;
         }
         const bool keep = live && ((int)k >= firstIn - 1);
         res = keep ? res : 0.0f;
         rs = keep ? rs : inf;
-        idd[outIdx] = res;
-        rsig[outIdx] = rs;
+        iddP[off] = res;
+        rsigP[off] = rs;
         // row minimum of rSigmaEff for the tile radius; its sign carries "some voxel of this row has dose > 0"
         // (a tile without dose is skipped by the superposition exactly like the reference's __syncthreads_or, cuh:456)
         // rs is positive or +inf: its bit pattern orders like an unsigned integer -> one REDUX instead of 5 shuffle+min pairs
         const unsigned rsBits = __float_as_uint(rs);
         const float m = __any_sync(0xffffffffu, (int)rsBits < 0) ? warp_min(rs) : __uint_as_float(__reduce_min_sync(0xffffffffu, rsBits));
         const bool anyDose = __any_sync(0xffffffffu, res > 0.0f);
-        if (lane == 0) rowMin[rmIdx] = anyDose ? m : -m;
-        inIdx += R; outIdx += R; rmIdx += (size_t)q.Ry * (q.Rx / 32);
+        if (lane == 0) rowMinP[rmOff] = anyDose ? m : -m;
+        off += (unsigned)R; rmOff += rmStride;
+    };
+    unsigned k = first;
+    // a ray never comes back to life: once no lane of the warp is live (rays outside the field; every ray past its range)
+    // the rest of the row is "no dose, sigma undefined" - two thirds of all warp-steps on C3 - and is written by the
+    // minimal loop below instead of the full step
+    while (k < last && __any_sync(0xffffffffu, live)) {
+        step(k, wS0, rhoS0, dS0, xS0, tS0, wS1, rhoS1, dS1, xS1, tS1);
+        ++k;
+        if (k >= last || !__any_sync(0xffffffffu, live)) break;
+        step(k, wS1, rhoS1, dS1, xS1, tS1, wS0, rhoS0, dS0, xS0, tS0);
+        ++k;
+    }
+    for (; k < last; ++k) {
+        iddP[off] = 0.0f;
+        rsigP[off] = inf;
+        if (lane == 0) rowMinP[rmOff] = -inf;
+        off += (unsigned)R; rmOff += rmStride;
     }
     firstPassive[(size_t)l * R + ray] = (int)afterLast;
     const int wm = warp_max_i((int)afterLast);

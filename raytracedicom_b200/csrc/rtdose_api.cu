@@ -386,6 +386,12 @@ rtd_status beamPhaseB1(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opt
         lr.energyIdx = lp.energyIdx; lr.energyScaleFact = lp.energyScale; lr.peakDepth = lp.peakDepth;
         lr.entrySigmaX = w.entrySig[2 * l]; lr.entrySigmaY = w.entrySig[2 * l + 1]; lr.afterLastStep = lp.afterLast;
     }
+    {   // launch order of the layers in the IDD / sigma kernel: longest depth scan first
+        std::vector<int> ord(w.Lc);
+        for (int l = 0; l < w.Lc; ++l) ord[l] = l;
+        std::stable_sort(ord.begin(), ord.end(), [&](int a, int c) { return w.layers[a].afterLast > w.layers[c].afterLast; });
+        for (int l = 0; l < w.Lc; ++l) w.layers[l].order = ord[l];
+    }
     w.doTransfer = false;
     if (!w.live) return RTD_OK;   // the beam never enters the patient: nothing to add
 
@@ -470,7 +476,7 @@ rtd_status beamPhaseB2(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opt
     q.first = w.bfi; q.nz = nz; q.Rx = Rx; q.Ry = Ry; q.nozzle = o.noNozzle ? 0 : 1; q.doseToMedium = o.doseToMedium ? 1 : 0;
     const size_t stepSmem = size_t(nz) * 8;     // per-step voxel width + volume, computed once per CTA
     if (stepSmem > 48 * 1024) RTD_CUDA(cudaFuncSetAttribute(idd_sigma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stepSmem));
-    idd_sigma_kernel<<<dim3(tilesX, tilesY, L), 256, stepSmem, strm>>>(w.density.as<float>(), w.wepl.as<float>(), w.rayW.as<float>(),
+    idd_sigma_kernel<<<dim3(tilesX * tilesY, 1, L), 256, stepSmem, strm>>>(w.density.as<float>(), w.wepl.as<float>(), w.rayW.as<float>(),
         w.firstIn.as<int>(), w.firstOut.as<int>(), w.layerDev.as<LayerParams>(), q, ctx->iddTex.tex, ctx->rrlTex.tex,
         w.idd.as<float>(), w.rsig.as<float>(), w.rowMin.as<float>(), w.firstPassive.as<int>(), dLfp);
     RTD_CUDA(cudaEventRecord(evs[2], strm));
