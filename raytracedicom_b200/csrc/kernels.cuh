@@ -59,6 +59,7 @@ constexpr int TR_THREADS = (TR_NW + 1) * 32;
 
 __global__ void __launch_bounds__(TR_THREADS)
 trace_bev_kernel(const TraceParams p, cudaTextureObject_t ctTex, cudaTextureObject_t densTex, cudaTextureObject_t spTex,
+                 cudaTextureObject_t densSpTex /* 0, or both LUTs as one float2 texture (same length and scale) */,
                  float* __restrict__ density, float* __restrict__ wepl, int* __restrict__ firstInside,
                  int* __restrict__ firstOutside, const int Rx, const int R) {
     __shared__ float sSp[2][TR_ROUND][32];
@@ -92,8 +93,16 @@ trace_bev_kernel(const TraceParams p, cudaTextureObject_t ctTex, cudaTextureObje
                 }
 #pragma unroll
                 for (int j = 0; j < TR_CH; ++j) {
-                    const float d = tex1D<float>(densTex, f_fma(hu[j], p.densityScale, 0.5f));
-                    const float s = tex1D<float>(spTex, f_fma(hu[j], p.spScale, 0.5f));
+                    // the tracer is bound by the texture pipe (3 fetches per sample): when the density and stopping-power
+                    // LUTs share length and scale they are one float2 texture, filtered per channel with the same weights
+                    float d, s;
+                    if (densSpTex) {
+                        const float2 ds = tex1D<float2>(densSpTex, f_fma(hu[j], p.densityScale, 0.5f));
+                        d = ds.x; s = ds.y;
+                    } else {
+                        d = tex1D<float>(densTex, f_fma(hu[j], p.densityScale, 0.5f));
+                        s = tex1D<float>(spTex, f_fma(hu[j], p.spScale, 0.5f));
+                    }
                     if (base + j < S) density[(size_t)(base + j) * R + ray] = d;
                     sSp[r & 1][warp * TR_CH + j][lane] = s;
                     sHu[r & 1][warp * TR_CH + j][lane] = hu[j];

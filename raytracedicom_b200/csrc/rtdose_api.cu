@@ -95,7 +95,7 @@ struct rtd_ctx {
     // LUTs (host copies of the small vectors the host logic needs)
     std::vector<float> energies, peakDepths, scaleFacts;
     int nEnergySamples = 0, nEnergies = 0; float densScale = 0, spScale = 0, rrlScale = 0;
-    TexArr iddTex, densTex, spTex, rrlTex, ctTex;
+    TexArr iddTex, densTex, spTex, densSpTex, rrlTex, ctTex;   // densSpTex: density + SP as one float2 LUT when they share length and scale
     int ctDims[3] = {0, 0, 0}, doseDims[3] = {0, 0, 0};
     DevBuf dose;
     std::vector<BeamWs*> ws;
@@ -337,7 +337,7 @@ rtd_status beamPhaseA(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opts
     if (io) io->h2d += int64_t(nW) * 4;
     // weplMin buffer layout: [0]=beamFirstInside, [1]=beamFirstOutside (ints), [2..] weplMin floats
     int* sc = w.weplMin.as<int>();
-    trace_bev_kernel<<<w.R / 32, TR_THREADS, 0, st>>>(tp, ctx->ctTex.tex, ctx->densTex.tex, ctx->spTex.tex,
+    trace_bev_kernel<<<w.R / 32, TR_THREADS, 0, st>>>(tp, ctx->ctTex.tex, ctx->densTex.tex, ctx->spTex.tex, ctx->densSpTex.tex,
         w.density.as<float>(), w.wepl.as<float>(), w.firstIn.as<int>(), w.firstOut.as<int>(), w.grid.dimX, w.R);
     slice_reduce_kernel<<<w.S, 256, 0, st>>>(w.wepl.as<float>(), w.firstIn.as<int>(), w.firstOut.as<int>(), w.R,
         w.weplMin.as<float>() + 2, sc, sc + 1);
@@ -714,7 +714,7 @@ void rtd_destroy(rtd_ctx* ctx) {
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     for (BeamWs* w : ctx->ws) { w->release(); delete w; }
-    ctx->iddTex.release(); ctx->densTex.release(); ctx->spTex.release(); ctx->rrlTex.release(); ctx->ctTex.release();
+    ctx->iddTex.release(); ctx->densTex.release(); ctx->spTex.release(); ctx->densSpTex.release(); ctx->rrlTex.release(); ctx->ctTex.release();
     ctx->dose.release(); ctx->xferCount.release(); ctx->hXferCount.release();
     for (cudaEvent_t e : ctx->events) cudaEventDestroy(e);
     for (cudaStream_t s_ : ctx->bstreams) { cudaStreamSynchronize(s_); cudaStreamDestroy(s_); }
@@ -748,6 +748,16 @@ rtd_status rtd_set_luts(rtd_ctx* ctx, const rtd_luts* l) {
     RTD_CUDA(upload1D(ctx->densTex, l->densityVector, l->nDensitySamples, ctx->stream));
     RTD_CUDA(upload1D(ctx->spTex, l->spVector, l->nSpSamples, ctx->stream));
     RTD_CUDA(upload1D(ctx->rrlTex, l->rRlVector, l->nRRlSamples, ctx->stream));
+    ctx->densSpTex.release();
+    std::vector<float2> both;
+    if (l->nDensitySamples == l->nSpSamples && l->densityScaleFact == l->spScaleFact) {
+        both.resize(l->nDensitySamples);
+        for (int i = 0; i < l->nDensitySamples; ++i) both[i] = make_float2(l->densityVector[i], l->spVector[i]);
+        cudaChannelFormatDesc fd = cudaCreateChannelDesc<float2>();
+        RTD_CUDA(cudaMallocArray(&ctx->densSpTex.arr, &fd, both.size()));
+        RTD_CUDA(cudaMemcpy2DToArrayAsync(ctx->densSpTex.arr, 0, 0, both.data(), both.size() * 8, both.size() * 8, 1, cudaMemcpyHostToDevice, ctx->stream));
+        RTD_CUDA(makeTexture(ctx->densSpTex, cudaAddressModeClamp));
+    }
     RTD_CUDA(cudaStreamSynchronize(ctx->stream));
     ctx->haveLuts = true;
     return RTD_OK;
