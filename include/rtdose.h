@@ -94,7 +94,10 @@ typedef struct {
     int   doseToMedium;      /* 1: the reference built with DOSE_TO_WATER off: voxel mass = density x volume (kernel_wrapper.cu:314-318) */
     int   atomicDose;        /* 1: the transfers add with red.global.add.f32: the dose grid may then be ONE buffer shared by all
                                 ranks of a node (rtd_shared_dose_*), written over NVLink - no separate reduce collective */
-    int   reserved[1];
+    int   ctPull;            /* rtd_plan_dose, 1: a PINNED host CT is read by the GPU itself (ct_pull_rows_kernel): per CT row only the x
+                                interval the tracers can touch crosses PCIe (C3: 51 MB instead of 60 MB of boxes). Measured SLOWER end to
+                                end on B200 (3.2 vs 2.9 ms: the pull kernels compete with the dose kernels for SMs, the copy engines do
+                                not), so the default 0 keeps the axis-aligned sub-volume copies */
 } rtd_opts;
 
 /* Stage timing of the last rtd_dose* call (CUDA events; with concurrent beams the per-stage figures are sums over the

@@ -718,4 +718,104 @@ __global__ void push_nonzero_tail_kernel(const float* __restrict__ src, float* _
     if (i < n && src[i] != 0.0f) atomicAdd(dst + i, src[i]);
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// One-call host path, CT side (rtd_plan_dose with a page-locked CT): the GPU PULLS the texels a beam's tracer can touch
+// straight out of the caller's host memory (mapped pointer, coalesced reads over PCIe) into the CT array (surface writes).
+// What is pulled is a per-row x interval [lo, hi] for every (y, z) row of the CT - much closer to the oblique, divergent
+// frustum than any set of axis-aligned boxes - and a row keeps the interval that is already resident from earlier beams.
+//
+// ct_mark_rows_kernel: the frustum's boundary surface is tiled by small patches (two consecutive steps x two adjacent
+// rays on the perimeter of the ray grid; the first and last step for every 2 x 2 block of rays). Every sample position
+// is trilinear-affine in (i, j, k), so a patch lies inside the bounding box of its 4 corner samples; every row that box
+// touches gets the box's x extent. A row's interval between its boundary crossings then covers every interior sample of
+// the row as well. Slack: texel pair of the linear filter (+1) and 2 texels for the tracer's fp32 position accumulation.
+__device__ __forceinline__ void ct_sample_pos(const TraceParams& p, const float s1, const float s2, const int i, const int j, const int k, float (&u)[3]) {
+    const float fi = (float)i, fj = (float)j, fk = (float)k;
+    const float I[3] = {p.coefIdxI.x, p.coefIdxI.y, p.coefIdxI.z}, J[3] = {p.coefIdxJ.x, p.coefIdxJ.y, p.coefIdxJ.z};
+    const float T[3] = {p.transl.x, p.transl.y, p.transl.z}, O[3] = {p.coefOffset.x, p.coefOffset.y, p.coefOffset.z};
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+        const float st = T[d] + I[d] * fi * s1 + J[d] * fj * s2;
+        const float in = (O[d] - I[d] * fi / p.distX - J[d] * fj / p.distY) * p.delta.z;
+        u[d] = st + fk * in;          // texture coordinate - 1/2: texels floor(u), floor(u) + 1
+    }
+}
+
+__global__ void __launch_bounds__(256)
+ct_mark_rows_kernel(const TraceParams p, const int Rx, const int Ry, const int S, const int nx, const int ny, const int nz,
+                    int* __restrict__ needLo, int* __restrict__ needHi) {
+    const int nPerim = 2 * (Rx + Ry);                 // perimeter ray pairs (r, next r), closed loop incl. corners twice: harmless
+    const long long nSide = (long long)nPerim * max(S - 1, 1);
+    const long long nFace = 2LL * max(Rx - 1, 1) * max(Ry - 1, 1);
+    const long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
+    if (idx >= nSide + nFace) return;
+    int i0, j0, i1, j1, k0, k1;
+    if (idx < nSide) {
+        const int e = (int)(idx % nPerim), k = (int)(idx / nPerim);
+        k0 = k; k1 = min(k + 1, S - 1);
+        if (e < Rx) { i0 = e; i1 = min(e + 1, Rx - 1); j0 = j1 = 0; }
+        else if (e < 2 * Rx) { i0 = e - Rx; i1 = min(i0 + 1, Rx - 1); j0 = j1 = Ry - 1; }
+        else if (e < 2 * Rx + Ry) { j0 = e - 2 * Rx; j1 = min(j0 + 1, Ry - 1); i0 = i1 = 0; }
+        else { j0 = e - 2 * Rx - Ry; j1 = min(j0 + 1, Ry - 1); i0 = i1 = Rx - 1; }
+    } else {
+        long long f = idx - nSide;
+        const int w = max(Rx - 1, 1), h = max(Ry - 1, 1);
+        const int side = (int)(f / ((long long)w * h)); f -= (long long)side * w * h;
+        i0 = (int)(f % w); j0 = (int)(f / w); i1 = min(i0 + 1, Rx - 1); j1 = min(j0 + 1, Ry - 1);
+        k0 = k1 = side ? S - 1 : 0;
+    }
+    const float s1 = 1.0f - p.corner.z / p.distX, s2 = 1.0f - p.corner.z / p.distY;
+    float mn[3] = {3.0e38f, 3.0e38f, 3.0e38f}, mx[3] = {-3.0e38f, -3.0e38f, -3.0e38f};
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+        float u[3];
+        ct_sample_pos(p, s1, s2, (c & 1) ? i1 : i0, (c & 2) ? j1 : j0, (c & 4) ? k1 : k0, u);
+#pragma unroll
+        for (int d = 0; d < 3; ++d) { mn[d] = fminf(mn[d], u[d]); mx[d] = fmaxf(mx[d], u[d]); }
+    }
+    if (!(fabsf(mn[0]) < 1.0e9f && fabsf(mx[0]) < 1.0e9f && fabsf(mn[1]) < 1.0e9f && fabsf(mx[1]) < 1.0e9f && fabsf(mn[2]) < 1.0e9f && fabsf(mx[2]) < 1.0e9f)) return;
+    const int x0 = max((int)floorf(mn[0]) - 2, 0), x1 = min((int)floorf(mx[0]) + 3, nx - 1);
+    const int y0 = max((int)floorf(mn[1]) - 2, 0), y1 = min((int)floorf(mx[1]) + 3, ny - 1);
+    const int z0 = max((int)floorf(mn[2]) - 2, 0), z1 = min((int)floorf(mx[2]) + 3, nz - 1);
+    // x0 > x1 (patch beside the volume) still has to mark its rows: the row may be entered further along, and the hull of
+    // all patches of the row is what counts; clamp the interval to the volume's edge instead of dropping it
+    const int lo = min(x0, nx - 1), hi = max(x1, 0);
+    for (int z = z0; z <= z1; ++z)
+        for (int y = y0; y <= y1; ++y) {
+            const int r = z * ny + y;
+            if (lo < needLo[r]) atomicMin(needLo + r, lo);
+            if (hi > needHi[r]) atomicMax(needHi + r, hi);
+        }
+}
+
+// One warp per CT row: copies the part of [needLo, needHi] that is not resident yet from the caller's (mapped) host CT
+// into the array, 128 contiguous bytes per warp access, and extends the row's resident interval.
+__global__ void __launch_bounds__(256)
+ct_pull_rows_kernel(const float* __restrict__ hostCt, cudaSurfaceObject_t ctSurf, const int nx, const int ny, const int nz,
+                    const int* __restrict__ needLo, const int* __restrict__ needHi, int* __restrict__ resLo, int* __restrict__ resHi,
+                    unsigned long long* __restrict__ pulledBytes) {
+    const int row = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (row >= ny * nz) return;
+    const int nl = needLo[row], nh = needHi[row];
+    if (nh < nl) return;
+    const int rl = resLo[row], rh = resHi[row];
+    const int y = row % ny, z = row / ny;
+    const float* src = hostCt + (size_t)row * nx;
+    unsigned n = 0;
+    auto copy = [&](int a, int b) {                   // texels a..b, aligned down to 32 floats so that every access is one 128 B line
+        for (int x = (a & ~31) + lane; x <= b; x += 8 * 32) {
+            float v[8];                               // 8 independent 128 B reads in flight per warp (PCIe round trip ~2 us)
+#pragma unroll
+            for (int q = 0; q < 8; ++q) { const int xx = x + 32 * q; v[q] = (xx >= a && xx <= b) ? __ldcs(src + xx) : 0.0f; }
+#pragma unroll
+            for (int q = 0; q < 8; ++q) { const int xx = x + 32 * q; if (xx >= a && xx <= b) { surf3Dwrite(v[q], ctSurf, xx * 4, y, z); ++n; } }
+        }
+    };
+    if (rh < rl) copy(nl, nh);
+    else { if (nl < rl) copy(nl, rl - 1); if (nh > rh) copy(rh + 1, nh); }
+    if (lane == 0 && (rh < rl || nl < rl || nh > rh)) { resLo[row] = (rh < rl) ? nl : min(nl, rl); resHi[row] = (rh < rl) ? nh : max(nh, rh); }
+    n = __reduce_add_sync(0xffffffffu, n);
+    if (lane == 0 && n) atomicAdd(pulledBytes, 4ull * n);
+}
+
 }  // namespace rtd

@@ -44,8 +44,8 @@ struct PinBuf {
 };
 
 struct TexArr {
-    cudaArray_t arr = nullptr; cudaTextureObject_t tex = 0;
-    void release() { if (tex) cudaDestroyTextureObject(tex); if (arr) cudaFreeArray(arr); tex = 0; arr = nullptr; }
+    cudaArray_t arr = nullptr; cudaTextureObject_t tex = 0; cudaSurfaceObject_t surf = 0;
+    void release() { if (tex) cudaDestroyTextureObject(tex); if (surf) cudaDestroySurfaceObject(surf); if (arr) cudaFreeArray(arr); tex = 0; surf = 0; arr = nullptr; }
 };
 
 struct Box { int lo[3], hi[3]; };   // inclusive voxel box (x, y, z)
@@ -56,7 +56,10 @@ inline bool boxInside(const Box& a, const Box& b) {   // a inside b
 inline int64_t boxVoxels(const Box& b) { return int64_t(b.hi[0] - b.lo[0] + 1) * (b.hi[1] - b.lo[1] + 1) * (b.hi[2] - b.lo[2] + 1); }
 
 // Host buffers of a one-call plan (rtd_plan_dose / rtd_dose): only the sub-volumes the plan touches are moved.
-struct HostIo { const float* ct = nullptr; float* dose = nullptr; bool zeroCopy = false; int64_t h2d = 0, d2h = 0; };
+struct HostIo {
+    const float* ct = nullptr; float* dose = nullptr; bool zeroCopy = false; int64_t h2d = 0, d2h = 0;
+    const float* ctMapped = nullptr;      // device-side alias of a page-locked ct: the CT rows are pulled by a kernel (ct_pull_rows_kernel)
+};
 
 struct BeamWs {
     // geometry / host results
@@ -89,6 +92,7 @@ struct rtd_ctx {
     cudaStream_t cstream = nullptr;       // copy stream of the one-call host path (CT / dose-in sub-volumes)
     bool ctPartial = false;               // the CT array holds only the sub-volumes of the last rtd_plan_dose
     std::vector<Box> ctBoxes, doseBoxes;  // sub-volumes moved by the current call
+    DevBuf ctRows;                        // int [4][nz * ny]: needLo, needHi (per beam), resLo, resHi (per call) of the pulled CT rows
     DevBuf xferCount; PinBuf hXferCount;  // dose voxels modified by the transfers of the current call
     std::string err;
     bool haveLuts = false, haveCt = false, haveDose = false;
@@ -155,8 +159,11 @@ rtd_status ensureCtArray(rtd_ctx* ctx, int nx, int ny, int nz) {
         ctx->ctTex.release();
         ctx->haveCt = false;
         cudaChannelFormatDesc fd = cudaCreateChannelDesc<float>();
-        RTD_CUDA(cudaMalloc3DArray(&ctx->ctTex.arr, &fd, make_cudaExtent(nx, ny, nz)));
+        RTD_CUDA(cudaMalloc3DArray(&ctx->ctTex.arr, &fd, make_cudaExtent(nx, ny, nz), cudaArraySurfaceLoadStore));
         RTD_CUDA(makeTexture(ctx->ctTex, cudaAddressModeBorder));
+        cudaResourceDesc rd; memset(&rd, 0, sizeof rd);
+        rd.resType = cudaResourceTypeArray; rd.res.array.array = ctx->ctTex.arr;
+        RTD_CUDA(cudaCreateSurfaceObject(&ctx->ctTex.surf, &rd));
         ctx->ctDims[0] = nx; ctx->ctDims[1] = ny; ctx->ctDims[2] = nz;
     }
     return RTD_OK;
@@ -220,16 +227,63 @@ void ctBoxesOfBeam(const TraceParams& p, int Rx, int Ry, int S, const int dims[3
             addBox(dst, b, dims);
         }
     };
-    // segment length: short segments follow an oblique beam closely but pay the slack on every box, long ones drag the
-    // beam's bounding box along; take the candidate that moves the fewest voxels
-    int best = S; int64_t bestVox = -1;
+    // Second family: DISJOINT slabs along the CT axis the beam mostly travels along (depth segments overlap each other by
+    // their slack on every side, which for oblique beams doubles the bytes). Per step k the samples of the whole ray grid lie
+    // inside the box of the 4 corner rays (pos is bilinear in (i, j)); a slab [a0, a1] of texels along the dominant axis can
+    // only be touched by steps whose box reaches it (2 / 3 texels of slack as above); the transverse extent of those steps is
+    // bounded by the corner rays at the first and last such step (pos is linear in k for a fixed ray).
+    auto slabBoxes = [&](int width, std::vector<Box>& dst) -> bool {
+        if (S < 2) return false;
+        std::vector<double> mn(size_t(S) * 3, 1e30), mx(size_t(S) * 3, -1e30);
+        double st[4][3], in[4][3];
+        for (int c = 0; c < 4; ++c) { start((c & 1) ? Rx - 1 : 0, (c & 2) ? Ry - 1 : 0, st[c]); inc((c & 1) ? Rx - 1 : 0, (c & 2) ? Ry - 1 : 0, in[c]); }
+        for (int k = 0; k < S; ++k)
+            for (int c = 0; c < 4; ++c)
+                for (int d = 0; d < 3; ++d) {
+                    const double v = st[c][d] + k * in[c][d];
+                    if (!(std::fabs(v) < 1e9)) return false;
+                    mn[size_t(k) * 3 + d] = std::min(mn[size_t(k) * 3 + d], v); mx[size_t(k) * 3 + d] = std::max(mx[size_t(k) * 3 + d], v);
+                }
+        int a = 0;
+        for (int d = 1; d < 3; ++d) if (std::fabs(in[0][d]) > std::fabs(in[0][a])) a = d;
+        double lo = 1e30, hi = -1e30;
+        for (int k = 0; k < S; ++k) { lo = std::min(lo, mn[size_t(k) * 3 + a]); hi = std::max(hi, mx[size_t(k) * 3 + a]); }
+        const int loA = std::max(int(std::floor(lo)) - 2, 0), hiA = std::min(int(std::floor(hi)) + 3, dims[a] - 1);
+        for (int a0 = loA; a0 <= hiA; a0 += width) {
+            const int a1 = std::min(a0 + width - 1, hiA);
+            int k0 = -1, k1 = -1;
+            for (int k = 0; k < S; ++k)
+                if (int(std::floor(mx[size_t(k) * 3 + a])) + 3 >= a0 && int(std::floor(mn[size_t(k) * 3 + a])) - 2 <= a1) { if (k0 < 0) k0 = k; k1 = k; }
+            if (k0 < 0) continue;
+            Box b;
+            for (int d = 0; d < 3; ++d) {
+                b.lo[d] = int(std::floor(std::min(mn[size_t(k0) * 3 + d], mn[size_t(k1) * 3 + d]))) - 2;
+                b.hi[d] = int(std::floor(std::max(mx[size_t(k0) * 3 + d], mx[size_t(k1) * 3 + d]))) + 3;
+            }
+            b.lo[a] = a0; b.hi[a] = a1;
+            addBox(dst, b, dims);
+        }
+        return true;
+    };
+    // take the candidate that moves the fewest voxels: depth segments of several lengths (short ones follow an oblique beam
+    // closely but pay the slack on every box, long ones drag the beam's bounding box along) or axis slabs (rows of >= 256 B
+    // when the slabs cut the x axis)
+    int best = S; int64_t bestVox = -1; bool bestSlab = false;
     for (int segLen : {32, 64, 128, 256, S}) {
         if (segLen > S) continue;
         std::vector<Box> tmp; boxesFor(segLen, tmp);
         int64_t vox = 0; for (const Box& b : tmp) vox += boxVoxels(b);
         if (bestVox < 0 || vox < bestVox) { bestVox = vox; best = segLen; }
     }
-    boxesFor(best, out);
+    for (int width : {64, 32}) {
+        std::vector<Box> tmp;
+        if (!slabBoxes(width, tmp)) break;
+        int64_t vox = 0; bool narrowRows = false;
+        for (const Box& b : tmp) { vox += boxVoxels(b); narrowRows |= (b.hi[0] - b.lo[0] + 1) < 64 && (b.hi[0] - b.lo[0] + 1) < dims[0]; }
+        if (width == 32 && narrowRows) continue;     // 128-byte rows starve the copy engine
+        if (vox < bestVox) { bestVox = vox; best = width; bestSlab = true; }
+    }
+    if (bestSlab) slabBoxes(best, out); else boxesFor(best, out);
 }
 
 // Dose boxes that enclose every voxel bev_to_grid_kernel can modify for this beam: voxels whose fan index lies within
@@ -325,11 +379,28 @@ rtd_status beamPhaseA(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opts
     const TraceParams tp = makeTraceParams(ctx->densScale, ctx->spScale, b.steps, w.grid.rayIdxToGantry, w.dist, w.gtii);
     if (io && io->ct) {
         // one-call host path: upload the CT sub-volumes this beam's tracer samples (copy stream), then let the beam's stream go
-        const size_t n0 = ctx->ctBoxes.size();
-        ctBoxesOfBeam(tp, w.grid.dimX, w.grid.dimY, w.S, ctx->ctDims, ctx->ctBoxes);
-        for (size_t i = n0; i < ctx->ctBoxes.size(); ++i) {
-            RTD_CUDA(copyCtBox(ctx, io->ct, ctx->ctBoxes[i], ctx->cstream));
-            io->h2d += boxVoxels(ctx->ctBoxes[i]) * 4;
+        if (io->ctMapped) {
+            // page-locked CT: the GPU pulls, per CT row, the x interval this beam's tracer can touch and that is not resident yet
+            const int rows = ctx->ctDims[1] * ctx->ctDims[2];
+            int* need = ctx->ctRows.as<int>();
+            RTD_CUDA(cudaMemsetAsync(need, 0x7f, size_t(rows) * 4, ctx->cstream));            // needLo = "nothing"
+            RTD_CUDA(cudaMemsetAsync(need + rows, 0xff, size_t(rows) * 4, ctx->cstream));     // needHi = -1
+            const int Rx = w.grid.dimX, Ry = w.grid.dimY;
+            const long long patches = 2LL * (Rx + Ry) * std::max(w.S - 1, 1) + 2LL * std::max(Rx - 1, 1) * std::max(Ry - 1, 1);
+            ct_mark_rows_kernel<<<(unsigned)((patches + 255) / 256), 256, 0, ctx->cstream>>>(tp, Rx, Ry, w.S, ctx->ctDims[0], ctx->ctDims[1], ctx->ctDims[2],
+                                                                                             need, need + rows);
+            ct_pull_rows_kernel<<<(rows + 7) / 8, 256, 0, ctx->cstream>>>(io->ctMapped, ctx->ctTex.surf, ctx->ctDims[0], ctx->ctDims[1], ctx->ctDims[2],
+                                                                          need, need + rows, need + 2 * rows, need + 3 * rows,
+                                                                          ctx->xferCount.as<unsigned long long>() + 1);
+            launches += 2;
+            RTD_CUDA(cudaGetLastError());
+        } else {
+            const size_t n0 = ctx->ctBoxes.size();
+            ctBoxesOfBeam(tp, w.grid.dimX, w.grid.dimY, w.S, ctx->ctDims, ctx->ctBoxes);
+            for (size_t i = n0; i < ctx->ctBoxes.size(); ++i) {
+                RTD_CUDA(copyCtBox(ctx, io->ct, ctx->ctBoxes[i], ctx->cstream));
+                io->h2d += boxVoxels(ctx->ctBoxes[i]) * 4;
+            }
         }
         RTD_CUDA(cudaEventRecord(evCt, ctx->cstream));
         RTD_CUDA(cudaStreamWaitEvent(st, evCt, 0));
@@ -566,10 +637,16 @@ rtd_status doseCore(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* dDos
     while ((int)ctx->ws.size() < nBeams) ctx->ws.push_back(new BeamWs());
     ctx->nBeamsLast = nBeams; ctx->optsLast = o;
     ctx->ctBoxes.clear(); ctx->doseBoxes.clear();
-    RTD_CUDA(ctx->xferCount.ensure(8)); RTD_CUDA(ctx->hXferCount.ensure(8));
+    RTD_CUDA(ctx->xferCount.ensure(16)); RTD_CUDA(ctx->hXferCount.ensure(16));   // [0] dose voxels modified, [1] CT bytes pulled
+    if (io && io->ctMapped) RTD_CUDA(ctx->ctRows.ensure(size_t(ctx->ctDims[1]) * ctx->ctDims[2] * 16));
+    RTD_CUDA(cudaMemsetAsync(ctx->xferCount.p, 0, 16, ctx->stream));
     RTD_CUDA(cudaEventRecord(evBegin, ctx->stream));
-    RTD_CUDA(cudaMemsetAsync(ctx->xferCount.p, 0, 8, ctx->stream));
     if (io) RTD_CUDA(cudaStreamWaitEvent(ctx->cstream, evBegin, 0));
+    if (io && io->ctMapped) {   // nothing of the caller's CT is resident at the start of a call (its content may have changed)
+        const size_t rows = size_t(ctx->ctDims[1]) * ctx->ctDims[2];
+        RTD_CUDA(cudaMemsetAsync(ctx->ctRows.as<int>() + 2 * rows, 0x7f, rows * 4, ctx->cstream));
+        RTD_CUDA(cudaMemsetAsync(ctx->ctRows.as<int>() + 3 * rows, 0xff, rows * 4, ctx->cstream));
+    }
     // Beams are independent until the transfer into the shared dose grid: unless opts.serialBeams is set every beam runs
     // on its own stream so that the latency-bound stages (tracer, IDD/sigma depth scans) of different beams overlap.
     const bool serial = o.serialBeams != 0 || nBeams == 1;
@@ -629,7 +706,7 @@ rtd_status doseCore(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* dDos
     }
     cudaEvent_t evXferEnd = ev(ctx, 7);
     RTD_CUDA(cudaEventRecord(evXferEnd, ctx->stream));
-    RTD_CUDA(cudaMemcpyAsync(ctx->hXferCount.p, ctx->xferCount.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    RTD_CUDA(cudaMemcpyAsync(ctx->hXferCount.p, ctx->xferCount.p, 16, cudaMemcpyDeviceToHost, ctx->stream));
     if (io && io->dose && !io->zeroCopy) {
         if (!doseInWaited) RTD_CUDA(cudaStreamWaitEvent(ctx->stream, evDoseIn, 0));
         for (const Box& bx : ctx->doseBoxes) { RTD_CUDA(copyDoseBox(ctx, io->dose, dDose, bx, false, ctx->stream)); io->d2h += boxVoxels(bx) * 4; }
@@ -639,6 +716,7 @@ rtd_status doseCore(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* dDos
     int64_t updates = 0, taps = 0; bool ok = true;
     for (int b = 0; b < nBeams; ++b) ok = beamFinish(ctx, *ctx->ws[b], updates, taps) && ok;
     const int64_t modified = (int64_t)*ctx->hXferCount.as<unsigned long long>();
+    if (io && io->ctMapped) io->h2d += (int64_t)ctx->hXferCount.as<unsigned long long>()[1];   // CT bytes the pull kernels read over PCIe
     if (io && io->dose && io->zeroCopy) { io->h2d += modified * 4; io->d2h += modified * 4; }   // the transfers read-modify-write the caller's pinned grid in place
     if (tm) {
         memset(tm, 0, sizeof *tm);
@@ -694,7 +772,8 @@ rtd_status rtd_create(rtd_ctx** out, int device) {
     rtd_ctx* ctx = new rtd_ctx();
     ctx->device = device;
     if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return RTD_ERR_CUDA; }
-    if (cudaStreamCreateWithFlags(&ctx->cstream, cudaStreamNonBlocking) != cudaSuccess) { cudaStreamDestroy(ctx->stream); delete ctx; return RTD_ERR_CUDA; }
+    int prLo = 0, prHi = 0; cudaDeviceGetStreamPriorityRange(&prLo, &prHi);   // the copy stream also runs the CT pull kernels: highest priority
+    if (cudaStreamCreateWithPriority(&ctx->cstream, cudaStreamNonBlocking, prHi) != cudaSuccess) { cudaStreamDestroy(ctx->stream); delete ctx; return RTD_ERR_CUDA; }
     cudaDeviceGetAttribute(&ctx->smCount, cudaDevAttrMultiProcessorCount, device);
     rtd_default_opts(&ctx->optsLast);
     cudaFuncSetAttribute(ks_kernel<KS_NT_C, 17, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)KS_SMEM_C);
@@ -715,7 +794,7 @@ void rtd_destroy(rtd_ctx* ctx) {
     cudaStreamSynchronize(ctx->stream);
     for (BeamWs* w : ctx->ws) { w->release(); delete w; }
     ctx->iddTex.release(); ctx->densTex.release(); ctx->spTex.release(); ctx->densSpTex.release(); ctx->rrlTex.release(); ctx->ctTex.release();
-    ctx->dose.release(); ctx->xferCount.release(); ctx->hXferCount.release();
+    ctx->dose.release(); ctx->xferCount.release(); ctx->hXferCount.release(); ctx->ctRows.release();
     for (cudaEvent_t e : ctx->events) cudaEventDestroy(e);
     for (cudaStream_t s_ : ctx->bstreams) { cudaStreamSynchronize(s_); cudaStreamDestroy(s_); }
     cudaStreamSynchronize(ctx->cstream); cudaStreamDestroy(ctx->cstream);
@@ -793,6 +872,16 @@ rtd_status rtd_dose_device(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, floa
 static rtd_status doseHost(rtd_ctx* ctx, const float* ct, const rtd_beam* beams, int nBeams, float* dose, float* dDose, const rtd_opts* opts, rtd_timing* tm) {
     rtd_opts o; if (opts) o = *opts; else rtd_default_opts(&o);
     HostIo io; io.ct = ct; io.dose = dose;
+    if (ct && o.ctPull) {
+        const size_t n = size_t(ctx->ctDims[0]) * ctx->ctDims[1] * ctx->ctDims[2];
+        cudaPointerAttributes a0, a1;
+        if (cudaPointerGetAttributes(&a0, ct) == cudaSuccess && cudaPointerGetAttributes(&a1, ct + (n - 1)) == cudaSuccess &&
+            a0.type == cudaMemoryTypeHost && a1.type == cudaMemoryTypeHost && a0.devicePointer &&
+            (char*)a1.devicePointer - (char*)a0.devicePointer == (ptrdiff_t)((n - 1) * 4) && (ctx->ctDims[0] % 32) == 0 &&
+            ((uintptr_t)a0.devicePointer & 127) == 0)
+            io.ctMapped = (const float*)a0.devicePointer;
+        cudaGetLastError();
+    }
     if (dose) {
         const size_t n = size_t(ctx->doseDims[0]) * ctx->doseDims[1] * ctx->doseDims[2];
         // Pinned (cudaHostAlloc / cudaHostRegister, as HostPinnedImage3D does, host_image_3d.cuh:24) dose grids are

@@ -279,6 +279,23 @@ def test_one_call_host_path_moves_sub_volumes_only_and_matches(eng, name, pinned
     # fewer bytes than the dense host path, which moves 2 volumes up and 1 down
     if name == "c3":
         assert t.h2dBytes < 0.6 * 2 * din.nbytes and t.d2hBytes < 0.6 * din.nbytes
+    if pinned:
+        # opts.ctPull: the GPU reads a page-locked CT itself, per CT row only the x interval the tracers can touch (kernel
+        # ct_mark_rows / ct_pull_rows instead of copy-engine boxes). Same poison, same requirements, fewer bytes.
+        eng.set_ct(np.full_like(case.ct, np.nan))
+        ct_pinned = host_copy(case.ct)
+        pulled = host_copy(np.zeros_like(din))
+        eng.opts.ctPull = 1
+        try:
+            tp = eng.plan_dose(ct_pinned, case.beams, pulled)
+        finally:
+            eng.opts.ctPull = 0
+        for b in range(len(case.beams)):
+            assert bits_equal(eng.fetch(b, "wepl"), wepl[b])
+            assert np.array_equal(eng.fetch(b, "first_inside"), fin[b])
+        assert np.isfinite(pulled).all() and np.array_equal(pulled != 0, dense != 0)
+        assert rel_to_max(pulled, dense)[0] <= 2e-6
+        assert 0 < tp.h2dBytes <= t.h2dBytes
     # a partially resident CT must not be reused silently
     with pytest.raises(engine.RtdError) as ei:
         eng.dose(case.beams, whole)
