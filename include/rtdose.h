@@ -220,6 +220,10 @@ rtd_status rtd_get_beam_report(const rtd_ctx* ctx, int beamNo, rtd_beam_report* 
 rtd_status rtd_get_layer_report(const rtd_ctx* ctx, int beamNo, int layerNo, rtd_layer_report* out);
 /* Copies an intermediate of the last call to host memory (needs opts.keepIntermediates=1 for per-layer arrays). */
 rtd_status rtd_debug_fetch(rtd_ctx* ctx, int beamNo, rtd_fetch_what what, int layerNo, void* dst, size_t dstBytes);
+/* Host geometry only (no device needed): the CT sub-volumes rtd_plan_dose would upload for this beam into a CT of
+ * nx x ny x nz voxels, as inclusive boxes (x0, y0, z0, x1, y1, z1). Returns the number of boxes (may exceed maxBoxes; only
+ * maxBoxes are written) or -1 on bad input. Lets CPU tests check that every texel the tracer can fetch is covered. */
+int rtd_debug_ct_boxes(const rtd_beam* beam, int nx, int ny, int nz, int* boxes6, int maxBoxes);
 
 /* The CUDA stream (cudaStream_t) all work of this context is issued on, for callers that order NCCL /
  * torch work after rtd_dose_device. */

@@ -1033,6 +1033,23 @@ rtd_status rtd_get_layer_report(const rtd_ctx* ctx, int beamNo, int layerNo, rtd
     return RTD_OK;
 }
 
+int rtd_debug_ct_boxes(const rtd_beam* b, int nx, int ny, int nz, int* boxes6, int maxBoxes) {
+    if (!b || !b->sigmas || b->nLayers <= 0 || b->sx <= 0 || b->sy <= 0 || nx <= 0 || ny <= 0 || nz <= 0 || b->steps == 0) return -1;
+    rtd_opts o; rtd_default_opts(&o);
+    float mx = b->sigmas[0], my = b->sigmas[1];
+    for (int l = 1; l < b->nLayers; ++l) { mx = std::max(mx, b->sigmas[2 * l]); my = std::max(my, b->sigmas[2 * l + 1]); }
+    const RayGrid grid = makeRayGrid(b->spotDelta, b->spotOffset, b->sx, b->sy, b->raySpacing, mx, my, o.convSigmaCutoff);
+    if (grid.dimX <= 0 || grid.dimY <= 0) return -1;
+    Affine gtii; gtii.m = m3(b->gantryToImIdxM); gtii.v = v3(b->gantryToImIdxV[0], b->gantryToImIdxV[1], b->gantryToImIdxV[2]);
+    const TraceParams tp = makeTraceParams(1.0f, 1.0f, b->steps, grid.rayIdxToGantry, b->sourceDist, gtii);
+    const int dims[3] = {nx, ny, nz};
+    std::vector<Box> v;
+    ctBoxesOfBeam(tp, grid.dimX, grid.dimY, (int)b->steps, dims, v);
+    for (size_t i = 0; i < v.size() && (int)i < maxBoxes && boxes6; ++i)
+        for (int d = 0; d < 3; ++d) { boxes6[6 * i + d] = v[i].lo[d]; boxes6[6 * i + 3 + d] = v[i].hi[d]; }
+    return (int)v.size();
+}
+
 rtd_status rtd_debug_fetch(rtd_ctx* ctx, int beamNo, rtd_fetch_what what, int layerNo, void* dst, size_t dstBytes) {
     if (!ctx || !dst || beamNo < 0 || beamNo >= ctx->nBeamsLast) return RTD_ERR_INVALID;
     BeamWs& w = *ctx->ws[beamNo];

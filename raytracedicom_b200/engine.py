@@ -95,7 +95,7 @@ class RtdError(RuntimeError):
 EXPORTS = ["rtd_default_opts", "rtd_create", "rtd_destroy", "rtd_last_error", "rtd_version", "rtd_set_luts", "rtd_set_ct",
            "rtd_set_ct_device", "rtd_set_dose_grid", "rtd_dose", "rtd_dose_device", "rtd_plan_dose", "rtd_plan_dose_device", "rtd_add_device_to_host", "rtd_shared_dose_create", "rtd_shared_dose_open", "rtd_shared_dose_close", "rtd_push_dose_to_peer",
            "rtd_get_beam_report",
-           "rtd_get_layer_report", "rtd_debug_fetch", "rtd_stream"]
+           "rtd_get_layer_report", "rtd_debug_fetch", "rtd_debug_ct_boxes", "rtd_stream"]
 
 _lib = None
 
@@ -132,6 +132,7 @@ def load_library() -> C.CDLL:
     lib.rtd_get_beam_report.argtypes = [vp, C.c_int, C.POINTER(RtdBeamReport)]; lib.rtd_get_beam_report.restype = C.c_int
     lib.rtd_get_layer_report.argtypes = [vp, C.c_int, C.c_int, C.POINTER(RtdLayerReport)]; lib.rtd_get_layer_report.restype = C.c_int
     lib.rtd_debug_fetch.argtypes = [vp, C.c_int, C.c_int, C.c_int, vp, C.c_size_t]; lib.rtd_debug_fetch.restype = C.c_int
+    lib.rtd_debug_ct_boxes.argtypes = [C.POINTER(RtdBeam), C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.c_int]; lib.rtd_debug_ct_boxes.restype = C.c_int
     lib.rtd_stream.argtypes = [vp]; lib.rtd_stream.restype = vp
     _lib = lib
     return lib
@@ -166,6 +167,21 @@ def pack_beams(beams: Sequence[Beam]):
         rb.gantryToDoseIdxV = (C.c_float * 3)(*_f32(b.gantry_to_dose_v).ravel())
         rb.layerBegin, rb.layerEnd = getattr(b, "layer_begin", 0), getattr(b, "layer_end", 0)
     return arr, keep
+
+
+def ct_boxes(beam: Beam, ct_dims_xyz) -> np.ndarray:
+    """The CT sub-volumes rtd_plan_dose uploads for ``beam`` into a CT of (nx, ny, nz) voxels: int array [n][6] of inclusive
+    boxes (x0, y0, z0, x1, y1, z1). Host geometry only - works without a GPU (rtd_debug_ct_boxes)."""
+    lib = load_library()
+    arr, keep = pack_beams([beam])
+    nx, ny, nz = (int(v) for v in ct_dims_xyz)
+    n = lib.rtd_debug_ct_boxes(arr, nx, ny, nz, None, 0)
+    if n < 0:
+        raise ValueError("rtd_debug_ct_boxes: bad beam or CT dims")
+    out = np.zeros((max(n, 1), 6), np.int32)
+    lib.rtd_debug_ct_boxes(arr, nx, ny, nz, out.ctypes.data_as(C.POINTER(C.c_int)), n)
+    del keep
+    return out[:n]
 
 
 class DoseEngine:
