@@ -9,7 +9,7 @@
 //   K3a spot_to_ray_kernel    <- xConvGathResampGpu / yConvGathResampGpu gpu_convolution_2d.cu:16-59
 //   K2  idd_sigma_kernel      <- fillIddAndSigma kernel_wrapper.cu:189-379, fill_idd_and_sigma_params.cu:28-83
 //       tile_radius_kernel    <- tileRadCalc kernel_wrapper.cuh:256-313 ; batch_kernel <- host batching cu:966-976
-//   K3b ks_kernel             <- kernelSuperposition<rad> kernel_wrapper.cuh:432-489
+//   K3b ks2_kernel (ks2.cuh)  <- kernelSuperposition<rad> kernel_wrapper.cuh:432-489
 //   K4  bev_to_grid_kernel    <- primTransfDiv kernel_wrapper.cu:69-97, transfer_param_struct_div3.cu:22-34
 #pragma once
 #include <cuda_runtime.h>
@@ -477,139 +477,25 @@ __global__ void batch_kernel(const int* __restrict__ hist, const int L, const in
     }
 }
 
-// Work list: one packed entry per live tile: layer<<24 | slice<<12 | tile.
+// Items (slice, tile) that have at least one layer with an applied radius above 16: the work list of ks2_kernel<32, .>,
+// which runs only 3 warps per SM and must not spend them scanning the whole beam. Deepest slices first.
 __global__ void __launch_bounds__(256)
-fill_list_kernel(const uint8_t* __restrict__ radMap, const int* __restrict__ batchRad, const int* __restrict__ rbOffset,
-                 int* __restrict__ rbCursor, const int nz, const int tiles, uint32_t* __restrict__ list) {
-    const int l = blockIdx.y;
-    const int idx = blockIdx.x * 256 + threadIdx.x;
-    if (idx >= nz * tiles) return;
-    const unsigned r = radMap[(size_t)l * nz * tiles + idx];
-    if (r > 32) return;
-    const int rb = batchRad[l * 34 + r];
-    if (rb <= 16) return;   // radii <= 16 are enumerated directly by ks2_kernel (ks2.cuh); the list only feeds ks_kernel<.,17,32>
-    const int pos = rbOffset[rb] + atomicAdd(rbCursor + rb, 1);
-    list[pos] = ((uint32_t)l << 24) | ((uint32_t)(idx / tiles) << 12) | (uint32_t)(idx % tiles);
+big_items_kernel(const uint8_t* __restrict__ radMap, const int* __restrict__ batchRad, const int L, const int nz, const int tiles,
+                 const int* __restrict__ bigTiles /* batch_kernel's offset of radius 16 = tiles with a larger applied radius */,
+                 int* __restrict__ count, uint32_t* __restrict__ items) {
+    if (*bigTiles == 0) return;                       // shallow target: nothing to list
+    const int t = blockIdx.x * 256 + threadIdx.x;
+    const int nItems = nz * tiles;
+    if (t >= nItems) return;
+    const int idx = nItems - 1 - t;
+    bool big = false;
+    for (int l = 0; l < L && !big; ++l) {
+        const unsigned r = radMap[(size_t)l * nItems + idx];
+        big = r <= 32u && batchRad[l * 34 + r] > 16;
+    }
+    if (big) items[atomicAdd(count, 1)] = (uint32_t)idx;
 }
 
-// ---------------------------------------------------------------------------------------------------------
-// K3b: kernel superposition. out[Y][X] += dose(x,y) e_xy[|X-x|] e_xy[|Y-y|] over the 32x8 sources of a tile with
-// the erf-difference weights of cuh:459-467 and the batch radius RB.
-// Formulation: output-row stationary. Thread q owns output row Y = q-RB of the (8+2RB) x (32+2RB) patch and keeps
-// a sliding window of 2RB+1 column accumulators in registers; all lanes of a warp walk the SAME source at the same
-// time, so the source's horizontal weights e[0..RB] are warp-uniform 128-bit shared-memory broadcasts feeding
-// 2RB+1 FMAs each, and only the vertical weight is lane-specific. Finished columns leave the window into a
-// shared patch that is added to the haloed BEV dose with coalesced reductions.
-struct KsParams {
-    const float* idd; const float* rsig; float* bev;
-    const uint32_t* list; const int* batchRad; const uint8_t* radMap;
-    int Rx, Ry, nz, first, tilesX, tiles;
-};
-
-__host__ __device__ constexpr int ks_str(int rb) { return (((rb + 1 + 3) / 4 * 4) % 8 == 0) ? ((rb + 1 + 3) / 4 * 4 + 4) : ((rb + 1 + 3) / 4 * 4); }
-__host__ __device__ constexpr int ks_smem_floats(int rb) { return 256 * ks_str(rb) + 256 + (8 + 2 * rb) * (32 + 2 * rb + 1); }
-
-template <int NT, int RB>
-__device__ __forceinline__ void ks_tile(const KsParams& p, const int l, const int kk, const int tile, float* smem) {
-    constexpr int STR = ks_str(RB);
-    constexpr int NR = 8 + 2 * RB, NC = 32 + 2 * RB, NCP = NC + 1, W = 2 * RB + 1;
-    float* sE = smem;                  // [256][STR]
-    float* sD = smem + 256 * STR;      // [256]
-    float* sO = sD + 256;              // [NR][NCP]
-    const int tid = threadIdx.x;
-    const int tx = tile % p.tilesX, ty = tile / p.tilesX;
-    const int R = p.Rx * p.Ry;
-    const size_t src0 = ((size_t)l * p.nz + kk) * R + (size_t)(ty * 8) * p.Rx + tx * 32;
-    for (int s = tid; s < 256; s += NT) {
-        const size_t gi = src0 + (size_t)(s >> 5) * p.Rx + (s & 31);
-        const float dose = p.idd[gi];
-        const float r = p.rsig[gi];
-        sD[s] = dose;
-        float erfNew = erff(r * 0.5f), erfOld = -erfNew;       // cuh:459-467
-        float e[STR];
-#pragma unroll
-        for (int i = 0; i < STR; ++i) {
-            if (i <= RB) {
-                e[i] = 0.5f * (erfNew - erfOld);
-                erfOld = erfNew;
-                erfNew = erff(r * (float(i) + 1.5f));
-            } else e[i] = 0.0f;
-        }
-#pragma unroll
-        for (int i = 0; i < STR; i += 4) *reinterpret_cast<float4*>(sE + s * STR + i) = make_float4(e[i], e[i + 1], e[i + 2], e[i + 3]);
-    }
-    __syncthreads();
-    if (tid < NR) {
-        const int q = tid;
-        float win[W];
-#pragma unroll
-        for (int j = 0; j < W; ++j) win[j] = 0.0f;
-        float* orow = sO + q * NCP;
-        for (int x = 0; x < 32; ++x) {
-#pragma unroll
-            for (int y = 0; y < 8; ++y) {
-                const int s = y * 32 + x;
-                const int dyv = abs(q - RB - y);
-                const float ey = sE[s * STR + min(dyv, RB)];
-                const float hy = (dyv <= RB) ? sD[s] * ey : 0.0f;
-                float ex[STR];
-#pragma unroll
-                for (int i = 0; i < STR; i += 4) {
-                    const float4 v = *reinterpret_cast<const float4*>(sE + s * STR + i);
-                    ex[i] = v.x; ex[i + 1] = v.y; ex[i + 2] = v.z; ex[i + 3] = v.w;
-                }
-#pragma unroll
-                for (int j = 0; j < W; ++j) win[j] = fmaf(hy, ex[(j < RB) ? (RB - j) : (j - RB)], win[j]);
-            }
-            orow[x] = win[0];
-#pragma unroll
-            for (int j = 0; j + 1 < W; ++j) win[j] = win[j + 1];
-            win[W - 1] = 0.0f;
-        }
-#pragma unroll
-        for (int j = 0; j + 1 < W; ++j) orow[32 + j] = win[j];
-    }
-    __syncthreads();
-    const int pitch = p.Rx + 64;
-    float* out = p.bev + ((size_t)(kk + p.first) * (p.Ry + 64) + (ty * 8 + 32 - RB)) * pitch + tx * 32 + 32 - RB;
-    for (int i = tid; i < NR * NC; i += NT) {
-        const int rr = i / NC, cc = i - rr * NC;
-        const float v = sO[rr * NCP + cc];
-        if (v != 0.0f) atomicAdd(out + (size_t)rr * pitch + cc, v);
-    }
-    __syncthreads();
-}
-
-template <int NT, int RLO, int RHI>
-__global__ void __launch_bounds__(NT)
-ks_kernel(const KsParams p, const int* __restrict__ rbOffset, const int* __restrict__ stats, int* __restrict__ workCounter) {
-    extern __shared__ __align__(16) float smem[];
-    __shared__ int sItem;
-    // list is ordered by descending radius: this launch covers radii [RLO, RHI]
-    const int start = rbOffset[RHI];
-    const int end = (RLO == 0) ? stats[1] : rbOffset[RLO - 1];
-    for (;;) {
-        if (threadIdx.x == 0) sItem = start + atomicAdd(workCounter, 1);
-        __syncthreads();
-        const int item = sItem;
-        __syncthreads();
-        if (item >= end) break;
-        const uint32_t e = p.list[item];
-        const int l = e >> 24, kk = (e >> 12) & 0xfff, tile = e & 0xfff;
-        const int rad = p.radMap[((size_t)l * p.nz + kk) * p.tiles + tile];
-        const int rb = p.batchRad[l * 34 + rad];
-        switch (rb) {
-#define RTD_KS_CASE(N) case N: if (N >= RLO && N <= RHI) ks_tile<NT, (N >= RLO && N <= RHI) ? N : RLO>(p, l, kk, tile, smem); break;
-            RTD_KS_CASE(0) RTD_KS_CASE(1) RTD_KS_CASE(2) RTD_KS_CASE(3) RTD_KS_CASE(4) RTD_KS_CASE(5) RTD_KS_CASE(6) RTD_KS_CASE(7)
-            RTD_KS_CASE(8) RTD_KS_CASE(9) RTD_KS_CASE(10) RTD_KS_CASE(11) RTD_KS_CASE(12) RTD_KS_CASE(13) RTD_KS_CASE(14) RTD_KS_CASE(15)
-            RTD_KS_CASE(16) RTD_KS_CASE(17) RTD_KS_CASE(18) RTD_KS_CASE(19) RTD_KS_CASE(20) RTD_KS_CASE(21) RTD_KS_CASE(22) RTD_KS_CASE(23)
-            RTD_KS_CASE(24) RTD_KS_CASE(25) RTD_KS_CASE(26) RTD_KS_CASE(27) RTD_KS_CASE(28) RTD_KS_CASE(29) RTD_KS_CASE(30) RTD_KS_CASE(31)
-            RTD_KS_CASE(32)
-#undef RTD_KS_CASE
-            default: break;
-        }
-    }
-}
 
 // ---------------------------------------------------------------------------------------------------------
 // K4: BEV dose -> dose grid, gather with trilinear interpolation straight from the linear haloed BEV volume

@@ -25,6 +25,7 @@ struct Ks2Params {
     const uint8_t* radMap;          // [L][nz][tiles] own radius, 255 = not live
     const int* layerFirstPassive;   // [L]
     int L, Rx, Ry, nz, first, tilesX, tiles;
+    const int* bigCount; const uint32_t* bigItems;   // items with a layer of applied radius > 16 (big_items_kernel)
 };
 
 // erf(x) for x >= 0 as 1 - 2^(x Q(x)), Q = degree-7 fit of log2(erfc(x))/x on [0,4] (erf(4) rounds to 1 in fp32).
@@ -44,7 +45,7 @@ __device__ __forceinline__ float ks_erf_pos(float x) {
     return 1.0f - exp2f(x * q);
 }
 
-constexpr int KS2_MAXRB = 16;       // larger batch radii go through the block-wide ks_kernel<.,17,32>
+constexpr int KS2_MAXRB = 32;       // largest batch radius (RTD_MAX_SUPERP_R)
 constexpr int KS2_MAXL = 256;
 
 // Warp-private patch, COLUMN-major: patch[X][Y], X = tile column + RBMAX (32 + 2 RBMAX columns), Y = tile row + RBMAX
@@ -64,8 +65,9 @@ __host__ __device__ constexpr int ks2_col_pitch(int rbmax) {
 __host__ __device__ constexpr int ks2_patch_floats(int rbmax) { return ks2_cols(rbmax) * ks2_col_pitch(rbmax); }
 __host__ __device__ constexpr int ks2_table_floats(int rbmax) { return 8 * (rbmax + 1) * 32; }
 __host__ __device__ constexpr int ks2_warp_floats(int rbmax) { return ks2_patch_floats(rbmax) + ks2_table_floats(rbmax); }
-static_assert(ks2_col_pitch(16) == 44 && ks2_col_pitch(8) == 28, "column pitch");
-static_assert((ks2_col_pitch(16) - ks2_rows(16)) * 2 * ks2_cols(16) >= KS2_MAXL && (ks2_col_pitch(8) - ks2_rows(8)) * 2 * ks2_cols(8) >= KS2_MAXL, "layer list fits the column pads");
+static_assert(ks2_col_pitch(32) == 76 && ks2_col_pitch(16) == 44 && ks2_col_pitch(8) == 28, "column pitch");
+static_assert((ks2_col_pitch(16) - ks2_rows(16)) * 2 * ks2_cols(16) >= KS2_MAXL && (ks2_col_pitch(8) - ks2_rows(8)) * 2 * ks2_cols(8) >= KS2_MAXL &&
+              (ks2_col_pitch(32) - ks2_rows(32)) * 2 * ks2_cols(32) >= KS2_MAXL, "layer list fits the column pads");
 
 // All 8 source rows of the tile with batch radius RB into the patch of a kernel instantiated for radii <= RBMAX.
 //   tab    : tab[(y*(RB+1) + i)*32 + lane] = e_y[i] of the lane's 8 voxels
@@ -115,11 +117,96 @@ __device__ __forceinline__ void ks2_tile(const float* __restrict__ tab, const fl
     }
 }
 
-// RBMAX: 8 -> items whose largest applied radius (among radii <= 16) is <= 8; 16 -> items with 9..16.
+// Adds NR register-held output rows, starting at patch row Y0 of the column at `col`, with 128-bit read-modify-writes
+// (rows of the aligned window that lie outside [Y0, Y0 + NR) are rewritten unchanged).
+template <int NR, int Y0>
+__device__ __forceinline__ void ks2_rmw(float* __restrict__ col, const float (&acc)[NR]) {
+    constexpr int A = Y0 & 3, YS = Y0 - A, NV = (A + NR + 3) / 4;
+    float4* c = reinterpret_cast<float4*>(col + YS);
+#pragma unroll
+    for (int q = 0; q < NV; ++q) {
+        float4 v = c[q];
+        if (4 * q + 0 - A >= 0 && 4 * q + 0 - A < NR) v.x += acc[(4 * q + 0 - A >= 0 && 4 * q + 0 - A < NR) ? 4 * q + 0 - A : 0];
+        if (4 * q + 1 - A >= 0 && 4 * q + 1 - A < NR) v.y += acc[(4 * q + 1 - A >= 0 && 4 * q + 1 - A < NR) ? 4 * q + 1 - A : 0];
+        if (4 * q + 2 - A >= 0 && 4 * q + 2 - A < NR) v.z += acc[(4 * q + 2 - A >= 0 && 4 * q + 2 - A < NR) ? 4 * q + 2 - A : 0];
+        if (4 * q + 3 - A >= 0 && 4 * q + 3 - A < NR) v.w += acc[(4 * q + 3 - A >= 0 && 4 * q + 3 - A < NR) ? 4 * q + 3 - A : 0];
+        c[q] = v;
+    }
+}
+
+// Batch radii 17..32 (patch of the RBMAX = 32 kernel). The row weights of all 8 voxels of a lane no longer fit the register
+// file at once (8 x 33), so the vertical offsets are split into two bands that run one after the other over all column
+// offsets j: the central band |i| <= 16 (8 x 17 weights, 40 output rows - the register shape of ks2_tile<16>) and the two
+// outer bands 17 <= |i| <= RB, which share their 8 x (RB - 16) weights and produce RB - 9 output rows above and RB - 9
+// below the tile. Same FMA count as a single pass, 86 instead of 72 rows of read-modify-write per column offset.
+template <int RB>
+__device__ __forceinline__ void ks2_tile_big(const float* __restrict__ tab, const float (&d)[8], float* __restrict__ patch, const int lane) {
+    constexpr int RBMAX = 32, P = 8, RC = 16, PC = ks2_col_pitch(RBMAX), TS = RB + 1;
+    static_assert(RB > RC && RB <= RBMAX, "radius class");
+    float* const col0 = patch + (lane + RBMAX) * PC;
+    {   // central band: output rows -RC .. P-1+RC
+        constexpr int W = 2 * RC + 1, NRP = P + 2 * RC;
+        float e[P][RC + 1];
+#pragma unroll
+        for (int y = 0; y < P; ++y)
+#pragma unroll
+            for (int i = 0; i <= RC; ++i) e[y][i] = tab[(y * TS + i) * 32 + lane];
+#pragma unroll 1
+        for (int j = 0; j <= RB; ++j) {
+            float acc[NRP];
+#pragma unroll
+            for (int Y = 0; Y < NRP; ++Y) acc[Y] = 0.0f;
+#pragma unroll
+            for (int y = 0; y < P; ++y) {
+                const float g = d[y] * tab[(y * TS + j) * 32 + lane];
+#pragma unroll
+                for (int i = 0; i < W; ++i) acc[y + i] = fmaf(g, e[y][(i < RC) ? (RC - i) : (i - RC)], acc[y + i]);
+            }
+            ks2_rmw<NRP, RBMAX - RC>(col0 + j * PC, acc);
+            __syncwarp();
+            if (j) { ks2_rmw<NRP, RBMAX - RC>(col0 - j * PC, acc); __syncwarp(); }
+        }
+    }
+    {   // outer bands: i = RC+1 .. RB below the source row (output rows RC+1 .. P-1+RB) and above it (-RB .. P-1-RC-1)
+        constexpr int N2 = RB - RC, NB = P + N2 - 1;
+        float e[P][N2];
+#pragma unroll
+        for (int y = 0; y < P; ++y)
+#pragma unroll
+            for (int k = 0; k < N2; ++k) e[y][k] = tab[(y * TS + RC + 1 + k) * 32 + lane];
+#pragma unroll 1
+        for (int j = 0; j <= RB; ++j) {
+            float lo[NB], up[NB];
+#pragma unroll
+            for (int Y = 0; Y < NB; ++Y) { lo[Y] = 0.0f; up[Y] = 0.0f; }
+#pragma unroll
+            for (int y = 0; y < P; ++y) {
+                const float g = d[y] * tab[(y * TS + j) * 32 + lane];
+#pragma unroll
+                for (int k = 0; k < N2; ++k) {
+                    lo[y + k] = fmaf(g, e[y][k], lo[y + k]);                        // output row y + (RC + 1 + k)
+                    up[y + N2 - 1 - k] = fmaf(g, e[y][k], up[y + N2 - 1 - k]);      // output row y - (RC + 1 + k)
+                }
+            }
+            ks2_rmw<NB, RBMAX - RB>(col0 + j * PC, up);
+            ks2_rmw<NB, RBMAX + RC + 1>(col0 + j * PC, lo);
+            __syncwarp();
+            if (j) {
+                ks2_rmw<NB, RBMAX - RB>(col0 - j * PC, up);
+                ks2_rmw<NB, RBMAX + RC + 1>(col0 - j * PC, lo);
+                __syncwarp();
+            }
+        }
+    }
+}
+
+// The layers of an item (slice, tile) are split by applied radius: those with radius <= 16 are accumulated by the RBMAX = 8
+// kernel (if the largest of them is <= 8) or the RBMAX = 16 kernel (9..16), those with radius 17..32 by the RBMAX = 32
+// kernel, whose 63 KB per warp leave only 3 warps per SM - small radii would run badly there.
 template <int RBMAX, int WARPS>
 __global__ void __launch_bounds__(WARPS * 32)
 ks2_kernel(const Ks2Params p, int* __restrict__ workCounter) {
-    constexpr int RBMIN = (RBMAX == 8) ? 0 : 9;
+    constexpr int RBMIN = (RBMAX == 8) ? 0 : (RBMAX == 16) ? 9 : 17;
     constexpr int PC = ks2_col_pitch(RBMAX), ROWS = ks2_rows(RBMAX);
     extern __shared__ __align__(16) float smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -127,15 +214,19 @@ ks2_kernel(const Ks2Params p, int* __restrict__ workCounter) {
     float* tab = patch + ks2_patch_floats(RBMAX);
     // layer list entry q (layer | rb << 8) lives in the pad of patch column q / 8
     auto llist = [&](int q) -> uint16_t& { return reinterpret_cast<uint16_t*>(patch + (q >> 3) * PC + ROWS)[q & 7]; };
-    const int nItems = p.nz * p.tiles;
+    // The RBMAX = 32 kernel runs only 3 warps per SM: it walks the list of items that have a layer with radius > 16
+    // (big_items_kernel) instead of scanning the whole beam; the list is empty for shallow targets.
+    constexpr int NCH = 1;
+    const int nItems = (RBMAX == 32) ? *p.bigCount : p.nz * p.tiles;
     const int R = p.Rx * p.Ry;
     const int bevPitch = p.Rx + 64;
     for (;;) {
         int it = 0;
         if (lane == 0) it = atomicAdd(workCounter, 1);
         it = __shfl_sync(0xffffffffu, it, 0);
-        if (it >= nItems) break;
-        const int idx = nItems - 1 - it;            // deepest slices (largest radii) first
+        if (it >= nItems * NCH) break;
+        const int idx = (RBMAX == 32) ? (int)p.bigItems[it] : nItems - 1 - it / NCH;      // deepest slices (largest radii) first
+        const int chunk = it % NCH;
         const int kk = idx / p.tiles, tile = idx - kk * p.tiles;
         // compact list of the layers that are live at this (slice, tile), with their applied radius
         int imax = -1, n = 0;
@@ -144,13 +235,14 @@ ks2_kernel(const Ks2Params p, int* __restrict__ workCounter) {
             int rb = -1;
             if (l < p.L && kk < p.layerFirstPassive[l] - p.first) {
                 const unsigned own = p.radMap[((size_t)l * p.nz + kk) * p.tiles + tile];
-                if (own <= 32u) { rb = p.batchRad[l * 34 + own]; if (rb > KS2_MAXRB) rb = -1; }
+                if (own <= 32u) { rb = p.batchRad[l * 34 + own]; if (rb > KS2_MAXRB || (RBMAX == 32 ? rb <= 16 : rb > 16)) rb = -1; }   // > 32 is reported as an error by the host
             }
             const unsigned m = __ballot_sync(0xffffffffu, rb >= 0);
-            if (rb >= 0) llist(n + __popc(m & ((1u << lane) - 1u))) = (uint16_t)(l | (rb << 8));
+            const int pos = n + __popc(m & ((1u << lane) - 1u));       // ordinal among the accepted layers of the item
+            if (rb >= 0 && pos % NCH == chunk) { llist(pos / NCH) = (uint16_t)(l | (rb << 8)); imax = max(imax, rb); }
             n += __popc(m);
-            imax = max(imax, rb);
         }
+        n = (n > chunk) ? (n - chunk + NCH - 1) / NCH : 0;             // entries of this work unit
         imax = __reduce_max_sync(0xffffffffu, imax);
         if (imax < RBMIN || imax > RBMAX) continue;
         // zero the columns this item can touch (rows 0..ROWS-1 only: the pads hold the layer list)
@@ -207,10 +299,12 @@ ks2_kernel(const Ks2Params p, int* __restrict__ workCounter) {
             }
             __syncwarp();
             switch (rb) {
-#define RTD_KS2_CASE(N) case N: if (N <= RBMAX) ks2_tile<(N <= RBMAX) ? N : 0, RBMAX>(tab, d, patch, lane); break;
+#define RTD_KS2_CASE(N) case N: if constexpr (N <= RBMAX) { if constexpr (N <= 16) ks2_tile<N, RBMAX>(tab, d, patch, lane); else ks2_tile_big<(N > 16) ? N : 17>(tab, d, patch, lane); } break;
                 RTD_KS2_CASE(0) RTD_KS2_CASE(1) RTD_KS2_CASE(2) RTD_KS2_CASE(3) RTD_KS2_CASE(4) RTD_KS2_CASE(5) RTD_KS2_CASE(6)
                 RTD_KS2_CASE(7) RTD_KS2_CASE(8) RTD_KS2_CASE(9) RTD_KS2_CASE(10) RTD_KS2_CASE(11) RTD_KS2_CASE(12) RTD_KS2_CASE(13)
-                RTD_KS2_CASE(14) RTD_KS2_CASE(15) RTD_KS2_CASE(16)
+                RTD_KS2_CASE(14) RTD_KS2_CASE(15) RTD_KS2_CASE(16) RTD_KS2_CASE(17) RTD_KS2_CASE(18) RTD_KS2_CASE(19) RTD_KS2_CASE(20)
+                RTD_KS2_CASE(21) RTD_KS2_CASE(22) RTD_KS2_CASE(23) RTD_KS2_CASE(24) RTD_KS2_CASE(25) RTD_KS2_CASE(26) RTD_KS2_CASE(27)
+                RTD_KS2_CASE(28) RTD_KS2_CASE(29) RTD_KS2_CASE(30) RTD_KS2_CASE(31) RTD_KS2_CASE(32)
 #undef RTD_KS2_CASE
                 default: break;
             }

@@ -107,16 +107,15 @@ struct rtd_ctx {
     std::vector<cudaEvent_t> events;
     std::vector<cudaStream_t> bstreams;   // per-beam streams (concurrent beams)
     int smCount = 148;
-    int ksBlocksA = 0, ksBlocksB = 0, ksBlocksC = 0, ks2Blocks8 = 0, ks2Blocks16 = 0;
+    int ks2Blocks8 = 0, ks2Blocks16 = 0, ks2Blocks32 = 0;
     rtd_opts optsLast;
 };
 
 namespace {
 
-constexpr int KS_NT_A = 64, KS_NT_B = 96, KS_NT_C = 128;
-constexpr int KS2_WARPS_8 = 15, KS2_WARPS_16 = 8;   // warps per CTA: as many as the per-warp shared memory allows on one SM
-constexpr size_t KS2_SMEM_8 = size_t(KS2_WARPS_8) * ks2_warp_floats(8) * 4, KS2_SMEM_16 = size_t(KS2_WARPS_16) * ks2_warp_floats(16) * 4;
-constexpr size_t KS_SMEM_A = ks_smem_floats(8) * 4, KS_SMEM_B = ks_smem_floats(16) * 4, KS_SMEM_C = ks_smem_floats(32) * 4;
+constexpr int KS2_WARPS_8 = 15, KS2_WARPS_16 = 8, KS2_WARPS_32 = 3;   // warps per CTA: as many as the per-warp shared memory allows on one SM
+constexpr size_t KS2_SMEM_8 = size_t(KS2_WARPS_8) * ks2_warp_floats(8) * 4, KS2_SMEM_16 = size_t(KS2_WARPS_16) * ks2_warp_floats(16) * 4,
+                 KS2_SMEM_32 = size_t(KS2_WARPS_32) * ks2_warp_floats(32) * 4;
 
 rtd_status fail(rtd_ctx* c, rtd_status s, const std::string& msg) { if (c) c->err = msg; return s; }
 
@@ -556,19 +555,16 @@ rtd_status beamPhaseB2(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opt
     const int gx = (nz * tiles + 255) / 256;
     tile_radius_kernel<<<dim3(gx, L), 256, 0, strm>>>(w.rowMin.as<float>(), dLfp, w.bfi, nz, Rx, Ry, o.ksSigmaCutoff, w.radMap.as<uint8_t>(), dHist);
     batch_kernel<<<1, 64, 0, strm>>>(dHist, L, o.minTilesInBatch, w.batchRad.as<int>(), w.rbOffset.as<int>(), dStats);
-    fill_list_kernel<<<dim3(gx, L), 256, 0, strm>>>(w.radMap.as<uint8_t>(), w.batchRad.as<int>(), w.rbOffset.as<int>(), dCursor, nz, tiles, w.list.as<uint32_t>());
+    big_items_kernel<<<gx, 256, 0, strm>>>(w.radMap.as<uint8_t>(), w.batchRad.as<int>(), L, nz, tiles, w.rbOffset.as<int>() + 16, dCursor, w.list.as<uint32_t>());
     RTD_CUDA(cudaEventRecord(evs[3], strm));
 
-    // K3b: radii 17..32 (rare) through the block-wide kernel and its work list; radii <= 16 through the layer-fused
-    // warp-autonomous kernel (ks2.cuh), one launch per patch-size class
-    KsParams kp;
-    kp.idd = w.idd.as<float>(); kp.rsig = w.rsig.as<float>(); kp.bev = w.bev.as<float>(); kp.list = w.list.as<uint32_t>();
-    kp.batchRad = w.batchRad.as<int>(); kp.radMap = w.radMap.as<uint8_t>();
-    kp.Rx = Rx; kp.Ry = Ry; kp.nz = nz; kp.first = w.bfi; kp.tilesX = tilesX; kp.tiles = tiles;
-    ks_kernel<KS_NT_C, 17, 32><<<ctx->ksBlocksC, KS_NT_C, KS_SMEM_C, strm>>>(kp, w.rbOffset.as<int>(), dStats, dWork + 0);
+    // K3b: layer-fused, warp-autonomous superposition (ks2.cuh), one launch per patch-size class; the heaviest class first
     Ks2Params k2;
-    k2.idd = kp.idd; k2.rsig = kp.rsig; k2.bev = kp.bev; k2.batchRad = kp.batchRad; k2.radMap = kp.radMap; k2.layerFirstPassive = dLfp;
+    k2.idd = w.idd.as<float>(); k2.rsig = w.rsig.as<float>(); k2.bev = w.bev.as<float>(); k2.batchRad = w.batchRad.as<int>();
+    k2.radMap = w.radMap.as<uint8_t>(); k2.layerFirstPassive = dLfp;
     k2.L = L; k2.Rx = Rx; k2.Ry = Ry; k2.nz = nz; k2.first = w.bfi; k2.tilesX = tilesX; k2.tiles = tiles;
+    k2.bigCount = dCursor; k2.bigItems = w.list.as<uint32_t>();
+    ks2_kernel<32, KS2_WARPS_32><<<ctx->ks2Blocks32, KS2_WARPS_32 * 32, KS2_SMEM_32, strm>>>(k2, dWork + 0);
     ks2_kernel<16, KS2_WARPS_16><<<ctx->ks2Blocks16, KS2_WARPS_16 * 32, KS2_SMEM_16, strm>>>(k2, dWork + 1);
     ks2_kernel<8, KS2_WARPS_8><<<ctx->ks2Blocks8, KS2_WARPS_8 * 32, KS2_SMEM_8, strm>>>(k2, dWork + 2);
     RTD_CUDA(cudaEventRecord(evs[4], strm));
@@ -776,13 +772,13 @@ rtd_status rtd_create(rtd_ctx** out, int device) {
     if (cudaStreamCreateWithPriority(&ctx->cstream, cudaStreamNonBlocking, prHi) != cudaSuccess) { cudaStreamDestroy(ctx->stream); delete ctx; return RTD_ERR_CUDA; }
     cudaDeviceGetAttribute(&ctx->smCount, cudaDevAttrMultiProcessorCount, device);
     rtd_default_opts(&ctx->optsLast);
-    cudaFuncSetAttribute(ks_kernel<KS_NT_C, 17, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)KS_SMEM_C);
     cudaFuncSetAttribute(ks2_kernel<16, KS2_WARPS_16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)KS2_SMEM_16);
     cudaFuncSetAttribute(ks2_kernel<8, KS2_WARPS_8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)KS2_SMEM_8);
+    cudaFuncSetAttribute(ks2_kernel<32, KS2_WARPS_32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)KS2_SMEM_32);
     int occ = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ks_kernel<KS_NT_C, 17, 32>, KS_NT_C, KS_SMEM_C); ctx->ksBlocksC = std::max(occ, 1) * ctx->smCount;
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ks2_kernel<16, KS2_WARPS_16>, KS2_WARPS_16 * 32, KS2_SMEM_16); ctx->ks2Blocks16 = std::max(occ, 1) * ctx->smCount;
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ks2_kernel<8, KS2_WARPS_8>, KS2_WARPS_8 * 32, KS2_SMEM_8); ctx->ks2Blocks8 = std::max(occ, 1) * ctx->smCount;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ks2_kernel<32, KS2_WARPS_32>, KS2_WARPS_32 * 32, KS2_SMEM_32); ctx->ks2Blocks32 = std::max(occ, 1) * ctx->smCount;
     if (cudaGetLastError() != cudaSuccess) { cudaStreamDestroy(ctx->stream); delete ctx; return RTD_ERR_CUDA; }
     *out = ctx;
     return RTD_OK;

@@ -376,3 +376,44 @@ def test_push_dose_to_peer_adds_only_dose_holding_groups(eng):
     assert torch.equal(d_dst.cpu(), want)
     with pytest.raises(engine.RtdError):
         eng.push_dose_to_peer(d_src.data_ptr() + 4, d_dst.data_ptr(), 8)
+
+
+def deep_fine_case():
+    """Deep target on a fine ray grid: 0.5 mm rays, ~150-165 MeV in water with a bone slab -> applied superposition radii
+    from a few rays at the entrance up to ~30 at the Bragg peak, i.e. every radius class of the superposition kernels
+    including the two-band path for radii 17..32 (ks2_tile_big)."""
+    luts = cases.load_packaged_luts() if hasattr(cases, "load_packaged_luts") else None
+    if luts is None:
+        from raytracedicom_b200.energy_reader import load_packaged_luts
+        luts = load_packaged_luts()
+    nx, ny, nz = 64, 64, 230
+    ct = np.full((nz, ny, nx), 1000.0, np.float32)
+    ct[-6:, :, :] = 0.0
+    ct[150:160, :, :32] = 1800.0
+    energies = np.array([150.0, 165.0], np.float32)
+    rng = cases.Lcg(cases.SEED + 11)
+    w = (60.0 + 40.0 * rng.uniform(2 * 3 * 3)).astype(np.float32).reshape(2, 3, 3)
+    sig = np.array([[3.0, 3.2], [2.9, 3.1]], np.float32)
+    m = np.eye(3, dtype=np.float32); v = np.array([31.5, 31.5, 115.0], np.float32)
+    b = cases.Beam(w, energies, sig, (0.5, 0.5), 226, (2000.0, 1800.0), (4.0, 4.0, -1.0), (-4.0, -4.0, 112.0), m, v)
+    return cases.Case("deep_fine", ct, [b], luts)
+
+
+def test_large_radius_classes_against_oracle(eng, oracle):
+    case = deep_fine_case()
+    dose, t = run_case(eng, case)
+    o = oracle.run_beam(case, 0)
+    rep = eng.beam_report(0)
+    for k in ("lSteps", "bSteps", "rSteps", "tSteps", "beamFirstInside", "beamFirstOutside", "beamFirstGuaranteedPassive",
+              "beamFirstCalculatedPassive", "updates", "bboxMin", "bboxMax"):
+        assert rep[k] == o[k], k
+    applied = set()
+    for l in range(rep["nLayers"]):
+        lr = eng.layer_report(0, l)
+        assert list(lr["radiusHist"]) == list(o["hist"][l])
+        applied |= {int(lr["batchRadius"][r]) for r in range(33) if lr["radiusHist"][r] > 0}
+    assert max(applied) >= 24 and min(applied) <= 8 and any(9 <= r <= 16 for r in applied)      # all three kernel classes ran
+    assert t["updates"] == o["updates"] and t["ksTaps"] == o["ksTaps"]
+    err, nf = rel_to_max(dose, o["dose"])
+    assert nf == 0 and err <= 2e-4 <= DOSE_TOL
+    assert gamma_pass_rate(dose, o["dose"], case.spacing) >= 0.999
