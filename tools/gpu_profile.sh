@@ -6,7 +6,7 @@ CMD="python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu-baseline"
 $CMD > gpurun_out/plain.log 2>&1 || { tail -5 gpurun_out/plain.log; exit 1; }
 ncu --metrics gpu__time_duration.sum --clock-control none -c 800 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_launches.log 2>&1
 echo "launch list rc=$?"
-ncu --set full --clock-control none --import-source on -k regex:ks2_kernel -s 6 -c 6 -o gpurun_out/prof_ks2 -f $CMD > gpurun_out/ncu_full.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:ks2_kernel -s 9 -c 9 -o gpurun_out/prof_ks2 -f $CMD > gpurun_out/ncu_full.log 2>&1
 echo "full rc=$?"
 ncu --set full --clock-control none --import-source on -k regex:'idd_sigma_kernel|bev_to_grid_kernel|trace_bev_kernel' -s 9 -c 9 -o gpurun_out/prof_rest -f $CMD > gpurun_out/ncu_full2.log 2>&1
 echo "full2 rc=$?"
