@@ -323,6 +323,7 @@ def main():
     barrier()
     t_wall = time.perf_counter() - t_wall0
     ms_local = sum(a.elapsed_time(b) for a, b in evs) / args.steps
+    ms_each_local = [round(a.elapsed_time(b), 4) for a, b in evs]      # rank 0's own per-step times (spread / outliers)
     # stage timings / roofline: a few extra steps with the beams serialised on one stream, so that the library's stage
     # events bracket each kernel alone (with concurrent beams the stages of different beams overlap in time)
     conc_stage = dict(stage)
@@ -437,7 +438,7 @@ def main():
                            "sharding": (f"(beam, layer-range) work items, LPT over {world} rank(s); " + ("every rank adds the dose-holding float4 groups of its slab into ONE grid on rank 0 over NVLink (CUDA IPC, red.global.add.v4.f32), no dense collective" if push else "every rank's transfer kernels add into ONE dose grid on rank 0 over NVLink (CUDA IPC, red.global.add.f32), no separate collective" if peer else "partial dose grids (reachable z-slab) summed by one NCCL reduce")) if world > 1 else "single GPU",
                            "l2": "256 MiB buffer written between timed iterations (L2 flush); CT 4*%d B and BEV arrays exceed L2" % (nx * ny * nz)},
                 "plan_ms": ms_step, "updates_per_step": U,
-                "stage_total_ms_per_rank": rank_stage_ms, "work_items_per_rank": [len(p) for p in parts],
+                "ms_each_step_rank0": ms_each_local, "stage_total_ms_per_rank": rank_stage_ms, "work_items_per_rank": [len(p) for p in parts],
                 "stage_ms_rank0": {k: stage[k] / args.steps for k in ("msTrace", "msSetup", "msConv", "msIddSigma", "msRadius", "msSuperp", "msTransfer", "msTotal")},
                 "stage_note": "stage_ms_rank0 and roofline come from 3 extra steps with opts.serialBeams=1 (stages bracketed alone); the timed steps run one stream per beam",
                 "serial_beams_plan_ms": stage["msTotal"] / args.steps,
