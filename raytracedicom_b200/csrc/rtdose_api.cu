@@ -274,6 +274,8 @@ void ctBoxesOfBeam(const TraceParams& p, int Rx, int Ry, int S, const int dims[3
         int64_t vox = 0; for (const Box& b : tmp) vox += boxVoxels(b);
         if (bestVox < 0 || vox < bestVox) { bestVox = vox; best = segLen; }
     }
+    // slab thickness 64: measured on B200 (C3, end to end): 40 -> 3.22 ms, 48 -> 3.06, 56 -> 3.04, 64 -> 2.82, 96 -> 2.87,
+    // 128 -> 2.88, 192 -> 2.94 (thinner slabs move fewer bytes but their short rows starve the copy engine)
     for (int width : {64, 32}) {
         std::vector<Box> tmp;
         if (!slabBoxes(width, tmp)) break;
