@@ -410,9 +410,9 @@ def main():
         peak, peak_src, sm_max = load_peaks()
         reps = [eng.beam_report(b) for b in range(len(mine))]
         live = [r for r in reps if r["beamFirstCalculatedPassive"] > r["beamFirstInside"]]
-        # on C3 two ks2 launches per live beam do the work (radius classes <= 8 and 9..16); the launch of the 17..32 class
-        # finds an empty item list there (a few microseconds inside msSuperp). Workloads with deep targets (C2, C4, C5)
-        # also use the third class; their roofline line still divides by two launches per beam.
+        # on C3 two ks2 launches per live beam do the work (radius classes <= 8 and 9..16); the launches of the 17..24 and
+        # 25..32 classes find an empty item list there (a few microseconds inside msSuperp). Workloads with deep targets
+        # (C2, C4, C5) also use those classes; their roofline line still divides by two launches per beam.
         ks_launches = max(1, 2 * len(live))
         traffic, traffic_src = None, None
         tp = os.path.join(ROOT, "profiles", "r01_ncu_ks2_traffic.json")

@@ -65,9 +65,10 @@ __host__ __device__ constexpr int ks2_col_pitch(int rbmax) {
 __host__ __device__ constexpr int ks2_patch_floats(int rbmax) { return ks2_cols(rbmax) * ks2_col_pitch(rbmax); }
 __host__ __device__ constexpr int ks2_table_floats(int rbmax) { return 8 * (rbmax + 1) * 32; }
 __host__ __device__ constexpr int ks2_warp_floats(int rbmax) { return ks2_patch_floats(rbmax) + ks2_table_floats(rbmax); }
-static_assert(ks2_col_pitch(32) == 76 && ks2_col_pitch(16) == 44 && ks2_col_pitch(8) == 28, "column pitch");
+static_assert(ks2_col_pitch(32) == 76 && ks2_col_pitch(24) == 60 && ks2_col_pitch(16) == 44 && ks2_col_pitch(8) == 28, "column pitch");
 static_assert((ks2_col_pitch(16) - ks2_rows(16)) * 2 * ks2_cols(16) >= KS2_MAXL && (ks2_col_pitch(8) - ks2_rows(8)) * 2 * ks2_cols(8) >= KS2_MAXL &&
-              (ks2_col_pitch(32) - ks2_rows(32)) * 2 * ks2_cols(32) >= KS2_MAXL, "layer list fits the column pads");
+              (ks2_col_pitch(32) - ks2_rows(32)) * 2 * ks2_cols(32) >= KS2_MAXL && (ks2_col_pitch(24) - ks2_rows(24)) * 2 * ks2_cols(24) >= KS2_MAXL,
+              "layer list fits the column pads");
 
 // All 8 source rows of the tile with batch radius RB into the patch of a kernel instantiated for radii <= RBMAX.
 //   tab    : tab[(y*(RB+1) + i)*32 + lane] = e_y[i] of the lane's 8 voxels
@@ -134,14 +135,14 @@ __device__ __forceinline__ void ks2_rmw(float* __restrict__ col, const float (&a
     }
 }
 
-// Batch radii 17..32 (patch of the RBMAX = 32 kernel). The row weights of all 8 voxels of a lane no longer fit the register
+// Batch radii 17..32 (patch of the RBMAX = 24 or RBMAX = 32 kernel). The row weights of all 8 voxels of a lane no longer fit the register
 // file at once (8 x 33), so the vertical offsets are split into two bands that run one after the other over all column
 // offsets j: the central band |i| <= 16 (8 x 17 weights, 40 output rows - the register shape of ks2_tile<16>) and the two
 // outer bands 17 <= |i| <= RB, which share their 8 x (RB - 16) weights and produce RB - 9 output rows above and RB - 9
 // below the tile. Same FMA count as a single pass, 86 instead of 72 rows of read-modify-write per column offset.
-template <int RB>
+template <int RB, int RBMAX>
 __device__ __forceinline__ void ks2_tile_big(const float* __restrict__ tab, const float (&d)[8], float* __restrict__ patch, const int lane) {
-    constexpr int RBMAX = 32, P = 8, RC = 16, PC = ks2_col_pitch(RBMAX), TS = RB + 1;
+    constexpr int P = 8, RC = 16, PC = ks2_col_pitch(RBMAX), TS = RB + 1;
     static_assert(RB > RC && RB <= RBMAX, "radius class");
     float* const col0 = patch + (lane + RBMAX) * PC;
     {   // central band: output rows -RC .. P-1+RC
@@ -201,12 +202,15 @@ __device__ __forceinline__ void ks2_tile_big(const float* __restrict__ tab, cons
 }
 
 // The layers of an item (slice, tile) are split by applied radius: those with radius <= 16 are accumulated by the RBMAX = 8
-// kernel (if the largest of them is <= 8) or the RBMAX = 16 kernel (9..16), those with radius 17..32 by the RBMAX = 32
-// kernel, whose 63 KB per warp leave only 3 warps per SM - small radii would run badly there.
+// kernel (if the largest of them is <= 8) or the RBMAX = 16 kernel (9..16), those with radius 17..32 by the RBMAX = 24
+// kernel (if the largest of them is <= 24: 45 KB of patch + table per warp, 5 warps per SM) or the RBMAX = 32 kernel
+// (25..32), whose 63 KB per warp leave only 3 warps per SM - small radii would run badly there.
 template <int RBMAX, int WARPS>
 __global__ void __launch_bounds__(WARPS * 32)
 ks2_kernel(const Ks2Params p, int* __restrict__ workCounter) {
-    constexpr int RBMIN = (RBMAX == 8) ? 0 : (RBMAX == 16) ? 9 : 17;
+    constexpr int RBMIN = (RBMAX == 8) ? 0 : (RBMAX == 16) ? 9 : (RBMAX == 24) ? 17 : 25;      // the item's largest radius
+    constexpr bool BIG = RBMAX > 16;                  // which layers of an item: applied radius 17..32 or 0..16
+    constexpr int LAYER_RMIN = BIG ? 17 : 0;
     constexpr int PC = ks2_col_pitch(RBMAX), ROWS = ks2_rows(RBMAX);
     extern __shared__ __align__(16) float smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -214,10 +218,10 @@ ks2_kernel(const Ks2Params p, int* __restrict__ workCounter) {
     float* tab = patch + ks2_patch_floats(RBMAX);
     // layer list entry q (layer | rb << 8) lives in the pad of patch column q / 8
     auto llist = [&](int q) -> uint16_t& { return reinterpret_cast<uint16_t*>(patch + (q >> 3) * PC + ROWS)[q & 7]; };
-    // The RBMAX = 32 kernel runs only 3 warps per SM: it walks the list of items that have a layer with radius > 16
+    // The RBMAX = 24 / 32 kernels run only 5 / 3 warps per SM: they walk the list of items that have a layer with radius > 16
     // (big_items_kernel) instead of scanning the whole beam; the list is empty for shallow targets.
     constexpr int NCH = 1;
-    const int nItems = (RBMAX == 32) ? *p.bigCount : p.nz * p.tiles;
+    const int nItems = BIG ? *p.bigCount : p.nz * p.tiles;
     const int R = p.Rx * p.Ry;
     const int bevPitch = p.Rx + 64;
     for (;;) {
@@ -225,7 +229,7 @@ ks2_kernel(const Ks2Params p, int* __restrict__ workCounter) {
         if (lane == 0) it = atomicAdd(workCounter, 1);
         it = __shfl_sync(0xffffffffu, it, 0);
         if (it >= nItems * NCH) break;
-        const int idx = (RBMAX == 32) ? (int)p.bigItems[it] : nItems - 1 - it / NCH;      // deepest slices (largest radii) first
+        const int idx = BIG ? (int)p.bigItems[it] : nItems - 1 - it / NCH;      // deepest slices (largest radii) first
         const int chunk = it % NCH;
         const int kk = idx / p.tiles, tile = idx - kk * p.tiles;
         // compact list of the layers that are live at this (slice, tile), with their applied radius
@@ -235,7 +239,7 @@ ks2_kernel(const Ks2Params p, int* __restrict__ workCounter) {
             int rb = -1;
             if (l < p.L && kk < p.layerFirstPassive[l] - p.first) {
                 const unsigned own = p.radMap[((size_t)l * p.nz + kk) * p.tiles + tile];
-                if (own <= 32u) { rb = p.batchRad[l * 34 + own]; if (rb > KS2_MAXRB || (RBMAX == 32 ? rb <= 16 : rb > 16)) rb = -1; }   // > 32 is reported as an error by the host
+                if (own <= 32u) { rb = p.batchRad[l * 34 + own]; if (rb > KS2_MAXRB || (BIG ? rb <= 16 : rb > 16)) rb = -1; }   // > 32 is reported as an error by the host
             }
             const unsigned m = __ballot_sync(0xffffffffu, rb >= 0);
             const int pos = n + __popc(m & ((1u << lane) - 1u));       // ordinal among the accepted layers of the item
@@ -299,7 +303,7 @@ ks2_kernel(const Ks2Params p, int* __restrict__ workCounter) {
             }
             __syncwarp();
             switch (rb) {
-#define RTD_KS2_CASE(N) case N: if constexpr (N <= RBMAX) { if constexpr (N <= 16) ks2_tile<N, RBMAX>(tab, d, patch, lane); else ks2_tile_big<(N > 16) ? N : 17>(tab, d, patch, lane); } break;
+#define RTD_KS2_CASE(N) case N: if constexpr (N <= RBMAX && N >= LAYER_RMIN) { if constexpr (N <= 16) ks2_tile<N, RBMAX>(tab, d, patch, lane); else ks2_tile_big<(N > 16) ? N : 17, BIG ? RBMAX : 32>(tab, d, patch, lane); } break;
                 RTD_KS2_CASE(0) RTD_KS2_CASE(1) RTD_KS2_CASE(2) RTD_KS2_CASE(3) RTD_KS2_CASE(4) RTD_KS2_CASE(5) RTD_KS2_CASE(6)
                 RTD_KS2_CASE(7) RTD_KS2_CASE(8) RTD_KS2_CASE(9) RTD_KS2_CASE(10) RTD_KS2_CASE(11) RTD_KS2_CASE(12) RTD_KS2_CASE(13)
                 RTD_KS2_CASE(14) RTD_KS2_CASE(15) RTD_KS2_CASE(16) RTD_KS2_CASE(17) RTD_KS2_CASE(18) RTD_KS2_CASE(19) RTD_KS2_CASE(20)

@@ -107,15 +107,16 @@ struct rtd_ctx {
     std::vector<cudaEvent_t> events;
     std::vector<cudaStream_t> bstreams;   // per-beam streams (concurrent beams)
     int smCount = 148;
-    int ks2Blocks8 = 0, ks2Blocks16 = 0, ks2Blocks32 = 0;
+    int ks2Blocks8 = 0, ks2Blocks16 = 0, ks2Blocks24 = 0, ks2Blocks32 = 0;
     rtd_opts optsLast;
 };
 
 namespace {
 
-constexpr int KS2_WARPS_8 = 15, KS2_WARPS_16 = 8, KS2_WARPS_32 = 3;   // warps per CTA: as many as the per-warp shared memory allows on one SM
+constexpr int KS2_WARPS_8 = 15, KS2_WARPS_16 = 8, KS2_WARPS_24 = 5, KS2_WARPS_32 = 3;   // warps per CTA: as many as the per-warp shared memory allows on one SM
 constexpr size_t KS2_SMEM_8 = size_t(KS2_WARPS_8) * ks2_warp_floats(8) * 4, KS2_SMEM_16 = size_t(KS2_WARPS_16) * ks2_warp_floats(16) * 4,
-                 KS2_SMEM_32 = size_t(KS2_WARPS_32) * ks2_warp_floats(32) * 4;
+                 KS2_SMEM_24 = size_t(KS2_WARPS_24) * ks2_warp_floats(24) * 4, KS2_SMEM_32 = size_t(KS2_WARPS_32) * ks2_warp_floats(32) * 4;
+static_assert(KS2_SMEM_8 <= 227 * 1024 && KS2_SMEM_16 <= 227 * 1024 && KS2_SMEM_24 <= 227 * 1024 && KS2_SMEM_32 <= 227 * 1024, "one CTA per SM");
 
 rtd_status fail(rtd_ctx* c, rtd_status s, const std::string& msg) { if (c) c->err = msg; return s; }
 
@@ -567,6 +568,7 @@ rtd_status beamPhaseB2(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opt
     k2.L = L; k2.Rx = Rx; k2.Ry = Ry; k2.nz = nz; k2.first = w.bfi; k2.tilesX = tilesX; k2.tiles = tiles;
     k2.bigCount = dCursor; k2.bigItems = w.list.as<uint32_t>();
     ks2_kernel<32, KS2_WARPS_32><<<ctx->ks2Blocks32, KS2_WARPS_32 * 32, KS2_SMEM_32, strm>>>(k2, dWork + 0);
+    ks2_kernel<24, KS2_WARPS_24><<<ctx->ks2Blocks24, KS2_WARPS_24 * 32, KS2_SMEM_24, strm>>>(k2, dWork + 3);
     ks2_kernel<16, KS2_WARPS_16><<<ctx->ks2Blocks16, KS2_WARPS_16 * 32, KS2_SMEM_16, strm>>>(k2, dWork + 1);
     ks2_kernel<8, KS2_WARPS_8><<<ctx->ks2Blocks8, KS2_WARPS_8 * 32, KS2_SMEM_8, strm>>>(k2, dWork + 2);
     RTD_CUDA(cudaEventRecord(evs[4], strm));
@@ -579,7 +581,7 @@ rtd_status beamPhaseB2(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opt
         bev_to_grid_kernel<<<w.gpGrid, 256, 0, ctx->stream>>>(w.bev.as<float>(), dDose, w.gp, ctx->xferCount.as<unsigned long long>());
         launches += 1;
     }
-    launches += 8;
+    launches += 9;
     RTD_CUDA(cudaGetLastError());
     RTD_CUDA(cudaEventRecord(evs[5], ctx->stream));
     // results for the reports: control block + batch radii
@@ -777,10 +779,12 @@ rtd_status rtd_create(rtd_ctx** out, int device) {
     cudaFuncSetAttribute(ks2_kernel<16, KS2_WARPS_16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)KS2_SMEM_16);
     cudaFuncSetAttribute(ks2_kernel<8, KS2_WARPS_8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)KS2_SMEM_8);
     cudaFuncSetAttribute(ks2_kernel<32, KS2_WARPS_32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)KS2_SMEM_32);
+    cudaFuncSetAttribute(ks2_kernel<24, KS2_WARPS_24>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)KS2_SMEM_24);
     int occ = 0;
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ks2_kernel<16, KS2_WARPS_16>, KS2_WARPS_16 * 32, KS2_SMEM_16); ctx->ks2Blocks16 = std::max(occ, 1) * ctx->smCount;
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ks2_kernel<8, KS2_WARPS_8>, KS2_WARPS_8 * 32, KS2_SMEM_8); ctx->ks2Blocks8 = std::max(occ, 1) * ctx->smCount;
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ks2_kernel<32, KS2_WARPS_32>, KS2_WARPS_32 * 32, KS2_SMEM_32); ctx->ks2Blocks32 = std::max(occ, 1) * ctx->smCount;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ks2_kernel<24, KS2_WARPS_24>, KS2_WARPS_24 * 32, KS2_SMEM_24); ctx->ks2Blocks24 = std::max(occ, 1) * ctx->smCount;
     if (cudaGetLastError() != cudaSuccess) { cudaStreamDestroy(ctx->stream); delete ctx; return RTD_ERR_CUDA; }
     *out = ctx;
     return RTD_OK;

@@ -381,7 +381,7 @@ def test_push_dose_to_peer_adds_only_dose_holding_groups(eng):
 def deep_fine_case():
     """Deep target on a fine ray grid: 0.5 mm rays, ~150-165 MeV in water with a bone slab -> applied superposition radii
     from a few rays at the entrance up to ~30 at the Bragg peak, i.e. every radius class of the superposition kernels
-    including the two-band path for radii 17..32 (ks2_tile_big)."""
+    including the two-band path for radii 17..32 (ks2_tile_big) in both of its kernels (patches for radii <= 24 and <= 32)."""
     luts = cases.load_packaged_luts() if hasattr(cases, "load_packaged_luts") else None
     if luts is None:
         from raytracedicom_b200.energy_reader import load_packaged_luts
@@ -412,7 +412,8 @@ def test_large_radius_classes_against_oracle(eng, oracle):
         lr = eng.layer_report(0, l)
         assert list(lr["radiusHist"]) == list(o["hist"][l])
         applied |= {int(lr["batchRadius"][r]) for r in range(33) if lr["radiusHist"][r] > 0}
-    assert max(applied) >= 24 and min(applied) <= 8 and any(9 <= r <= 16 for r in applied)      # all three kernel classes ran
+    # every kernel class ran: <8>, <16>, <24> (radii 17..24 at depths where no layer is wider) and <32>
+    assert max(applied) >= 25 and min(applied) <= 8 and any(9 <= r <= 16 for r in applied) and any(17 <= r <= 24 for r in applied)
     assert t["updates"] == o["updates"] and t["ksTaps"] == o["ksTaps"]
     err, nf = rel_to_max(dose, o["dose"])
     assert nf == 0 and err <= 2e-4 <= DOSE_TOL
