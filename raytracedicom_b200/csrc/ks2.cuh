@@ -26,6 +26,8 @@ struct Ks2Params {
     const int* layerFirstPassive;   // [L]
     int L, Rx, Ry, nz, first, tilesX, tiles;
     const int* bigCount; const uint32_t* bigItems;   // items with a layer of applied radius > 16 (big_items_kernel)
+    int bodyStep;                   // 1, 2 or 4: radii <= 16 run in the unrolled body of the next multiple (see ks2_kernel);
+                                    // 0 = 2 if the beam has items with a radius > 16 (*bigCount > 0), else 1
 };
 
 // erf(x) for x >= 0 as 1 - 2^(x Q(x)), Q = degree-7 fit of log2(erfc(x))/x on [0,4] (erf(4) rounds to 1 in fp32).
@@ -75,7 +77,7 @@ static_assert((ks2_col_pitch(16) - ks2_rows(16)) * 2 * ks2_cols(16) >= KS2_MAXL 
 //   d      : dose of the lane's 8 voxels
 //   patch  : column-major patch of this warp
 template <int RB, int RBMAX>
-__device__ __forceinline__ void ks2_tile(const float* __restrict__ tab, const float (&d)[8], float* __restrict__ patch, const int lane) {
+__device__ __forceinline__ void ks2_tile(const float* __restrict__ tab, const float (&d)[8], float* __restrict__ patch, const int lane, const int jmax) {
     constexpr int P = 8, W = 2 * RB + 1, NRP = P + 2 * RB, PC = ks2_col_pitch(RBMAX);
     constexpr int Y0 = RBMAX - RB;            // patch row of the first output row (tile row -RB)
     constexpr int A = Y0 & 3, YS = Y0 - A;    // 128-bit window [YS, YS + 4 NV) around the NRP output rows
@@ -88,7 +90,7 @@ __device__ __forceinline__ void ks2_tile(const float* __restrict__ tab, const fl
         for (int i = 0; i <= RB; ++i) e[y][i] = tab[(y * (RB + 1) + i) * 32 + lane];
     float* const col0 = patch + (lane + RBMAX) * PC + YS;     // the lane's own column (offset j = 0)
 #pragma unroll 1
-    for (int j = 0; j <= RB; ++j) {
+    for (int j = 0; j <= jmax; ++j) {       // jmax = applied radius (<= RB: a radius may run in the body of a larger one)
         float acc[NRP];
 #pragma unroll
         for (int Y = 0; Y < NRP; ++Y) acc[Y] = 0.0f;
@@ -221,7 +223,12 @@ ks2_kernel(const Ks2Params p, int* __restrict__ workCounter) {
     // The RBMAX = 24 / 32 kernels run only 5 / 3 warps per SM: they walk the list of items that have a layer with radius > 16
     // (big_items_kernel) instead of scanning the whole beam; the list is empty for shallow targets.
     constexpr int NCH = 1;
-    const int nItems = BIG ? *p.bigCount : p.nz * p.tiles;
+    const int nBig = *p.bigCount;
+    const int nItems = BIG ? nBig : p.nz * p.tiles;
+    // Beams that reach radii > 16 spread their layers over many different radii: the per-radius bodies (~108 KB of code in
+    // the RBMAX = 16 kernel) then miss the instruction caches, and running odd radii in the next even body pays
+    // (C4 superposition 15.7 -> 13.3 ms); beams that stay <= 16 are better off with the exact body (C3 1.14 vs 1.16 ms).
+    const int bodyStep = p.bodyStep ? p.bodyStep : (nBig > 0 ? 2 : 1);
     const int R = p.Rx * p.Ry;
     const int bevPitch = p.Rx + 64;
     for (;;) {
@@ -268,6 +275,10 @@ ks2_kernel(const Ks2Params p, int* __restrict__ workCounter) {
         }
         for (int q = 0; q < n; ++q) {
             const int rb = llist(q) >> 8;
+            // body = radius whose unrolled code runs: with bodyStep 2 / 4 a radius <= 16 uses the body of the next multiple
+            // with zero weights beyond rb and the column loop still ending at rb - the same sums bit for bit, a few more
+            // FMAs, but 1/2 or 1/4 of the code working set (instruction-fetch stalls, profiles/r01_ncu_full_ks2_c4.txt)
+            const int body = BIG ? rb : min((rb + bodyStep - 1) & -bodyStep, RBMAX);
             float d[8], r[8];
 #pragma unroll
             for (int y = 0; y < 8; ++y) { d[y] = dn[y]; r[y] = rn[y]; }
@@ -286,7 +297,7 @@ ks2_kernel(const Ks2Params p, int* __restrict__ workCounter) {
             {
                 float x[8], erfOld[8];
                 float* t = tab + lane;
-                const int rowStride = (rb + 1) * 32;
+                const int rowStride = (body + 1) * 32;
 #pragma unroll
                 for (int y = 0; y < 8; ++y) { x[y] = r[y] * 0.5f; erfOld[y] = ks_erf_pos(x[y]); t[y * rowStride] = erfOld[y]; }
 #pragma unroll 1
@@ -300,10 +311,15 @@ ks2_kernel(const Ks2Params p, int* __restrict__ workCounter) {
                         erfOld[y] = erfNew;
                     }
                 }
+                for (int i = rb + 1; i <= body; ++i) {
+                    t += 32;
+#pragma unroll
+                    for (int y = 0; y < 8; ++y) t[y * rowStride] = 0.0f;
+                }
             }
             __syncwarp();
-            switch (rb) {
-#define RTD_KS2_CASE(N) case N: if constexpr (N <= RBMAX && N >= LAYER_RMIN) { if constexpr (N <= 16) ks2_tile<N, RBMAX>(tab, d, patch, lane); else ks2_tile_big<(N > 16) ? N : 17, BIG ? RBMAX : 32>(tab, d, patch, lane); } break;
+            switch (body) {
+#define RTD_KS2_CASE(N) case N: if constexpr (N <= RBMAX && N >= LAYER_RMIN) { if constexpr (N <= 16) ks2_tile<N, RBMAX>(tab, d, patch, lane, rb); else ks2_tile_big<(N > 16) ? N : 17, BIG ? RBMAX : 32>(tab, d, patch, lane); } break;
                 RTD_KS2_CASE(0) RTD_KS2_CASE(1) RTD_KS2_CASE(2) RTD_KS2_CASE(3) RTD_KS2_CASE(4) RTD_KS2_CASE(5) RTD_KS2_CASE(6)
                 RTD_KS2_CASE(7) RTD_KS2_CASE(8) RTD_KS2_CASE(9) RTD_KS2_CASE(10) RTD_KS2_CASE(11) RTD_KS2_CASE(12) RTD_KS2_CASE(13)
                 RTD_KS2_CASE(14) RTD_KS2_CASE(15) RTD_KS2_CASE(16) RTD_KS2_CASE(17) RTD_KS2_CASE(18) RTD_KS2_CASE(19) RTD_KS2_CASE(20)

@@ -108,6 +108,7 @@ struct rtd_ctx {
     std::vector<cudaStream_t> bstreams;   // per-beam streams (concurrent beams)
     int smCount = 148;
     int ks2Blocks8 = 0, ks2Blocks16 = 0, ks2Blocks24 = 0, ks2Blocks32 = 0;
+    int ks2BodyStep = 0;            // Ks2Params::bodyStep, 0 = per beam on the device (RTD_KS2_BODY_STEP = 1 | 2 | 4 overrides, for measurements)
     rtd_opts optsLast;
 };
 
@@ -566,7 +567,7 @@ rtd_status beamPhaseB2(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opt
     k2.idd = w.idd.as<float>(); k2.rsig = w.rsig.as<float>(); k2.bev = w.bev.as<float>(); k2.batchRad = w.batchRad.as<int>();
     k2.radMap = w.radMap.as<uint8_t>(); k2.layerFirstPassive = dLfp;
     k2.L = L; k2.Rx = Rx; k2.Ry = Ry; k2.nz = nz; k2.first = w.bfi; k2.tilesX = tilesX; k2.tiles = tiles;
-    k2.bigCount = dCursor; k2.bigItems = w.list.as<uint32_t>();
+    k2.bigCount = dCursor; k2.bigItems = w.list.as<uint32_t>(); k2.bodyStep = ctx->ks2BodyStep;
     ks2_kernel<32, KS2_WARPS_32><<<ctx->ks2Blocks32, KS2_WARPS_32 * 32, KS2_SMEM_32, strm>>>(k2, dWork + 0);
     ks2_kernel<24, KS2_WARPS_24><<<ctx->ks2Blocks24, KS2_WARPS_24 * 32, KS2_SMEM_24, strm>>>(k2, dWork + 3);
     ks2_kernel<16, KS2_WARPS_16><<<ctx->ks2Blocks16, KS2_WARPS_16 * 32, KS2_SMEM_16, strm>>>(k2, dWork + 1);
@@ -776,6 +777,7 @@ rtd_status rtd_create(rtd_ctx** out, int device) {
     if (cudaStreamCreateWithPriority(&ctx->cstream, cudaStreamNonBlocking, prHi) != cudaSuccess) { cudaStreamDestroy(ctx->stream); delete ctx; return RTD_ERR_CUDA; }
     cudaDeviceGetAttribute(&ctx->smCount, cudaDevAttrMultiProcessorCount, device);
     rtd_default_opts(&ctx->optsLast);
+    if (const char* e = getenv("RTD_KS2_BODY_STEP")) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4) ctx->ks2BodyStep = v; }
     cudaFuncSetAttribute(ks2_kernel<16, KS2_WARPS_16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)KS2_SMEM_16);
     cudaFuncSetAttribute(ks2_kernel<8, KS2_WARPS_8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)KS2_SMEM_8);
     cudaFuncSetAttribute(ks2_kernel<32, KS2_WARPS_32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)KS2_SMEM_32);
