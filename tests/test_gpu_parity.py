@@ -418,3 +418,25 @@ def test_large_radius_classes_against_oracle(eng, oracle):
     err, nf = rel_to_max(dose, o["dose"])
     assert nf == 0 and err <= 2e-4 <= DOSE_TOL
     assert gamma_pass_rate(dose, o["dose"], case.spacing) >= 0.999
+
+
+def test_superposition_body_step_does_not_change_the_dose(monkeypatch):
+    """Ks2Params::bodyStep (csrc/ks2.cuh) only selects which unrolled per-radius body runs a radius <= 16 (zero weights
+    beyond the applied radius): the patch sums are bit-identical, so the dose may differ only by the order of the fp32
+    atomics. Default (chosen per beam on the device) and the overrides 1 / 2 / 4 on the case that uses every radius class."""
+    case = deep_fine_case()
+    doses = {}
+    for step in (None, "1", "2", "4"):
+        if step is None:
+            monkeypatch.delenv("RTD_KS2_BODY_STEP", raising=False)
+        else:
+            monkeypatch.setenv("RTD_KS2_BODY_STEP", step)
+        e = engine.DoseEngine(0)       # the override is read when the context is created
+        try:
+            doses[step], t = run_case(e, case)
+        finally:
+            e.close()
+        assert t["updates"] > 0
+    for step in ("1", "2", "4"):
+        err, nf = rel_to_max(doses[step], doses[None])
+        assert nf == 0 and err <= 1e-5, (step, err)
