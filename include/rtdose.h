@@ -158,7 +158,8 @@ typedef enum {
 } rtd_fetch_what;
 
 void        rtd_default_opts(rtd_opts* o);
-rtd_status  rtd_create(rtd_ctx** out, int device);
+rtd_status  rtd_create(rtd_ctx** out, int device);    /* RTD_ERR_NO_DEVICE without a CUDA device (no CPU fallback). Environment, read here, for
+                                                          measurements only: RTD_KS2_BODY_STEP = 1 | 2 | 4 (csrc/ks2.cuh, results unchanged) */
 void        rtd_destroy(rtd_ctx* ctx);
 const char* rtd_last_error(const rtd_ctx* ctx);   /* message of the last non-OK status ("" if none) */
 const char* rtd_version(void);
