@@ -87,7 +87,6 @@ def partition(beams: Sequence[Beam], luts, world_size: int, chunks_per_beam: int
 def _partition_contiguous(beams: Sequence[Beam], luts, world_size: int) -> List[List[WorkItem]]:
     costs = [layer_cost(b, luts) for b in beams]
     fixed = [piece_cost(b) for b in beams]
-    n_layers = sum(len(c) for c in costs)
 
     def fill(target: float) -> List[List[WorkItem]]:
         """Greedy: a rank takes layers in plan order until its load (layers + one piece_cost per beam touched) reaches
@@ -95,23 +94,19 @@ def _partition_contiguous(beams: Sequence[Beam], luts, world_size: int) -> List[
         rest. Ranks left with nothing stay empty."""
         out: List[List[WorkItem]] = [[] for _ in range(world_size)]
         r, load = 0, 0.0
-        left = n_layers
         for b, c in enumerate(costs):
             lo = 0
             started = False
             for l in range(len(c)):
                 add = c[l] + (0.0 if started else fixed[b])
-                ranks_after = world_size - 1 - r
                 over = load + add - target
-                if r < world_size - 1 and load > 0.0 and over > 0.0 and over > target - load and left >= 1:
+                if r < world_size - 1 and load > 0.0 and over > 0.0 and over > target - load:
                     if started:
                         out[r].append((b, lo, l))
                     r, load, lo, started = r + 1, 0.0, l, False
                     add = c[l] + fixed[b]
                 load += add
                 started = True
-                left -= 1
-                del ranks_after
             out[r].append((b, lo, len(c)))
         return out
 

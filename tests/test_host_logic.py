@@ -104,3 +104,35 @@ def test_energy_reader_loads_the_nuclear_luts_like_the_reference():
         assert e.nuclearCorr == model and e.nucWeightMatrix.shape == base.ciddMatrix.shape == e.nucSqSigmaMatrix.shape
         assert -0.05 < e.nucWeightMatrix.min() and e.nucWeightMatrix.max() < 1.0 and np.isfinite(e.nucSqSigmaMatrix).all()
         assert np.array_equal(e.ciddMatrix, base.ciddMatrix)
+
+
+def test_partition_properties_on_random_plans():
+    """Random plans (1-5 beams, 1-24 layers each) on 1-16 ranks, both partition rules: every (beam, layer) exactly once,
+    items ordered and non-empty; the contiguous rule creates at most world - 1 extra beam pieces and its makespan stays
+    within one largest item (layer + piece cost) of the average load."""
+    luts = load_packaged_luts()
+    rng = np.random.default_rng(7)
+    for _ in range(40):
+        beams = []
+        for _b in range(int(rng.integers(1, 6))):
+            lo = float(rng.uniform(70, 150))
+            en = cases.lut_energies(luts, lo, lo + float(rng.uniform(1, 60)), int(rng.integers(1, 25)))
+            beams.append(cases.Beam(rng.uniform(size=(len(en), 3, 3)).astype(np.float32), en, cases.empirical_sigma(luts, en)))
+        lc = [sharding.layer_cost(b, luts) for b in beams]
+        pc = [sharding.piece_cost(b) for b in beams]
+        for world in (1, 2, 3, 5, 8, 16):
+            for chunks in (0, 2):
+                parts = sharding.partition(beams, luts, world, chunks)
+                assert len(parts) == world
+                seen = [np.zeros(b.n_layers, int) for b in beams]
+                for items in parts:
+                    assert items == sorted(items)
+                    for b, l0, l1 in items:
+                        assert 0 <= l0 < l1 <= beams[b].n_layers
+                        seen[b][l0:l1] += 1
+                assert all(np.all(s == 1) for s in seen)
+                if chunks == 0 and world > 1:
+                    assert sum(len(items) for items in parts) <= len(beams) + world - 1
+                    loads = [sum(lc[b][l0:l1].sum() + pc[b] for b, l0, l1 in items) for items in parts]
+                    average = (sum(c.sum() for c in lc) + sum(pc)) / world
+                    assert max(loads) <= average + 1.01 * max(c.max() + p for c, p in zip(lc, pc))
