@@ -1057,7 +1057,7 @@ int rtd_debug_ct_boxes(const rtd_beam* b, int nx, int ny, int nz, int* boxes6, i
 rtd_status rtd_debug_fetch(rtd_ctx* ctx, int beamNo, rtd_fetch_what what, int layerNo, void* dst, size_t dstBytes) {
     if (!ctx || !dst || beamNo < 0 || beamNo >= ctx->nBeamsLast) return RTD_ERR_INVALID;
     BeamWs& w = *ctx->ws[beamNo];
-    const size_t R = w.R, S = w.S, L = w.L, nz = w.nz > 0 ? w.nz : 0;
+    const size_t R = w.R, S = w.S, nz = w.nz > 0 ? w.nz : 0;
     const size_t tiles = size_t(w.grid.dimX / 32) * (w.grid.dimY / 8);
     const void* src = nullptr; size_t bytes = 0;
     const bool perLayer = (what == RTD_FETCH_IDD || what == RTD_FETCH_RSIGMA || what == RTD_FETCH_FIRST_PASSIVE || what == RTD_FETCH_TILE_RADIUS);
