@@ -72,12 +72,22 @@ _BIN_FMT = {"US": "<H", "SS": "<h", "UL": "<I", "SL": "<i", "FL": "<f", "FD": "<
 Value = Union[str, bytes, int, float, list]
 
 
+class MissingAttribute(KeyError, ValueError):
+    """A required attribute is absent (the C++ reader's std::runtime_error "... missing", host/dicom_reader.cpp)."""
+
+    def __str__(self):
+        return str(self.args[0]) if self.args else ""
+
+
 class Dataset(dict):
     """tag -> value. Values: str / list of str for string VRs (numbers for DS, IS), list of numbers for binary VRs,
     bytes for OB/OW/UN, list of Dataset for SQ. Access by keyword: ``ds["Rows"]``, ``ds.get_kw("Rows")``."""
 
     def __getitem__(self, key):
-        return dict.__getitem__(self, KEYWORD_TO_TAG[key] if isinstance(key, str) else key)
+        try:
+            return dict.__getitem__(self, KEYWORD_TO_TAG[key] if isinstance(key, str) else key)
+        except KeyError:
+            raise MissingAttribute(f"DICOM attribute {key} missing") from None
 
     def __setitem__(self, key, value):
         dict.__setitem__(self, KEYWORD_TO_TAG[key] if isinstance(key, str) else key, value)
@@ -205,6 +215,8 @@ def _parse(buf: bytes, pos: int, end: int, explicit: bool, stop_at_item_end: boo
             continue
         if length == 0xFFFFFFFF:
             raise ValueError(f"undefined length on non-sequence ({g:04x},{e:04x}): encapsulated pixel data is not supported")
+        if pos + length > len(buf):
+            raise ValueError(f"value of ({g:04x},{e:04x}) runs past the end of the file (truncated?)")
         ds[(g, e)] = _decode_value(vr, buf[pos:pos + length])
         pos += length
     return ds, pos
@@ -215,14 +227,19 @@ def read_file(path: str) -> Dataset:
     if len(buf) < 132 or buf[128:132] != b"DICM":
         raise ValueError(f"{path}: not a DICOM Part-10 file")
     pos = 132
-    g, e, vr, ln, glen = struct.unpack_from("<HH2sHI", buf, pos)
-    if (g, e) != (0x0002, 0x0000):
-        raise ValueError(f"{path}: file meta group length missing")
-    meta, _ = _parse(buf, pos + 12, pos + 12 + glen, True)
-    ts = meta[(0x0002, 0x0010)]
-    if ts not in (IMPLICIT_LE, EXPLICIT_LE):
-        raise ValueError(f"{path}: transfer syntax {ts} not supported (uncompressed little endian only)")
-    ds, _ = _parse(buf, pos + 12 + glen, len(buf), ts == EXPLICIT_LE)
+    try:
+        g, e, vr, ln, glen = struct.unpack_from("<HH2sHI", buf, pos)
+        if (g, e) != (0x0002, 0x0000):
+            raise ValueError(f"{path}: file meta group length missing")
+        if pos + 12 + glen > len(buf):
+            raise ValueError(f"{path}: file meta group runs past the end of the file")
+        meta, _ = _parse(buf, pos + 12, pos + 12 + glen, True)
+        ts = meta[(0x0002, 0x0010)]
+        if ts not in (IMPLICIT_LE, EXPLICIT_LE):
+            raise ValueError(f"{path}: transfer syntax {ts} not supported (uncompressed little endian only)")
+        ds, _ = _parse(buf, pos + 12 + glen, len(buf), ts == EXPLICIT_LE)
+    except (struct.error, IndexError, UnicodeDecodeError, RecursionError, TypeError) as err:      # cut-off or corrupt element headers / values
+        raise ValueError(f"{path}: truncated or corrupt DICOM data ({err})") from None
     ds.update(meta)
     return ds
 
@@ -293,6 +310,13 @@ def read_ion_plan(path: str) -> List[dict]:
             xy = cp.floats("ScanSpotPositionMap")
             w = cp.floats("ScanSpotMetersetWeights")
             fw = cp.floats("ScanningSpotSize")
+            if len(fw) != 2:
+                raise ValueError(f"{path}: incomplete ion control point (ScanningSpotSize)")
+            en = float(cp["NominalBeamEnergy"])
+            if not (0.0 < en < 1.0e4 and 0.0 < fw[0] < 1.0e4 and 0.0 < fw[1] < 1.0e4 and 0 <= n <= 10 ** 7):
+                raise ValueError(f"{path}: ion control point with an energy, spot size or spot count out of range")
+            if len(xy) < 2 * n or len(w) < n:
+                raise ValueError(f"{path}: scan spot map shorter than NumberOfScanSpotPositions")
             layers.append({"energy": float(cp["NominalBeamEnergy"]), "fwhm": (fw[0], fw[1]),
                            "x": np.array(xy[0:2 * n:2], np.float32), "y": np.array(xy[1:2 * n:2], np.float32),
                            "w": np.array(w[:n], np.float32)})

@@ -288,6 +288,8 @@ std::vector<PlanBeam> readIonPlan(const std::string& path) {
             const std::vector<double> e = numbers(cp, tag(0x300A, 0x0114)), np = numbers(cp, tag(0x300A, 0x0392)), xy = numbers(cp, tag(0x300A, 0x0394)),
                                       w = numbers(cp, tag(0x300A, 0x0396)), fw = numbers(cp, tag(0x300A, 0x0398));
             if (e.empty() || np.empty() || fw.size() != 2) throw std::runtime_error("incomplete ion control point in beam " + pb.name);
+            if (!(e[0] > 0.0 && e[0] < 1.0e4) || !(fw[0] > 0.0 && fw[0] < 1.0e4) || !(fw[1] > 0.0 && fw[1] < 1.0e4) || !(np[0] >= 0.0 && np[0] <= 1.0e7))
+                throw std::runtime_error("ion control point with an energy, spot size or spot count out of range in beam " + pb.name);
             const size_t n = size_t(np[0]);
             if (xy.size() < 2 * n || w.size() < n) throw std::runtime_error("scan spot map shorter than NumberOfScanSpotPositions in beam " + pb.name);
             PlanLayer l; l.energy = float(e[0]); l.fwhmX = float(fw[0]); l.fwhmY = float(fw[1]);
@@ -306,10 +308,15 @@ namespace {
 
 constexpr double kFwhmToSigma = 2.355;   // rbe_1p1.hpp:90
 constexpr double kLatticeTol = 1.0e-3;   // mm
+constexpr double kMaxPosition = 1.0e4;   // mm: anything farther from the axis than 10 m is a corrupt file
+constexpr double kMaxLatticeNodes = 4096.0;
 
 void lattice(const std::vector<double>& values, double defaultPitch, int minCount, double& x0, double& pitch, int& n) {
     std::vector<double> u;
-    for (double v : values) u.push_back(std::nearbyint(v / kLatticeTol) * kLatticeTol);
+    for (double v : values) {
+        if (!std::isfinite(v) || std::fabs(v) > kMaxPosition) throw std::runtime_error("scan spot position is not a finite distance in mm");
+        u.push_back(std::nearbyint(v / kLatticeTol) * kLatticeTol);
+    }
     std::sort(u.begin(), u.end());
     u.erase(std::unique(u.begin(), u.end()), u.end());
     if (u.size() == 1) pitch = defaultPitch;
@@ -321,7 +328,9 @@ void lattice(const std::vector<double>& values, double defaultPitch, int minCoun
             if (std::fabs(k - std::nearbyint(k)) * pitch > 10 * kLatticeTol) throw std::runtime_error("scan spot positions do not lie on a regular lattice");
         }
     }
-    n = int(std::nearbyint((u.back() - u.front()) / pitch)) + 1;
+    const double nodes = std::nearbyint((u.back() - u.front()) / pitch) + 1.0;
+    if (!(nodes <= kMaxLatticeNodes)) throw std::runtime_error("scan spot lattice has too many nodes");
+    n = int(nodes);
     x0 = u.front();
     for (int side = 0; n < minCount; side ^= 1) { if (side == 0) x0 -= pitch; ++n; }
 }
@@ -344,6 +353,7 @@ std::unique_ptr<PlanBeamSettings> beamFromPlan(const PlanBeam& pb, const Float3A
         const PlanLayer& l = pb.layers[li];
         for (size_t j = 0; j < l.x.size(); ++j) {
             const int ix = int(std::nearbyint((double(l.x[j]) - x0) / dx)), iy = int(std::nearbyint((double(l.y[j]) - y0) / dy));
+            if (ix < 0 || ix >= sx || iy < 0 || iy >= sy || !std::isfinite(l.w[j])) throw std::runtime_error("scan spot outside its lattice or non-finite weight in beam " + pb.name);
             out->weights[(li * sy + iy) * sx + ix] += l.w[j];       // repaintings of one position add up
         }
         energies[li] = l.energy;

@@ -26,6 +26,8 @@ from . import cases
 
 FWHM_TO_SIGMA = 2.355     # rbe_1p1.hpp:90
 LATTICE_TOL = 1.0e-3      # mm
+MAX_POSITION = 1.0e4      # mm: anything farther from the axis than 10 m is a corrupt file
+MAX_LATTICE_NODES = 4096
 
 
 def gantry_to_patient(gantry_deg: float, couch_deg: float) -> np.ndarray:
@@ -41,7 +43,12 @@ def gantry_to_patient(gantry_deg: float, couch_deg: float) -> np.ndarray:
 def _lattice(values: np.ndarray, default_pitch: float, min_count: int):
     """Distinct positions -> (origin, pitch, count) of the regular lattice they lie on; padded with zero-weight nodes to
     ``min_count`` (a one-spot plan still gets a ray grid of at least 32 x 32 rays)."""
-    u = np.unique(np.round(values.astype(np.float64) / LATTICE_TOL) * LATTICE_TOL)
+    values = np.asarray(values, np.float64)
+    if values.size == 0:
+        raise ValueError("beam has no scan spots")
+    if not np.all(np.isfinite(values)) or np.max(np.abs(values)) > MAX_POSITION:
+        raise ValueError("scan spot position is not a finite distance in mm")
+    u = np.unique(np.round(values / LATTICE_TOL) * LATTICE_TOL)
     if u.size == 1:
         pitch = float(default_pitch)
     else:
@@ -49,7 +56,10 @@ def _lattice(values: np.ndarray, default_pitch: float, min_count: int):
         k = (u - u[0]) / pitch
         if np.max(np.abs(k - np.round(k))) * pitch > 10 * LATTICE_TOL:
             raise ValueError("scan spot positions do not lie on a regular lattice")
-    n = int(round((u[-1] - u[0]) / pitch)) + 1
+    nodes = round((u[-1] - u[0]) / pitch) + 1
+    if not nodes <= MAX_LATTICE_NODES:
+        raise ValueError("scan spot lattice has too many nodes")
+    n = int(nodes)
     x0 = float(u[0])
     side = 0
     while n < min_count:          # alternately one node before, one after: a single spot ends up in the centre
@@ -74,6 +84,8 @@ def beam_settings_from_plan(beam: dict, ct_shape: Sequence[int], im_idx_to_world
     for li, l in enumerate(layers):
         ix = np.rint((l["x"].astype(np.float64) - x0) / dx).astype(int)
         iy = np.rint((l["y"].astype(np.float64) - y0) / dy).astype(int)
+        if ix.size and (ix.min() < 0 or ix.max() >= sx or iy.min() < 0 or iy.max() >= sy or not np.all(np.isfinite(l["w"]))):
+            raise ValueError("scan spot outside its lattice or non-finite weight in beam " + str(beam.get("name", "")))
         np.add.at(w[li], (iy, ix), l["w"].astype(np.float32))      # repaintings of one position add up
     energies = np.array([l["energy"] for l in layers], np.float32)
     sigmas = np.array([[l["fwhm"][0] / FWHM_TO_SIGMA, l["fwhm"][1] / FWHM_TO_SIGMA] for l in layers], np.float32)

@@ -2,6 +2,7 @@
 RT Ion Plan reader (role of rti::beam_module_ion) and the plan -> BeamSettings mapping the reference's main() leaves out
 (src/main.cu:171-197). The C++ host driver and the Python mirror must produce byte-identical plans."""
 import os
+import shutil
 import subprocess
 
 import numpy as np
@@ -196,3 +197,56 @@ def test_driver_dose_from_dicom_matches_binding_and_oracle(tmp_path, exe, lut_di
     for b in range(2):
         oracle.run_beam(c, b, dose=ref)
     assert rel_to_max(got, ref)[0] <= 1e-3
+
+
+def _mutate(buf, rng):
+    b = bytearray(buf); k = int(rng.integers(0, 4))
+    if k == 0:
+        b = b[:int(rng.integers(0, len(b)))]                                   # truncated file
+    elif k == 1:
+        for _ in range(int(rng.integers(1, 6))):
+            b[int(rng.integers(0, len(b)))] = int(rng.integers(0, 256))        # flipped bytes (tags, VRs, lengths, values)
+    elif k == 2:
+        p = int(rng.integers(132, min(len(b), 1500))); b[p:p + 4] = bytes(rng.integers(0, 256, 4, dtype=np.uint8))
+    else:
+        p = int(rng.integers(132, len(b))); b[p:p + 4] = b"\xff\xff\xff\xff"   # undefined length / NaN float
+    return bytes(b)
+
+
+def test_corrupt_dicom_is_an_error_never_a_crash(tmp_path, exe, lut_dir):
+    """Truncated and byte-flipped CT slices / plans: the Python mirror raises ValueError (nothing else) or reads the file;
+    the C++ driver exits with status 0 or 1 and a message - no signal, no hang (a NaN spot position used to index
+    outside the weight grid in beamFromPlan)."""
+    base = str(tmp_path / "base")
+    dl.generate_water_cube(base, n=24, margin=4)
+    plan_bytes = open(os.path.join(base, "rtplan.dcm"), "rb").read()
+    names = sorted(os.listdir(os.path.join(base, "ct")))
+    slice_bytes = open(os.path.join(base, "ct", names[0]), "rb").read()
+    rng = np.random.default_rng(11)
+    d = str(tmp_path / "t")
+    rejected = 0
+    for trial in range(90):
+        shutil.rmtree(d, ignore_errors=True); shutil.copytree(base, d)
+        if trial % 2 == 0:
+            open(os.path.join(d, "rtplan.dcm"), "wb").write(_mutate(plan_bytes, rng))
+        else:
+            open(os.path.join(d, "ct", names[int(rng.integers(0, len(names)))]), "wb").write(_mutate(slice_bytes, rng))
+        try:
+            plan.case_from_dicom(os.path.join(d, "ct"), os.path.join(d, "rtplan.dcm"))
+        except ValueError:
+            rejected += 1
+        if trial % 5 == 0:
+            r = subprocess.run([exe, "--ct_dir", os.path.join(d, "ct"), "--rtplan", os.path.join(d, "rtplan.dcm"), "--phys_data", lut_dir,
+                                "--dump_case", str(tmp_path / "o.rtdcase")], capture_output=True, timeout=60)
+            assert r.returncode in (0, 1), (trial, r.returncode, r.stderr[-200:])
+    assert 10 < rejected < 90
+    # the case that used to crash: a NaN in the scan spot position map
+    beams = dl.read_ion_plan(os.path.join(base, "rtplan.dcm"))
+    beams[0]["layers"][0]["x"][0] = np.nan
+    ct, m, o = dl.read_ct_series(os.path.join(base, "ct"))
+    with pytest.raises(ValueError, match="finite"):
+        plan.beam_settings_from_plan(beams[0], ct.shape, m, o)
+    dl.write_ion_plan(os.path.join(base, "nan.dcm"), beams)
+    r = subprocess.run([exe, "--ct_dir", os.path.join(base, "ct"), "--rtplan", os.path.join(base, "nan.dcm"), "--phys_data", lut_dir,
+                        "--dump_case", str(tmp_path / "o.rtdcase")], capture_output=True, text=True, errors="replace", timeout=60)
+    assert r.returncode == 1 and "finite" in (r.stdout + r.stderr)
