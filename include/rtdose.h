@@ -85,7 +85,9 @@ typedef struct {
     float ksSigmaCutoff;     /* KS_SIGMA_CUTOFF   3.0  */
     float rayWeightCutoff;   /* RAY_WEIGHT_CUTOFF 1.0  */
     int   minTilesInBatch;   /* 16, src/kernel_wrapper.cuh:29 */
-    int   keepIntermediates; /* 1: keep per-beam BEV arrays of every layer for rtd_debug_fetch */
+    int   ks2BodyStep;       /* measurement hook of the superposition kernels (csrc/ks2.cuh, Ks2Params::bodyStep; results unchanged):
+                                0 (default) = chosen per beam on the device, 1 | 2 | 4 = a radius <= 16 runs in the unrolled body of the
+                                next multiple */
     int   serialBeams;       /* 1: run the beams one after the other on one stream (stage timings then do not overlap);
                                 0 (default): one stream per beam, transfers into the dose grid serialised in beam order */
     int   noZeroCopyDose;    /* 0 (default): a PINNED host dose grid is accumulated in place by the transfer kernels (only voxels
@@ -121,6 +123,8 @@ typedef struct {
     int64_t h2dBytes;    /* bytes copied host->device inside the call (CT sub-volumes, dose-in sub-volumes, weights, parameters) */
     int64_t d2hBytes;    /* bytes copied device->host inside the call (dose sub-volumes, reductions, reports) */
     int64_t doseVoxelsModified;   /* dose-grid voxels that received dose (summed over beams) */
+    int     ksLaunchesWithWork;   /* superposition launches (beam x radius class) that processed at least one item */
+    int     reserved0;
 } rtd_timing;
 
 typedef struct {
@@ -158,8 +162,10 @@ typedef enum {
 } rtd_fetch_what;
 
 void        rtd_default_opts(rtd_opts* o);
-rtd_status  rtd_create(rtd_ctx** out, int device);    /* RTD_ERR_NO_DEVICE without a CUDA device (no CPU fallback). Environment, read here, for
-                                                          measurements only: RTD_KS2_BODY_STEP = 1 | 2 | 4 (csrc/ks2.cuh, results unchanged) */
+rtd_status  rtd_create(rtd_ctx** out, int device);    /* RTD_ERR_NO_DEVICE without a CUDA device (no CPU fallback) */
+/* Same, with the caller's stream (a cudaStream_t of `device`) as the context's main stream: the caller keeps owning it (rtd_destroy
+ * leaves it alone) and can order its own work - NCCL, torch, copies - on it around the rtd_* calls without a host sync. */
+rtd_status  rtd_create_on_stream(rtd_ctx** out, int device, void* cudaStream);
 void        rtd_destroy(rtd_ctx* ctx);
 const char* rtd_last_error(const rtd_ctx* ctx);   /* message of the last non-OK status ("" if none) */
 const char* rtd_version(void);
@@ -219,7 +225,7 @@ rtd_status rtd_add_device_to_host(rtd_ctx* ctx, const float* dSrc, float* hostDs
 /* Integer/index outputs of the last call (the reference's bit-exact quantities). */
 rtd_status rtd_get_beam_report(const rtd_ctx* ctx, int beamNo, rtd_beam_report* out);
 rtd_status rtd_get_layer_report(const rtd_ctx* ctx, int beamNo, int layerNo, rtd_layer_report* out);
-/* Copies an intermediate of the last call to host memory (needs opts.keepIntermediates=1 for per-layer arrays). */
+/* Copies an intermediate of the last call to host memory (every beam keeps its arrays until the next call). */
 rtd_status rtd_debug_fetch(rtd_ctx* ctx, int beamNo, rtd_fetch_what what, int layerNo, void* dst, size_t dstBytes);
 /* Host geometry only (no device needed): the CT sub-volumes rtd_plan_dose would upload for this beam into a CT of
  * nx x ny x nz voxels, as inclusive boxes (x0, y0, z0, x1, y1, z1). Returns the number of boxes (may exceed maxBoxes; only

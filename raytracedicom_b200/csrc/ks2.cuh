@@ -7,9 +7,11 @@
 //     accumulating them into a warp-private shared-memory patch, so the haloed BEV dose receives one global reduction
 //     per item instead of one per (item, layer): ~L times fewer global atomics, and no block barriers at all;
 //   * lane x owns the source column x of the tile.  The erf-difference weights of its 8 voxels (same recurrence as
-//     cuh:459-467, same libdevice erff) go through a warp-private table so that the hot loop is a SMALL rolled loop
+//     cuh:459-467; erf itself is ks_erf_pos below, a single-range fit with 1e-7 absolute error instead of libdevice's erff -
+//     a deliberate, bounded numerics deviation) go through a warp-private table so that the hot loop is a SMALL rolled loop
 //     over the column offset j (instruction-cache resident) with the row weights e[y][|i|] held in registers:
-//     per j the lane accumulates a whole output column (P+2RB rows) in registers - P(2RB+1) FMAs, no memory traffic -
+//     per j the lane accumulates a whole output column (P+2RB rows) in registers - P(2RB+1) FMAs as packed FFMA2 over row
+//     pairs, no memory traffic -
 //     and adds it to the patch columns x+j and x-j (the horizontal weight is symmetric: +j and -j share the FMAs); the
 //     patch is column-major so that this read-modify-write is 128-bit wide (see ks2_col_pitch);
 //   * the radius applied to a tile is still the reference's BATCH radius (cuh:443-448 vs 459-473).
@@ -72,68 +74,122 @@ static_assert((ks2_col_pitch(16) - ks2_rows(16)) * 2 * ks2_cols(16) >= KS2_MAXL 
               (ks2_col_pitch(32) - ks2_rows(32)) * 2 * ks2_cols(32) >= KS2_MAXL && (ks2_col_pitch(24) - ks2_rows(24)) * 2 * ks2_cols(24) >= KS2_MAXL,
               "layer list fits the column pads");
 
-// All 8 source rows of the tile with batch radius RB into the patch of a kernel instantiated for radii <= RBMAX.
-//   tab    : tab[(y*(RB+1) + i)*32 + lane] = e_y[i] of the lane's 8 voxels
-//   d      : dose of the lane's 8 voxels
-//   patch  : column-major patch of this warp
-template <int RB, int RBMAX>
-__device__ __forceinline__ void ks2_tile(const float* __restrict__ tab, const float (&d)[8], float* __restrict__ patch, const int lane, const int jmax) {
-    constexpr int P = 8, W = 2 * RB + 1, NRP = P + 2 * RB, PC = ks2_col_pitch(RBMAX);
-    constexpr int Y0 = RBMAX - RB;            // patch row of the first output row (tile row -RB)
-    constexpr int A = Y0 & 3, YS = Y0 - A;    // 128-bit window [YS, YS + 4 NV) around the NRP output rows
-    constexpr int NV = (A + NRP + 3) / 4;
-    static_assert(YS + 4 * NV <= ks2_rows(RBMAX), "window stays inside the column");
-    float e[P][RB + 1];
+// Packed fp32 (sm_100: fma.rn.f32x2 -> FFMA2, add.f32x2 -> FADD2; two IEEE fp32 operations per issue slot). The superposition is
+// bound by instruction issue and shared-memory wavefronts, not by the FMA pipe (profiles/r01_ncu_full_ks2.txt: issue-active 56 %,
+// FMA pipe 35 %), so halving the issue slots of the FMA block and of the patch read-modify-write is what pays.
+typedef unsigned long long ks_u64;
+__device__ __forceinline__ ks_u64 ks_pk(float lo, float hi) { ks_u64 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ void ks_upk(ks_u64 v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ ks_u64 ks_fma2(ks_u64 a, ks_u64 b, ks_u64 c) { ks_u64 d; asm("fma.rn.ftz.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c)); return d; }
+__device__ __forceinline__ ks_u64 ks_add2(ks_u64 a, ks_u64 b) { ks_u64 d; asm("add.rn.ftz.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+__device__ __forceinline__ void ks_fma_lo(ks_u64& c, float a, float b) { float lo, hi; ks_upk(c, lo, hi); lo = fmaf(a, b, lo); c = ks_pk(lo, hi); }
+__device__ __forceinline__ void ks_fma_hi(ks_u64& c, float a, float b) { float lo, hi; ks_upk(c, lo, hi); hi = fmaf(a, b, hi); c = ks_pk(lo, hi); }
+
+// The 8 source voxels of a lane (rows y = 0..7 of its column) with one vertical weight each, packed by ROW PAIRS: the voxels of rows
+// y and y + 1 at the same vertical offset land in adjacent output rows, so {out[Y], out[Y+1]} += {g[y], g[y+1]} * {e[y], e[y+1]} is one
+// FFMA2 with no duplicated operand. The output column is held as 64-bit pairs aligned with the 128-bit words of the patch column
+// ("window" index w, pair m = w / 2); a vertical offset whose row-0 output has an even window index pairs rows (0,1)(2,3)(4,5)(6,7),
+// an odd one pairs (1,2)(3,4)(5,6) and leaves rows 0 and 7 to scalar FFMAs on the halves of their pairs. The parity is a compile-time
+// property of the weight index, so each weight is stored once, in the pairing its parity needs: 8 registers per weight index as before.
+struct Ks2W {              // dose x vertical weight of one vertical offset for the lane's 8 voxels
+    ks_u64 p[4];           // even parity: rows (0,1)(2,3)(4,5)(6,7); odd parity: rows (1,2)(3,4)(5,6), p[3] unused
+    float s0, s7;          // odd parity: rows 0 and 7
+};
+struct Ks2G {              // horizontal weight of the lane's 8 voxels for one column offset, in both pairings
+    ks_u64 e[4], o[3]; float s0, s7;
+};
+__device__ __forceinline__ Ks2W ks2_load_w(const float* __restrict__ t /* &tab[k * 32 + lane] */, const int rowStride, const float (&d)[8], const bool odd) {
+    float v[8];
 #pragma unroll
-    for (int y = 0; y < P; ++y)
+    for (int y = 0; y < 8; ++y) v[y] = d[y] * t[y * rowStride];
+    Ks2W w;
+    if (!odd) {
 #pragma unroll
-        for (int i = 0; i <= RB; ++i) e[y][i] = tab[(y * (RB + 1) + i) * 32 + lane];
-    float* const col0 = patch + (lane + RBMAX) * PC + YS;     // the lane's own column (offset j = 0)
-#pragma unroll 1
-    for (int j = 0; j <= jmax; ++j) {       // jmax = applied radius (<= RB: a radius may run in the body of a larger one)
-        float acc[NRP];
+        for (int p = 0; p < 4; ++p) w.p[p] = ks_pk(v[2 * p], v[2 * p + 1]);
+        w.s0 = 0.0f; w.s7 = 0.0f;
+    } else {
 #pragma unroll
-        for (int Y = 0; Y < NRP; ++Y) acc[Y] = 0.0f;
+        for (int p = 0; p < 3; ++p) w.p[p] = ks_pk(v[2 * p + 1], v[2 * p + 2]);
+        w.p[3] = 0ull; w.s0 = v[0]; w.s7 = v[7];
+    }
+    return w;
+}
+__device__ __forceinline__ float ks_lds_again(const float* p) {        // a second, independent copy of a shared-memory word
+    float v; asm volatile("ld.volatile.shared.f32 %0, [%1];" : "=f"(v) : "r"((unsigned)__cvta_generic_to_shared(p))); return v;
+}
+__device__ __forceinline__ Ks2G ks2_make_g(const float* __restrict__ t /* &tab[j * 32 + lane] */, const int rowStride) {
+    // rows 1..6 are needed in two register pairings, (0,1)(2,3)(4,5)(6,7) and (1,2)(3,4)(5,6). A 64-bit operand is an aligned register
+    // pair, so the second pairing needs its own copies; left to ptxas these become ~3 MOVs per use (it re-creates the pairs),
+    // loaded a second time they cost 6 LDS per column offset and no MOV.
+    float g[8], h[6];
 #pragma unroll
-        for (int y = 0; y < P; ++y) {
-            const float g = d[y] * tab[(y * (RB + 1) + j) * 32 + lane];
+    for (int y = 0; y < 8; ++y) g[y] = t[y * rowStride];
 #pragma unroll
-            for (int i = 0; i < W; ++i) acc[y + i] = fmaf(g, e[y][(i < RB) ? (RB - i) : (i - RB)], acc[y + i]);
-        }
-        // the horizontal weight is symmetric: the same output column goes to patch columns x+j and x-j. Within one phase
-        // every lane owns a different column; rows of the window outside the NRP outputs are rewritten unchanged.
+    for (int y = 0; y < 6; ++y) h[y] = ks_lds_again(t + (y + 1) * rowStride);
+    Ks2G r;
 #pragma unroll
-        for (int side = 0; side < 2; ++side) {
-            if (side == 1 && j == 0) break;
-            float4* c = reinterpret_cast<float4*>(side == 0 ? col0 + j * PC : col0 - j * PC);
+    for (int p = 0; p < 4; ++p) r.e[p] = ks_pk(g[2 * p], g[2 * p + 1]);
 #pragma unroll
-            for (int q = 0; q < NV; ++q) {
-                float4 v = c[q];
-                if (4 * q + 0 - A >= 0 && 4 * q + 0 - A < NRP) v.x += acc[(4 * q + 0 - A >= 0 && 4 * q + 0 - A < NRP) ? 4 * q + 0 - A : 0];
-                if (4 * q + 1 - A >= 0 && 4 * q + 1 - A < NRP) v.y += acc[(4 * q + 1 - A >= 0 && 4 * q + 1 - A < NRP) ? 4 * q + 1 - A : 0];
-                if (4 * q + 2 - A >= 0 && 4 * q + 2 - A < NRP) v.z += acc[(4 * q + 2 - A >= 0 && 4 * q + 2 - A < NRP) ? 4 * q + 2 - A : 0];
-                if (4 * q + 3 - A >= 0 && 4 * q + 3 - A < NRP) v.w += acc[(4 * q + 3 - A >= 0 && 4 * q + 3 - A < NRP) ? 4 * q + 3 - A : 0];
-                c[q] = v;
-            }
-            __syncwarp();
-        }
+    for (int p = 0; p < 3; ++p) r.o[p] = ks_pk(h[2 * p], h[2 * p + 1]);
+    r.s0 = g[0]; r.s7 = g[7];
+    return r;
+}
+// acc (window pairs) += g * w for the weight whose row-0 output has window index w0 (compile-time after unrolling)
+template <int NP>
+__device__ __forceinline__ void ks2_fma8(ks_u64 (&acc)[NP], const Ks2G& g, const Ks2W& w, const int w0) {
+    if ((w0 & 1) == 0) {
+#pragma unroll
+        for (int p = 0; p < 4; ++p) acc[(w0 >> 1) + p] = ks_fma2(g.e[p], w.p[p], acc[(w0 >> 1) + p]);
+    } else {
+        ks_fma_hi(acc[w0 >> 1], g.s0, w.s0);
+#pragma unroll
+        for (int p = 0; p < 3; ++p) acc[((w0 + 1) >> 1) + p] = ks_fma2(g.o[p], w.p[p], acc[((w0 + 1) >> 1) + p]);
+        ks_fma_lo(acc[(w0 + 7) >> 1], g.s7, w.s7);
     }
 }
-
-// Adds NR register-held output rows, starting at patch row Y0 of the column at `col`, with 128-bit read-modify-writes
-// (rows of the aligned window that lie outside [Y0, Y0 + NR) are rewritten unchanged).
-template <int NR, int Y0>
-__device__ __forceinline__ void ks2_rmw(float* __restrict__ col, const float (&acc)[NR]) {
-    constexpr int A = Y0 & 3, YS = Y0 - A, NV = (A + NR + 3) / 4;
-    float4* c = reinterpret_cast<float4*>(col + YS);
+// Adds NV 128-bit words of register-held window pairs onto the patch column at `col` (16-byte aligned); window entries outside the
+// output rows are zero and leave their patch rows unchanged.
+template <int NV>
+__device__ __forceinline__ void ks2_rmw(float* __restrict__ col, const ks_u64 (&acc)[2 * NV]) {
+    float4* c = reinterpret_cast<float4*>(col);
 #pragma unroll
     for (int q = 0; q < NV; ++q) {
         float4 v = c[q];
-        if (4 * q + 0 - A >= 0 && 4 * q + 0 - A < NR) v.x += acc[(4 * q + 0 - A >= 0 && 4 * q + 0 - A < NR) ? 4 * q + 0 - A : 0];
-        if (4 * q + 1 - A >= 0 && 4 * q + 1 - A < NR) v.y += acc[(4 * q + 1 - A >= 0 && 4 * q + 1 - A < NR) ? 4 * q + 1 - A : 0];
-        if (4 * q + 2 - A >= 0 && 4 * q + 2 - A < NR) v.z += acc[(4 * q + 2 - A >= 0 && 4 * q + 2 - A < NR) ? 4 * q + 2 - A : 0];
-        if (4 * q + 3 - A >= 0 && 4 * q + 3 - A < NR) v.w += acc[(4 * q + 3 - A >= 0 && 4 * q + 3 - A < NR) ? 4 * q + 3 - A : 0];
+        const ks_u64 lo = ks_add2(ks_pk(v.x, v.y), acc[2 * q]), hi = ks_add2(ks_pk(v.z, v.w), acc[2 * q + 1]);
+        ks_upk(lo, v.x, v.y); ks_upk(hi, v.z, v.w);
         c[q] = v;
+    }
+}
+
+// All 8 source rows of the tile, vertical offsets |i| <= RB, column offsets 0..jmax, into the patch of a kernel instantiated for radii
+// <= RBMAX.
+//   tab    : tab[(y*TS + i)*32 + lane] = e_y[i] of the lane's 8 voxels (TS = table row stride in entries)
+//   d      : dose of the lane's 8 voxels
+//   patch  : column-major patch of this warp
+template <int RB, int RBMAX, int TS>
+__device__ __forceinline__ void ks2_tile(const float* __restrict__ tab, const float (&d)[8], float* __restrict__ patch, const int lane, const int jmax) {
+    constexpr int P = 8, W = 2 * RB + 1, NRP = P + 2 * RB, PC = ks2_col_pitch(RBMAX);
+    constexpr int Y0 = RBMAX - RB;            // patch row of the first output row (tile row -RB)
+    constexpr int A = Y0 & 3, YS = Y0 - A;    // 128-bit window [YS, YS + 4 NV) around the NRP output rows: window index = output row + A
+    constexpr int NV = (A + NRP + 3) / 4;
+    static_assert(YS + 4 * NV <= ks2_rows(RBMAX), "window stays inside the column");
+    Ks2W e[RB + 1];                           // weight index k = |i|: offsets -k and +k have row-0 window indices RB -+ k + A, same parity
+#pragma unroll
+    for (int k = 0; k <= RB; ++k) e[k] = ks2_load_w(tab + k * 32 + lane, TS * 32, d, ((RB + k + A) & 1) != 0);
+    float* const col0 = patch + (lane + RBMAX) * PC + YS;     // the lane's own column (offset j = 0)
+#pragma unroll 1
+    for (int j = 0; j <= jmax; ++j) {       // jmax = applied radius (<= RB: a radius may run in the body of a larger one)
+        const Ks2G g = ks2_make_g(tab + j * 32 + lane, TS * 32);
+        ks_u64 acc[2 * NV];
+#pragma unroll
+        for (int m = 0; m < 2 * NV; ++m) acc[m] = 0ull;
+#pragma unroll
+        for (int i = 0; i < W; ++i) ks2_fma8<2 * NV>(acc, g, e[(i < RB) ? (RB - i) : (i - RB)], i + A);
+        // the horizontal weight is symmetric: the same output column goes to patch columns x+j and x-j. Within one phase
+        // every lane owns a different column.
+        ks2_rmw<NV>(col0 + j * PC, acc);
+        __syncwarp();
+        if (j) { ks2_rmw<NV>(col0 - j * PC, acc); __syncwarp(); }
     }
 }
 
@@ -146,57 +202,35 @@ template <int RB, int RBMAX>
 __device__ __forceinline__ void ks2_tile_big(const float* __restrict__ tab, const float (&d)[8], float* __restrict__ patch, const int lane) {
     constexpr int P = 8, RC = 16, PC = ks2_col_pitch(RBMAX), TS = RB + 1;
     static_assert(RB > RC && RB <= RBMAX, "radius class");
-    float* const col0 = patch + (lane + RBMAX) * PC;
-    {   // central band: output rows -RC .. P-1+RC
-        constexpr int W = 2 * RC + 1, NRP = P + 2 * RC;
-        float e[P][RC + 1];
-#pragma unroll
-        for (int y = 0; y < P; ++y)
-#pragma unroll
-            for (int i = 0; i <= RC; ++i) e[y][i] = tab[(y * TS + i) * 32 + lane];
-#pragma unroll 1
-        for (int j = 0; j <= RB; ++j) {
-            float acc[NRP];
-#pragma unroll
-            for (int Y = 0; Y < NRP; ++Y) acc[Y] = 0.0f;
-#pragma unroll
-            for (int y = 0; y < P; ++y) {
-                const float g = d[y] * tab[(y * TS + j) * 32 + lane];
-#pragma unroll
-                for (int i = 0; i < W; ++i) acc[y + i] = fmaf(g, e[y][(i < RC) ? (RC - i) : (i - RC)], acc[y + i]);
-            }
-            ks2_rmw<NRP, RBMAX - RC>(col0 + j * PC, acc);
-            __syncwarp();
-            if (j) { ks2_rmw<NRP, RBMAX - RC>(col0 - j * PC, acc); __syncwarp(); }
-        }
-    }
+    ks2_tile<RC, RBMAX, TS>(tab, d, patch, lane, RB);        // central band: output rows -RC .. P-1+RC
     {   // outer bands: i = RC+1 .. RB below the source row (output rows RC+1 .. P-1+RB) and above it (-RB .. P-1-RC-1)
         constexpr int N2 = RB - RC, NB = P + N2 - 1;
-        float e[P][N2];
+        constexpr int YU = RBMAX - RB, AU = YU & 3, NVU = (AU + NB + 3) / 4;               // upper band: first output row -RB
+        constexpr int YL = RBMAX + RC + 1, AL = YL & 3, NVL = (AL + NB + 3) / 4;           // lower band: first output row RC+1
+        static_assert(((AL ^ (N2 - 1 + AU)) & 1) == 0, "both bands pair the rows of a weight the same way");
+        float* const col0 = patch + (lane + RBMAX) * PC;
+        Ks2W e[N2];                           // weight index k <-> offset RC + 1 + k: lower band window k + AL, upper band N2 - 1 - k + AU
 #pragma unroll
-        for (int y = 0; y < P; ++y)
-#pragma unroll
-            for (int k = 0; k < N2; ++k) e[y][k] = tab[(y * TS + RC + 1 + k) * 32 + lane];
+        for (int k = 0; k < N2; ++k) e[k] = ks2_load_w(tab + (RC + 1 + k) * 32 + lane, TS * 32, d, ((k + AL) & 1) != 0);
 #pragma unroll 1
         for (int j = 0; j <= RB; ++j) {
-            float lo[NB], up[NB];
+            const Ks2G g = ks2_make_g(tab + j * 32 + lane, TS * 32);
+            ks_u64 lo[2 * NVL], up[2 * NVU];
 #pragma unroll
-            for (int Y = 0; Y < NB; ++Y) { lo[Y] = 0.0f; up[Y] = 0.0f; }
+            for (int m = 0; m < 2 * NVL; ++m) lo[m] = 0ull;
 #pragma unroll
-            for (int y = 0; y < P; ++y) {
-                const float g = d[y] * tab[(y * TS + j) * 32 + lane];
+            for (int m = 0; m < 2 * NVU; ++m) up[m] = 0ull;
 #pragma unroll
-                for (int k = 0; k < N2; ++k) {
-                    lo[y + k] = fmaf(g, e[y][k], lo[y + k]);                        // output row y + (RC + 1 + k)
-                    up[y + N2 - 1 - k] = fmaf(g, e[y][k], up[y + N2 - 1 - k]);      // output row y - (RC + 1 + k)
-                }
+            for (int k = 0; k < N2; ++k) {
+                ks2_fma8<2 * NVL>(lo, g, e[k], k + AL);                  // output row y + (RC + 1 + k)
+                ks2_fma8<2 * NVU>(up, g, e[k], N2 - 1 - k + AU);         // output row y - (RC + 1 + k)
             }
-            ks2_rmw<NB, RBMAX - RB>(col0 + j * PC, up);
-            ks2_rmw<NB, RBMAX + RC + 1>(col0 + j * PC, lo);
+            ks2_rmw<NVU>(col0 + j * PC + (YU - AU), up);
+            ks2_rmw<NVL>(col0 + j * PC + (YL - AL), lo);
             __syncwarp();
             if (j) {
-                ks2_rmw<NB, RBMAX - RB>(col0 - j * PC, up);
-                ks2_rmw<NB, RBMAX + RC + 1>(col0 - j * PC, lo);
+                ks2_rmw<NVU>(col0 - j * PC + (YU - AU), up);
+                ks2_rmw<NVL>(col0 - j * PC + (YL - AL), lo);
                 __syncwarp();
             }
         }
@@ -209,7 +243,7 @@ __device__ __forceinline__ void ks2_tile_big(const float* __restrict__ tab, cons
 // (25..32), whose 63 KB per warp leave only 3 warps per SM - small radii would run badly there.
 template <int RBMAX, int WARPS>
 __global__ void __launch_bounds__(WARPS * 32)
-ks2_kernel(const Ks2Params p, int* __restrict__ workCounter) {
+ks2_kernel(const Ks2Params p, int* __restrict__ workCounter, int* __restrict__ itemsDone) {
     constexpr int RBMIN = (RBMAX == 8) ? 0 : (RBMAX == 16) ? 9 : (RBMAX == 24) ? 17 : 25;      // the item's largest radius
     constexpr bool BIG = RBMAX > 16;                  // which layers of an item: applied radius 17..32 or 0..16
     constexpr int LAYER_RMIN = BIG ? 17 : 0;
@@ -256,23 +290,29 @@ ks2_kernel(const Ks2Params p, int* __restrict__ workCounter) {
         n = (n > chunk) ? (n - chunk + NCH - 1) / NCH : 0;             // entries of this work unit
         imax = __reduce_max_sync(0xffffffffu, imax);
         if (imax < RBMIN || imax > RBMAX) continue;
+        if (lane == 0) atomicAdd(itemsDone, 1);
         // zero the columns this item can touch (rows 0..ROWS-1 only: the pads hold the layer list)
-        const int nr = 8 + 2 * imax, nc = 32 + 2 * imax, c0 = RBMAX - imax;
-        for (int i = lane; i < nc * (ROWS / 4); i += 32) {
+        // (the column range is widened to whole groups of 4: the final reduction below adds 16-byte groups of 4 columns)
+        const int nr = 8 + 2 * imax, c0 = RBMAX - imax;
+        const int cz0 = c0 & ~3, ncz = ((c0 + 32 + 2 * imax + 3) & ~3) - cz0;
+        for (int i = lane; i < ncz * (ROWS / 4); i += 32) {
             const int c = i / (ROWS / 4), q = i - c * (ROWS / 4);
-            reinterpret_cast<float4*>(patch + (c0 + c) * PC)[q] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            reinterpret_cast<float4*>(patch + (cz0 + c) * PC)[q] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
         }
         __syncwarp();
         const int tx = tile % p.tilesX, ty = tile / p.tilesX;
         const size_t tileOff = (size_t)kk * R + (size_t)(ty * 8) * p.Rx + tx * 32 + lane;
         const size_t layerStride = (size_t)p.nz * R;
-        // software pipeline: the next layer's 16 loads are in flight while the current layer is processed
-        float dn[8], rn[8];
-        {
-            const size_t src = (size_t)(llist(0) & 0xff) * layerStride + tileOff;
+        // the next layer's 16 row segments are requested into L2 while the current layer is processed (a register prefetch would
+        // cost 16 of the 255 registers the packed FMA block needs: ptxas then re-creates its operand pairs with MOVs)
+        auto prefetchLayer = [&](const int q) {       // called by lanes 0..3: lane -> sector lane of each 128-byte row segment
+            const size_t src = (size_t)(llist(q) & 0xff) * layerStride + tileOff + 7 * lane;
 #pragma unroll
-            for (int y = 0; y < 8; ++y) { dn[y] = __ldg(p.idd + src + (size_t)y * p.Rx); rn[y] = __ldg(p.rsig + src + (size_t)y * p.Rx); }
-        }
+            for (int y = 0; y < 8; ++y) {
+                asm volatile("prefetch.global.L2 [%0];" :: "l"(p.idd + src + (size_t)y * p.Rx));
+                asm volatile("prefetch.global.L2 [%0];" :: "l"(p.rsig + src + (size_t)y * p.Rx));
+            }
+        };
         for (int q = 0; q < n; ++q) {
             const int rb = llist(q) >> 8;
             // body = radius whose unrolled code runs: with bodyStep 2 / 4 a radius <= 16 uses the body of the next multiple
@@ -280,13 +320,12 @@ ks2_kernel(const Ks2Params p, int* __restrict__ workCounter) {
             // FMAs, but 1/2 or 1/4 of the code working set (instruction-fetch stalls, profiles/r01_ncu_full_ks2_c4.txt)
             const int body = BIG ? rb : min((rb + bodyStep - 1) & -bodyStep, RBMAX);
             float d[8], r[8];
+            {
+                const size_t src = (size_t)(llist(q) & 0xff) * layerStride + tileOff;
 #pragma unroll
-            for (int y = 0; y < 8; ++y) { d[y] = dn[y]; r[y] = rn[y]; }
-            if (q + 1 < n) {
-                const size_t src = (size_t)(llist(q + 1) & 0xff) * layerStride + tileOff;
-#pragma unroll
-                for (int y = 0; y < 8; ++y) { dn[y] = __ldg(p.idd + src + (size_t)y * p.Rx); rn[y] = __ldg(p.rsig + src + (size_t)y * p.Rx); }
+                for (int y = 0; y < 8; ++y) { d[y] = __ldg(p.idd + src + (size_t)y * p.Rx); r[y] = __ldg(p.rsig + src + (size_t)y * p.Rx); }
             }
+            if (q + 1 < n && lane < 4) prefetchLayer(q + 1);      // a 32-ray row segment = 128 B = 4 sectors: one lane per sector
             bool any = false;
 #pragma unroll
             for (int y = 0; y < 8; ++y) any |= d[y] > 0.0f;
@@ -319,7 +358,7 @@ ks2_kernel(const Ks2Params p, int* __restrict__ workCounter) {
             }
             __syncwarp();
             switch (body) {
-#define RTD_KS2_CASE(N) case N: if constexpr (N <= RBMAX && N >= LAYER_RMIN) { if constexpr (N <= 16) ks2_tile<N, RBMAX>(tab, d, patch, lane, rb); else ks2_tile_big<(N > 16) ? N : 17, BIG ? RBMAX : 32>(tab, d, patch, lane); } break;
+#define RTD_KS2_CASE(N) case N: if constexpr (N <= RBMAX && N >= LAYER_RMIN) { if constexpr (N <= 16) ks2_tile<N, RBMAX, N + 1>(tab, d, patch, lane, rb); else ks2_tile_big<(N > 16) ? N : 17, BIG ? RBMAX : 32>(tab, d, patch, lane); } break;
                 RTD_KS2_CASE(0) RTD_KS2_CASE(1) RTD_KS2_CASE(2) RTD_KS2_CASE(3) RTD_KS2_CASE(4) RTD_KS2_CASE(5) RTD_KS2_CASE(6)
                 RTD_KS2_CASE(7) RTD_KS2_CASE(8) RTD_KS2_CASE(9) RTD_KS2_CASE(10) RTD_KS2_CASE(11) RTD_KS2_CASE(12) RTD_KS2_CASE(13)
                 RTD_KS2_CASE(14) RTD_KS2_CASE(15) RTD_KS2_CASE(16) RTD_KS2_CASE(17) RTD_KS2_CASE(18) RTD_KS2_CASE(19) RTD_KS2_CASE(20)
@@ -331,12 +370,21 @@ ks2_kernel(const Ks2Params p, int* __restrict__ workCounter) {
             __syncwarp();
         }
         // one reduction of the touched part of the patch into the haloed BEV dose (z index = absolute step, 32-px halo):
-        // patch (column c0 + cc, row c0 + rr)  ->  BEV (tile column - imax + cc, tile row - imax + rr)
-        float* out = p.bev + ((size_t)(kk + p.first) * (p.Ry + 64) + (ty * 8 + 32 - imax)) * bevPitch + tx * 32 + 32 - imax;
-        for (int rr = 0; rr < nr; ++rr) {
-            for (int cc = lane; cc < nc; cc += 32) {
-                const float v = patch[(c0 + cc) * PC + c0 + rr];
-                if (v != 0.0f) atomicAdd(out + (size_t)rr * bevPitch + cc, v);
+        // patch (column pc, row pr)  ->  BEV (tile column - RBMAX + pc, tile row - RBMAX + pr). A lane takes one row of a 16-byte
+        // group of 4 columns: lanes 0..15 / 16..31 = 16 consecutive rows of two adjacent groups, so that the four scalar reads are
+        // conflict-free (consecutive rows of one patch column) and the two groups of a row fill one 32-byte sector of the BEV;
+        // RBMAX, the BEV pitch and the tile origin are multiples of 4, so every group is 16-byte aligned: red.global.add.v4.f32
+        float* out = p.bev + ((size_t)(kk + p.first) * (p.Ry + 64) + (ty * 8 + 32 - RBMAX)) * bevPitch + tx * 32 + 32 - RBMAX;
+        for (int r0 = c0; r0 < c0 + nr; r0 += 16) {
+            const int pr = r0 + (lane & 15);
+            for (int g0 = cz0; g0 < cz0 + ncz; g0 += 8) {
+                const int pc = g0 + 4 * (lane >> 4);
+                if (pr < c0 + nr && pc < cz0 + ncz) {
+                    const float* src = patch + pc * PC + pr;
+                    const float4 v = make_float4(src[0], src[PC], src[2 * PC], src[3 * PC]);
+                    if (v.x != 0.0f || v.y != 0.0f || v.z != 0.0f || v.w != 0.0f)
+                        atomicAdd(reinterpret_cast<float4*>(out + (size_t)pr * bevPitch + pc), v);
+                }
             }
         }
         __syncwarp();

@@ -89,6 +89,7 @@ struct BeamWs {
 
 struct rtd_ctx {
     int device = 0; cudaStream_t stream = nullptr;
+    bool ownStream = true;                // false: the caller's stream (rtd_create_on_stream), never destroyed here
     cudaStream_t cstream = nullptr;       // copy stream of the one-call host path (CT / dose-in sub-volumes)
     bool ctPartial = false;               // the CT array holds only the sub-volumes of the last rtd_plan_dose
     std::vector<Box> ctBoxes, doseBoxes;  // sub-volumes moved by the current call
@@ -108,7 +109,6 @@ struct rtd_ctx {
     std::vector<cudaStream_t> bstreams;   // per-beam streams (concurrent beams)
     int smCount = 148;
     int ks2Blocks8 = 0, ks2Blocks16 = 0, ks2Blocks24 = 0, ks2Blocks32 = 0;
-    int ks2BodyStep = 0;            // Ks2Params::bodyStep, 0 = per beam on the device (RTD_KS2_BODY_STEP = 1 | 2 | 4 overrides, for measurements)
     rtd_opts optsLast;
 };
 
@@ -351,12 +351,41 @@ cudaError_t copyDoseBox(rtd_ctx* ctx, float* host, float* dev, const Box& b, boo
     return cudaMemcpy3DAsync(&cp, st);
 }
 
+// Every beam of a plan is checked before anything is launched: the C ABI (and the --case reader of the host driver) can be handed
+// arbitrary bytes, and a non-positive spot pitch or a non-finite sigma would make the `while (dist < lim)` loops of
+// spot_to_ray_kernel endless (the reference has the same loops, gpu_convolution_2d.cu:24-33, but only ever sees its own main()).
+const char* validateBeam(const rtd_beam& b, const rtd_opts& o) {
+    if (b.nLayers <= 0 || b.sx <= 0 || b.sy <= 0 || !b.weights || !b.energies || !b.sigmas) return "Empty list";   // findMax on an empty vector, vector_find.h:22-25
+    if (b.steps == 0 || b.steps > 4095) return "beam.steps must be in [1, 4095]";
+    if (b.nLayers > 255) return "at most 255 energy layers per beam";
+    if (int64_t(b.sx) * b.sy > (1 << 24)) return "spot grid too large";
+    auto fin = [](float v) { return std::isfinite(v); };
+    for (int i = 0; i < 2; ++i) {
+        if (!fin(b.spotDelta[i]) || !(b.spotDelta[i] > 0.0f)) return "beam.spotDelta x / y must be finite and > 0";
+        if (!fin(b.raySpacing[i]) || !(b.raySpacing[i] > 0.0f)) return "beam.raySpacing must be finite and > 0";
+        if (std::isnan(b.sourceDist[i]) || b.sourceDist[i] == 0.0f) return "beam.sourceDist must be non-zero (INFINITY = parallel beam)";
+    }
+    if (!fin(b.spotDelta[2]) || b.spotDelta[2] == 0.0f) return "beam.spotDelta z (signed step length) must be finite and non-zero";
+    for (int i = 0; i < 3; ++i) if (!fin(b.spotOffset[i]) || !fin(b.gantryToImIdxV[i]) || !fin(b.gantryToDoseIdxV[i])) return "beam offsets / translations must be finite";
+    for (int i = 0; i < 9; ++i) if (!fin(b.gantryToImIdxM[i]) || !fin(b.gantryToDoseIdxM[i])) return "beam matrices must be finite";
+    for (int l = 0; l < b.nLayers; ++l) {
+        if (!fin(b.energies[l])) return "beam.energies must be finite";
+        if (!fin(b.sigmas[2 * l]) || !fin(b.sigmas[2 * l + 1]) || !(b.sigmas[2 * l] > 0.0f) || !(b.sigmas[2 * l + 1] > 0.0f)) return "beam.sigmas must be finite and > 0";
+    }
+    if (!(b.layerBegin == 0 && b.layerEnd == 0) && (b.layerBegin < 0 || b.layerEnd > b.nLayers || b.layerBegin >= b.layerEnd)) return "beam.layerBegin/layerEnd out of range";
+    if (!fin(o.convSigmaCutoff) || !(o.convSigmaCutoff > 0.0f) || !fin(o.ksSigmaCutoff) || !(o.ksSigmaCutoff > 0.0f) || !fin(o.bpDepthCutoff) || !fin(o.rayWeightCutoff))
+        return "opts cut-offs must be finite (sigma cut-offs > 0)";
+    // the pre-convolution visits (2 cutoff sigma / spotDelta) spots per ray and axis: bound it
+    float mx = 0.0f, my = 0.0f;
+    for (int l = 0; l < b.nLayers; ++l) { mx = std::max(mx, b.sigmas[2 * l]); my = std::max(my, b.sigmas[2 * l + 1]); }
+    if (o.convSigmaCutoff * mx / b.spotDelta[0] > 1.0e4f || o.convSigmaCutoff * my / b.spotDelta[1] > 1.0e4f) return "spot sigma is more than 1e4 spot pitches";
+    const double nxr = (double(b.sx) * b.spotDelta[0] + 2.0 * o.convSigmaCutoff * mx) / b.raySpacing[0], nyr = (double(b.sy) * b.spotDelta[1] + 2.0 * o.convSigmaCutoff * my) / b.raySpacing[1];
+    if (!(nxr < 1.0e5) || !(nyr < 1.0e5) || (nxr / 32.0 + 1.0) * (nyr / 8.0 + 1.0) > 4095.0) return "ray grid has more than 4095 tiles";
+    return nullptr;
+}
+
 // Everything that can be done for a beam before any device result is known (cu:612-663, 766-790).
 rtd_status beamPhaseA(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opts& o, int& launches, cudaStream_t st, HostIo* io, cudaEvent_t evCt) {
-    if (b.nLayers <= 0 || b.sx <= 0 || b.sy <= 0 || !b.weights || !b.energies || !b.sigmas)
-        return fail(ctx, RTD_ERR_INVALID, "Empty list");   // findMax on an empty vector, vector_find.h:22-25
-    if (b.steps == 0 || b.steps > 4095) return fail(ctx, RTD_ERR_INVALID, "beam.steps must be in [1, 4095]");
-    if (b.nLayers > 255) return fail(ctx, RTD_ERR_INVALID, "at most 255 energy layers per beam");
     float mx = b.sigmas[0], my = b.sigmas[1];
     for (int l = 1; l < b.nLayers; ++l) { mx = std::max(mx, b.sigmas[2 * l]); my = std::max(my, b.sigmas[2 * l + 1]); }
     w.grid = makeRayGrid(b.spotDelta, b.spotOffset, b.sx, b.sy, b.raySpacing, mx, my, o.convSigmaCutoff);
@@ -510,8 +539,8 @@ rtd_status beamPhaseB2(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opt
     RTD_CUDA(w.idd.ensure(LnzR * 4)); RTD_CUDA(w.rsig.ensure(LnzR * 4));
     RTD_CUDA(w.rowMin.ensure(size_t(L) * nz * Ry * tilesX * 4));
     RTD_CUDA(w.firstPassive.ensure(size_t(L) * R * 4));
-    // one zero-initialised control block: lfp[L] | hist[L*34] | rbCursor[33] | stats[4] | work[4]
-    const size_t ctlInts = size_t(L) + size_t(L) * 34 + 33 + 4 + 4;
+    // one zero-initialised control block: lfp[L] | hist[L*34] | rbCursor[33] | stats[4] | work[4] | ksItems[4]
+    const size_t ctlInts = size_t(L) + size_t(L) * 34 + 33 + 4 + 4 + 4;
     RTD_CUDA(w.lfp.ensure(ctlInts * 4));
     RTD_CUDA(w.batchRad.ensure(size_t(L) * 34 * 4)); RTD_CUDA(w.rbOffset.ensure(33 * 4));
     RTD_CUDA(w.radMap.ensure(size_t(L) * nz * tiles)); RTD_CUDA(w.list.ensure(size_t(L) * nz * tiles * 4));
@@ -567,11 +596,12 @@ rtd_status beamPhaseB2(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opt
     k2.idd = w.idd.as<float>(); k2.rsig = w.rsig.as<float>(); k2.bev = w.bev.as<float>(); k2.batchRad = w.batchRad.as<int>();
     k2.radMap = w.radMap.as<uint8_t>(); k2.layerFirstPassive = dLfp;
     k2.L = L; k2.Rx = Rx; k2.Ry = Ry; k2.nz = nz; k2.first = w.bfi; k2.tilesX = tilesX; k2.tiles = tiles;
-    k2.bigCount = dCursor; k2.bigItems = w.list.as<uint32_t>(); k2.bodyStep = ctx->ks2BodyStep;
-    ks2_kernel<32, KS2_WARPS_32><<<ctx->ks2Blocks32, KS2_WARPS_32 * 32, KS2_SMEM_32, strm>>>(k2, dWork + 0);
-    ks2_kernel<24, KS2_WARPS_24><<<ctx->ks2Blocks24, KS2_WARPS_24 * 32, KS2_SMEM_24, strm>>>(k2, dWork + 3);
-    ks2_kernel<16, KS2_WARPS_16><<<ctx->ks2Blocks16, KS2_WARPS_16 * 32, KS2_SMEM_16, strm>>>(k2, dWork + 1);
-    ks2_kernel<8, KS2_WARPS_8><<<ctx->ks2Blocks8, KS2_WARPS_8 * 32, KS2_SMEM_8, strm>>>(k2, dWork + 2);
+    k2.bigCount = dCursor; k2.bigItems = w.list.as<uint32_t>(); k2.bodyStep = (o.ks2BodyStep == 1 || o.ks2BodyStep == 2 || o.ks2BodyStep == 4) ? o.ks2BodyStep : 0;
+    int* dKsItems = dWork + 4;      // items each radius class processed (rtd_timing.ksLaunchesWithWork)
+    ks2_kernel<32, KS2_WARPS_32><<<ctx->ks2Blocks32, KS2_WARPS_32 * 32, KS2_SMEM_32, strm>>>(k2, dWork + 0, dKsItems + 0);
+    ks2_kernel<24, KS2_WARPS_24><<<ctx->ks2Blocks24, KS2_WARPS_24 * 32, KS2_SMEM_24, strm>>>(k2, dWork + 3, dKsItems + 1);
+    ks2_kernel<16, KS2_WARPS_16><<<ctx->ks2Blocks16, KS2_WARPS_16 * 32, KS2_SMEM_16, strm>>>(k2, dWork + 1, dKsItems + 2);
+    ks2_kernel<8, KS2_WARPS_8><<<ctx->ks2Blocks8, KS2_WARPS_8 * 32, KS2_SMEM_8, strm>>>(k2, dWork + 2, dKsItems + 3);
     RTD_CUDA(cudaEventRecord(evs[4], strm));
 
     // K4: the dose grid is shared by all beams: transfers are serialised on the context's main stream, in beam order,
@@ -593,11 +623,13 @@ rtd_status beamPhaseB2(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opt
 }
 
 // After the final sync: integer reports (cu:955-957, 1185-1210) and the metric counters.
-bool beamFinish(rtd_ctx* ctx, BeamWs& w, int64_t& updates, int64_t& taps) {
+bool beamFinish(rtd_ctx* ctx, BeamWs& w, int64_t& updates, int64_t& taps, int& ksLaunches) {
     if (!w.live) return true;
     const int L = w.Lc;
-    const size_t ctlInts = size_t(L) + size_t(L) * 34 + 33 + 4 + 4;
+    const size_t ctlInts = size_t(L) + size_t(L) * 34 + 33 + 4 + 4 + 4;
     const int* lfp = w.hOut.as<int>(); const int* hist = lfp + L; const int* stats = hist + size_t(L) * 34 + 33;
+    const int* ksItems = stats + 8;
+    for (int i = 0; i < 4; ++i) if (ksItems[i] > 0) ++ksLaunches;
     const int* brad = w.hOut.as<int>() + ctlInts;
     int fcp = 0; int64_t u = 0, t = 0;
     for (int l = 0; l < L; ++l) {
@@ -632,9 +664,11 @@ bool beamFinish(rtd_ctx* ctx, BeamWs& w, int64_t& updates, int64_t& taps) {
 constexpr size_t EV_BEAM0 = 8, EV_PER_BEAM = 10;   // events 0..7 are per call; per beam: 0..5 stages, 6 traced, 7 done, 8 CT boxes uploaded
 cudaEvent_t evBeam(rtd_ctx* ctx, int b, int i) { return ev(ctx, EV_BEAM0 + size_t(b) * EV_PER_BEAM + i); }
 
-rtd_status doseCore(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* dDose, const rtd_opts& o, rtd_timing* tm,
-                    cudaEvent_t evBegin, cudaEvent_t evEnd, HostIo* io) {
+rtd_status doseCoreImpl(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* dDose, const rtd_opts& o, rtd_timing* tm,
+                        cudaEvent_t evBegin, cudaEvent_t evEnd, HostIo* io) {
     int launches = 0;
+    for (int b = 0; b < nBeams; ++b)
+        if (const char* why = validateBeam(beams[b], o)) return fail(ctx, RTD_ERR_INVALID, why);
     while ((int)ctx->ws.size() < nBeams) ctx->ws.push_back(new BeamWs());
     ctx->nBeamsLast = nBeams; ctx->optsLast = o;
     ctx->ctBoxes.clear(); ctx->doseBoxes.clear();
@@ -714,14 +748,14 @@ rtd_status doseCore(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* dDos
     }
     RTD_CUDA(cudaEventRecord(evEnd, ctx->stream));
     RTD_CUDA(cudaStreamSynchronize(ctx->stream));                         // host sync 2 of 2
-    int64_t updates = 0, taps = 0; bool ok = true;
-    for (int b = 0; b < nBeams; ++b) ok = beamFinish(ctx, *ctx->ws[b], updates, taps) && ok;
+    int64_t updates = 0, taps = 0; bool ok = true; int ksLaunches = 0;
+    for (int b = 0; b < nBeams; ++b) ok = beamFinish(ctx, *ctx->ws[b], updates, taps, ksLaunches) && ok;
     const int64_t modified = (int64_t)*ctx->hXferCount.as<unsigned long long>();
     if (io && io->ctMapped) io->h2d += (int64_t)ctx->hXferCount.as<unsigned long long>()[1];   // CT bytes the pull kernels read over PCIe
     if (io && io->dose && io->zeroCopy) { io->h2d += modified * 4; io->d2h += modified * 4; }   // the transfers read-modify-write the caller's pinned grid in place
     if (tm) {
         memset(tm, 0, sizeof *tm);
-        tm->updates = updates; tm->ksTaps = taps; tm->kernelLaunches = launches; tm->hostSyncs = hostSyncs;
+        tm->updates = updates; tm->ksTaps = taps; tm->kernelLaunches = launches; tm->hostSyncs = hostSyncs; tm->ksLaunchesWithWork = ksLaunches;
         float ms = 0;
         cudaEventElapsedTime(&ms, evBegin, evTraceEnd); tm->msTrace = ms;
         cudaEvent_t prev = evTraceEnd;
@@ -749,6 +783,21 @@ rtd_status doseCore(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* dDos
     return RTD_OK;
 }
 
+// A failure in the middle of a plan leaves work queued on the per-beam streams and the copy stream: drain them all before the
+// status reaches the caller, who may free or reuse its buffers right away.
+rtd_status doseCore(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* dDose, const rtd_opts& o, rtd_timing* tm,
+                    cudaEvent_t evBegin, cudaEvent_t evEnd, HostIo* io) {
+    const rtd_status s = doseCoreImpl(ctx, beams, nBeams, dDose, o, tm, evBegin, evEnd, io);
+    if (s != RTD_OK) {
+        const std::string msg = ctx->err;
+        for (cudaStream_t bs : ctx->bstreams) cudaStreamSynchronize(bs);
+        cudaStreamSynchronize(ctx->cstream); cudaStreamSynchronize(ctx->stream);
+        cudaGetLastError();
+        ctx->err = msg;
+    }
+    return s;
+}
+
 }  // namespace
 
 // =========================================================================================================
@@ -760,10 +809,10 @@ void rtd_default_opts(rtd_opts* o) {
     if (!o) return;
     memset(o, 0, sizeof *o);
     o->bpDepthCutoff = 1.05f; o->convSigmaCutoff = 3.0f; o->ksSigmaCutoff = 3.0f; o->rayWeightCutoff = 1.0f;
-    o->minTilesInBatch = 16; o->keepIntermediates = 1;
+    o->minTilesInBatch = 16;
 }
 
-rtd_status rtd_create(rtd_ctx** out, int device) {
+static rtd_status createCommon(rtd_ctx** out, int device, cudaStream_t userStream, bool haveUserStream) {
     if (!out) return RTD_ERR_INVALID;
     *out = nullptr;
     int n = 0;
@@ -772,12 +821,12 @@ rtd_status rtd_create(rtd_ctx** out, int device) {
     if (cudaSetDevice(device) != cudaSuccess) return RTD_ERR_CUDA;
     rtd_ctx* ctx = new rtd_ctx();
     ctx->device = device;
-    if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return RTD_ERR_CUDA; }
+    if (haveUserStream) { ctx->stream = userStream; ctx->ownStream = false; }
+    else if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return RTD_ERR_CUDA; }
     int prLo = 0, prHi = 0; cudaDeviceGetStreamPriorityRange(&prLo, &prHi);   // the copy stream also runs the CT pull kernels: highest priority
-    if (cudaStreamCreateWithPriority(&ctx->cstream, cudaStreamNonBlocking, prHi) != cudaSuccess) { cudaStreamDestroy(ctx->stream); delete ctx; return RTD_ERR_CUDA; }
+    if (cudaStreamCreateWithPriority(&ctx->cstream, cudaStreamNonBlocking, prHi) != cudaSuccess) { if (ctx->ownStream) cudaStreamDestroy(ctx->stream); delete ctx; return RTD_ERR_CUDA; }
     cudaDeviceGetAttribute(&ctx->smCount, cudaDevAttrMultiProcessorCount, device);
     rtd_default_opts(&ctx->optsLast);
-    if (const char* e = getenv("RTD_KS2_BODY_STEP")) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4) ctx->ks2BodyStep = v; }
     cudaFuncSetAttribute(ks2_kernel<16, KS2_WARPS_16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)KS2_SMEM_16);
     cudaFuncSetAttribute(ks2_kernel<8, KS2_WARPS_8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)KS2_SMEM_8);
     cudaFuncSetAttribute(ks2_kernel<32, KS2_WARPS_32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)KS2_SMEM_32);
@@ -787,10 +836,13 @@ rtd_status rtd_create(rtd_ctx** out, int device) {
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ks2_kernel<8, KS2_WARPS_8>, KS2_WARPS_8 * 32, KS2_SMEM_8); ctx->ks2Blocks8 = std::max(occ, 1) * ctx->smCount;
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ks2_kernel<32, KS2_WARPS_32>, KS2_WARPS_32 * 32, KS2_SMEM_32); ctx->ks2Blocks32 = std::max(occ, 1) * ctx->smCount;
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ks2_kernel<24, KS2_WARPS_24>, KS2_WARPS_24 * 32, KS2_SMEM_24); ctx->ks2Blocks24 = std::max(occ, 1) * ctx->smCount;
-    if (cudaGetLastError() != cudaSuccess) { cudaStreamDestroy(ctx->stream); delete ctx; return RTD_ERR_CUDA; }
+    if (cudaGetLastError() != cudaSuccess) { cudaStreamDestroy(ctx->cstream); if (ctx->ownStream) cudaStreamDestroy(ctx->stream); delete ctx; return RTD_ERR_CUDA; }
     *out = ctx;
     return RTD_OK;
 }
+
+rtd_status rtd_create(rtd_ctx** out, int device) { return createCommon(out, device, nullptr, false); }
+rtd_status rtd_create_on_stream(rtd_ctx** out, int device, void* cudaStream) { return createCommon(out, device, (cudaStream_t)cudaStream, true); }
 
 void rtd_destroy(rtd_ctx* ctx) {
     if (!ctx) return;
@@ -802,7 +854,7 @@ void rtd_destroy(rtd_ctx* ctx) {
     for (cudaEvent_t e : ctx->events) cudaEventDestroy(e);
     for (cudaStream_t s_ : ctx->bstreams) { cudaStreamSynchronize(s_); cudaStreamDestroy(s_); }
     cudaStreamSynchronize(ctx->cstream); cudaStreamDestroy(ctx->cstream);
-    cudaStreamDestroy(ctx->stream);
+    if (ctx->ownStream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
 
@@ -903,9 +955,7 @@ static rtd_status doseHost(rtd_ctx* ctx, const float* ct, const rtd_beam* beams,
         if (mapped) { io.zeroCopy = true; dDose = mapped; }
         else { RTD_CUDA(ctx->dose.ensure(n * 4)); dDose = ctx->dose.as<float>(); }
     }
-    rtd_status s = doseCore(ctx, beams, nBeams, dDose, o, tm, ev(ctx, 0), ev(ctx, 1), &io);
-    if (s != RTD_OK) { cudaStreamSynchronize(ctx->cstream); cudaStreamSynchronize(ctx->stream); }
-    return s;
+    return doseCore(ctx, beams, nBeams, dDose, o, tm, ev(ctx, 0), ev(ctx, 1), &io);
 }
 
 rtd_status rtd_dose(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* dose, const rtd_opts* opts, rtd_timing* tm) {

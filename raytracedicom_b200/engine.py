@@ -46,7 +46,7 @@ class RtdBeam(C.Structure):
 
 class RtdOpts(C.Structure):
     _fields_ = [("bpDepthCutoff", C.c_float), ("convSigmaCutoff", C.c_float), ("ksSigmaCutoff", C.c_float),
-                ("rayWeightCutoff", C.c_float), ("minTilesInBatch", C.c_int), ("keepIntermediates", C.c_int),
+                ("rayWeightCutoff", C.c_float), ("minTilesInBatch", C.c_int), ("ks2BodyStep", C.c_int),
                 ("serialBeams", C.c_int), ("noZeroCopyDose", C.c_int), ("noNozzle", C.c_int), ("doseToMedium", C.c_int),
                 ("atomicDose", C.c_int), ("ctPull", C.c_int)]
 
@@ -56,7 +56,7 @@ class RtdTiming(C.Structure):
                 ("msConv", C.c_float), ("msIddSigma", C.c_float), ("msRadius", C.c_float), ("msSuperp", C.c_float),
                 ("msTransfer", C.c_float), ("msDownload", C.c_float), ("updates", C.c_int64), ("ksTaps", C.c_int64),
                 ("kernelLaunches", C.c_int), ("hostSyncs", C.c_int), ("h2dBytes", C.c_int64), ("d2hBytes", C.c_int64),
-                ("doseVoxelsModified", C.c_int64)]
+                ("doseVoxelsModified", C.c_int64), ("ksLaunchesWithWork", C.c_int), ("reserved0", C.c_int)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -92,7 +92,7 @@ class RtdError(RuntimeError):
         self.status = status
 
 
-EXPORTS = ["rtd_default_opts", "rtd_create", "rtd_destroy", "rtd_last_error", "rtd_version", "rtd_set_luts", "rtd_set_ct",
+EXPORTS = ["rtd_default_opts", "rtd_create", "rtd_create_on_stream", "rtd_destroy", "rtd_last_error", "rtd_version", "rtd_set_luts", "rtd_set_ct",
            "rtd_set_ct_device", "rtd_set_dose_grid", "rtd_dose", "rtd_dose_device", "rtd_plan_dose", "rtd_plan_dose_device", "rtd_add_device_to_host", "rtd_shared_dose_create", "rtd_shared_dose_open", "rtd_shared_dose_close", "rtd_push_dose_to_peer",
            "rtd_get_beam_report",
            "rtd_get_layer_report", "rtd_debug_fetch", "rtd_debug_ct_boxes", "rtd_stream"]
@@ -112,6 +112,7 @@ def load_library() -> C.CDLL:
     vp = C.c_void_p
     lib.rtd_default_opts.argtypes = [C.POINTER(RtdOpts)]; lib.rtd_default_opts.restype = None
     lib.rtd_create.argtypes = [C.POINTER(vp), C.c_int]; lib.rtd_create.restype = C.c_int
+    lib.rtd_create_on_stream.argtypes = [C.POINTER(vp), C.c_int, vp]; lib.rtd_create_on_stream.restype = C.c_int
     lib.rtd_destroy.argtypes = [vp]; lib.rtd_destroy.restype = None
     lib.rtd_last_error.argtypes = [vp]; lib.rtd_last_error.restype = C.c_char_p
     lib.rtd_version.argtypes = []; lib.rtd_version.restype = C.c_char_p
@@ -187,10 +188,15 @@ def ct_boxes(beam: Beam, ct_dims_xyz) -> np.ndarray:
 class DoseEngine:
     """One context per GPU. Mirrors the life cycle inside cudaWrapperProtons: LUT upload, CT upload, per-plan dose."""
 
-    def __init__(self, device: int = 0):
+    def __init__(self, device: int = 0, stream: Optional[int] = None):
+        """``stream``: a cudaStream_t (integer handle) the caller owns, e.g. ``torch.cuda.Stream().cuda_stream``; the context then
+        issues its work on it (rtd_create_on_stream) and never destroys it."""
         self.lib = load_library()
         self._h = C.c_void_p()
-        st = self.lib.rtd_create(C.byref(self._h), int(device))
+        if stream is None:
+            st = self.lib.rtd_create(C.byref(self._h), int(device))
+        else:
+            st = self.lib.rtd_create_on_stream(C.byref(self._h), int(device), C.c_void_p(int(stream)))
         if st != 0:
             self._h = C.c_void_p()
             raise RtdError(st, "rtd_create failed (a CUDA device is required; there is no CPU fallback)")

@@ -144,12 +144,13 @@ def reduce_dose(dose_tensor, dst: int = 0, all_ranks: bool = False):
     return dose_tensor
 
 
-def dose_slab(beams: Sequence[Beam], dose_dims) -> Tuple[int, int]:
+def dose_slab(beams: Sequence[Beam], dose_dims, sigma_cutoff: float = 3.0) -> Tuple[int, int]:
     """Conservative z-slab [z0, z1] (inclusive, dose-grid slices) outside which NO beam of the plan can deposit dose,
     from geometry alone, identical on every rank: the haloed BEV volume of each beam over ALL tracer steps (ray grid =
     spot grid + 3 sigma + half a ray, rounded up to 32 x 8 rays, + the 32-ray halo of the superposition,
     kernel_wrapper.cu:612-663, kernel_wrapper.cuh:303-308) mapped through the divergence and gantryToDoseIdx
-    (float3_from_fan_transform.cu:37-42). Only this slab of the partial dose grids is zeroed and reduced over NCCL."""
+    (float3_from_fan_transform.cu:37-42). Only this slab of the partial dose grids is zeroed and reduced over NCCL.
+    ``sigma_cutoff`` is rtd_opts.convSigmaCutoff (CONV_SIGMA_CUTOFF, 3 by default): it sizes the ray grid."""
     nx, ny, nz = dose_dims
     lo, hi = nz, -1
     for b in beams:
@@ -158,10 +159,10 @@ def dose_slab(beams: Sequence[Beam], dose_dims) -> Tuple[int, int]:
         smax = np.max(np.asarray(b.sigmas, np.float64), axis=0)
         n = np.array([sx, sy], np.float64)
         d = np.array(b.spot_delta[:2], np.float64); o = np.array(b.spot_offset[:2], np.float64)
-        # the ray grid starts at ceil((first spot - 3 sigma - res/2) / res) and is rounded UP to 32 x 8 rays at its far end;
+        # the ray grid starts at ceil((first spot - cutoff sigma - res/2) / res) and is rounded UP to 32 x 8 rays at its far end;
         # 32 halo rays + 1 ray of interpolation reach + 1 of slack on both sides
-        m_lo = 3.0 * smax + 0.5 * res + 34.0 * res
-        m_hi = 3.0 * smax + 0.5 * res + (np.array([31.0, 7.0]) + 34.0) * res
+        m_lo = sigma_cutoff * smax + 0.5 * res + 34.0 * res
+        m_hi = sigma_cutoff * smax + 0.5 * res + (np.array([31.0, 7.0]) + 34.0) * res
         xy0 = np.minimum(o, o + (n - 1) * d) - m_lo
         xy1 = np.maximum(o, o + (n - 1) * d) + m_hi
         dz = float(b.spot_delta[2]); z0 = float(b.spot_offset[2])

@@ -47,6 +47,24 @@ def cmp_int(name, a, b, rep):
     return mism
 
 
+def gamma_pass_rate_cropped(dose, ref, spacing, dose_crit=0.01, dist_mm=1.0, cutoff=0.1):
+    """Global gamma(1 %/1 mm) pass rate on the voxels with ref >= 10 % of max (BASELINE.json: >= 99.9 %). A voxel whose own dose
+    difference is within the dose criterion passes at distance 0, so when max |D - Dref| <= 1 % of max the rate is exactly 1;
+    otherwise the 3x3x3 (+ interpolated) neighbourhood search of tests/conftest.py runs on the bounding box of the evaluated voxels."""
+    dmax = float(ref.max())
+    mask = ref >= cutoff * dmax
+    if not mask.any():
+        return 1.0
+    if float(np.abs(dose - ref)[mask].max()) <= dose_crit * dmax:
+        return 1.0
+    idx = np.argwhere(mask)
+    lo = np.maximum(idx.min(0) - 1, 0); hi = np.minimum(idx.max(0) + 2, ref.shape)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from conftest import gamma_pass_rate
+    sl = tuple(slice(int(a), int(b)) for a, b in zip(lo, hi))
+    return gamma_pass_rate(dose[sl], ref[sl], spacing, dose_crit, dist_mm, cutoff)     # the box holds the maximum of ref
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--case", default="mini")
@@ -165,6 +183,7 @@ def main():
     cmp_float("dose_vs_ref_stages", dose, total_ref, rep)
     dmax = float(total_ref.max())
     rep["dose_max_rel_err"] = float(np.abs(dose - total_ref).max() / dmax) if dmax > 0 else None
+    rep["gamma_1pct_1mm_pass_rate"] = gamma_pass_rate_cropped(dose, total_ref, case.spacing) if dmax > 0 else None
     if not args.no_ref_dose:
         dpath = os.path.join(tmp, "ref_dose.f32")
         r = subprocess.run([os.path.join(REF, "ref_dose"), cpath, dpath], capture_output=True, text=True, timeout=1200)
