@@ -100,6 +100,10 @@ typedef struct {
                                 interval the tracers can touch crosses PCIe (C3: 51 MB instead of 60 MB of boxes). Measured SLOWER end to
                                 end on B200 (3.2 vs 2.9 ms: the pull kernels compete with the dose kernels for SMs, the copy engines do
                                 not), so the default 0 keeps the axis-aligned sub-volume copies */
+    int   fullIntermediates; /* 1: the depth scan writes idd / rSigmaEff of EVERY (ray, step) as the reference does, for rtd_debug_fetch
+                                (RTD_FETCH_IDD / RTD_FETCH_RSIGMA). 0 (default): 32-ray row segments that hold no dose at a step are
+                                not written (the superposition never reads them; ~60 % of the scan's HBM writes on a head plan) and
+                                fetch as unspecified values */
 } rtd_opts;
 
 /* Stage timing of the last rtd_dose* call (CUDA events; with concurrent beams the per-stage figures are sums over the

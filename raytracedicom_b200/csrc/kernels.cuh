@@ -174,12 +174,152 @@ slice_reduce_kernel(const float* __restrict__ wepl, const int* __restrict__ firs
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// Per-beam set-up ON THE DEVICE. The reference (and round 1 of this engine) brings the tracer's reductions to the host, derives
+// the cut-off steps, the per-layer parameters and the transfer box there (kernel_wrapper.cu:792-849, 922-925, 1185-1218) and only
+// then launches the rest of the beam: a host round trip in the middle of every beam. Here one small CTA does that arithmetic and
+// leaves the results in device memory (BeamDev, LayerParams[], entry sigmas, step table); every later kernel of the beam reads its
+// data-dependent parameters from there and is launched with a grid that depends on the geometry alone, so a plan is issued without
+// any host synchronisation and the host reads the integers back after the final sync for its reports.
+// Host formulas are evaluated with IEEE round-to-nearest intrinsics in the host's operation order (the host code is compiled
+// without FMA contraction): the same bits as round 1's host code, which the integer parity tests pin.
+struct LayerParams {          // per-layer constants, kernel_wrapper.cu:829-849, 922-925
+    float energyIdx, energyScale, peakDepth;
+    int afterLast;
+    int order;                // launch order: grid.z = i runs layer layers[i].order, deepest layers (longest depth scans) first
+};
+struct LayerIn {              // what the host knows about a layer before the tracer has run
+    float energyIdx, energyScale, peakDepth, thr /* BP_DEPTH_CUTOFF x peakDepth */, ca, cb /* sigmaSqAirCoefs, host IEEE */, sigX, sigY;
+};
+struct GridParams {
+    TransferParams t;
+    int minX, minY, minZ, maxX, maxY, maxZ;   // inclusive bbox in dose indices
+    int nx, ny, nz;                           // dose dims
+    int W, H, first, zEnd;                    // BEV dims (haloed) and valid slice range [first, zEnd)
+    int atomic;                               // 1: red.global.add.f32 (the dose grid is shared by several GPUs over NVLink)
+    int tilesX, tilesY, zChunks;              // work units of bev_to_grid_kernel: 32 x 8 columns x a chunk of the z range; 0 = nothing to do
+};
+static_assert(sizeof(GridParams) % 4 == 0 && sizeof(GridParams) / 4 <= 256, "GridParams is copied by one CTA");
+struct BeamDev {
+    int bfi, bfo, Zg, nz;                     // beamFirstInside / Outside, beamFirstGuaranteedPassive, slices kept per layer = max(Zg - bfi, 0)
+    float entryZ, pixelSpX, pixelSpY, pad0;   // K3a: ray pitch at the entry plane
+    GridParams grid;                          // K4
+};
+struct SetupIn {
+    int S, L;
+    float rayResZ, rayOffZ, distX, distY, rayDx, rayDy;
+    float thrAll;                             // BP_DEPTH_CUTOFF x peak depth of the beam's highest energy
+    IdxT fitf; Affine gtdi; float dist[2];    // rayIdxToGantry, gantryToDoseIdx, source distances: transfer box
+    TransferParams t0; float ftfiOffZ;        // transfer parameters for shift (32, 32, 0); the z shift -bfi is added here
+    int Rx, Ry, nx, ny, nz, smCount, atomic;
+    FillGeom g;                               // step table
+};
+
+namespace ieee {   // host arithmetic on the device: one rounding per operation, no contraction, IEEE division and square root
+__device__ __forceinline__ float add(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float sub(float a, float b) { return __fsub_rn(a, b); }
+__device__ __forceinline__ float mul(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float div(float a, float b) { return __fdiv_rn(a, b); }
+__device__ __forceinline__ float dot3(V3 a, V3 b) { return add(add(mul(a.x, b.x), mul(a.y, b.y)), mul(a.z, b.z)); }
+// float3_from_fan_transform.cu:37-42 as host_geom.hpp's fromFan evaluates it
+__device__ __forceinline__ V3 fromFan(const IdxT& fitf, const float distX, const float distY, const Affine& gtii, V3 f) {
+    V3 p; p.x = add(mul(f.x, fitf.delta.x), fitf.offset.x); p.y = add(mul(f.y, fitf.delta.y), fitf.offset.y); p.z = add(mul(f.z, fitf.delta.z), fitf.offset.z);
+    p.x = mul(p.x, sub(1.0f, div(p.z, distX)));
+    p.y = mul(p.y, sub(1.0f, div(p.z, distY)));
+    V3 r; r.x = add(dot3(gtii.m.r0, p), gtii.v.x); r.y = add(dot3(gtii.m.r1, p), gtii.v.y); r.z = add(dot3(gtii.m.r2, p), gtii.v.z);
+    return r;
+}
+__device__ __forceinline__ int firstLargerOrdered(const float* __restrict__ list, int n, float value) {     // vector_find.h:62-82
+    int upper = n - 1, lower = 0;
+    if (list[n - 1] <= value) return upper;
+    if (list[0] > value) return 0;
+    while (upper - lower > 1) { const int pivot = (upper + lower) / 2; if (list[pivot] <= value) lower = pivot; else upper = pivot; }
+    return lower + 1;
+}
+}  // namespace ieee
+
+// block = 256 threads, one CTA per beam. trace: [0] = beamFirstInside, [1] = beamFirstOutside (ints), [2..] weplMin[S] (slice_reduce_kernel).
+__global__ void __launch_bounds__(256)
+beam_setup_kernel(const SetupIn in, const int* __restrict__ trace, const LayerIn* __restrict__ lin,
+                  BeamDev* __restrict__ bd, LayerParams* __restrict__ layers, float2* __restrict__ sigmas, float2* __restrict__ stepTab) {
+    __shared__ int sZg, sBfi;
+    __shared__ int sAfter[256];
+    const float* weplMin = reinterpret_cast<const float*>(trace + 2);
+    if (threadIdx.x == 0) {
+        sBfi = trace[0];
+        sZg = min(ieee::firstLargerOrdered(weplMin, in.S, in.thrAll), trace[1]);      // kernel_wrapper.cu:792-796
+    }
+    __syncthreads();
+    const int bfi = sBfi, Zg = sZg, nz = max(Zg - bfi, 0);
+    const float entryZ = ieee::add(ieee::mul((float)bfi, in.rayResZ), in.rayOffZ);
+    for (int l = threadIdx.x; l < in.L; l += 256) {
+        const LayerIn li = lin[l];
+        // entry sigma (cu:838-841): sqrt(ca z^2 + cb z + sigma^2), host arithmetic
+        const float air = ieee::add(ieee::mul(ieee::mul(li.ca, entryZ), entryZ), ieee::mul(li.cb, entryZ));
+        sigmas[l] = make_float2(__fsqrt_rn(ieee::add(air, ieee::mul(li.sigX, li.sigX))), __fsqrt_rn(ieee::add(air, ieee::mul(li.sigY, li.sigY))));
+        const unsigned localAfterLast = (unsigned)ieee::firstLargerOrdered(weplMin, in.S, li.thr);     // cu:922-924
+        sAfter[l] = (int)min(localAfterLast, (unsigned)Zg);
+    }
+    __syncthreads();
+    for (int l = threadIdx.x; l < in.L; l += 256) {
+        // launch order of the layers in the IDD / sigma kernel: longest depth scan first (stable)
+        int rank = 0;
+        for (int m = 0; m < in.L; ++m) rank += (sAfter[m] > sAfter[l]) || (sAfter[m] == sAfter[l] && m < l);
+        const LayerIn li = lin[l];
+        layers[l].energyIdx = li.energyIdx; layers[l].energyScale = li.energyScale; layers[l].peakDepth = li.peakDepth;
+        layers[l].afterLast = sAfter[l];
+        layers[rank].order = l;
+    }
+    // voxelWidth(k) (fill_idd_and_sigma_params.cu:42-46) and stepVol(k) (cu:72) depend on the step only: one table per beam,
+    // evaluated with the instruction sequence the depth scan used to run per (ray, step) - bit-identical
+    for (int kk = threadIdx.x; kk < nz; kk += 256) {
+        const unsigned k = (unsigned)(bfi + kk);
+        const float fk = u2f(k);
+        const float zk = f_fma(in.g.delta.z, fk, in.g.corner.z);
+        const float vwx = f_mul(in.g.delta.x, f_sub(1.0f, f_div(zk, in.g.distX)));
+        const float vwy = f_mul(in.g.delta.y, f_sub(1.0f, f_div(zk, in.g.distY)));
+        stepTab[kk] = make_float2(f_mul(f_add(vwx, vwy), 0.5f), f_fma(in.g.volSq, u2f(k * k), f_fma(in.g.volLin, fk, in.g.volConst)));
+    }
+    if (threadIdx.x == 0) {
+        BeamDev b;
+        b.bfi = bfi; b.bfo = trace[1]; b.Zg = Zg; b.nz = nz; b.entryZ = entryZ; b.pad0 = 0.0f;
+        b.pixelSpX = ieee::mul(in.rayDx, ieee::sub(1.0f, ieee::div(entryZ, in.distX)));       // cu:849-854
+        b.pixelSpY = ieee::mul(in.rayDy, ieee::sub(1.0f, ieee::div(entryZ, in.distY)));
+        GridParams& gp = b.grid;
+        gp.t = in.t0;
+        gp.t.globalOffset.z = ieee::add(in.ftfiOffZ, -(float)bfi);
+        gp.nx = in.nx; gp.ny = in.ny; gp.nz = in.nz;
+        gp.W = in.Rx + 64; gp.H = in.Ry + 64; gp.first = bfi; gp.zEnd = Zg; gp.atomic = in.atomic;
+        gp.tilesX = gp.tilesY = gp.zChunks = 0;
+        gp.minX = gp.minY = gp.minZ = 0; gp.maxX = gp.maxY = gp.maxZ = -1;
+        if (nz > 0) {
+            // K4 box (cu:1185-1218); the z-range uses Zg instead of beamFirstCalculatedPassive: a superset box that only adds
+            // voxels whose interpolated BEV dose is exactly 0
+            const float xv[2] = {-32.0f, (float)(in.Rx + 32 - 1)}, yv[2] = {-32.0f, (float)(in.Ry + 32 - 1)}, zv[2] = {(float)bfi, (float)(Zg - 1)};
+            V3 mx = v3(-1.f, -1.f, -1.f), mn = v3(100000.f, 100000.f, 100000.f);
+            for (int c = 0; c < 8; ++c) {
+                const V3 p = ieee::fromFan(in.fitf, in.dist[0], in.dist[1], in.gtdi, v3(xv[c & 1], yv[(c >> 1) & 1], zv[c >> 2]));
+                mx.x = fmaxf(mx.x, p.x); mx.y = fmaxf(mx.y, p.y); mx.z = fmaxf(mx.z, p.z);
+                mn.x = fminf(mn.x, p.x); mn.y = fminf(mn.y, p.y); mn.z = fminf(mn.z, p.z);
+            }
+            gp.minX = max(((int)floorf(mn.x) / 32) * 32, 0); gp.minY = max((int)floorf(mn.y), 0); gp.minZ = max((int)floorf(mn.z), 0);
+            gp.maxX = min((int)ceilf(mx.x), in.nx - 1); gp.maxY = min((int)ceilf(mx.y), in.ny - 1); gp.maxZ = min((int)ceilf(mx.z), in.nz - 1);
+            if (gp.maxX >= gp.minX && gp.maxY >= gp.minY && gp.maxZ >= gp.minZ) {
+                gp.tilesX = (gp.maxX - gp.minX + 32) / 32; gp.tilesY = (gp.maxY - gp.minY + 8) / 8;
+                const int tilesXY = gp.tilesX * gp.tilesY, nzBox = gp.maxZ - gp.minZ + 1;
+                gp.zChunks = max(1, min(min((8 * in.smCount + tilesXY - 1) / tilesXY, nzBox), 64));     // ~8 work units per SM
+            }
+        }
+        *bd = b;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // K3a: spot weights -> ray weights. One CTA = (32 ray columns, one layer): the x-pass result for all Sy spot
 // rows stays in shared memory and the y-pass reads it from there (the reference round-trips an intermediate
 // array through global memory between two launches, gpu_convolution_2d.cu:69-70).
-struct ConvParams {
+struct ConvParams {           // the ray pitch at the entry plane (pixelSpX / Y) depends on the tracer: BeamDev
     int inW, inH, outW, outH;
-    float pixelSpX, pixelSpY, offX, offY, deltaX, deltaY, cutoff;
+    float offX, offY, deltaX, deltaY, cutoff;
 };
 
 __device__ __forceinline__ float conv_weight(float dist, float rSig) {   // gpu_convolution_2d.cu:28
@@ -187,14 +327,17 @@ __device__ __forceinline__ float conv_weight(float dist, float rSig) {   // gpu_
 }
 
 __global__ void __launch_bounds__(256)
-spot_to_ray_kernel(const float* __restrict__ in, const float2* __restrict__ sigmas, float* __restrict__ out, const ConvParams c) {
+spot_to_ray_kernel(const float* __restrict__ in, const float2* __restrict__ sigmas, float* __restrict__ out, const ConvParams c,
+                   const BeamDev* __restrict__ bd) {
     extern __shared__ float sInterm[];   // [inH][32]
+    if (bd->nz <= 0) return;             // the beam never enters the patient
+    const float pixelSpX = bd->pixelSpX, pixelSpY = bd->pixelSpY;
     const int layer = blockIdx.y;
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     const int ox = blockIdx.x * 32 + tx;
     const float2 sg = sigmas[layer];
     {   // x pass (gpu_convolution_2d.cu:16-35)
-        const float sigEff = f_div(sg.x, c.pixelSpX);
+        const float sigEff = f_div(sg.x, pixelSpX);
         const float rSig = f_div(f_rsqrt(2.0f), sigEff);
         const float lim = f_fma(sigEff, c.cutoff, 0.5f);
         const float fo = i2f(ox);
@@ -214,7 +357,7 @@ spot_to_ray_kernel(const float* __restrict__ in, const float2* __restrict__ sigm
     }
     __syncthreads();
     {   // y pass (gpu_convolution_2d.cu:37-59)
-        const float sigEff = f_div(sg.y, c.pixelSpY);
+        const float sigEff = f_div(sg.y, pixelSpY);
         const float rSig = f_div(f_rsqrt(2.0f), sigEff);
         const float lim = f_fma(sigEff, c.cutoff, 0.5f);
         for (int oy = ty; oy < c.outH; oy += 8) {
@@ -235,42 +378,43 @@ spot_to_ray_kernel(const float* __restrict__ in, const float2* __restrict__ sigm
 // ---------------------------------------------------------------------------------------------------------
 // K2: integrated depth dose + lateral sigma for ALL energy layers in one launch (grid.z = layer; the
 // reference launches once per layer and syncs with the host three times per layer, cu:916-976).
-struct LayerParams {          // per-layer constants, kernel_wrapper.cu:829-849, 922-925
-    float energyIdx, energyScale, peakDepth;
-    int afterLast;
-    int order;                // launch order: grid.z = i runs layer layers[i].order, deepest layers (longest depth scans) first
-};
 struct IddParams {
     FillGeom g;
     float rrlScale, bpCutoff, rayWeightCutoff;
-    int first;                // beamFirstInside
-    int nz;                   // Zg - first: slices kept per layer
     int Rx, Ry;
     int nozzle;               // 0 = the reference's -DNO_NOZZLE build (fill_idd_and_sigma_params.cu:76-82)
     int doseToMedium;         // 1 = the reference built without -DDOSE_TO_WATER (kernel_wrapper.cu:314-318)
+    int writeAll;             // 1: every (ray, step) of idd / rSigmaEff is written (rtd_opts.fullIntermediates, for rtd_debug_fetch);
+                              // 0: row segments without dose are left alone - the superposition never reads them (see the step lambda)
 };
 
-__global__ void __launch_bounds__(256)
+// Thread = (ray, layer), warp = 32-ray row segment, CTA = ONE warp... x IDD_WARPS: the depth scan of a row segment is a serial chain
+// whose length differs wildly between segments (rays outside the field end at once, two thirds of all segments on C3), so
+// small CTAs give their slot back as soon as their own segments end instead of waiting for the longest of eight; the per-step
+// table the CTA used to build in shared memory is the beam's stepTab (beam_setup_kernel), read through L1.
+constexpr int IDD_WARPS = 2;
+__global__ void __launch_bounds__(IDD_WARPS * 32)
 idd_sigma_kernel(const float* __restrict__ density, const float* __restrict__ wepl, const float* __restrict__ rayWeights,
                  const int* __restrict__ firstInside, const int* __restrict__ firstOutside,
-                 const LayerParams* __restrict__ layers, const IddParams q,
+                 const LayerParams* __restrict__ layers, const BeamDev* __restrict__ bd, const float2* __restrict__ stepTab, const IddParams q,
                  cudaTextureObject_t iddTex, cudaTextureObject_t rrlTex,
                  float* __restrict__ idd, float* __restrict__ rsig, float* __restrict__ rowMin,
                  int* __restrict__ firstPassive, int* __restrict__ layerFirstPassive) {
+    const int nz = bd->nz;
+    if (nz <= 0) return;
     // CTAs are handed out in grid order and not all of them are resident at once: the layers with the longest depth scan go
     // first so that the short ones fill the tail instead of the other way round
     const int l = layers[blockIdx.z].order;
-    // a warp owns a 32-ray row segment; the 8 warps of a CTA own 8 CONSECUTIVE segments in memory order (for Rx = 128: two
-    // full ray rows), so that a CTA's stores of one step form 1 KB runs instead of eight 128 B pieces 4 Rx bytes apart
     const int tilesX = q.Rx / 32;
-    const int seg = blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int seg = blockIdx.x * IDD_WARPS + (threadIdx.x >> 5);
+    if (seg >= tilesX * q.Ry) return;
     const int segX = seg % tilesX;
     const int x = segX * 32 + (threadIdx.x & 31);
-    const int y = min(seg / tilesX, q.Ry - 1);          // Ry is a multiple of 8: segments never run past the grid
+    const int y = seg / tilesX;
     const int R = q.Rx * q.Ry;
     const int ray = y * q.Rx + x;
     const LayerParams lp = layers[l];
-    const unsigned first = (unsigned)q.first;
+    const unsigned first = (unsigned)bd->bfi;
 
     const int firstIn = firstInside[ray];
     unsigned afterLast = (unsigned)min(firstOutside[ray], lp.afterLast);
@@ -293,33 +437,18 @@ idd_sigma_kernel(const float* __restrict__ density, const float* __restrict__ we
     const float thr = f_mul(lp.peakDepth, q.bpCutoff);
     const float inf = __int_as_float(0x7f800000);
 
-    // voxelWidth(k) (fill_idd_and_sigma_params.cu:42-46) and stepVol(k) (cu:72) depend on the step only: evaluated once per
-    // CTA into shared memory with the same instruction sequence (bit-identical), which takes 2 of the 9 MUFU operations and
-    // ~10 FP32 instructions out of every (ray, step) iteration
-    extern __shared__ float sStep[];          // [2][nz]: 0.5 (vwx + vwy), stepVol
-    for (unsigned kk = threadIdx.x; first + kk < (unsigned)lp.afterLast && kk < (unsigned)q.nz; kk += 256) {
-        const unsigned k = first + kk;
-        const float fk = u2f(k);
-        const float zk = f_fma(q.g.delta.z, fk, q.g.corner.z);
-        const float vwx = f_mul(q.g.delta.x, f_sub(1.0f, f_div(zk, q.g.distX)));
-        const float vwy = f_mul(q.g.delta.y, f_sub(1.0f, f_div(zk, q.g.distY)));
-        sStep[kk] = f_mul(f_add(vwx, vwy), 0.5f);
-        sStep[q.nz + kk] = f_fma(q.g.volSq, u2f(k * k), f_fma(q.g.volLin, fk, q.g.volConst));
-    }
-    __syncthreads();
-
     // per-thread base pointers + one 32-bit running offset per array (a slab of one layer / one beam stays far below 2^32
     // elements): one IMAD.WIDE per access instead of 64-bit index chains
     const float* const weplP = wepl + (size_t)first * R + ray;
     const float* const densP = density + (size_t)first * R + ray;
-    float* const iddP = idd + (size_t)l * q.nz * R + ray;
-    float* const rsigP = rsig + (size_t)l * q.nz * R + ray;
-    float* const rowMinP = rowMin + ((size_t)l * q.nz * q.Ry + y) * (q.Rx / 32) + segX;
+    float* const iddP = idd + (size_t)l * nz * R + ray;
+    float* const rsigP = rsig + (size_t)l * nz * R + ray;
+    float* const rowMinP = rowMin + ((size_t)l * nz * q.Ry + y) * (q.Rx / 32) + segX;
     const unsigned rmStride = (unsigned)(q.Ry * (q.Rx / 32));
     unsigned off = 0, rmOff = 0;
     const int lane = threadIdx.x & 31;
-    // The depth scan is a dependent chain per ray, and with ~10 warps per scheduler the load -> texture -> arithmetic latency
-    // of one step is what a step costs. Software pipeline over two statically named slots (step s lives in slot s & 1, the
+    // The depth scan is a dependent chain per ray, and the load -> texture -> arithmetic latency of one step is what a step costs.
+    // Software pipeline over two statically named slots (step s lives in slot s & 1, the
     // loop is unrolled by two so that no register is rotated at the back edge - a rotating MOV would wait for the request
     // issued in the same iteration): at step k the slot of step k is copied out and re-used for the WEPL / density request
     // of step k + 2, and the two LUT fetches of step k + 1 (IDD at its WEPL, 1/X0 at its density) are issued from the other
@@ -348,6 +477,7 @@ idd_sigma_kernel(const float* __restrict__ density, const float* __restrict__ we
     auto step = [&](const unsigned k, float& wC, float& rhoC, const float& dC, const float& xC, const float& tC,
                     const float& wN, const float& rhoN, float& dN, float& xN, float& tN) {
         const float w = wC, rho = rhoC;
+        const float2 st = __ldg(stepTab + (k - first));          // 0.5 (vwx + vwy), stepVol of this step
         if (live && k + 1 < last) {
             dN = tex2D<float>(iddTex, f_fma(wN, lp.energyScale, 0.5f), eRow);
             xN = tex1D<float>(rrlTex, f_fma(rhoN, q.rrlScale, 0.5f));
@@ -366,11 +496,11 @@ idd_sigma_kernel(const float* __restrict__ density, const float* __restrict__ we
             } else {
                 sigmaSq = f_fma(f_mul(f_add(incScat, incDiv), -1.5f), rho, sigmaSq);
             }
-            rs = f_div(sStep[k - first], f_mul(f_add(f_sqrt(sigmaSq), 0.21f), 1.41421356f));
+            rs = f_div(st.x, f_mul(f_add(f_sqrt(sigmaSq), 0.21f), 1.41421356f));
             const bool within = !(w > thr);
             live = within && (k != afterLast);
             afterLast = within ? afterLast : k;
-            const float vol = sStep[q.nz + k - first];
+            const float vol = st.y;
             const float mass = q.doseToMedium ? f_mul(rho, vol) : f_mul(f_sub(w, wOld), vol);
             const float d = dC;
             if (mass > 1e-2f) res = f_div(f_mul(rayWeight, f_sub(d, dOld)), mass);
@@ -379,21 +509,23 @@ idd_sigma_kernel(const float* __restrict__ density, const float* __restrict__ we
         const bool keep = live && ((int)k >= firstIn - 1);
         res = keep ? res : 0.0f;
         rs = keep ? rs : inf;
-        iddP[off] = res;
-        rsigP[off] = rs;
         // row minimum of rSigmaEff for the tile radius; its sign carries "some voxel of this row has dose > 0"
         // (a tile without dose is skipped by the superposition exactly like the reference's __syncthreads_or, cuh:456)
         // rs is positive or +inf: its bit pattern orders like an unsigned integer -> one REDUX instead of 5 shuffle+min pairs
         const unsigned rsBits = __float_as_uint(rs);
         const float m = __any_sync(0xffffffffu, (int)rsBits < 0) ? warp_min(rs) : __uint_as_float(__reduce_min_sync(0xffffffffu, rsBits));
         const bool anyDose = __any_sync(0xffffffffu, res > 0.0f);
+        // A row segment without dose contributes nothing to the superposition whatever its sigma, and the tile radius needs only
+        // its minimum (rowMin): its 2 x 128 B are not written. If another row of the same 32 x 8 tile has dose at this step the
+        // superposition does read the segment - tile_radius_kernel, which looks at the tile's eight row minima anyway, then
+        // fills it with (0, +inf). On C3 this removes ~60 % of the kernel's HBM writes.
+        if (anyDose || q.writeAll) { iddP[off] = res; rsigP[off] = rs; }
         if (lane == 0) rowMinP[rmOff] = anyDose ? m : -m;
         off += (unsigned)R; rmOff += rmStride;
     };
     unsigned k = first;
     // a ray never comes back to life: once no lane of the warp is live (rays outside the field; every ray past its range)
-    // the rest of the row is "no dose, sigma undefined" - two thirds of all warp-steps on C3 - and is written by the
-    // minimal loop below instead of the full step
+    // the rest of the row is "no dose, sigma undefined": only its row minimum is written
     while (k < last && __any_sync(0xffffffffu, live)) {
         step(k, wS0, rhoS0, dS0, xS0, tS0, wS1, rhoS1, dS1, xS1, tS1);
         ++k;
@@ -401,12 +533,10 @@ idd_sigma_kernel(const float* __restrict__ density, const float* __restrict__ we
         step(k, wS1, rhoS1, dS1, xS1, tS1, wS0, rhoS0, dS0, xS0, tS0);
         ++k;
     }
-    for (; k < last; ++k) {
-        iddP[off] = 0.0f;
-        rsigP[off] = inf;
-        if (lane == 0) rowMinP[rmOff] = -inf;
-        off += (unsigned)R; rmOff += rmStride;
+    if (q.writeAll) {
+        for (unsigned kk = k; kk < last; ++kk) { iddP[off + (kk - k) * (unsigned)R] = 0.0f; rsigP[off + (kk - k) * (unsigned)R] = inf; }
     }
+    for (unsigned kk = k + lane; kk < last; kk += 32) rowMinP[rmOff + (kk - k) * rmStride] = -inf;
     firstPassive[(size_t)l * R + ray] = (int)afterLast;
     const int wm = warp_max_i((int)afterLast);
     if (lane == 0) atomicMax(layerFirstPassive + l, wm);
@@ -414,15 +544,20 @@ idd_sigma_kernel(const float* __restrict__ density, const float* __restrict__ we
 
 // ---------------------------------------------------------------------------------------------------------
 // Tile radius (own radius of every live 32x8 tile) + per-layer 34-bin histogram. One thread per (tile, slice);
-// grid = (ceil(nz*tiles/256), L).
+// grid = (ceil(S*tiles/256), L): sized for the worst case, the beam's slice count comes from BeamDev.
+// Also completes the sparse output of idd_sigma_kernel: in a tile that has dose, the row segments that have none were not written
+// and get (0, +inf) here.
 __global__ void __launch_bounds__(256)
-tile_radius_kernel(const float* __restrict__ rowMin, const int* __restrict__ layerFirstPassive, const int first, const int nz,
-                   const int Rx, const int Ry, const float ksCutoff, uint8_t* __restrict__ radMap, int* __restrict__ hist) {
+tile_radius_kernel(const float* __restrict__ rowMin, const int* __restrict__ layerFirstPassive, const BeamDev* __restrict__ bd,
+                   const int Rx, const int Ry, const float ksCutoff, const int fillRows, uint8_t* __restrict__ radMap, int* __restrict__ hist,
+                   float* __restrict__ idd, float* __restrict__ rsig) {
     __shared__ int sHist[34];
+    const int nz = bd->nz, first = bd->bfi;
+    const int tilesX = Rx / 32, tilesY = Ry / 8, tiles = tilesX * tilesY;
+    if ((long long)blockIdx.x * 256 >= (long long)nz * tiles) return;        // block-uniform
     const int l = blockIdx.y;
     if (threadIdx.x < 34) sHist[threadIdx.x] = 0;
     __syncthreads();
-    const int tilesX = Rx / 32, tilesY = Ry / 8, tiles = tilesX * tilesY;
     const int nLive = min(max(layerFirstPassive[l] - first, 0), nz);
     const int idx = blockIdx.x * 256 + threadIdx.x;
     if (idx < nz * tiles) {
@@ -430,14 +565,29 @@ tile_radius_kernel(const float* __restrict__ rowMin, const int* __restrict__ lay
         uint8_t r8 = 255;
         if (kk < nLive) {
             const float* p = rowMin + (((size_t)l * nz + kk) * Ry + ty * 8) * tilesX + tx;
-            float m = fabsf(p[0]);
-            bool anyDose = p[0] > 0.0f;
+            float v[8];
 #pragma unroll
-            for (int i = 1; i < 8; ++i) { const float v = p[(size_t)i * tilesX]; anyDose |= v > 0.0f; if (fabsf(v) < m) m = fabsf(v); }
+            for (int i = 0; i < 8; ++i) v[i] = p[(size_t)i * tilesX];
+            float m = fabsf(v[0]);
+            bool anyDose = v[0] > 0.0f;
+#pragma unroll
+            for (int i = 1; i < 8; ++i) { anyDose |= v[i] > 0.0f; if (fabsf(v[i]) < m) m = fabsf(v[i]); }
             // kernel_wrapper.cuh:303
             const unsigned rad = min((unsigned)f_toint_rz(f_add(f_div(ksCutoff, f_mul(f_sqrt(2.0f), m)), 0.5f)), 33u);
             r8 = anyDose ? (uint8_t)rad : (uint8_t)254;   // 254: live tile (counted in the histogram) that deposits nothing
             atomicAdd(&sHist[rad], 1);
+            if (anyDose && fillRows) {
+                const float inf = __int_as_float(0x7f800000);
+                const size_t base = ((size_t)l * nz + kk) * ((size_t)Rx * Ry) + (size_t)(ty * 8) * Rx + tx * 32;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    if (v[i] > 0.0f) continue;
+                    float4* a = reinterpret_cast<float4*>(idd + base + (size_t)i * Rx);
+                    float4* b = reinterpret_cast<float4*>(rsig + base + (size_t)i * Rx);
+#pragma unroll
+                    for (int c = 0; c < 8; ++c) { a[c] = make_float4(0.0f, 0.0f, 0.0f, 0.0f); b[c] = make_float4(inf, inf, inf, inf); }
+                }
+            }
         }
         radMap[((size_t)l * nz + kk) * tiles + t] = r8;
     }
@@ -480,10 +630,11 @@ __global__ void batch_kernel(const int* __restrict__ hist, const int L, const in
 // Items (slice, tile) that have at least one layer with an applied radius above 16: the work list of ks2_kernel<32, .>,
 // which runs only 3 warps per SM and must not spend them scanning the whole beam. Deepest slices first.
 __global__ void __launch_bounds__(256)
-big_items_kernel(const uint8_t* __restrict__ radMap, const int* __restrict__ batchRad, const int L, const int nz, const int tiles,
+big_items_kernel(const uint8_t* __restrict__ radMap, const int* __restrict__ batchRad, const int L, const BeamDev* __restrict__ bd, const int tiles,
                  const int* __restrict__ bigTiles /* batch_kernel's offset of radius 16 = tiles with a larger applied radius */,
                  int* __restrict__ count, uint32_t* __restrict__ items) {
     if (*bigTiles == 0) return;                       // shallow target: nothing to list
+    const int nz = bd->nz;
     const int t = blockIdx.x * 256 + threadIdx.x;
     const int nItems = nz * tiles;
     if (t >= nItems) return;
@@ -503,13 +654,6 @@ big_items_kernel(const uint8_t* __restrict__ radMap, const int* __restrict__ bat
 // with tools/texprobe (profiles/r01_texture_filter_model.md): per axis q = floor((c-0.5)*256+0.5), texel q>>8,
 // fraction q&255; eight INTEGER weights summing to 256 split z -> x -> y with round-half-up on the "+1" branch and
 // round-half-down on the x0 branch's y split; texels outside [first, zEnd) x [0,H) x [0,W) read 0 (border mode).
-struct GridParams {
-    TransferParams t;
-    int minX, minY, minZ, maxX, maxY, maxZ;   // inclusive bbox in dose indices
-    int nx, ny, nz;                           // dose dims
-    int W, H, first, zEnd;                    // BEV dims (haloed) and valid slice range [first, zEnd)
-    int atomic;                               // 1: red.global.add.f32 (the dose grid is shared by several GPUs over NVLink)
-};
 
 __device__ __forceinline__ int tex_q(float c) {   // fixed-point texel coordinate, 8 fractional bits
     return __float2int_rd(fmaf(c - 0.5f, 256.0f, 0.5f));
@@ -528,45 +672,63 @@ __device__ __forceinline__ float bev_plane(const float* __restrict__ pl, const G
     return fmaf((float)(x0 - w01), v00, fmaf((float)(x1 - w11), v10, fmaf((float)w01, v01, (float)w11 * v11)));
 }
 
+// Clears the slices [bfi, Zg) of the haloed BEV dose (the only ones the superposition writes and the transfer reads).
 __global__ void __launch_bounds__(256)
-bev_to_grid_kernel(const float* __restrict__ bev, float* __restrict__ dose, const GridParams g, unsigned long long* __restrict__ modified) {
-    const int x = g.minX + blockIdx.x * 32 + (threadIdx.x & 31);
-    const int y = g.minY + blockIdx.y * 8 + (threadIdx.x >> 5);
-    if (y >= g.ny) return;               // warp-uniform (a warp is one row of 32 x)
-    const bool inside = x < g.nx;
+bev_zero_kernel(float* __restrict__ bev, const BeamDev* __restrict__ bd, const int planeFloats /* (Rx + 64)(Ry + 64), a multiple of 4 */) {
+    const int nz = bd->nz;
+    if (nz <= 0) return;
+    float4* p = reinterpret_cast<float4*>(bev + (size_t)bd->bfi * planeFloats);
+    const size_t n4 = (size_t)nz * (planeFloats / 4);
+    for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += (size_t)gridDim.x * 256) p[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+}
+
+// Persistent: the grid is sized from the machine, the work units (32 x 8 dose columns x one chunk of the box's z range) from the
+// transfer box in BeamDev, which only the device knows when the kernel is launched.
+__global__ void __launch_bounds__(256)
+bev_to_grid_kernel(const float* __restrict__ bev, float* __restrict__ dose, const BeamDev* __restrict__ bd, unsigned long long* __restrict__ modified) {
+    __shared__ GridParams sg;
+    if (threadIdx.x < sizeof(GridParams) / 4) reinterpret_cast<int*>(&sg)[threadIdx.x] = reinterpret_cast<const int*>(&bd->grid)[threadIdx.x];
+    __syncthreads();
+    const GridParams& g = sg;
+    const int nUnits = g.tilesX * g.tilesY * g.zChunks;
     unsigned nMod = 0;
-    // init(i,j) (transfer_param_struct_div3.cu:22-25)
-    const float fi = i2f(x), fj = i2f(y);
-    const float sx = f_add(f_fma(g.t.coefIdxI.x, fi, f_mul(g.t.coefIdxJ.x, fj)), g.t.coefOffset.x);
-    const float sy = f_add(f_fma(g.t.coefIdxI.y, fi, f_mul(g.t.coefIdxJ.y, fj)), g.t.coefOffset.y);
-    const float sz = f_add(f_fma(g.t.coefIdxI.z, fi, f_mul(g.t.coefIdxJ.z, fj)), g.t.coefOffset.z);
-    // blockIdx.z splits the z range so that a box of a few hundred (x, y) tiles still fills the machine
-    const int zPer = (g.maxZ - g.minZ + (int)gridDim.z) / (int)gridDim.z;
-    const int zBeg = g.minZ + (int)blockIdx.z * zPer, zEnd = min(zBeg + zPer - 1, g.maxZ);
-    float* res = dose + ((size_t)zBeg * g.ny + y) * g.nx + x;
     const size_t zs = (size_t)g.nx * g.ny;
     const size_t plane = (size_t)g.W * g.H;
     const int D = g.zEnd - g.first;
     const float* base = bev + (size_t)g.first * plane;
-    for (int z = inside ? zBeg : zEnd + 1; z <= zEnd; ++z, res += zs) {
-        // getFanIdx(k) (cu:27-34) + HALF
-        const float fk = i2f(z);
-        const float rx = f_fma(g.t.inc.x, fk, sx), ry = f_fma(g.t.inc.y, fk, sy), rz = f_fma(g.t.inc.z, fk, sz);
-        const float mx = f_add(f_div(rz, f_sub(g.t.normDistX, rz)), 1.0f);
-        const float my = f_add(f_div(rz, f_sub(g.t.normDistY, rz)), 1.0f);
-        const float cx = f_add(f_fma(rx, mx, g.t.globalOffset.x), 0.5f);
-        const float cy = f_add(f_fma(ry, my, g.t.globalOffset.y), 0.5f);
-        const float cz = f_add(f_add(rz, g.t.globalOffset.z), 0.5f);
-        // coarse reject (also keeps the fixed-point conversion in range)
-        if (!(cx > -1.0f && cy > -1.0f && cz > -1.0f && cx < (float)(g.W + 1) && cy < (float)(g.H + 1) && cz < (float)(D + 1))) continue;
-        const int qx = tex_q(cx), qy = tex_q(cy), qz = tex_q(cz);
-        const int ix = qx >> 8, iy = qy >> 8, iz = qz >> 8;
-        const int a = qx & 255, b = qy & 255, c = qz & 255;
-        float acc = 0.0f;
-        if ((unsigned)iz < (unsigned)D && c != 256) acc = bev_plane(base + (size_t)iz * plane, g, ix, iy, a, b, 256 - c);
-        if ((unsigned)(iz + 1) < (unsigned)D && c != 0) acc += bev_plane(base + (size_t)(iz + 1) * plane, g, ix, iy, a, b, c);
-        const float v = acc * (1.0f / 256.0f);
-        if (v > 0.0f) { if (g.atomic) atomicAdd(res, v); else *res += v; ++nMod; }
+    const int zPer = g.zChunks > 0 ? (g.maxZ - g.minZ + g.zChunks) / g.zChunks : 0;
+    for (int unit = blockIdx.x; unit < nUnits; unit += gridDim.x) {
+        const int bz = unit / (g.tilesX * g.tilesY), rem = unit - bz * (g.tilesX * g.tilesY), by = rem / g.tilesX, bx = rem - by * g.tilesX;
+        const int x = g.minX + bx * 32 + (threadIdx.x & 31);
+        const int y = g.minY + by * 8 + (threadIdx.x >> 5);
+        if (y >= g.ny || x >= g.nx) continue;
+        // init(i,j) (transfer_param_struct_div3.cu:22-25)
+        const float fi = i2f(x), fj = i2f(y);
+        const float sx = f_add(f_fma(g.t.coefIdxI.x, fi, f_mul(g.t.coefIdxJ.x, fj)), g.t.coefOffset.x);
+        const float sy = f_add(f_fma(g.t.coefIdxI.y, fi, f_mul(g.t.coefIdxJ.y, fj)), g.t.coefOffset.y);
+        const float sz = f_add(f_fma(g.t.coefIdxI.z, fi, f_mul(g.t.coefIdxJ.z, fj)), g.t.coefOffset.z);
+        const int zBeg = g.minZ + bz * zPer, zEnd = min(zBeg + zPer - 1, g.maxZ);
+        float* res = dose + ((size_t)zBeg * g.ny + y) * g.nx + x;
+        for (int z = zBeg; z <= zEnd; ++z, res += zs) {
+            // getFanIdx(k) (cu:27-34) + HALF
+            const float fk = i2f(z);
+            const float rx = f_fma(g.t.inc.x, fk, sx), ry = f_fma(g.t.inc.y, fk, sy), rz = f_fma(g.t.inc.z, fk, sz);
+            const float mx = f_add(f_div(rz, f_sub(g.t.normDistX, rz)), 1.0f);
+            const float my = f_add(f_div(rz, f_sub(g.t.normDistY, rz)), 1.0f);
+            const float cx = f_add(f_fma(rx, mx, g.t.globalOffset.x), 0.5f);
+            const float cy = f_add(f_fma(ry, my, g.t.globalOffset.y), 0.5f);
+            const float cz = f_add(f_add(rz, g.t.globalOffset.z), 0.5f);
+            // coarse reject (also keeps the fixed-point conversion in range)
+            if (!(cx > -1.0f && cy > -1.0f && cz > -1.0f && cx < (float)(g.W + 1) && cy < (float)(g.H + 1) && cz < (float)(D + 1))) continue;
+            const int qx = tex_q(cx), qy = tex_q(cy), qz = tex_q(cz);
+            const int ix = qx >> 8, iy = qy >> 8, iz = qz >> 8;
+            const int a = qx & 255, b = qy & 255, c = qz & 255;
+            float acc = 0.0f;
+            if ((unsigned)iz < (unsigned)D && c != 256) acc = bev_plane(base + (size_t)iz * plane, g, ix, iy, a, b, 256 - c);
+            if ((unsigned)(iz + 1) < (unsigned)D && c != 0) acc += bev_plane(base + (size_t)(iz + 1) * plane, g, ix, iy, a, b, c);
+            const float v = acc * (1.0f / 256.0f);
+            if (v > 0.0f) { if (g.atomic) atomicAdd(res, v); else *res += v; ++nMod; }
+        }
     }
     // voxels modified by this launch (the bytes a host-resident dose grid exchanges over PCIe): one atomic per warp
     if (modified) {

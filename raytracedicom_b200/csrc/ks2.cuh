@@ -18,6 +18,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include "kernels.cuh"
 
 namespace rtd {
 
@@ -26,7 +27,8 @@ struct Ks2Params {
     const int* batchRad;            // [L][34] radius applied to a tile of own radius r
     const uint8_t* radMap;          // [L][nz][tiles] own radius, 255 = not live
     const int* layerFirstPassive;   // [L]
-    int L, Rx, Ry, nz, first, tilesX, tiles;
+    const BeamDev* bd;              // slices per layer (nz) and first slice (bfi): known to the device only (beam_setup_kernel)
+    int L, Rx, Ry, tilesX, tiles;
     const int* bigCount; const uint32_t* bigItems;   // items with a layer of applied radius > 16 (big_items_kernel)
     int bodyStep;                   // 1, 2 or 4: radii <= 16 run in the unrolled body of the next multiple (see ks2_kernel);
                                     // 0 = 2 if the beam has items with a radius > 16 (*bigCount > 0), else 1
@@ -257,8 +259,10 @@ ks2_kernel(const Ks2Params p, int* __restrict__ workCounter, int* __restrict__ i
     // The RBMAX = 24 / 32 kernels run only 5 / 3 warps per SM: they walk the list of items that have a layer with radius > 16
     // (big_items_kernel) instead of scanning the whole beam; the list is empty for shallow targets.
     constexpr int NCH = 1;
+    const int nz = p.bd->nz, first = p.bd->bfi;
+    if (nz <= 0) return;
     const int nBig = *p.bigCount;
-    const int nItems = BIG ? nBig : p.nz * p.tiles;
+    const int nItems = BIG ? nBig : nz * p.tiles;
     // Beams that reach radii > 16 spread their layers over many different radii: the per-radius bodies (~108 KB of code in
     // the RBMAX = 16 kernel) then miss the instruction caches, and running odd radii in the next even body pays
     // (C4 superposition 15.7 -> 13.3 ms); beams that stay <= 16 are better off with the exact body (C3 1.14 vs 1.16 ms).
@@ -278,8 +282,8 @@ ks2_kernel(const Ks2Params p, int* __restrict__ workCounter, int* __restrict__ i
         for (int l0 = 0; l0 < p.L; l0 += 32) {
             const int l = l0 + lane;
             int rb = -1;
-            if (l < p.L && kk < p.layerFirstPassive[l] - p.first) {
-                const unsigned own = p.radMap[((size_t)l * p.nz + kk) * p.tiles + tile];
+            if (l < p.L && kk < p.layerFirstPassive[l] - first) {
+                const unsigned own = p.radMap[((size_t)l * nz + kk) * p.tiles + tile];
                 if (own <= 32u) { rb = p.batchRad[l * 34 + own]; if (rb > KS2_MAXRB || (BIG ? rb <= 16 : rb > 16)) rb = -1; }   // > 32 is reported as an error by the host
             }
             const unsigned m = __ballot_sync(0xffffffffu, rb >= 0);
@@ -302,7 +306,7 @@ ks2_kernel(const Ks2Params p, int* __restrict__ workCounter, int* __restrict__ i
         __syncwarp();
         const int tx = tile % p.tilesX, ty = tile / p.tilesX;
         const size_t tileOff = (size_t)kk * R + (size_t)(ty * 8) * p.Rx + tx * 32 + lane;
-        const size_t layerStride = (size_t)p.nz * R;
+        const size_t layerStride = (size_t)nz * R;
         // the next layer's 16 row segments are requested into L2 while the current layer is processed (a register prefetch would
         // cost 16 of the 255 registers the packed FMA block needs: ptxas then re-creates its operand pairs with MOVs)
         auto prefetchLayer = [&](const int q) {       // called by lanes 0..3: lane -> sector lane of each 128-byte row segment
@@ -374,7 +378,7 @@ ks2_kernel(const Ks2Params p, int* __restrict__ workCounter, int* __restrict__ i
         // group of 4 columns: lanes 0..15 / 16..31 = 16 consecutive rows of two adjacent groups, so that the four scalar reads are
         // conflict-free (consecutive rows of one patch column) and the two groups of a row fill one 32-byte sector of the BEV;
         // RBMAX, the BEV pitch and the tile origin are multiples of 4, so every group is 16-byte aligned: red.global.add.v4.f32
-        float* out = p.bev + ((size_t)(kk + p.first) * (p.Ry + 64) + (ty * 8 + 32 - RBMAX)) * bevPitch + tx * 32 + 32 - RBMAX;
+        float* out = p.bev + ((size_t)(kk + first) * (p.Ry + 64) + (ty * 8 + 32 - RBMAX)) * bevPitch + tx * 32 + 32 - RBMAX;
         for (int r0 = c0; r0 < c0 + nr; r0 += 16) {
             const int pr = r0 + (lane & 15);
             for (int g0 = cz0; g0 < cz0 + ncz; g0 += 8) {

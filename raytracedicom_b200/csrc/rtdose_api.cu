@@ -18,8 +18,10 @@ namespace {
 
 struct DevBuf {
     void* p = nullptr; size_t cap = 0;
+    static long& reallocs() { static long n = 0; return n; }      // any growth invalidates captured launch sequences
     cudaError_t ensure(size_t bytes) {
         if (bytes <= cap) return cudaSuccess;
+        ++reallocs();
         if (p) { cudaError_t e = cudaFree(p); if (e != cudaSuccess) return e; p = nullptr; cap = 0; }
         size_t want = bytes + bytes / 8;
         cudaError_t e = cudaMalloc(&p, want);
@@ -62,26 +64,28 @@ struct HostIo {
 };
 
 struct BeamWs {
-    // geometry / host results
+    // geometry (host, before anything runs)
     RayGrid grid; int S = 0, L = 0, R = 0, sx = 0, sy = 0;
     int l0 = 0, Lc = 0;   // computed layer range [l0, l0+Lc) of the beam's L layers (rtd_beam.layerBegin/End)
     float dist[2]; Affine gtii, gtdi;
+    std::vector<LayerIn> lin;             // [Lc]
+    // results of the device-side set-up (beam_setup_kernel), on the host after the final sync of the call
     int bfi = 0, bfo = 0, Zg = 0, nz = 0; bool live = false;
     float entryZ = 0;
-    GridParams gp; bool doTransfer = false; dim3 gpGrid;
-    std::vector<LayerParams> layers; std::vector<float> entrySig;   // [2L]
+    BeamDev hostDev;
     rtd_beam_report rep; std::vector<rtd_layer_report> lrep;
     // device
-    DevBuf density, wepl, firstIn, firstOut, weplMin, scalars, spotW, sigmas, rayW, layerDev, idd, rsig, rowMin,
-           firstPassive, lfp, hist, batchRad, rbOffset, rbCursor, stats, work, radMap, list, bev;
-    PinBuf hTrace;   // [2 ints][S floats]
-    PinBuf hStage;   // staging for sigmas + LayerParams uploads and weights
-    PinBuf hOut;     // lfp[L], hist[L*34], batchRad[L*34], stats[4]
+    DevBuf density, wepl, firstIn, firstOut, weplMin, spotW, sigmas, rayW, layerIn, layerDev, beamDev, stepTab, idd, rsig, rowMin,
+           firstPassive, lfp, batchRad, rbOffset, radMap, list, bev;
+    PinBuf hStage;   // staging of the uploads: spot weights | LayerIn[Lc]
+    PinBuf hOut;     // BeamDev | LayerParams[Lc] | entry sigmas[Lc] | control block | batchRad[Lc*34]
+    size_t ctlInts() const { return size_t(Lc) + size_t(Lc) * 34 + 33 + 4 + 4 + 4; }   // lfp[L] | hist[L*34] | bigCursor[33] | stats[4] | work[4] | ksItems[4]
+    size_t outCtlOff() const { return (sizeof(BeamDev) + size_t(Lc) * (sizeof(LayerParams) + sizeof(float2)) + 15) / 16 * 16; }
     void release() {
-        DevBuf* all[] = {&density, &wepl, &firstIn, &firstOut, &weplMin, &scalars, &spotW, &sigmas, &rayW, &layerDev, &idd, &rsig,
-                         &rowMin, &firstPassive, &lfp, &hist, &batchRad, &rbOffset, &rbCursor, &stats, &work, &radMap, &list, &bev};
+        DevBuf* all[] = {&density, &wepl, &firstIn, &firstOut, &weplMin, &spotW, &sigmas, &rayW, &layerIn, &layerDev, &beamDev, &stepTab, &idd, &rsig,
+                         &rowMin, &firstPassive, &lfp, &batchRad, &rbOffset, &radMap, &list, &bev};
         for (DevBuf* b : all) b->release();
-        hTrace.release(); hStage.release(); hOut.release();
+        hStage.release(); hOut.release();
     }
 };
 
@@ -293,10 +297,11 @@ void ctBoxesOfBeam(const TraceParams& p, int Rx, int Ry, int S, const int dims[3
 // one texel of the haloed BEV volume [-32, Rx+32) x [-32, Ry+32) x [bfi, Zg) (trilinear, border 0), clipped to the
 // kernel's own coverage. fromFan is affine in each fan index separately -> corners suffice.
 void doseBoxesOfBeam(const BeamWs& w, const int dims[3], std::vector<Box>& out) {
-    const GridParams& g = w.gp;
+    const GridParams& g = w.hostDev.grid;
+    if (g.zChunks <= 0) return;
     Box cover;
-    cover.lo[0] = g.minX; cover.hi[0] = std::min(g.minX + int(w.gpGrid.x) * 32 - 1, g.nx - 1);
-    cover.lo[1] = g.minY; cover.hi[1] = std::min(g.minY + int(w.gpGrid.y) * 8 - 1, g.ny - 1);
+    cover.lo[0] = g.minX; cover.hi[0] = std::min(g.minX + g.tilesX * 32 - 1, g.nx - 1);
+    cover.lo[1] = g.minY; cover.hi[1] = std::min(g.minY + g.tilesY * 8 - 1, g.ny - 1);
     cover.lo[2] = g.minZ; cover.hi[2] = g.maxZ;
     const int Rx = w.grid.dimX, Ry = w.grid.dimY;
     const int segLen = 48;
@@ -384,42 +389,83 @@ const char* validateBeam(const rtd_beam& b, const rtd_opts& o) {
     return nullptr;
 }
 
-// Everything that can be done for a beam before any device result is known (cu:612-663, 766-790).
-rtd_status beamPhaseA(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opts& o, int& launches, cudaStream_t st, HostIo* io, cudaEvent_t evCt) {
+constexpr size_t EV_BEAM0 = 8, EV_PER_BEAM = 12;   // events 0..7 are per call; per beam: 0 begin, 1 traced, 2 set up, 3 conv, 4 idd, 5 radius, 6 superp, 7 transfer, 8 done, 9 CT uploaded, 10 BeamDev on the host
+cudaEvent_t evBeam(rtd_ctx* ctx, int b, int i) { return ev(ctx, EV_BEAM0 + size_t(b) * EV_PER_BEAM + i); }
+
+// Part 1 of a beam, everything up to the superposition: launched without knowing any device result (cu:612-1100). The grids
+// depend on the geometry alone; cut-offs, slice counts and the transfer box live in BeamDev (beam_setup_kernel).
+rtd_status beamEnqueue(rtd_ctx* ctx, int beamNo, const rtd_beam& b, BeamWs& w, const rtd_opts& o, int& launches, cudaStream_t st, HostIo* io) {
     float mx = b.sigmas[0], my = b.sigmas[1];
     for (int l = 1; l < b.nLayers; ++l) { mx = std::max(mx, b.sigmas[2 * l]); my = std::max(my, b.sigmas[2 * l + 1]); }
     w.grid = makeRayGrid(b.spotDelta, b.spotOffset, b.sx, b.sy, b.raySpacing, mx, my, o.convSigmaCutoff);
     if (w.grid.dimX <= 0 || w.grid.dimY <= 0) return fail(ctx, RTD_ERR_INVALID, "empty ray grid");
     w.S = (int)b.steps; w.L = b.nLayers; w.R = w.grid.dimX * w.grid.dimY; w.sx = b.sx; w.sy = b.sy;
     if (b.layerBegin == 0 && b.layerEnd == 0) { w.l0 = 0; w.Lc = b.nLayers; }
-    else {
-        if (b.layerBegin < 0 || b.layerEnd > b.nLayers || b.layerBegin >= b.layerEnd) return fail(ctx, RTD_ERR_INVALID, "beam.layerBegin/layerEnd out of range");
-        w.l0 = b.layerBegin; w.Lc = b.layerEnd - b.layerBegin;
-    }
+    else { w.l0 = b.layerBegin; w.Lc = b.layerEnd - b.layerBegin; }
     if ((w.grid.dimX / 32) * (w.grid.dimY / 8) > 4095) return fail(ctx, RTD_ERR_INVALID, "ray grid has more than 4095 tiles");
     w.dist[0] = b.sourceDist[0]; w.dist[1] = b.sourceDist[1];
     w.gtii.m = m3(b.gantryToImIdxM); w.gtii.v = v3(b.gantryToImIdxV[0], b.gantryToImIdxV[1], b.gantryToImIdxV[2]);
     w.gtdi.m = m3(b.gantryToDoseIdxM); w.gtdi.v = v3(b.gantryToDoseIdxV[0], b.gantryToDoseIdxV[1], b.gantryToDoseIdxV[2]);
-    const size_t RS = size_t(w.R) * w.S;
+    const int Rx = w.grid.dimX, Ry = w.grid.dimY, R = w.R, S = w.S, L = w.Lc;
+    const int tilesX = Rx / 32, tilesY = Ry / 8, tiles = tilesX * tilesY;
+
+    // ---- workspace, sized for the worst case (every step of the tracer live): nothing here depends on a device result
+    const size_t RS = size_t(R) * S, LSR = size_t(L) * S * R;
     RTD_CUDA(w.density.ensure(RS * 4)); RTD_CUDA(w.wepl.ensure(RS * 4));
-    RTD_CUDA(w.firstIn.ensure(size_t(w.R) * 4)); RTD_CUDA(w.firstOut.ensure(size_t(w.R) * 4));
-    RTD_CUDA(w.weplMin.ensure(size_t(w.S) * 4 + 8)); RTD_CUDA(w.hTrace.ensure(size_t(w.S) * 4 + 8));
-    const size_t nW = size_t(b.sx) * b.sy * w.Lc;
-    RTD_CUDA(w.spotW.ensure(nW * 4)); RTD_CUDA(w.hStage.ensure(nW * 4 + size_t(w.Lc) * (8 + sizeof(LayerParams))));
+    RTD_CUDA(w.firstIn.ensure(size_t(R) * 4)); RTD_CUDA(w.firstOut.ensure(size_t(R) * 4));
+    RTD_CUDA(w.weplMin.ensure(size_t(S) * 4 + 8));
+    const size_t nW = size_t(b.sx) * b.sy * L;
+    RTD_CUDA(w.spotW.ensure(nW * 4)); RTD_CUDA(w.hStage.ensure(nW * 4 + size_t(L) * sizeof(LayerIn) + 16));
+    RTD_CUDA(w.sigmas.ensure(size_t(L) * 8)); RTD_CUDA(w.layerIn.ensure(size_t(L) * sizeof(LayerIn))); RTD_CUDA(w.layerDev.ensure(size_t(L) * sizeof(LayerParams)));
+    RTD_CUDA(w.beamDev.ensure(sizeof(BeamDev))); RTD_CUDA(w.stepTab.ensure(size_t(S) * 8));
+    RTD_CUDA(w.rayW.ensure(size_t(L) * R * 4));
+    RTD_CUDA(w.idd.ensure(LSR * 4)); RTD_CUDA(w.rsig.ensure(LSR * 4));
+    RTD_CUDA(w.rowMin.ensure(size_t(L) * S * Ry * tilesX * 4));
+    RTD_CUDA(w.firstPassive.ensure(size_t(L) * R * 4));
+    const size_t ctlInts = w.ctlInts();
+    RTD_CUDA(w.lfp.ensure(ctlInts * 4));
+    RTD_CUDA(w.batchRad.ensure(size_t(L) * 34 * 4)); RTD_CUDA(w.rbOffset.ensure(33 * 4));
+    RTD_CUDA(w.radMap.ensure(size_t(L) * S * tiles)); RTD_CUDA(w.list.ensure(size_t(S) * tiles * 4));
+    const int planeFloats = (Ry + 64) * (Rx + 64);
+    RTD_CUDA(w.bev.ensure(size_t(S) * planeFloats * 4));
+    RTD_CUDA(w.hOut.ensure(w.outCtlOff() + (ctlInts + size_t(L) * 34) * 4));
+
+    // ---- host part of the per-layer parameters (cu:829-838): needs the LUTs only
+    const float* E = ctx->energies.data(); const int nE = ctx->nEnergies;
+    float maxEnergy = b.energies[0];
+    for (int l = 1; l < w.L; ++l) maxEnergy = std::max(maxEnergy, b.energies[l]);
+    const float maxPeakDepth = vectorInterpolate(ctx->peakDepths.data(), nE, findDecimalOrdered(E, nE, maxEnergy));
+    w.lin.resize(L);
+    for (int l = 0; l < L; ++l) {
+        const int al = w.l0 + l;   // absolute layer number in the beam
+        LayerIn& li = w.lin[l];
+        li.energyIdx = findDecimalOrdered(E, nE, b.energies[al]);
+        li.energyScale = vectorInterpolate(ctx->scaleFacts.data(), nE, li.energyIdx);
+        li.peakDepth = vectorInterpolate(ctx->peakDepths.data(), nE, li.energyIdx);
+        li.thr = o.bpDepthCutoff * li.peakDepth;
+        sigmaSqAirCoefsHost(li.peakDepth, !o.noNozzle, li.ca, li.cb);
+        li.sigX = b.sigmas[2 * al]; li.sigY = b.sigmas[2 * al + 1];
+    }
     memcpy(w.hStage.p, b.weights + size_t(b.sx) * b.sy * w.l0, nW * 4);
+    char* stLin = w.hStage.as<char>() + (nW * 4 + 15) / 16 * 16;
+    memcpy(stLin, w.lin.data(), size_t(L) * sizeof(LayerIn));
+
+    RTD_CUDA(cudaEventRecord(evBeam(ctx, beamNo, 0), st));
     RTD_CUDA(cudaMemcpyAsync(w.spotW.p, w.hStage.p, nW * 4, cudaMemcpyHostToDevice, st));
+    RTD_CUDA(cudaMemcpyAsync(w.layerIn.p, stLin, size_t(L) * sizeof(LayerIn), cudaMemcpyHostToDevice, st));
+    RTD_CUDA(cudaMemsetAsync(w.lfp.p, 0, ctlInts * 4, st));
     const TraceParams tp = makeTraceParams(ctx->densScale, ctx->spScale, b.steps, w.grid.rayIdxToGantry, w.dist, w.gtii);
     if (io && io->ct) {
         // one-call host path: upload the CT sub-volumes this beam's tracer samples (copy stream), then let the beam's stream go
+        cudaEvent_t evCt = evBeam(ctx, beamNo, 9);
         if (io->ctMapped) {
             // page-locked CT: the GPU pulls, per CT row, the x interval this beam's tracer can touch and that is not resident yet
             const int rows = ctx->ctDims[1] * ctx->ctDims[2];
             int* need = ctx->ctRows.as<int>();
             RTD_CUDA(cudaMemsetAsync(need, 0x7f, size_t(rows) * 4, ctx->cstream));            // needLo = "nothing"
             RTD_CUDA(cudaMemsetAsync(need + rows, 0xff, size_t(rows) * 4, ctx->cstream));     // needHi = -1
-            const int Rx = w.grid.dimX, Ry = w.grid.dimY;
-            const long long patches = 2LL * (Rx + Ry) * std::max(w.S - 1, 1) + 2LL * std::max(Rx - 1, 1) * std::max(Ry - 1, 1);
-            ct_mark_rows_kernel<<<(unsigned)((patches + 255) / 256), 256, 0, ctx->cstream>>>(tp, Rx, Ry, w.S, ctx->ctDims[0], ctx->ctDims[1], ctx->ctDims[2],
+            const long long patches = 2LL * (Rx + Ry) * std::max(S - 1, 1) + 2LL * std::max(Rx - 1, 1) * std::max(Ry - 1, 1);
+            ct_mark_rows_kernel<<<(unsigned)((patches + 255) / 256), 256, 0, ctx->cstream>>>(tp, Rx, Ry, S, ctx->ctDims[0], ctx->ctDims[1], ctx->ctDims[2],
                                                                                              need, need + rows);
             ct_pull_rows_kernel<<<(rows + 7) / 8, 256, 0, ctx->cstream>>>(io->ctMapped, ctx->ctTex.surf, ctx->ctDims[0], ctx->ctDims[1], ctx->ctDims[2],
                                                                           need, need + rows, need + 2 * rows, need + 3 * rows,
@@ -428,7 +474,7 @@ rtd_status beamPhaseA(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opts
             RTD_CUDA(cudaGetLastError());
         } else {
             const size_t n0 = ctx->ctBoxes.size();
-            ctBoxesOfBeam(tp, w.grid.dimX, w.grid.dimY, w.S, ctx->ctDims, ctx->ctBoxes);
+            ctBoxesOfBeam(tp, Rx, Ry, S, ctx->ctDims, ctx->ctBoxes);
             for (size_t i = n0; i < ctx->ctBoxes.size(); ++i) {
                 RTD_CUDA(copyCtBox(ctx, io->ct, ctx->ctBoxes[i], ctx->cstream));
                 io->h2d += boxVoxels(ctx->ctBoxes[i]) * 4;
@@ -437,200 +483,128 @@ rtd_status beamPhaseA(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opts
         RTD_CUDA(cudaEventRecord(evCt, ctx->cstream));
         RTD_CUDA(cudaStreamWaitEvent(st, evCt, 0));
     }
-    if (io) io->h2d += int64_t(nW) * 4;
-    // weplMin buffer layout: [0]=beamFirstInside, [1]=beamFirstOutside (ints), [2..] weplMin floats
+    if (io) io->h2d += int64_t(nW) * 4 + int64_t(L) * sizeof(LayerIn);
+
+    // K1 + reductions. weplMin buffer layout: [0] = beamFirstInside, [1] = beamFirstOutside (ints), [2..] weplMin floats
     int* sc = w.weplMin.as<int>();
-    trace_bev_kernel<<<w.R / 32, TR_THREADS, 0, st>>>(tp, ctx->ctTex.tex, ctx->densTex.tex, ctx->spTex.tex, ctx->densSpTex.tex,
-        w.density.as<float>(), w.wepl.as<float>(), w.firstIn.as<int>(), w.firstOut.as<int>(), w.grid.dimX, w.R);
-    slice_reduce_kernel<<<w.S, 256, 0, st>>>(w.wepl.as<float>(), w.firstIn.as<int>(), w.firstOut.as<int>(), w.R,
-        w.weplMin.as<float>() + 2, sc, sc + 1);
-    launches += 2;
-    RTD_CUDA(cudaGetLastError());
-    RTD_CUDA(cudaMemcpyAsync(w.hTrace.p, w.weplMin.p, size_t(w.S) * 4 + 8, cudaMemcpyDeviceToHost, st));
-    if (io) io->d2h += int64_t(w.S) * 4 + 8;
-    return RTD_OK;
-}
+    trace_bev_kernel<<<R / 32, TR_THREADS, 0, st>>>(tp, ctx->ctTex.tex, ctx->densTex.tex, ctx->spTex.tex, ctx->densSpTex.tex,
+        w.density.as<float>(), w.wepl.as<float>(), w.firstIn.as<int>(), w.firstOut.as<int>(), Rx, R);
+    slice_reduce_kernel<<<S, 256, 0, st>>>(w.wepl.as<float>(), w.firstIn.as<int>(), w.firstOut.as<int>(), R, w.weplMin.as<float>() + 2, sc, sc + 1);
+    RTD_CUDA(cudaEventRecord(evBeam(ctx, beamNo, 1), st));
 
-// Host logic that needs the tracer's reductions (cu:792-849, 922-925) + all remaining launches of the beam.
-rtd_status beamPhaseB1(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opts& o) {
-    const int* sc = w.hTrace.as<int>();
-    const float* weplMin = w.hTrace.as<float>() + 2;
-    w.bfi = sc[0]; w.bfo = sc[1];
-    const float rayResZ = w.grid.rayIdxToGantry.delta.z, rayOffZ = w.grid.rayIdxToGantry.offset.z;
-    w.entryZ = float(w.bfi) * rayResZ + rayOffZ;
-    float maxEnergy = b.energies[0];
-    for (int l = 1; l < w.L; ++l) maxEnergy = std::max(maxEnergy, b.energies[l]);
-    const float* E = ctx->energies.data(); const int nE = ctx->nEnergies;
-    const float maxEnergyIdx = findDecimalOrdered(E, nE, maxEnergy);
-    const float maxPeakDepth = vectorInterpolate(ctx->peakDepths.data(), nE, maxEnergyIdx);
-    const int firstPastCutoffAll = findFirstLargerOrdered(weplMin, w.S, o.bpDepthCutoff * maxPeakDepth);
-    w.Zg = std::min(firstPastCutoffAll, w.bfo);
-    w.nz = w.Zg - w.bfi;
-    w.live = w.nz > 0;
-    w.layers.resize(w.Lc); w.entrySig.resize(2 * size_t(w.Lc));
-    w.lrep.assign(w.L, rtd_layer_report());
-    memset(&w.rep, 0, sizeof w.rep);
-    w.rep.lSteps = w.grid.lSteps; w.rep.bSteps = w.grid.bSteps; w.rep.rSteps = w.grid.rSteps; w.rep.tSteps = w.grid.tSteps;
-    w.rep.rayDimX = w.grid.dimX; w.rep.rayDimY = w.grid.dimY; w.rep.steps = w.S; w.rep.nLayers = w.L;
-    w.rep.beamFirstInside = w.bfi; w.rep.beamFirstOutside = w.bfo; w.rep.beamFirstGuaranteedPassive = w.Zg; w.rep.entryZ = w.entryZ;
-    for (int l = 0; l < w.Lc; ++l) {
-        const int al = w.l0 + l;   // absolute layer number in the beam
-        LayerParams& lp = w.layers[l];
-        lp.energyIdx = findDecimalOrdered(E, nE, b.energies[al]);
-        lp.energyScale = vectorInterpolate(ctx->scaleFacts.data(), nE, lp.energyIdx);
-        lp.peakDepth = vectorInterpolate(ctx->peakDepths.data(), nE, lp.energyIdx);
-        float ca, cb; sigmaSqAirCoefsHost(lp.peakDepth, !o.noNozzle, ca, cb);
-        const float sxg = b.sigmas[2 * al], syg = b.sigmas[2 * al + 1], z = w.entryZ;
-        w.entrySig[2 * l] = sqrtf(ca * z * z + cb * z + sxg * sxg);
-        w.entrySig[2 * l + 1] = sqrtf(ca * z * z + cb * z + syg * syg);
-        const unsigned localAfterLast = (unsigned)findFirstLargerOrdered(weplMin, w.S, o.bpDepthCutoff * lp.peakDepth);
-        lp.afterLast = (int)std::min(localAfterLast, (unsigned)w.Zg);
-        rtd_layer_report& lr = w.lrep[al];
-        lr.energyIdx = lp.energyIdx; lr.energyScaleFact = lp.energyScale; lr.peakDepth = lp.peakDepth;
-        lr.entrySigmaX = w.entrySig[2 * l]; lr.entrySigmaY = w.entrySig[2 * l + 1]; lr.afterLastStep = lp.afterLast;
-    }
-    {   // launch order of the layers in the IDD / sigma kernel: longest depth scan first
-        std::vector<int> ord(w.Lc);
-        for (int l = 0; l < w.Lc; ++l) ord[l] = l;
-        std::stable_sort(ord.begin(), ord.end(), [&](int a, int c) { return w.layers[a].afterLast > w.layers[c].afterLast; });
-        for (int l = 0; l < w.Lc; ++l) w.layers[l].order = ord[l];
-    }
-    w.doTransfer = false;
-    if (!w.live) return RTD_OK;   // the beam never enters the patient: nothing to add
+    // per-beam set-up on the device (the host round trip of cu:781-849)
+    SetupIn in;
+    in.S = S; in.L = L;
+    in.rayResZ = w.grid.rayIdxToGantry.delta.z; in.rayOffZ = w.grid.rayIdxToGantry.offset.z;
+    in.distX = w.dist[0]; in.distY = w.dist[1]; in.rayDx = w.grid.rayIdxToGantry.delta.x; in.rayDy = w.grid.rayIdxToGantry.delta.y;
+    in.thrAll = o.bpDepthCutoff * maxPeakDepth;
+    in.fitf = w.grid.rayIdxToGantry; in.gtdi = w.gtdi; in.dist[0] = w.dist[0]; in.dist[1] = w.dist[1];
+    in.t0 = makeTransferParams(w.grid.rayIdxToGantry, w.dist, w.gtdi, v3(float(RTD_MAX_SUPERP_R), float(RTD_MAX_SUPERP_R), 0.0f));
+    in.ftfiOffZ = inverse(w.grid.rayIdxToGantry).offset.z;
+    in.Rx = Rx; in.Ry = Ry; in.nx = ctx->doseDims[0]; in.ny = ctx->doseDims[1]; in.nz = ctx->doseDims[2];
+    in.smCount = ctx->smCount; in.atomic = o.atomicDose ? 1 : 0;
+    in.g = makeFillGeom(w.grid.rayIdxToGantry, w.dist);
+    BeamDev* bd = w.beamDev.as<BeamDev>();
+    beam_setup_kernel<<<1, 256, 0, st>>>(in, sc, w.layerIn.as<LayerIn>(), bd, w.layerDev.as<LayerParams>(), w.sigmas.as<float2>(), w.stepTab.as<float2>());
+    // what the host wants to know about the set-up (reports; the dose boxes of a pageable host grid)
+    RTD_CUDA(cudaMemcpyAsync(w.hOut.p, w.beamDev.p, sizeof(BeamDev), cudaMemcpyDeviceToHost, st));
+    RTD_CUDA(cudaEventRecord(evBeam(ctx, beamNo, 10), st));
+    bev_zero_kernel<<<ctx->smCount * 4, 256, 0, st>>>(w.bev.as<float>(), bd, planeFloats);
+    RTD_CUDA(cudaEventRecord(evBeam(ctx, beamNo, 2), st));
 
-    // K4 box (cu:1185-1218); the z-range uses Zg instead of beamFirstCalculatedPassive: a superset box that only adds
-    // voxels whose interpolated BEV dose is exactly 0, so the result is identical and no host sync is needed here.
-    const int Rx = w.grid.dimX, Ry = w.grid.dimY;
-    const float xv[2] = {-float(RTD_MAX_SUPERP_R), float(Rx + RTD_MAX_SUPERP_R - 1)};
-    const float yv[2] = {-float(RTD_MAX_SUPERP_R), float(Ry + RTD_MAX_SUPERP_R - 1)};
-    const float zv[2] = {float(w.bfi), float(w.Zg - 1)};
-    V3 mx = v3(-1.f, -1.f, -1.f), mn = v3(100000.f, 100000.f, 100000.f);
-    for (int k = 0; k < 2; ++k) for (int j = 0; j < 2; ++j) for (int i = 0; i < 2; ++i) {
-        const V3 p = fromFan(w.grid.rayIdxToGantry, w.dist, w.gtdi, v3(xv[i], yv[j], zv[k]));
-        mx.x = std::max(mx.x, p.x); mx.y = std::max(mx.y, p.y); mx.z = std::max(mx.z, p.z);
-        mn.x = std::min(mn.x, p.x); mn.y = std::min(mn.y, p.y); mn.z = std::min(mn.z, p.z);
-    }
-    GridParams& gp = w.gp;
-    gp.t = makeTransferParams(w.grid.rayIdxToGantry, w.dist, w.gtdi, v3(float(RTD_MAX_SUPERP_R), float(RTD_MAX_SUPERP_R), -float(w.bfi)));
-    gp.minX = std::max((int(std::floor(mn.x)) / 32) * 32, 0); gp.minY = std::max(int(std::floor(mn.y)), 0); gp.minZ = std::max(int(std::floor(mn.z)), 0);
-    gp.maxX = std::min(int(std::ceil(mx.x)), ctx->doseDims[0] - 1); gp.maxY = std::min(int(std::ceil(mx.y)), ctx->doseDims[1] - 1);
-    gp.maxZ = std::min(int(std::ceil(mx.z)), ctx->doseDims[2] - 1);
-    gp.nx = ctx->doseDims[0]; gp.ny = ctx->doseDims[1]; gp.nz = ctx->doseDims[2];
-    gp.W = Rx + 64; gp.H = Ry + 64; gp.first = w.bfi; gp.zEnd = w.Zg; gp.atomic = o.atomicDose ? 1 : 0;
-    if (gp.maxX >= gp.minX && gp.maxY >= gp.minY && gp.maxZ >= gp.minZ) {
-        w.doTransfer = true;
-        w.gpGrid = dim3((gp.maxX - gp.minX + 32) / 32, (gp.maxY - gp.minY + 8) / 8);
-        const int tilesXY = int(w.gpGrid.x * w.gpGrid.y), nzBox = gp.maxZ - gp.minZ + 1;
-        w.gpGrid.z = unsigned(std::max(1, std::min({(8 * ctx->smCount + tilesXY - 1) / tilesXY, nzBox, 64})));   // ~8 CTAs per SM
-    }
-    return RTD_OK;
-}
-
-// All remaining launches of the beam.
-rtd_status beamPhaseB2(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opts& o, float* dDose, int& launches,
-                       cudaEvent_t* evs /*6 events: conv, idd, radius, superp, transfer, end*/, cudaStream_t strm, HostIo* io,
-                       cudaEvent_t evDoseIn, bool& doseInWaited) {
-    if (!w.live) return RTD_OK;
-    const int Rx = w.grid.dimX, Ry = w.grid.dimY, R = w.R, L = w.Lc, nz = w.nz;
-    const int tilesX = Rx / 32, tilesY = Ry / 8, tiles = tilesX * tilesY;
-    const size_t LnzR = size_t(L) * nz * R;
-    RTD_CUDA(w.sigmas.ensure(size_t(L) * 8)); RTD_CUDA(w.layerDev.ensure(size_t(L) * sizeof(LayerParams)));
-    RTD_CUDA(w.rayW.ensure(size_t(L) * R * 4));
-    RTD_CUDA(w.idd.ensure(LnzR * 4)); RTD_CUDA(w.rsig.ensure(LnzR * 4));
-    RTD_CUDA(w.rowMin.ensure(size_t(L) * nz * Ry * tilesX * 4));
-    RTD_CUDA(w.firstPassive.ensure(size_t(L) * R * 4));
-    // one zero-initialised control block: lfp[L] | hist[L*34] | rbCursor[33] | stats[4] | work[4] | ksItems[4]
-    const size_t ctlInts = size_t(L) + size_t(L) * 34 + 33 + 4 + 4 + 4;
-    RTD_CUDA(w.lfp.ensure(ctlInts * 4));
-    RTD_CUDA(w.batchRad.ensure(size_t(L) * 34 * 4)); RTD_CUDA(w.rbOffset.ensure(33 * 4));
-    RTD_CUDA(w.radMap.ensure(size_t(L) * nz * tiles)); RTD_CUDA(w.list.ensure(size_t(L) * nz * tiles * 4));
-    const size_t bevN = size_t(w.Zg) * (Ry + 64) * (Rx + 64);
-    RTD_CUDA(w.bev.ensure(bevN * 4));
-    RTD_CUDA(w.hOut.ensure((ctlInts + size_t(L) * 34) * 4));
     int* dLfp = w.lfp.as<int>(); int* dHist = dLfp + L; int* dCursor = dHist + size_t(L) * 34; int* dStats = dCursor + 33; int* dWork = dStats + 4;
-
-    // staging area after the weights: sigmas then layer params
-    const size_t nW = size_t(w.sx) * w.sy * L;   // L = computed layers
-    char* st = w.hStage.as<char>() + nW * 4;
-    memcpy(st, w.entrySig.data(), size_t(L) * 8);
-    memcpy(st + size_t(L) * 8, w.layers.data(), size_t(L) * sizeof(LayerParams));
-    RTD_CUDA(cudaMemcpyAsync(w.sigmas.p, st, size_t(L) * 8, cudaMemcpyHostToDevice, strm));
-    RTD_CUDA(cudaMemcpyAsync(w.layerDev.p, st + size_t(L) * 8, size_t(L) * sizeof(LayerParams), cudaMemcpyHostToDevice, strm));
-    RTD_CUDA(cudaMemsetAsync(w.lfp.p, 0, ctlInts * 4, strm));
-    RTD_CUDA(cudaMemsetAsync(w.bev.p, 0, bevN * 4, strm));
-    RTD_CUDA(cudaEventRecord(evs[0], strm));
-
     // K3a (cu:849-854)
     ConvParams cp;
     cp.inW = w.sx; cp.inH = w.sy; cp.outW = Rx; cp.outH = Ry;
-    const float pxMultX = 1.0f - w.entryZ / w.dist[0], pxMultY = 1.0f - w.entryZ / w.dist[1];
     const V3 rayD = w.grid.rayIdxToGantry.delta, rayO = w.grid.rayIdxToGantry.offset;
-    cp.pixelSpX = rayD.x * pxMultX; cp.pixelSpY = rayD.y * pxMultY;
     cp.deltaX = b.spotDelta[0] / rayD.x; cp.deltaY = b.spotDelta[1] / rayD.y;
     cp.offX = (b.spotOffset[0] - rayO.x) / rayD.x; cp.offY = (b.spotOffset[1] - rayO.y) / rayD.y;
     cp.cutoff = o.convSigmaCutoff;
-    spot_to_ray_kernel<<<dim3(Rx / 32, L), 256, size_t(w.sy) * 32 * 4, strm>>>(w.spotW.as<float>(), w.sigmas.as<float2>(), w.rayW.as<float>(), cp);
-    RTD_CUDA(cudaEventRecord(evs[1], strm));
+    spot_to_ray_kernel<<<dim3(Rx / 32, L), 256, size_t(w.sy) * 32 * 4, st>>>(w.spotW.as<float>(), w.sigmas.as<float2>(), w.rayW.as<float>(), cp, bd);
+    RTD_CUDA(cudaEventRecord(evBeam(ctx, beamNo, 3), st));
 
     // K2
     IddParams q;
-    q.g = makeFillGeom(w.grid.rayIdxToGantry, w.dist);
+    q.g = in.g;
     q.rrlScale = ctx->rrlScale; q.bpCutoff = o.bpDepthCutoff; q.rayWeightCutoff = o.rayWeightCutoff;
-    q.first = w.bfi; q.nz = nz; q.Rx = Rx; q.Ry = Ry; q.nozzle = o.noNozzle ? 0 : 1; q.doseToMedium = o.doseToMedium ? 1 : 0;
-    const size_t stepSmem = size_t(nz) * 8;     // per-step voxel width + volume, computed once per CTA
-    if (stepSmem > 48 * 1024) RTD_CUDA(cudaFuncSetAttribute(idd_sigma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stepSmem));
-    idd_sigma_kernel<<<dim3(tilesX * tilesY, 1, L), 256, stepSmem, strm>>>(w.density.as<float>(), w.wepl.as<float>(), w.rayW.as<float>(),
-        w.firstIn.as<int>(), w.firstOut.as<int>(), w.layerDev.as<LayerParams>(), q, ctx->iddTex.tex, ctx->rrlTex.tex,
+    q.Rx = Rx; q.Ry = Ry; q.nozzle = o.noNozzle ? 0 : 1; q.doseToMedium = o.doseToMedium ? 1 : 0; q.writeAll = o.fullIntermediates ? 1 : 0;
+    const int segs = tilesX * Ry;
+    idd_sigma_kernel<<<dim3((segs + IDD_WARPS - 1) / IDD_WARPS, 1, L), IDD_WARPS * 32, 0, st>>>(w.density.as<float>(), w.wepl.as<float>(), w.rayW.as<float>(),
+        w.firstIn.as<int>(), w.firstOut.as<int>(), w.layerDev.as<LayerParams>(), bd, w.stepTab.as<float2>(), q, ctx->iddTex.tex, ctx->rrlTex.tex,
         w.idd.as<float>(), w.rsig.as<float>(), w.rowMin.as<float>(), w.firstPassive.as<int>(), dLfp);
-    RTD_CUDA(cudaEventRecord(evs[2], strm));
+    RTD_CUDA(cudaEventRecord(evBeam(ctx, beamNo, 4), st));
 
-    // tile radii, batching, work list
-    const int gx = (nz * tiles + 255) / 256;
-    tile_radius_kernel<<<dim3(gx, L), 256, 0, strm>>>(w.rowMin.as<float>(), dLfp, w.bfi, nz, Rx, Ry, o.ksSigmaCutoff, w.radMap.as<uint8_t>(), dHist);
-    batch_kernel<<<1, 64, 0, strm>>>(dHist, L, o.minTilesInBatch, w.batchRad.as<int>(), w.rbOffset.as<int>(), dStats);
-    big_items_kernel<<<gx, 256, 0, strm>>>(w.radMap.as<uint8_t>(), w.batchRad.as<int>(), L, nz, tiles, w.rbOffset.as<int>() + 16, dCursor, w.list.as<uint32_t>());
-    RTD_CUDA(cudaEventRecord(evs[3], strm));
+    // tile radii, batching, work list (grids for the worst case nz = S; the kernels stop at the beam's own slice count)
+    const int gx = (S * tiles + 255) / 256;
+    tile_radius_kernel<<<dim3(gx, L), 256, 0, st>>>(w.rowMin.as<float>(), dLfp, bd, Rx, Ry, o.ksSigmaCutoff, q.writeAll ? 0 : 1, w.radMap.as<uint8_t>(), dHist,
+                                                     w.idd.as<float>(), w.rsig.as<float>());
+    batch_kernel<<<1, 64, 0, st>>>(dHist, L, o.minTilesInBatch, w.batchRad.as<int>(), w.rbOffset.as<int>(), dStats);
+    big_items_kernel<<<gx, 256, 0, st>>>(w.radMap.as<uint8_t>(), w.batchRad.as<int>(), L, bd, tiles, w.rbOffset.as<int>() + 16, dCursor, w.list.as<uint32_t>());
+    RTD_CUDA(cudaEventRecord(evBeam(ctx, beamNo, 5), st));
 
     // K3b: layer-fused, warp-autonomous superposition (ks2.cuh), one launch per patch-size class; the heaviest class first
     Ks2Params k2;
     k2.idd = w.idd.as<float>(); k2.rsig = w.rsig.as<float>(); k2.bev = w.bev.as<float>(); k2.batchRad = w.batchRad.as<int>();
-    k2.radMap = w.radMap.as<uint8_t>(); k2.layerFirstPassive = dLfp;
-    k2.L = L; k2.Rx = Rx; k2.Ry = Ry; k2.nz = nz; k2.first = w.bfi; k2.tilesX = tilesX; k2.tiles = tiles;
-    k2.bigCount = dCursor; k2.bigItems = w.list.as<uint32_t>(); k2.bodyStep = (o.ks2BodyStep == 1 || o.ks2BodyStep == 2 || o.ks2BodyStep == 4) ? o.ks2BodyStep : 0;
+    k2.radMap = w.radMap.as<uint8_t>(); k2.layerFirstPassive = dLfp; k2.bd = bd;
+    k2.L = L; k2.Rx = Rx; k2.Ry = Ry; k2.tilesX = tilesX; k2.tiles = tiles;
+    k2.bigCount = dCursor; k2.bigItems = w.list.as<uint32_t>();
+    k2.bodyStep = (o.ks2BodyStep == 1 || o.ks2BodyStep == 2 || o.ks2BodyStep == 4) ? o.ks2BodyStep : 0;
     int* dKsItems = dWork + 4;      // items each radius class processed (rtd_timing.ksLaunchesWithWork)
-    ks2_kernel<32, KS2_WARPS_32><<<ctx->ks2Blocks32, KS2_WARPS_32 * 32, KS2_SMEM_32, strm>>>(k2, dWork + 0, dKsItems + 0);
-    ks2_kernel<24, KS2_WARPS_24><<<ctx->ks2Blocks24, KS2_WARPS_24 * 32, KS2_SMEM_24, strm>>>(k2, dWork + 3, dKsItems + 1);
-    ks2_kernel<16, KS2_WARPS_16><<<ctx->ks2Blocks16, KS2_WARPS_16 * 32, KS2_SMEM_16, strm>>>(k2, dWork + 1, dKsItems + 2);
-    ks2_kernel<8, KS2_WARPS_8><<<ctx->ks2Blocks8, KS2_WARPS_8 * 32, KS2_SMEM_8, strm>>>(k2, dWork + 2, dKsItems + 3);
-    RTD_CUDA(cudaEventRecord(evs[4], strm));
-
-    // K4: the dose grid is shared by all beams: transfers are serialised on the context's main stream, in beam order,
-    // each one waiting for its own beam's superposition (and, on the one-call host path, for the dose-in sub-volumes)
-    RTD_CUDA(cudaStreamWaitEvent(ctx->stream, evs[4], 0));
-    if (w.doTransfer) {
-        if (io && io->dose && !io->zeroCopy && !doseInWaited) { RTD_CUDA(cudaStreamWaitEvent(ctx->stream, evDoseIn, 0)); doseInWaited = true; }
-        bev_to_grid_kernel<<<w.gpGrid, 256, 0, ctx->stream>>>(w.bev.as<float>(), dDose, w.gp, ctx->xferCount.as<unsigned long long>());
-        launches += 1;
-    }
-    launches += 9;
+    ks2_kernel<32, KS2_WARPS_32><<<ctx->ks2Blocks32, KS2_WARPS_32 * 32, KS2_SMEM_32, st>>>(k2, dWork + 0, dKsItems + 0);
+    ks2_kernel<24, KS2_WARPS_24><<<ctx->ks2Blocks24, KS2_WARPS_24 * 32, KS2_SMEM_24, st>>>(k2, dWork + 3, dKsItems + 1);
+    ks2_kernel<16, KS2_WARPS_16><<<ctx->ks2Blocks16, KS2_WARPS_16 * 32, KS2_SMEM_16, st>>>(k2, dWork + 1, dKsItems + 2);
+    ks2_kernel<8, KS2_WARPS_8><<<ctx->ks2Blocks8, KS2_WARPS_8 * 32, KS2_SMEM_8, st>>>(k2, dWork + 2, dKsItems + 3);
+    RTD_CUDA(cudaEventRecord(evBeam(ctx, beamNo, 6), st));
+    launches += 14;
     RTD_CUDA(cudaGetLastError());
-    RTD_CUDA(cudaEventRecord(evs[5], ctx->stream));
-    // results for the reports: control block + batch radii
-    RTD_CUDA(cudaMemcpyAsync(w.hOut.p, w.lfp.p, ctlInts * 4, cudaMemcpyDeviceToHost, strm));
-    RTD_CUDA(cudaMemcpyAsync(w.hOut.as<int>() + ctlInts, w.batchRad.p, size_t(L) * 34 * 4, cudaMemcpyDeviceToHost, strm));
-    if (io) { io->h2d += int64_t(L) * (8 + sizeof(LayerParams)); io->d2h += int64_t(ctlInts + size_t(L) * 34) * 4; }
+    return RTD_OK;
+}
+
+// Part 2 of a beam: the transfer into the dose grid, which all beams share - serialised on the context's main stream in beam
+// order, each one waiting for its own beam's superposition (and, on the host path with a pageable grid, for the dose-in
+// sub-volumes) - and the copies of the integer results for the reports.
+rtd_status beamTransfer(rtd_ctx* ctx, int beamNo, BeamWs& w, float* dDose, int& launches, cudaStream_t st, HostIo* io, cudaEvent_t evDoseIn, bool& doseInWaited) {
+    const int L = w.Lc;
+    RTD_CUDA(cudaStreamWaitEvent(ctx->stream, evBeam(ctx, beamNo, 6), 0));
+    if (io && io->dose && !io->zeroCopy && !doseInWaited) { RTD_CUDA(cudaStreamWaitEvent(ctx->stream, evDoseIn, 0)); doseInWaited = true; }
+    bev_to_grid_kernel<<<ctx->smCount * 8, 256, 0, ctx->stream>>>(w.bev.as<float>(), dDose, w.beamDev.as<BeamDev>(), ctx->xferCount.as<unsigned long long>());
+    launches += 1;
+    RTD_CUDA(cudaGetLastError());
+    RTD_CUDA(cudaEventRecord(evBeam(ctx, beamNo, 7), ctx->stream));
+    // results for the reports: layer parameters, entry sigmas, control block, batch radii
+    char* out = w.hOut.as<char>();
+    RTD_CUDA(cudaMemcpyAsync(out + sizeof(BeamDev), w.layerDev.p, size_t(L) * sizeof(LayerParams), cudaMemcpyDeviceToHost, st));
+    RTD_CUDA(cudaMemcpyAsync(out + sizeof(BeamDev) + size_t(L) * sizeof(LayerParams), w.sigmas.p, size_t(L) * 8, cudaMemcpyDeviceToHost, st));
+    RTD_CUDA(cudaMemcpyAsync(out + w.outCtlOff(), w.lfp.p, w.ctlInts() * 4, cudaMemcpyDeviceToHost, st));
+    RTD_CUDA(cudaMemcpyAsync(out + w.outCtlOff() + w.ctlInts() * 4, w.batchRad.p, size_t(L) * 34 * 4, cudaMemcpyDeviceToHost, st));
+    if (io) io->d2h += int64_t(sizeof(BeamDev)) + int64_t(L) * (sizeof(LayerParams) + 8) + int64_t(w.ctlInts() + size_t(L) * 34) * 4;
     return RTD_OK;
 }
 
 // After the final sync: integer reports (cu:955-957, 1185-1210) and the metric counters.
 bool beamFinish(rtd_ctx* ctx, BeamWs& w, int64_t& updates, int64_t& taps, int& ksLaunches) {
-    if (!w.live) return true;
     const int L = w.Lc;
-    const size_t ctlInts = size_t(L) + size_t(L) * 34 + 33 + 4 + 4 + 4;
-    const int* lfp = w.hOut.as<int>(); const int* hist = lfp + L; const int* stats = hist + size_t(L) * 34 + 33;
+    const char* out = w.hOut.as<char>();
+    memcpy(&w.hostDev, out, sizeof(BeamDev));
+    const LayerParams* lp = reinterpret_cast<const LayerParams*>(out + sizeof(BeamDev));
+    const float* esig = reinterpret_cast<const float*>(out + sizeof(BeamDev) + size_t(L) * sizeof(LayerParams));
+    w.bfi = w.hostDev.bfi; w.bfo = w.hostDev.bfo; w.Zg = w.hostDev.Zg; w.nz = w.hostDev.nz; w.entryZ = w.hostDev.entryZ;
+    w.live = w.nz > 0;
+    w.lrep.assign(w.L, rtd_layer_report());
+    memset(&w.rep, 0, sizeof w.rep);
+    w.rep.lSteps = w.grid.lSteps; w.rep.bSteps = w.grid.bSteps; w.rep.rSteps = w.grid.rSteps; w.rep.tSteps = w.grid.tSteps;
+    w.rep.rayDimX = w.grid.dimX; w.rep.rayDimY = w.grid.dimY; w.rep.steps = w.S; w.rep.nLayers = w.L;
+    w.rep.beamFirstInside = w.bfi; w.rep.beamFirstOutside = w.bfo; w.rep.beamFirstGuaranteedPassive = w.Zg; w.rep.entryZ = w.entryZ;
+    for (int l = 0; l < L; ++l) {
+        rtd_layer_report& lr = w.lrep[w.l0 + l];
+        lr.energyIdx = w.lin[l].energyIdx; lr.energyScaleFact = w.lin[l].energyScale; lr.peakDepth = w.lin[l].peakDepth;
+        lr.entrySigmaX = esig[2 * l]; lr.entrySigmaY = esig[2 * l + 1]; lr.afterLastStep = lp[l].afterLast;
+    }
+    if (!w.live) return true;
+    const int* lfp = reinterpret_cast<const int*>(out + w.outCtlOff()); const int* hist = lfp + L; const int* stats = hist + size_t(L) * 34 + 33;
     const int* ksItems = stats + 8;
     for (int i = 0; i < 4; ++i) if (ksItems[i] > 0) ++ksLaunches;
-    const int* brad = w.hOut.as<int>() + ctlInts;
+    const int* brad = lfp + w.ctlInts();
     int fcp = 0; int64_t u = 0, t = 0;
     for (int l = 0; l < L; ++l) {
         rtd_layer_report& lr = w.lrep[w.l0 + l];
@@ -661,9 +635,6 @@ bool beamFinish(rtd_ctx* ctx, BeamWs& w, int64_t& updates, int64_t& taps, int& k
     return stats[0] == 0;
 }
 
-constexpr size_t EV_BEAM0 = 8, EV_PER_BEAM = 10;   // events 0..7 are per call; per beam: 0..5 stages, 6 traced, 7 done, 8 CT boxes uploaded
-cudaEvent_t evBeam(rtd_ctx* ctx, int b, int i) { return ev(ctx, EV_BEAM0 + size_t(b) * EV_PER_BEAM + i); }
-
 rtd_status doseCoreImpl(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* dDose, const rtd_opts& o, rtd_timing* tm,
                         cudaEvent_t evBegin, cudaEvent_t evEnd, HostIo* io) {
     int launches = 0;
@@ -683,7 +654,8 @@ rtd_status doseCoreImpl(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* 
         RTD_CUDA(cudaMemsetAsync(ctx->ctRows.as<int>() + 3 * rows, 0xff, rows * 4, ctx->cstream));
     }
     // Beams are independent until the transfer into the shared dose grid: unless opts.serialBeams is set every beam runs
-    // on its own stream so that the latency-bound stages (tracer, IDD/sigma depth scans) of different beams overlap.
+    // on its own stream so that the latency-bound stages (tracer, IDD/sigma depth scans) of different beams overlap; on the
+    // one-call host path the CT sub-volumes of beam b+1 upload (copy stream) while beam b computes.
     const bool serial = o.serialBeams != 0 || nBeams == 1;
     auto beamStream = [&](int b) -> cudaStream_t {
         if (serial) return ctx->stream;
@@ -691,53 +663,30 @@ rtd_status doseCoreImpl(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* 
         while (ctx->bstreams.size() <= i) { cudaStream_t s_; cudaStreamCreateWithFlags(&s_, cudaStreamNonBlocking); ctx->bstreams.push_back(s_); }
         return ctx->bstreams[i];
     };
-    // One-call host path with several beams: the CT sub-volumes of beam b+1 upload while beam b computes. The host then
-    // waits for each beam's tracer reductions separately (nBeams + 1 host syncs instead of 2) and issues that beam's
-    // remaining launches at once. Needs a dose grid the transfers can write as soon as they run (device or pinned host).
-    const bool pipelined = io && io->ct && !serial && (io->zeroCopy || !io->dose);
     for (int b = 0; b < nBeams; ++b) {
         cudaStream_t st = beamStream(b);
         if (st != ctx->stream) RTD_CUDA(cudaStreamWaitEvent(st, evBegin, 0));
-        rtd_status s = beamPhaseA(ctx, beams[b], *ctx->ws[b], o, launches, st, io, evBeam(ctx, b, 8));
+        rtd_status s = beamEnqueue(ctx, b, beams[b], *ctx->ws[b], o, launches, st, io);
         if (s != RTD_OK) return s;
-        cudaEvent_t e = evBeam(ctx, b, 6);
-        RTD_CUDA(cudaEventRecord(e, st));
-        if (st != ctx->stream && !pipelined) RTD_CUDA(cudaStreamWaitEvent(ctx->stream, e, 0));
     }
-    cudaEvent_t evTraceEnd = ev(ctx, 2);
-    int hostSyncs = 2;
-    if (!pipelined) {
-        RTD_CUDA(cudaEventRecord(evTraceEnd, ctx->stream));
-        RTD_CUDA(cudaStreamSynchronize(ctx->stream));                     // host sync 1 of 2 (covers every beam stream)
-        for (int b = 0; b < nBeams; ++b) {
-            rtd_status s = beamPhaseB1(ctx, beams[b], *ctx->ws[b], o);
-            if (s != RTD_OK) return s;
-        }
-    } else {
-        evTraceEnd = evBeam(ctx, nBeams - 1, 6);
-        hostSyncs = nBeams + 1;
-    }
+    int hostSyncs = 1;
     cudaEvent_t evDoseIn = ev(ctx, 6);
     if (io && io->dose && !io->zeroCopy) {
-        // dose-in sub-volumes (accumulate semantics, cu:542) on the copy stream while the beams compute; every box is
-        // uploaded before the first transfer, so overlapping boxes of different beams are harmless
-        for (int b = 0; b < nBeams; ++b) if (ctx->ws[b]->doTransfer) doseBoxesOfBeam(*ctx->ws[b], ctx->doseDims, ctx->doseBoxes);
+        // pageable host dose grid: the sub-volumes the transfers can touch are staged through device memory, and their boxes
+        // need the transfer boxes on the host - the one case that still waits for the set-up kernels in the middle of a call.
+        // Every box is uploaded before the first transfer, so overlapping boxes of different beams are harmless.
+        for (int b = 0; b < nBeams; ++b) { RTD_CUDA(cudaEventSynchronize(evBeam(ctx, b, 10))); memcpy(&ctx->ws[b]->hostDev, ctx->ws[b]->hOut.p, sizeof(BeamDev)); }
+        hostSyncs = 2;
+        for (int b = 0; b < nBeams; ++b) { BeamWs& w = *ctx->ws[b]; w.bfi = w.hostDev.bfi; w.Zg = w.hostDev.Zg; doseBoxesOfBeam(w, ctx->doseDims, ctx->doseBoxes); }
         for (const Box& bx : ctx->doseBoxes) { RTD_CUDA(copyDoseBox(ctx, io->dose, dDose, bx, true, ctx->cstream)); io->h2d += boxVoxels(bx) * 4; }
         RTD_CUDA(cudaEventRecord(evDoseIn, ctx->cstream));
     }
     bool doseInWaited = false;
     for (int b = 0; b < nBeams; ++b) {
-        cudaEvent_t evs[6];
-        for (int i = 0; i < 6; ++i) evs[i] = evBeam(ctx, b, i);
         cudaStream_t st = beamStream(b);
-        if (pipelined) {
-            RTD_CUDA(cudaEventSynchronize(evBeam(ctx, b, 6)));            // this beam's tracer reductions are on the host
-            rtd_status s1 = beamPhaseB1(ctx, beams[b], *ctx->ws[b], o);
-            if (s1 != RTD_OK) return s1;
-        }
-        rtd_status s = beamPhaseB2(ctx, beams[b], *ctx->ws[b], o, dDose, launches, evs, st, io, evDoseIn, doseInWaited);
+        rtd_status s = beamTransfer(ctx, b, *ctx->ws[b], dDose, launches, st, io, evDoseIn, doseInWaited);
         if (s != RTD_OK) return s;
-        if (st != ctx->stream) { cudaEvent_t e = evBeam(ctx, b, 7); RTD_CUDA(cudaEventRecord(e, st)); RTD_CUDA(cudaStreamWaitEvent(ctx->stream, e, 0)); }
+        if (st != ctx->stream) { cudaEvent_t e = evBeam(ctx, b, 8); RTD_CUDA(cudaEventRecord(e, st)); RTD_CUDA(cudaStreamWaitEvent(ctx->stream, e, 0)); }
     }
     cudaEvent_t evXferEnd = ev(ctx, 7);
     RTD_CUDA(cudaEventRecord(evXferEnd, ctx->stream));
@@ -747,7 +696,7 @@ rtd_status doseCoreImpl(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* 
         for (const Box& bx : ctx->doseBoxes) { RTD_CUDA(copyDoseBox(ctx, io->dose, dDose, bx, false, ctx->stream)); io->d2h += boxVoxels(bx) * 4; }
     }
     RTD_CUDA(cudaEventRecord(evEnd, ctx->stream));
-    RTD_CUDA(cudaStreamSynchronize(ctx->stream));                         // host sync 2 of 2
+    RTD_CUDA(cudaStreamSynchronize(ctx->stream));                         // the one host sync of a plan
     int64_t updates = 0, taps = 0; bool ok = true; int ksLaunches = 0;
     for (int b = 0; b < nBeams; ++b) ok = beamFinish(ctx, *ctx->ws[b], updates, taps, ksLaunches) && ok;
     const int64_t modified = (int64_t)*ctx->hXferCount.as<unsigned long long>();
@@ -757,23 +706,20 @@ rtd_status doseCoreImpl(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* 
         memset(tm, 0, sizeof *tm);
         tm->updates = updates; tm->ksTaps = taps; tm->kernelLaunches = launches; tm->hostSyncs = hostSyncs; tm->ksLaunchesWithWork = ksLaunches;
         float ms = 0;
-        cudaEventElapsedTime(&ms, evBegin, evTraceEnd); tm->msTrace = ms;
-        cudaEvent_t prev = evTraceEnd;
         for (int b = 0; b < nBeams; ++b) {
-            if (!ctx->ws[b]->live) continue;
-            cudaEvent_t e[6];
-            for (int i = 0; i < 6; ++i) e[i] = evBeam(ctx, b, i);
-            cudaEventElapsedTime(&ms, prev, e[0]); tm->msSetup += std::max(ms, 0.0f);
-            cudaEventElapsedTime(&ms, e[0], e[1]); tm->msConv += ms;
-            cudaEventElapsedTime(&ms, e[1], e[2]); tm->msIddSigma += ms;
-            cudaEventElapsedTime(&ms, e[2], e[3]); tm->msRadius += ms;
-            cudaEventElapsedTime(&ms, e[3], e[4]); tm->msSuperp += ms;
-            cudaEventElapsedTime(&ms, e[4], e[5]); tm->msTransfer += ms;
-            prev = serial ? e[5] : evTraceEnd;
+            cudaEvent_t e[8];
+            for (int i = 0; i < 8; ++i) e[i] = evBeam(ctx, b, i);
+            cudaEventElapsedTime(&ms, e[0], e[1]); tm->msTrace += ms;
+            cudaEventElapsedTime(&ms, e[1], e[2]); tm->msSetup += ms;
+            cudaEventElapsedTime(&ms, e[2], e[3]); tm->msConv += ms;
+            cudaEventElapsedTime(&ms, e[3], e[4]); tm->msIddSigma += ms;
+            cudaEventElapsedTime(&ms, e[4], e[5]); tm->msRadius += ms;
+            cudaEventElapsedTime(&ms, e[5], e[6]); tm->msSuperp += ms;
+            cudaEventElapsedTime(&ms, e[6], e[7]); tm->msTransfer += std::max(ms, 0.0f);
         }
         cudaEventElapsedTime(&ms, evBegin, evEnd); tm->msTotal = ms;
         if (io) {
-            if (io->ct && nBeams > 0) { cudaEventElapsedTime(&ms, evBegin, evBeam(ctx, nBeams - 1, 8)); tm->msUpload = ms; }
+            if (io->ct && nBeams > 0) { cudaEventElapsedTime(&ms, evBegin, evBeam(ctx, nBeams - 1, 9)); tm->msUpload = ms; }
             if (io->dose) { cudaEventElapsedTime(&ms, evXferEnd, evEnd); tm->msDownload = ms; }
             tm->h2dBytes = io->h2d; tm->d2hBytes = io->d2h;
         }

@@ -45,6 +45,13 @@ def bits_equal(a, b):
 def test_mini_against_reference_golden(eng, mini_case, golden_mini):
     g = golden_mini
     dose, t = run_case(eng, mini_case)
+    # a second run that writes every (ray, step) of idd / rSigmaEff (the default skips row segments without dose): same dose
+    eng.opts.fullIntermediates = 1
+    try:
+        dose_full, _ = run_case(eng, mini_case)
+    finally:
+        eng.opts.fullIntermediates = 0
+    assert rel_to_max(dose_full, dose)[0] <= 2e-6
     rep = eng.beam_report(0)
     got = [rep[k] for k in ("lSteps", "bSteps", "rSteps", "tSteps", "rayDimX", "rayDimY", "beamFirstInside", "beamFirstOutside",
                             "beamFirstGuaranteedPassive", "beamFirstCalculatedPassive", "updates")]
@@ -143,6 +150,7 @@ def test_live_against_rebuilt_reference(name, layers, tmp_path):
         assert b["bev_dose"]["rel_to_max"] <= DOSE_TOL_TIGHT and b["bev_dose"]["nonfinite_mismatch"] == 0
     assert rep["dose_max_rel_err"] <= DOSE_TOL_TIGHT
     assert rep["dose_vs_wrapper_max_rel_err"] <= DOSE_TOL_TIGHT
+    assert rep["engine_sparse_vs_full_intermediates_max_rel"] <= 2e-6
     assert rep["gamma_1pct_1mm_pass_rate"] >= 0.999
 
 
@@ -157,6 +165,7 @@ def test_full_size_properties(eng, c3):
     assert whole.max() > 0 and np.isfinite(whole).all()
     reps = [eng.beam_report(b) for b in range(3)]
     assert t["updates"] == sum(r["updates"] for r in reps) > 5e7
+    assert t["hostSyncs"] == 1             # cut-offs, per-layer parameters and the transfer box are derived on the device
     # (1) run-to-run: only fp32 atomic order differs
     again, _ = run_case(eng, c3)
     assert rel_to_max(again, whole)[0] <= 2e-6

@@ -88,12 +88,17 @@ def main():
     eng.set_dose_grid(nx, ny, nz)
     dose = np.zeros((nz, ny, nx), np.float32)
     t0 = time.time(); tm = eng.dose(case.beams, dose); t1 = time.time()
+    rep["engine_timing_1st_call"] = tm.as_dict()
+    # second run with opts.fullIntermediates: the depth scan writes every (ray, step) of idd / rSigmaEff (the default leaves row
+    # segments without dose unwritten), so that the arrays can be compared with the reference's dumps below; the two doses must agree
     dose2 = np.zeros_like(dose)
+    eng.opts.fullIntermediates = 1
     tm = eng.dose(case.beams, dose2)
     rep["engine_timing_2nd_call"] = tm.as_dict()
     rep["engine_wall_first_call_s"] = t1 - t0
     rep["engine_dose_max"] = float(dose.max())
     rep["engine_rerun_max_abs_diff"] = float(np.abs(dose - dose2).max())
+    rep["engine_sparse_vs_full_intermediates_max_rel"] = float(np.abs(dose - dose2).max() / max(float(dose2.max()), 1e-30))
     rep["beams"] = []
     if args.no_ref:
         for b in range(len(case.beams)):
