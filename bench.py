@@ -292,72 +292,39 @@ def measure(R, case, steps, warmup, do_e2e, do_cpu, full):
     # zeroed and summed; the rest of every partial grid stays zero (checked once after the warm-up)
     z0, z1 = (0, nz - 1) if world == 1 else sharding.dose_slab(case.beams, case.dose_dims, sigma_cutoff=float(eng.opts.convSigmaCutoff))
     e2e_extra = {"mod": 0}
-    # N > 1, --reduce push / peer: ONE dose grid on rank 0, mapped by every rank over CUDA IPC (rtd_shared_dose_*)
-    peer = world > 1 and args.reduce in ("peer", "push")
-    push = args.reduce == "push"
-    shared_ptr, token = 0, torch.zeros(1, dtype=torch.int32, device=dev)
-    if peer:
+    # N > 1, --reduce push (default): the library's own multi-GPU call. rtd_group_create puts ONE dose grid + a control block on rank 0
+    # and maps it on every other rank over CUDA IPC; rtd_plan_dose_group partitions the plan, computes this rank's work items and
+    # sums the partial doses in that grid (vector reductions over NVLink, two stream-ordered barriers in device memory - no NCCL
+    # call and no torch op inside the step). --reduce nccl: the partition is applied here and the partial grids meet in one dense
+    # NCCL reduce (the baseline the default is measured against).
+    group = world > 1 and args.reduce == "push"
+    packed_all, keep_all = pack_beams(case.beams)
+    if group:
         handle = [None]
-        try:
-            if rank == 0:
-                shared_ptr, handle[0] = eng.shared_dose_create(nz * ny * nx)
-        except Exception as ex:          # noqa: BLE001 - reported in the JSON line
-            handle[0] = f"error: {ex}"
-        dist.broadcast_object_list(handle, src=0)
-        ok = torch.ones(1, dtype=torch.int32, device=dev)
-        if isinstance(handle[0], str):
-            ok.zero_()
-        elif rank != 0:
-            try:
-                shared_ptr = eng.shared_dose_open(handle[0])
-            except Exception:            # noqa: BLE001
-                ok.zero_()
-        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
-        peer = bool(ok.item())
-    own_grid = dose_dev
-    if peer:
-        class _Ext:                       # zero-copy torch view of the shared grid (rank 0 zeroes / reads it through torch)
-            __cuda_array_interface__ = {"shape": (nz, ny, nx), "typestr": "<f4", "data": (shared_ptr, False), "version": 2}
         if rank == 0:
+            handle[0] = eng.group_create(0, world, nz * ny * nx)
+        dist.broadcast_object_list(handle, src=0)
+        if rank != 0:
+            eng.group_create(rank, world, nz * ny * nx, handle[0])
+        if rank == 0:
+            class _Ext:                       # zero-copy torch view of the group's grid (rank 0 reads it through torch)
+                __cuda_array_interface__ = {"shape": (nz, ny, nx), "typestr": "<f4", "data": (eng.group_dose_ptr(), False), "version": 2}
             dose_dev = torch.as_tensor(_Ext(), device=dev)
-        # push: only rank 0 writes its grid while pushes of the others may land in it -> its own transfers are atomic too
-        eng.opts.atomicDose = 1 if (not push or rank == 0) else 0
-    push = push and peer
     slab = dose_dev[z0:z1 + 1]
-    slab_off = z0 * ny * nx * 4
-
-    def dose_target():
-        return shared_ptr if (peer and (rank == 0 or not push)) else dose_dev.data_ptr()
-
-    def stream_barrier():
-        # orders the streams of all ranks without a host sync: a 4-byte all-reduce on the engine's stream
-        dist.all_reduce(token)
-
-    def before_dose():
-        if not peer or push or rank == 0:
-            slab.zero_()
-        if peer:
-            stream_barrier()                                      # rank 0's grid is zeroed before anything is added into it
-
-    def after_dose():
-        if push and rank != 0:
-            eng.push_dose_to_peer(slab.data_ptr(), shared_ptr + slab_off, slab.numel())
-        if peer:
-            stream_barrier()                                      # every rank's contributions have landed
-        else:
-            sharding.reduce_dose(slab, dst=0)
 
     def step_device():
         with torch.cuda.stream(stream):
-            before_dose()
-            t = eng.dose_ptr(packed, len(mine), dose_target(), device=True)
-            after_dose()
+            if group:
+                return eng.plan_dose_group(0, cnx, cny, cnz, packed_all, len(case.beams))
+            slab.zero_()
+            t = eng.dose_ptr(packed, len(mine), dose_dev.data_ptr(), device=True)
+            sharding.reduce_dose(slab, dst=0)
         return t
 
     for _ in range(warmup):
         step_device()
     R.barrier()
-    if world > 1 and (not peer or push or rank == 0) and (bool(dose_dev[:z0].any().item()) or bool(dose_dev[z1 + 1:].any().item())):
+    if world > 1 and (not group or rank == 0) and (bool(dose_dev[:z0].any().item()) or bool(dose_dev[z1 + 1:].any().item())):
         raise SystemExit(f"bench.py: rank {rank} deposited dose outside the reduced slab [{z0}, {z1}]")
     sampler = ClockSampler(R.local) if full else None
     if sampler:
@@ -417,15 +384,11 @@ def measure(R, case, steps, warmup, do_e2e, do_cpu, full):
     if world > 1:
         if rank == 0:
             ref_grid = torch.zeros((nz, ny, nx), dtype=torch.float32, device=dev)
-            pk_all, keep_all = pack_beams(case.beams)
-            saved = eng.opts.atomicDose
-            eng.opts.atomicDose = 0
             with torch.cuda.stream(stream):
-                eng.dose_ptr(pk_all, len(case.beams), ref_grid.data_ptr(), device=True)
-            eng.opts.atomicDose = saved
+                eng.dose_ptr(packed_all, len(case.beams), ref_grid.data_ptr(), device=True)
             torch.cuda.synchronize()
             err_vs_1gpu = float((dose_dev - ref_grid).abs().max().item() / max(float(ref_grid.max().item()), 1e-30))
-            del ref_grid, keep_all
+            del ref_grid
         R.barrier()
 
     # ---- end-to-end through the host-facing call, host buffers, copies inside the timed region ----
@@ -436,13 +399,15 @@ def measure(R, case, steps, warmup, do_e2e, do_cpu, full):
             # HOST CT and HOST dose; the library copies the sub-volumes the plan touches (bytes reported by the library)
             if world == 1:
                 return eng.plan_dose_ptr(ct_host.data_ptr(), cnx, cny, cnz, packed, len(mine), dose_host.data_ptr())
-            # N > 1: every rank uploads the CT sub-volumes of its own work items and computes them into its partial grid;
-            # the partial grids meet as in the device-resident step; rank 0 adds the summed dose onto the caller's pinned host grid
-            # in place (rtd_add_device_to_host: only voxels that received dose cross PCIe)
+            # N > 1: rtd_plan_dose_group with the HOST CT and, on rank 0, the HOST dose grid: every rank uploads the CT sub-volumes of
+            # its own work items, the partial doses meet in the group's grid, rank 0 adds the plan's dose onto the caller's pinned
+            # host grid in place (only voxels that received dose cross PCIe)
             with torch.cuda.stream(stream):
-                before_dose()
-                t = eng.plan_dose_ptr(ct_host.data_ptr(), cnx, cny, cnz, packed, len(mine), dose_target(), device=True)
-                after_dose()
+                if group:
+                    return eng.plan_dose_group(ct_host.data_ptr(), cnx, cny, cnz, packed_all, len(case.beams), dose_host.data_ptr() if rank == 0 else 0)
+                slab.zero_()
+                t = eng.plan_dose_ptr(ct_host.data_ptr(), cnx, cny, cnz, packed, len(mine), dose_dev.data_ptr(), device=True)
+                sharding.reduce_dose(slab, dst=0)
             if rank == 0:
                 e2e_extra["mod"] = eng.add_device_to_host(slab.data_ptr(), dose_host.data_ptr() + z0 * ny * nx * 4, slab.numel())
             else:
@@ -501,8 +466,8 @@ def measure(R, case, steps, warmup, do_e2e, do_cpu, full):
             Rr = r["rayDimX"] * r["rayDimY"]
             box = max(0, r["bboxMax"][0] - r["bboxMin"][0] + 1) * max(0, r["bboxMax"][1] - r["bboxMin"][1] + 1) * max(0, r["bboxMax"][2] - r["bboxMin"][2] + 1)
             plan_bytes += 4 * box + 8 * Rr * r["steps"] + 8 * r["updates"] + 8 * (r["rayDimX"] + 64) * (r["rayDimY"] + 64) * max(0, r["beamFirstCalculatedPassive"] - r["beamFirstInside"]) + 8 * box
-        how = ("every rank adds the dose-holding float4 groups of its slab into ONE grid on rank 0 over NVLink (CUDA IPC, red.global.add.v4.f32), no dense collective" if push
-               else "every rank's transfer kernels add into ONE dose grid on rank 0 over NVLink (CUDA IPC, red.global.add.f32), no separate collective" if peer
+        how = ("rtd_plan_dose_group: every rank adds the dose-holding float4 groups of its slab into ONE grid on rank 0 over NVLink (CUDA IPC, "
+               "red.global.add.v4.f32), ordered by two barriers in device memory; no NCCL call inside the step" if group
                else "partial dose grids (reachable z-slab) summed by one NCCL reduce")
         res = {"value": U / (ms_step * 1e-3), "ms_per_step": ms_step, "updates_per_step": U, "ks_taps_per_step": taps,
                "sharding": (f"(beam, layer-range) work items, contiguous equal-cost runs over {world} ranks; " + how) if world > 1 else "single GPU",
@@ -539,17 +504,16 @@ def measure(R, case, steps, warmup, do_e2e, do_cpu, full):
             res["cpu_baseline"] = cpu_baseline_port(case)[0]
             res["cpu_stage_baseline"] = cpu_stage_baseline(case, gpu_stage_ms=stage["msConv"])
     # ordered teardown of this workload: torch tensors first, then the IPC mapping (non-owners unmap before the owner frees)
-    eng.opts.atomicDose = 0
     del evs, ms_t, upd_local, slab
-    dose_dev = own_grid = ct_dev = None
+    dose_dev = ct_dev = None
     torch.cuda.synchronize()
-    if peer:
+    if group:
         if rank != 0:
-            eng.shared_dose_close(shared_ptr, owner=False)
+            eng.group_destroy()
         R.barrier()
         if rank == 0:
-            eng.shared_dose_close(shared_ptr, owner=True)
-    del ct_host, dose_host
+            eng.group_destroy()
+    del ct_host, dose_host, keep_all
     return res
 
 
@@ -568,11 +532,10 @@ def main():
     ap.add_argument("--no-cold", action="store_true", help="skip the fresh-process measurement (key 'e2e_cold')")
     ap.add_argument("--cold-child", action="store_true", help=argparse.SUPPRESS)
     ap.add_argument("--lib", default=None, help="measure another build of librtdose.so (A/B of kernel variants)")
-    ap.add_argument("--reduce", default="push", choices=["push", "peer", "nccl"],
-                    help="N > 1, how the ranks' partial doses meet in ONE grid on rank 0 (mapped by every rank over CUDA IPC): 'push' = each "
-                         "rank adds the float4 groups of its slab that hold dose with 16-byte vector reductions over NVLink; 'peer' = the "
-                         "transfer kernels themselves add into the mapped grid (scalar reductions, NVLink packet-rate bound); "
-                         "'nccl' = local partial grids + one dense NCCL reduce of the reachable slab")
+    ap.add_argument("--reduce", default="push", choices=["push", "nccl"],
+                    help="N > 1, how the ranks' partial doses meet: 'push' = rtd_plan_dose_group (ONE grid on rank 0 mapped by every rank over "
+                         "CUDA IPC, 16-byte vector reductions over NVLink, barriers in device memory); 'nccl' = local partial grids + one dense "
+                         "NCCL reduce of the reachable slab")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -220,6 +220,35 @@ rtd_status rtd_shared_dose_close(rtd_ctx* ctx, float* dPtr, int owner);
  * on rtd_stream; several ranks may push concurrently. Both pointers 16-byte aligned. */
 rtd_status rtd_push_dose_to_peer(rtd_ctx* ctx, const float* dSrc, float* dPeerDst, size_t n);
 
+/* ---- One plan on the GPUs of a node, one process / context per GPU. The reference's beam loop (src/kernel_wrapper.cu:601)
+ * and layer loop (cu:916) are serial on one GPU; dose is linear in both, so (beam, layer range) work items are independent until the sum.
+ *
+ * rtd_partition / rtd_dose_slab are pure host functions (no device needed): the assignment of every (beam, layer) to a rank as
+ * consecutive runs of near-equal cost (chunksPerBeam = 0; > 0 splits every beam into that many ranges, LPT-assigned), and the z-slab
+ * of the dose grid the plan can reach. rtd_partition returns the number of work items (only maxItems are written), -1 on bad input;
+ * rtd_dose_slab 1 / 0 (empty) / -1.
+ *
+ * rtd_group_create: rank 0 allocates the plan's ONE dose grid (nDoseFloats floats + a control block) and writes its 64-byte CUDA IPC
+ * handle to handle64; the caller carries the handle to the other ranks (MPI, torch.distributed, a pipe ...), whose rtd_group_create
+ * reads it and maps the grid over NVLink / NVSwitch peer memory. rtd_group_dose: the grid as seen from this rank.
+ * rtd_group_barrier: a stream-ordered barrier of the ranks' streams (one remote atomic + polling in a one-thread kernel, no NCCL, no host
+ * sync); every rank must call it the same number of times.
+ * rtd_plan_dose_group: every rank passes the WHOLE plan. The call partitions it, computes this rank's work items (CT: the HOST volume
+ * ctHuPlus1000 - only the sub-volumes of this rank's items are uploaded - or, if NULL, the CT resident from rtd_set_ct), sums the
+ * partial doses in the group's grid (rank 0 computes into it directly, the others push the 16-byte groups that hold dose with vector
+ * reductions over NVLink; two barriers order "grid zeroed" and "all pushed") and, on rank 0 with hostDoseInOut != NULL, adds the plan's
+ * dose onto the caller's host grid. Returns when this rank's part is complete; on rank 0 the group's grid then holds the plan's dose
+ * (zero outside rtd_dose_slab's slab is NOT guaranteed: only the slab is zeroed and summed). timing: this rank's own. */
+typedef struct { int rank, beam, layerBegin, layerEnd; } rtd_work_item;
+int        rtd_partition(const rtd_beam* beams, int nBeams, const rtd_luts* luts, int world, int chunksPerBeam, rtd_work_item* items, int maxItems);
+int        rtd_dose_slab(const rtd_beam* beams, int nBeams, int nx, int ny, int nz, float convSigmaCutoff, int* z0, int* z1);
+rtd_status rtd_group_create(rtd_ctx* ctx, int rank, int world, size_t nDoseFloats, unsigned char* handle64);
+rtd_status rtd_group_destroy(rtd_ctx* ctx);
+float*     rtd_group_dose(rtd_ctx* ctx);
+rtd_status rtd_group_barrier(rtd_ctx* ctx);
+rtd_status rtd_plan_dose_group(rtd_ctx* ctx, const float* ctHuPlus1000, int nx, int ny, int nz, const rtd_beam* beams, int nBeams,
+                               float* hostDoseInOut, const rtd_opts* opts, rtd_timing* timing);
+
 /* Multi-GPU tail: after the ranks' partial dose grids have been summed on one device (NCCL reduce, issued
  * by the caller on rtd_stream), add the non-zero voxels of dSrc[0..n) onto the caller's HOST dose grid hostDst[0..n)
  * (the accumulate semantics of kernel_wrapper.cu:91-93 for the whole plan). A pinned hostDst is updated in place over

@@ -766,6 +766,28 @@ __global__ void push_nonzero_tail_kernel(const float* __restrict__ src, float* _
     if (i < n && src[i] != 0.0f) atomicAdd(dst + i, src[i]);
 }
 
+// Stream-ordered barrier between the GPUs of a node (rtd_group_*): every rank's stream runs this one-thread kernel at the same
+// point of its sequence. `ctr` lives behind the plan's dose grid on rank 0 (peer-mapped on the other ranks) and only ever counts
+// up: the k-th barrier of the group is over when it has seen k * world arrivals. Everything a rank queued before the barrier
+// (its zeroing of the grid, its reductions into the grid over NVLink) is ordered before its arrival (release at system scope), and
+// nothing queued after it starts before every rank has arrived (acquire). Replaces two 4-byte NCCL all-reduces per plan - each a
+// kernel launch plus a rendezvous - by one remote atomic and a few polls.
+__global__ void group_barrier_kernel(unsigned long long* __restrict__ ctr, const unsigned long long target, int* __restrict__ timedOut,
+                                     const unsigned long long maxNs) {
+    __threadfence_system();
+    asm volatile("red.release.sys.global.add.u64 [%0], 1;" :: "l"(ctr) : "memory");
+    unsigned long long t0, t1, seen;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    for (;;) {
+        asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(seen) : "l"(ctr) : "memory");
+        if (seen >= target) break;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+        if (t1 - t0 > maxNs) { *timedOut = 1; break; }      // a rank never arrived (it failed earlier): give the GPU back
+        __nanosleep(200);
+    }
+    __threadfence_system();
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // One-call host path, CT side (rtd_plan_dose with a page-locked CT): the GPU PULLS the texels a beam's tracer can touch
 // straight out of the caller's host memory (mapped pointer, coalesced reads over PCIe) into the CT array (surface writes).

@@ -51,6 +51,30 @@ __device__ __forceinline__ float ks_erf_pos(float x) {
     return 1.0f - exp2f(x * q);
 }
 
+// The weight table costs as many instructions as the taps for applied radii <= 6: two voxels (rows y, y + 1 of a lane) are evaluated
+// per instruction with packed fp32. h(x) = erf(x) / 2 = 0.5 - 0.5 * 2^(x Q(x)); min and ex2 have no packed form.
+typedef unsigned long long ks_u64;
+__device__ __forceinline__ ks_u64 ks_pk(float lo, float hi) { ks_u64 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ void ks_upk(ks_u64 v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ ks_u64 ks_fma2(ks_u64 a, ks_u64 b, ks_u64 c) { ks_u64 d; asm("fma.rn.ftz.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c)); return d; }
+__device__ __forceinline__ ks_u64 ks_add2(ks_u64 a, ks_u64 b) { ks_u64 d; asm("add.rn.ftz.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+__device__ __forceinline__ ks_u64 ks_mul2(ks_u64 a, ks_u64 b) { ks_u64 d; asm("mul.rn.ftz.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+__device__ __forceinline__ ks_u64 ks_bc(float v) { return ks_pk(v, v); }
+__device__ __forceinline__ ks_u64 ks_half_erf_pos2(ks_u64 x2) {
+    float x0, x1; ks_upk(x2, x0, x1);
+    const ks_u64 x = ks_pk(fminf(x0, 4.0f), fminf(x1, 4.0f));
+    ks_u64 q = ks_bc(-4.223215728e-05f);
+    q = ks_fma2(q, x, ks_bc(4.191363114e-04f));
+    q = ks_fma2(q, x, ks_bc(-1.401739311e-03f));
+    q = ks_fma2(q, x, ks_bc(-9.219333297e-04f));
+    q = ks_fma2(q, x, ks_bc(2.838649414e-02f));
+    q = ks_fma2(q, x, ks_bc(-1.485444903e-01f));
+    q = ks_fma2(q, x, ks_bc(-9.184023738e-01f));
+    q = ks_fma2(q, x, ks_bc(-1.627909660e+00f));
+    float a0, a1; ks_upk(ks_mul2(x, q), a0, a1);
+    return ks_fma2(ks_pk(exp2f(a0), exp2f(a1)), ks_bc(-0.5f), ks_bc(0.5f));
+}
+
 constexpr int KS2_MAXRB = 32;       // largest batch radius (RTD_MAX_SUPERP_R)
 constexpr int KS2_MAXL = 256;
 
@@ -79,11 +103,6 @@ static_assert((ks2_col_pitch(16) - ks2_rows(16)) * 2 * ks2_cols(16) >= KS2_MAXL 
 // Packed fp32 (sm_100: fma.rn.f32x2 -> FFMA2, add.f32x2 -> FADD2; two IEEE fp32 operations per issue slot). The superposition is
 // bound by instruction issue and shared-memory wavefronts, not by the FMA pipe (profiles/r01_ncu_full_ks2.txt: issue-active 56 %,
 // FMA pipe 35 %), so halving the issue slots of the FMA block and of the patch read-modify-write is what pays.
-typedef unsigned long long ks_u64;
-__device__ __forceinline__ ks_u64 ks_pk(float lo, float hi) { ks_u64 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
-__device__ __forceinline__ void ks_upk(ks_u64 v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
-__device__ __forceinline__ ks_u64 ks_fma2(ks_u64 a, ks_u64 b, ks_u64 c) { ks_u64 d; asm("fma.rn.ftz.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c)); return d; }
-__device__ __forceinline__ ks_u64 ks_add2(ks_u64 a, ks_u64 b) { ks_u64 d; asm("add.rn.ftz.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
 __device__ __forceinline__ void ks_fma_lo(ks_u64& c, float a, float b) { float lo, hi; ks_upk(c, lo, hi); lo = fmaf(a, b, lo); c = ks_pk(lo, hi); }
 __device__ __forceinline__ void ks_fma_hi(ks_u64& c, float a, float b) { float lo, hi; ks_upk(c, lo, hi); hi = fmaf(a, b, hi); c = ks_pk(lo, hi); }
 
@@ -125,7 +144,7 @@ __device__ __forceinline__ Ks2G ks2_make_g(const float* __restrict__ t /* &tab[j
     // loaded a second time they cost 6 LDS per column offset and no MOV.
     float g[8], h[6];
 #pragma unroll
-    for (int y = 0; y < 8; ++y) g[y] = t[y * rowStride];
+    for (int y = 0; y < 8; ++y) g[y] = ks_lds_again(t + y * rowStride);
 #pragma unroll
     for (int y = 0; y < 6; ++y) h[y] = ks_lds_again(t + (y + 1) * rowStride);
     Ks2G r;
@@ -179,14 +198,20 @@ __device__ __forceinline__ void ks2_tile(const float* __restrict__ tab, const fl
 #pragma unroll
     for (int k = 0; k <= RB; ++k) e[k] = ks2_load_w(tab + k * 32 + lane, TS * 32, d, ((RB + k + A) & 1) != 0);
     float* const col0 = patch + (lane + RBMAX) * PC + YS;     // the lane's own column (offset j = 0)
+    // the 14 shared-memory words of the next column offset are requested as soon as the FMA block has consumed this one's, so
+    // that they arrive under the patch read-modify-write instead of stalling the head of the next iteration; at the largest radii
+    // the register file has no room for them next to the accumulators (ptxas starts shuffling pairs): there they are loaded in place
+    constexpr bool EARLY_G = RB <= 12;
+    Ks2G g = ks2_make_g(tab + lane, TS * 32);
 #pragma unroll 1
     for (int j = 0; j <= jmax; ++j) {       // jmax = applied radius (<= RB: a radius may run in the body of a larger one)
-        const Ks2G g = ks2_make_g(tab + j * 32 + lane, TS * 32);
+        if (!EARLY_G && j) g = ks2_make_g(tab + j * 32 + lane, TS * 32);
         ks_u64 acc[2 * NV];
 #pragma unroll
         for (int m = 0; m < 2 * NV; ++m) acc[m] = 0ull;
 #pragma unroll
         for (int i = 0; i < W; ++i) ks2_fma8<2 * NV>(acc, g, e[(i < RB) ? (RB - i) : (i - RB)], i + A);
+        if (EARLY_G) g = ks2_make_g(tab + min(j + 1, RB) * 32 + lane, TS * 32);
         // the horizontal weight is symmetric: the same output column goes to patch columns x+j and x-j. Within one phase
         // every lane owns a different column.
         ks2_rmw<NV>(col0 + j * PC, acc);
@@ -269,11 +294,14 @@ ks2_kernel(const Ks2Params p, int* __restrict__ workCounter, int* __restrict__ i
     const int bodyStep = p.bodyStep ? p.bodyStep : (nBig > 0 ? 2 : 1);
     const int R = p.Rx * p.Ry;
     const int bevPitch = p.Rx + 64;
+    // the atomic that hands out the next item is issued a whole item ahead: its L2 round trip (~6 % of the small-radius kernel's
+    // samples when it sat at the head of the loop) is hidden under the current item
+    int itNext = 0;
+    if (lane == 0) itNext = atomicAdd(workCounter, 1);
     for (;;) {
-        int it = 0;
-        if (lane == 0) it = atomicAdd(workCounter, 1);
-        it = __shfl_sync(0xffffffffu, it, 0);
+        int it = __shfl_sync(0xffffffffu, itNext, 0);
         if (it >= nItems * NCH) break;
+        if (lane == 0) itNext = atomicAdd(workCounter, 1);
         const int idx = BIG ? (int)p.bigItems[it] : nItems - 1 - it / NCH;      // deepest slices (largest radii) first
         const int chunk = it % NCH;
         const int kk = idx / p.tiles, tile = idx - kk * p.tiles;
@@ -338,20 +366,27 @@ ks2_kernel(const Ks2Params p, int* __restrict__ workCounter, int* __restrict__ i
             // the 8 rows advance together so that 8 independent polynomial chains are in flight per lane; the argument
             // r (i + 1/2) is advanced by repeated addition
             {
-                float x[8], erfOld[8];
+                ks_u64 x[4], rr[4], hOld[4];
                 float* t = tab + lane;
                 const int rowStride = (body + 1) * 32;
 #pragma unroll
-                for (int y = 0; y < 8; ++y) { x[y] = r[y] * 0.5f; erfOld[y] = ks_erf_pos(x[y]); t[y * rowStride] = erfOld[y]; }
+                for (int pp = 0; pp < 4; ++pp) {
+                    rr[pp] = ks_pk(r[2 * pp], r[2 * pp + 1]);
+                    x[pp] = ks_mul2(rr[pp], ks_bc(0.5f));
+                    hOld[pp] = ks_half_erf_pos2(x[pp]);
+                    float a, b; ks_upk(ks_add2(hOld[pp], hOld[pp]), a, b);
+                    t[(2 * pp) * rowStride] = a; t[(2 * pp + 1) * rowStride] = b;
+                }
 #pragma unroll 1
                 for (int i = 1; i <= rb; ++i) {
                     t += 32;
 #pragma unroll
-                    for (int y = 0; y < 8; ++y) {
-                        x[y] += r[y];
-                        const float erfNew = ks_erf_pos(x[y]);
-                        t[y * rowStride] = 0.5f * (erfNew - erfOld[y]);
-                        erfOld[y] = erfNew;
+                    for (int pp = 0; pp < 4; ++pp) {
+                        x[pp] = ks_add2(x[pp], rr[pp]);
+                        const ks_u64 hNew = ks_half_erf_pos2(x[pp]);
+                        float a, b; ks_upk(ks_fma2(hOld[pp], ks_bc(-1.0f), hNew), a, b);
+                        t[(2 * pp) * rowStride] = a; t[(2 * pp + 1) * rowStride] = b;
+                        hOld[pp] = hNew;
                     }
                 }
                 for (int i = rb + 1; i <= body; ++i) {

@@ -11,6 +11,7 @@
 #include "../../include/rtdose.h"
 #include "kernels.cuh"
 #include "ks2.cuh"
+#include "sharding.hpp"
 
 using namespace rtd;
 
@@ -114,6 +115,13 @@ struct rtd_ctx {
     int smCount = 148;
     int ks2Blocks8 = 0, ks2Blocks16 = 0, ks2Blocks24 = 0, ks2Blocks32 = 0;
     rtd_opts optsLast;
+    // the ranks of a node that compute one plan together (rtd_group_*): ONE dose grid + control block on rank 0, mapped over CUDA IPC
+    int groupRank = -1, groupWorld = 0; size_t groupFloats = 0;
+    float* groupGrid = nullptr;                    // rank 0: own allocation; other ranks: peer mapping
+    unsigned long long* groupCtr = nullptr;        // arrival counter behind the grid (monotonic: barrier k waits for k * world arrivals)
+    unsigned long long groupEpoch = 0;
+    PinBuf groupFlag;                              // [0] = a barrier timed out
+    std::vector<rtd_beam> groupBeams;
 };
 
 namespace {
@@ -635,9 +643,12 @@ bool beamFinish(rtd_ctx* ctx, BeamWs& w, int64_t& updates, int64_t& taps, int& k
     return stats[0] == 0;
 }
 
-rtd_status doseCoreImpl(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* dDose, const rtd_opts& o, rtd_timing* tm,
-                        cudaEvent_t evBegin, cudaEvent_t evEnd, HostIo* io) {
-    int launches = 0;
+struct CallState { int launches = 0, hostSyncs = 1; bool serial = false; cudaEvent_t evXferEnd = nullptr; };
+
+// Everything of a call up to (not including) the final host synchronisation.
+rtd_status doseEnqueue(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* dDose, const rtd_opts& o,
+                       cudaEvent_t evBegin, cudaEvent_t evEnd, HostIo* io, CallState& cs) {
+    int& launches = cs.launches;
     for (int b = 0; b < nBeams; ++b)
         if (const char* why = validateBeam(beams[b], o)) return fail(ctx, RTD_ERR_INVALID, why);
     while ((int)ctx->ws.size() < nBeams) ctx->ws.push_back(new BeamWs());
@@ -657,21 +668,29 @@ rtd_status doseCoreImpl(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* 
     // on its own stream so that the latency-bound stages (tracer, IDD/sigma depth scans) of different beams overlap; on the
     // one-call host path the CT sub-volumes of beam b+1 upload (copy stream) while beam b computes.
     const bool serial = o.serialBeams != 0 || nBeams == 1;
+    cs.serial = serial;
     auto beamStream = [&](int b) -> cudaStream_t {
         if (serial) return ctx->stream;
         const size_t i = size_t(b) % 8;
         while (ctx->bstreams.size() <= i) { cudaStream_t s_; cudaStreamCreateWithFlags(&s_, cudaStreamNonBlocking); ctx->bstreams.push_back(s_); }
         return ctx->bstreams[i];
     };
+    int& hostSyncs = cs.hostSyncs;
+    cudaEvent_t evDoseIn = ev(ctx, 6);
+    const bool stagedDose = io && io->dose && !io->zeroCopy;      // pageable host grid: the transfers need its sub-volumes on the device first
+    bool doseInWaited = false;
     for (int b = 0; b < nBeams; ++b) {
         cudaStream_t st = beamStream(b);
         if (st != ctx->stream) RTD_CUDA(cudaStreamWaitEvent(st, evBegin, 0));
         rtd_status s = beamEnqueue(ctx, b, beams[b], *ctx->ws[b], o, launches, st, io);
         if (s != RTD_OK) return s;
+        if (!stagedDose) {
+            s = beamTransfer(ctx, b, *ctx->ws[b], dDose, launches, st, io, evDoseIn, doseInWaited);
+            if (s != RTD_OK) return s;
+            if (st != ctx->stream) { cudaEvent_t e = evBeam(ctx, b, 8); RTD_CUDA(cudaEventRecord(e, st)); RTD_CUDA(cudaStreamWaitEvent(ctx->stream, e, 0)); }
+        }
     }
-    int hostSyncs = 1;
-    cudaEvent_t evDoseIn = ev(ctx, 6);
-    if (io && io->dose && !io->zeroCopy) {
+    if (stagedDose) {
         // pageable host dose grid: the sub-volumes the transfers can touch are staged through device memory, and their boxes
         // need the transfer boxes on the host - the one case that still waits for the set-up kernels in the middle of a call.
         // Every box is uploaded before the first transfer, so overlapping boxes of different beams are harmless.
@@ -680,15 +699,15 @@ rtd_status doseCoreImpl(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* 
         for (int b = 0; b < nBeams; ++b) { BeamWs& w = *ctx->ws[b]; w.bfi = w.hostDev.bfi; w.Zg = w.hostDev.Zg; doseBoxesOfBeam(w, ctx->doseDims, ctx->doseBoxes); }
         for (const Box& bx : ctx->doseBoxes) { RTD_CUDA(copyDoseBox(ctx, io->dose, dDose, bx, true, ctx->cstream)); io->h2d += boxVoxels(bx) * 4; }
         RTD_CUDA(cudaEventRecord(evDoseIn, ctx->cstream));
-    }
-    bool doseInWaited = false;
-    for (int b = 0; b < nBeams; ++b) {
-        cudaStream_t st = beamStream(b);
-        rtd_status s = beamTransfer(ctx, b, *ctx->ws[b], dDose, launches, st, io, evDoseIn, doseInWaited);
-        if (s != RTD_OK) return s;
-        if (st != ctx->stream) { cudaEvent_t e = evBeam(ctx, b, 8); RTD_CUDA(cudaEventRecord(e, st)); RTD_CUDA(cudaStreamWaitEvent(ctx->stream, e, 0)); }
+        for (int b = 0; b < nBeams; ++b) {
+            cudaStream_t st = beamStream(b);
+            rtd_status s = beamTransfer(ctx, b, *ctx->ws[b], dDose, launches, st, io, evDoseIn, doseInWaited);
+            if (s != RTD_OK) return s;
+            if (st != ctx->stream) { cudaEvent_t e = evBeam(ctx, b, 8); RTD_CUDA(cudaEventRecord(e, st)); RTD_CUDA(cudaStreamWaitEvent(ctx->stream, e, 0)); }
+        }
     }
     cudaEvent_t evXferEnd = ev(ctx, 7);
+    cs.evXferEnd = evXferEnd;
     RTD_CUDA(cudaEventRecord(evXferEnd, ctx->stream));
     RTD_CUDA(cudaMemcpyAsync(ctx->hXferCount.p, ctx->xferCount.p, 16, cudaMemcpyDeviceToHost, ctx->stream));
     if (io && io->dose && !io->zeroCopy) {
@@ -696,7 +715,13 @@ rtd_status doseCoreImpl(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* 
         for (const Box& bx : ctx->doseBoxes) { RTD_CUDA(copyDoseBox(ctx, io->dose, dDose, bx, false, ctx->stream)); io->d2h += boxVoxels(bx) * 4; }
     }
     RTD_CUDA(cudaEventRecord(evEnd, ctx->stream));
-    RTD_CUDA(cudaStreamSynchronize(ctx->stream));                         // the one host sync of a plan
+    return RTD_OK;
+}
+
+// After the call's one host synchronisation: reports, counters, timing.
+rtd_status doseFinish(rtd_ctx* ctx, int nBeams, rtd_timing* tm, cudaEvent_t evBegin, cudaEvent_t evEnd, HostIo* io, const CallState& cs) {
+    const int launches = cs.launches, hostSyncs = cs.hostSyncs;
+    cudaEvent_t evXferEnd = cs.evXferEnd;
     int64_t updates = 0, taps = 0; bool ok = true; int ksLaunches = 0;
     for (int b = 0; b < nBeams; ++b) ok = beamFinish(ctx, *ctx->ws[b], updates, taps, ksLaunches) && ok;
     const int64_t modified = (int64_t)*ctx->hXferCount.as<unsigned long long>();
@@ -727,6 +752,15 @@ rtd_status doseCoreImpl(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* 
     }
     if (!ok) return fail(ctx, RTD_ERR_RADIUS, "Found larger than allowed kernel superposition radius");
     return RTD_OK;
+}
+
+rtd_status doseCoreImpl(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* dDose, const rtd_opts& o, rtd_timing* tm,
+                        cudaEvent_t evBegin, cudaEvent_t evEnd, HostIo* io) {
+    CallState cs;
+    rtd_status s = doseEnqueue(ctx, beams, nBeams, dDose, o, evBegin, evEnd, io, cs);
+    if (s != RTD_OK) return s;
+    RTD_CUDA(cudaStreamSynchronize(ctx->stream));                         // the one host sync of a plan
+    return doseFinish(ctx, nBeams, tm, evBegin, evEnd, io, cs);
 }
 
 // A failure in the middle of a plan leaves work queued on the per-beam streams and the copy stream: drain them all before the
@@ -1017,6 +1051,149 @@ rtd_status rtd_push_dose_to_peer(rtd_ctx* ctx, const float* dSrc, float* dPeerDs
     if (n & 3) push_nonzero_tail_kernel<<<1, 32, 0, ctx->stream>>>(dSrc + n4 * 4, dPeerDst + n4 * 4, (int)(n & 3));
     RTD_CUDA(cudaGetLastError());
     return RTD_OK;
+}
+
+// ---- one plan on the GPUs of a node: partition, barriers and the sum of the partial doses behind the C ABI ---------------
+int rtd_partition(const rtd_beam* beams, int nBeams, const rtd_luts* luts, int world, int chunksPerBeam, rtd_work_item* items, int maxItems) {
+    if (nBeams < 0 || (nBeams > 0 && !beams) || !luts || !luts->energiesPerU || !luts->peakDepths || luts->nEnergies < 2 || world < 1) return -1;
+    for (int b = 0; b < nBeams; ++b) if (beams[b].nLayers <= 0 || !beams[b].energies) return -1;
+    const std::vector<WorkItem> v = partitionPlan(beams, nBeams, luts->energiesPerU, luts->peakDepths, luts->nEnergies, world, chunksPerBeam);
+    for (size_t i = 0; i < v.size() && (int)i < maxItems && items; ++i) { items[i].rank = v[i].rank; items[i].beam = v[i].beam; items[i].layerBegin = v[i].lo; items[i].layerEnd = v[i].hi; }
+    return (int)v.size();
+}
+
+int rtd_dose_slab(const rtd_beam* beams, int nBeams, int nx, int ny, int nz, float convSigmaCutoff, int* z0, int* z1) {
+    if (nBeams < 0 || (nBeams > 0 && !beams) || nx <= 0 || ny <= 0 || nz <= 0 || !z0 || !z1) return -1;
+    for (int b = 0; b < nBeams; ++b) if (beams[b].nLayers <= 0 || !beams[b].sigmas) return -1;
+    const int dims[3] = {nx, ny, nz};
+    return doseSlab(beams, nBeams, dims, convSigmaCutoff, *z0, *z1) ? 1 : 0;
+}
+
+rtd_status rtd_group_destroy(rtd_ctx* ctx) {
+    if (!ctx) return RTD_ERR_INVALID;
+    if (!ctx->groupGrid) return RTD_OK;
+    RTD_CUDA(cudaSetDevice(ctx->device));
+    RTD_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (ctx->groupRank == 0) RTD_CUDA(cudaFree(ctx->groupGrid)); else RTD_CUDA(cudaIpcCloseMemHandle(ctx->groupGrid));
+    ctx->groupGrid = nullptr; ctx->groupCtr = nullptr; ctx->groupRank = -1; ctx->groupWorld = 0; ctx->groupFloats = 0; ctx->groupEpoch = 0;
+    return RTD_OK;
+}
+
+rtd_status rtd_group_create(rtd_ctx* ctx, int rank, int world, size_t nDoseFloats, unsigned char* handle64) {
+    if (!ctx) return RTD_ERR_INVALID;
+    if (!handle64 || world < 1 || rank < 0 || rank >= world || nDoseFloats == 0) return fail(ctx, RTD_ERR_INVALID, "rtd_group_create: bad arguments");
+    rtd_status s = rtd_group_destroy(ctx);
+    if (s != RTD_OK) return s;
+    RTD_CUDA(cudaSetDevice(ctx->device));
+    const size_t gridBytes = (nDoseFloats * 4 + 255) / 256 * 256;
+    void* p = nullptr;
+    if (rank == 0) {
+        RTD_CUDA(cudaMalloc(&p, gridBytes + 256));
+        cudaIpcMemHandle_t h;
+        cudaError_t e = cudaSuccess;
+        if (world > 1) e = cudaIpcGetMemHandle(&h, p); else memset(&h, 0, sizeof h);
+        if (e != cudaSuccess) { cudaFree(p); char b[256]; snprintf(b, sizeof b, "cudaIpcGetMemHandle: %s", cudaGetErrorString(e)); return fail(ctx, RTD_ERR_CUDA, b); }
+        RTD_CUDA(cudaMemsetAsync(p, 0, gridBytes + 256, ctx->stream));
+        RTD_CUDA(cudaStreamSynchronize(ctx->stream));
+        memcpy(handle64, &h, 64);
+    } else {
+        cudaIpcMemHandle_t h; memcpy(&h, handle64, 64);
+        RTD_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    }
+    RTD_CUDA(ctx->groupFlag.ensure(64));
+    memset(ctx->groupFlag.p, 0, 64);
+    ctx->groupGrid = (float*)p; ctx->groupCtr = (unsigned long long*)((char*)p + gridBytes);
+    ctx->groupRank = rank; ctx->groupWorld = world; ctx->groupFloats = nDoseFloats; ctx->groupEpoch = 0;
+    return RTD_OK;
+}
+
+float* rtd_group_dose(rtd_ctx* ctx) { return ctx ? ctx->groupGrid : nullptr; }
+
+static rtd_status groupBarrierEnqueue(rtd_ctx* ctx) {
+    if (ctx->groupWorld <= 1) return RTD_OK;
+    ++ctx->groupEpoch;
+    group_barrier_kernel<<<1, 1, 0, ctx->stream>>>(ctx->groupCtr, ctx->groupEpoch * (unsigned long long)ctx->groupWorld, ctx->groupFlag.as<int>(),
+                                                   10ull * 1000 * 1000 * 1000);
+    RTD_CUDA(cudaGetLastError());
+    return RTD_OK;
+}
+
+rtd_status rtd_group_barrier(rtd_ctx* ctx) {
+    if (!ctx) return RTD_ERR_INVALID;
+    if (!ctx->groupGrid) return fail(ctx, RTD_ERR_STATE, "rtd_group_barrier: no group (rtd_group_create)");
+    RTD_CUDA(cudaSetDevice(ctx->device));
+    return groupBarrierEnqueue(ctx);
+}
+
+rtd_status rtd_plan_dose_group(rtd_ctx* ctx, const float* ct, int nx, int ny, int nz, const rtd_beam* beams, int nBeams, float* hostDoseInOut,
+                               const rtd_opts* opts, rtd_timing* tm) {
+    if (!ctx) return RTD_ERR_INVALID;
+    if (!ctx->groupGrid) return fail(ctx, RTD_ERR_STATE, "rtd_plan_dose_group: no group (rtd_group_create)");
+    if (!ctx->haveLuts || !ctx->haveDose) return fail(ctx, RTD_ERR_STATE, "rtd_plan_dose_group: LUTs and dose grid must be set first");
+    if (nBeams < 0 || (nBeams > 0 && !beams)) return fail(ctx, RTD_ERR_INVALID, "rtd_plan_dose_group: bad beams");
+    const size_t nGrid = size_t(ctx->doseDims[0]) * ctx->doseDims[1] * ctx->doseDims[2];
+    if (nGrid != ctx->groupFloats) return fail(ctx, RTD_ERR_INVALID, "rtd_plan_dose_group: the group's grid does not have the dose grid's size");
+    RTD_CUDA(cudaSetDevice(ctx->device));
+    rtd_opts o; if (opts) o = *opts; else rtd_default_opts(&o);
+    for (int b = 0; b < nBeams; ++b)
+        if (const char* why = validateBeam(beams[b], o)) return fail(ctx, RTD_ERR_INVALID, why);
+    if (ct) {
+        if (nx <= 0 || ny <= 0 || nz <= 0) return fail(ctx, RTD_ERR_INVALID, "rtd_plan_dose_group: non-positive CT dims");
+        rtd_status s = ensureCtArray(ctx, nx, ny, nz);
+        if (s != RTD_OK) return s;
+        ctx->haveCt = true; ctx->ctPartial = true;
+    } else {
+        if (!ctx->haveCt || ctx->ctPartial) return fail(ctx, RTD_ERR_STATE, "rtd_plan_dose_group: no CT given and no complete CT resident (rtd_set_ct)");
+    }
+    const int rank = ctx->groupRank, world = ctx->groupWorld;
+    // this rank's work items: the same partition on every rank (a pure function of the plan)
+    const std::vector<WorkItem> items = partitionPlan(beams, nBeams, ctx->energies.data(), ctx->peakDepths.data(), ctx->nEnergies, world, 0);
+    ctx->groupBeams.clear();
+    for (const WorkItem& it : items) {
+        if (it.rank != rank) continue;
+        rtd_beam b = beams[it.beam];
+        if (!(it.lo == 0 && it.hi == b.nLayers)) { b.layerBegin = it.lo; b.layerEnd = it.hi; } else { b.layerBegin = 0; b.layerEnd = 0; }
+        ctx->groupBeams.push_back(b);
+    }
+    int z0 = 0, z1 = -1;
+    const bool haveSlab = doseSlab(beams, nBeams, ctx->doseDims, o.convSigmaCutoff, z0, z1);
+    const size_t sliceFloats = size_t(ctx->doseDims[0]) * ctx->doseDims[1];
+    const size_t slabOff = haveSlab ? size_t(z0) * sliceFloats : 0, slabN = haveSlab ? size_t(z1 - z0 + 1) * sliceFloats : 0;
+    float* target = ctx->groupGrid;
+    if (rank != 0) { RTD_CUDA(ctx->dose.ensure(nGrid * 4)); target = ctx->dose.as<float>(); }
+    cudaEvent_t evBegin = ev(ctx, 0), evEnd = ev(ctx, 1), evAll = ev(ctx, 3), evStart = ev(ctx, 4);
+    RTD_CUDA(cudaEventRecord(evStart, ctx->stream));
+    if (slabN) RTD_CUDA(cudaMemsetAsync(target + slabOff, 0, slabN * 4, ctx->stream));
+    rtd_status s = groupBarrierEnqueue(ctx);                 // the plan's grid is zeroed before anything is added into it
+    if (s != RTD_OK) return s;
+    // rank 0 computes straight into the plan's grid while the pushes of the others may land in it: its transfers add atomically
+    o.atomicDose = (rank == 0 && world > 1) ? 1 : o.atomicDose;
+    HostIo io; io.ct = ct;
+    CallState cs;
+    s = doseEnqueue(ctx, ctx->groupBeams.data(), (int)ctx->groupBeams.size(), target, o, evBegin, evEnd, ct ? &io : nullptr, cs);
+    if (s == RTD_OK && rank != 0 && slabN) s = rtd_push_dose_to_peer(ctx, target + slabOff, ctx->groupGrid + slabOff, slabN);
+    if (s == RTD_OK) s = groupBarrierEnqueue(ctx);           // every rank's contribution has landed
+    int64_t modified = 0;
+    if (s == RTD_OK && rank == 0 && hostDoseInOut && slabN) {
+        // the summed slab goes onto the caller's host grid (accumulate semantics, cu:542, 91-93): in place over PCIe if it is pinned
+        s = rtd_add_device_to_host(ctx, ctx->groupGrid + slabOff, hostDoseInOut + slabOff, slabN, &modified);
+    }
+    if (s == RTD_OK) { cudaError_t e = cudaEventRecord(evAll, ctx->stream); if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream); if (e != cudaSuccess) s = fail(ctx, RTD_ERR_CUDA, cudaGetErrorString(e)); }
+    if (s != RTD_OK) {
+        const std::string msg = ctx->err;
+        for (cudaStream_t bs : ctx->bstreams) cudaStreamSynchronize(bs);
+        cudaStreamSynchronize(ctx->cstream); cudaStreamSynchronize(ctx->stream); cudaGetLastError();
+        ctx->err = msg;
+        return s;
+    }
+    if (ctx->groupFlag.as<int>()[0]) { ctx->groupFlag.as<int>()[0] = 0; return fail(ctx, RTD_ERR_CUDA, "rtd_plan_dose_group: a rank of the group did not reach the barrier within 10 s"); }
+    s = doseFinish(ctx, (int)ctx->groupBeams.size(), tm, evBegin, evEnd, ct ? &io : nullptr, cs);
+    if (tm) {
+        float ms = 0; cudaEventElapsedTime(&ms, evStart, evAll); tm->msTotal = ms;      // zeroing, barriers, push and host tail included
+        if (modified) { tm->h2dBytes += modified * 4; tm->d2hBytes += modified * 4; tm->doseVoxelsModified = modified; }
+        tm->kernelLaunches += (world > 1 ? 2 : 0) + ((rank != 0 && slabN) ? 1 : 0) + ((rank == 0 && hostDoseInOut && slabN) ? 1 : 0);
+    }
+    return s;
 }
 
 rtd_status rtd_get_beam_report(const rtd_ctx* ctx, int beamNo, rtd_beam_report* out) {

@@ -86,6 +86,10 @@ class RtdLayerReport(C.Structure):
         return d
 
 
+class RtdWorkItem(C.Structure):
+    _fields_ = [("rank", C.c_int), ("beam", C.c_int), ("layerBegin", C.c_int), ("layerEnd", C.c_int)]
+
+
 class RtdError(RuntimeError):
     def __init__(self, status: int, msg: str):
         super().__init__(f"{STATUS.get(status, status)}: {msg}")
@@ -93,7 +97,7 @@ class RtdError(RuntimeError):
 
 
 EXPORTS = ["rtd_default_opts", "rtd_create", "rtd_create_on_stream", "rtd_destroy", "rtd_last_error", "rtd_version", "rtd_set_luts", "rtd_set_ct",
-           "rtd_set_ct_device", "rtd_set_dose_grid", "rtd_dose", "rtd_dose_device", "rtd_plan_dose", "rtd_plan_dose_device", "rtd_add_device_to_host", "rtd_shared_dose_create", "rtd_shared_dose_open", "rtd_shared_dose_close", "rtd_push_dose_to_peer",
+           "rtd_set_ct_device", "rtd_set_dose_grid", "rtd_dose", "rtd_dose_device", "rtd_plan_dose", "rtd_plan_dose_device", "rtd_add_device_to_host", "rtd_partition", "rtd_dose_slab", "rtd_group_create", "rtd_group_destroy", "rtd_group_dose", "rtd_group_barrier", "rtd_plan_dose_group", "rtd_shared_dose_create", "rtd_shared_dose_open", "rtd_shared_dose_close", "rtd_push_dose_to_peer",
            "rtd_get_beam_report",
            "rtd_get_layer_report", "rtd_debug_fetch", "rtd_debug_ct_boxes", "rtd_stream"]
 
@@ -130,6 +134,14 @@ def load_library() -> C.CDLL:
     lib.rtd_shared_dose_open.argtypes = [vp, C.c_char_p, C.POINTER(vp)]; lib.rtd_shared_dose_open.restype = C.c_int
     lib.rtd_shared_dose_close.argtypes = [vp, vp, C.c_int]; lib.rtd_shared_dose_close.restype = C.c_int
     lib.rtd_push_dose_to_peer.argtypes = [vp, vp, vp, C.c_size_t]; lib.rtd_push_dose_to_peer.restype = C.c_int
+    lib.rtd_partition.argtypes = [C.POINTER(RtdBeam), C.c_int, C.POINTER(RtdLuts), C.c_int, C.c_int, C.POINTER(RtdWorkItem), C.c_int]; lib.rtd_partition.restype = C.c_int
+    lib.rtd_dose_slab.argtypes = [C.POINTER(RtdBeam), C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.POINTER(C.c_int), C.POINTER(C.c_int)]; lib.rtd_dose_slab.restype = C.c_int
+    lib.rtd_group_create.argtypes = [vp, C.c_int, C.c_int, C.c_size_t, C.c_char_p]; lib.rtd_group_create.restype = C.c_int
+    lib.rtd_group_destroy.argtypes = [vp]; lib.rtd_group_destroy.restype = C.c_int
+    lib.rtd_group_dose.argtypes = [vp]; lib.rtd_group_dose.restype = vp
+    lib.rtd_group_barrier.argtypes = [vp]; lib.rtd_group_barrier.restype = C.c_int
+    lib.rtd_plan_dose_group.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.POINTER(RtdBeam), C.c_int, vp, C.POINTER(RtdOpts), C.POINTER(RtdTiming)]
+    lib.rtd_plan_dose_group.restype = C.c_int
     lib.rtd_get_beam_report.argtypes = [vp, C.c_int, C.POINTER(RtdBeamReport)]; lib.rtd_get_beam_report.restype = C.c_int
     lib.rtd_get_layer_report.argtypes = [vp, C.c_int, C.c_int, C.POINTER(RtdLayerReport)]; lib.rtd_get_layer_report.restype = C.c_int
     lib.rtd_debug_fetch.argtypes = [vp, C.c_int, C.c_int, C.c_int, vp, C.c_size_t]; lib.rtd_debug_fetch.restype = C.c_int
@@ -168,6 +180,44 @@ def pack_beams(beams: Sequence[Beam]):
         rb.gantryToDoseIdxV = (C.c_float * 3)(*_f32(b.gantry_to_dose_v).ravel())
         rb.layerBegin, rb.layerEnd = getattr(b, "layer_begin", 0), getattr(b, "layer_end", 0)
     return arr, keep
+
+
+def pack_luts(e: EnergyStruct):
+    """EnergyStruct -> (rtd_luts, keep-alive list)."""
+    arrs = [_f32(e.energiesPerU), _f32(e.peakDepths), _f32(e.scaleFacts), _f32(e.ciddMatrix), _f32(e.densityVector),
+            _f32(e.spVector), _f32(e.rRlVector)]
+    l = RtdLuts(e.nEnergySamples, e.nEnergies, _ptr(arrs[0]), _ptr(arrs[1]), _ptr(arrs[2]), _ptr(arrs[3]),
+                e.nDensitySamples, e.densityScaleFact, _ptr(arrs[4]), e.nSpSamples, e.spScaleFact, _ptr(arrs[5]),
+                e.nRRlSamples, e.rRlScaleFact, _ptr(arrs[6]))
+    return l, arrs
+
+
+def partition(beams: Sequence[Beam], luts: EnergyStruct, world_size: int, chunks_per_beam: int = 0):
+    """(rank, beam, first layer, one-past-last layer) work items of the plan on ``world_size`` ranks (rtd_partition: the
+    partitioner rtd_plan_dose_group itself uses; host only, no device needed)."""
+    lib = load_library()
+    arr, keep = pack_beams(beams)
+    l, keep2 = pack_luts(luts)
+    n = lib.rtd_partition(arr, len(beams), C.byref(l), int(world_size), int(chunks_per_beam), None, 0)
+    if n < 0:
+        raise ValueError("rtd_partition: bad plan / LUTs / world size")
+    items = (RtdWorkItem * max(n, 1))()
+    lib.rtd_partition(arr, len(beams), C.byref(l), int(world_size), int(chunks_per_beam), items, n)
+    del keep, keep2
+    return [(it.rank, it.beam, it.layerBegin, it.layerEnd) for it in items[:n]]
+
+
+def dose_slab(beams: Sequence[Beam], dose_dims_xyz, sigma_cutoff: float = 3.0):
+    """Inclusive z-slab (z0, z1) of the dose grid the plan can reach, (0, -1) if none (rtd_dose_slab; host only)."""
+    lib = load_library()
+    arr, keep = pack_beams(beams)
+    z0, z1 = C.c_int(0), C.c_int(-1)
+    nx, ny, nz = (int(v) for v in dose_dims_xyz)
+    r = lib.rtd_dose_slab(arr, len(beams), nx, ny, nz, float(sigma_cutoff), C.byref(z0), C.byref(z1))
+    if r < 0:
+        raise ValueError("rtd_dose_slab: bad plan / dims")
+    del keep
+    return (int(z0.value), int(z1.value)) if r == 1 else (0, -1)
 
 
 def ct_boxes(beam: Beam, ct_dims_xyz) -> np.ndarray:
@@ -230,11 +280,7 @@ class DoseEngine:
 
     def set_luts(self, e: EnergyStruct):
         e.validate()
-        arrs = [_f32(e.energiesPerU), _f32(e.peakDepths), _f32(e.scaleFacts), _f32(e.ciddMatrix), _f32(e.densityVector),
-                _f32(e.spVector), _f32(e.rRlVector)]
-        l = RtdLuts(e.nEnergySamples, e.nEnergies, _ptr(arrs[0]), _ptr(arrs[1]), _ptr(arrs[2]), _ptr(arrs[3]),
-                    e.nDensitySamples, e.densityScaleFact, _ptr(arrs[4]), e.nSpSamples, e.spScaleFact, _ptr(arrs[5]),
-                    e.nRRlSamples, e.rRlScaleFact, _ptr(arrs[6]))
+        l, arrs = pack_luts(e)
         self._check(self.lib.rtd_set_luts(self._h, C.byref(l)))
 
     def set_ct(self, ct: np.ndarray):
@@ -287,6 +333,28 @@ class DoseEngine:
         m = C.c_int64(0)
         self._check(self.lib.rtd_add_device_to_host(self._h, C.c_void_p(d_src_ptr), C.c_void_p(host_dst_ptr), n, C.byref(m)))
         return int(m.value)
+
+    # ---- one plan on the GPUs of a node (rtd_group_*) ----
+    def group_create(self, rank: int, world: int, n_dose_floats: int, handle: Optional[bytes] = None) -> bytes:
+        """Rank 0 creates the plan's dose grid and returns its 64-byte IPC handle; the other ranks pass that handle in."""
+        h = C.create_string_buffer(handle if handle is not None else b"\0" * 64, 64)
+        self._check(self.lib.rtd_group_create(self._h, int(rank), int(world), int(n_dose_floats), h))
+        return h.raw
+
+    def group_destroy(self):
+        self._check(self.lib.rtd_group_destroy(self._h))
+
+    def group_dose_ptr(self) -> int:
+        return int(self.lib.rtd_group_dose(self._h) or 0)
+
+    def group_barrier(self):
+        self._check(self.lib.rtd_group_barrier(self._h))
+
+    def plan_dose_group(self, ct_ptr: int, nx: int, ny: int, nz: int, packed, n_beams: int, host_dose_ptr: int = 0) -> RtdTiming:
+        """This rank's share of the WHOLE plan ``packed`` (rtd_plan_dose_group). ct_ptr = 0: the CT resident from set_ct."""
+        self._check(self.lib.rtd_plan_dose_group(self._h, C.c_void_p(ct_ptr) if ct_ptr else None, nx, ny, nz, packed, n_beams,
+                                                 C.c_void_p(host_dose_ptr) if host_dose_ptr else None, C.byref(self.opts), C.byref(self.timing)))
+        return self.timing
 
     def shared_dose_create(self, n_floats: int):
         """(device pointer, 64-byte IPC handle) of a zeroed dose grid other ranks of the node can map (rtd_shared_dose_create)."""

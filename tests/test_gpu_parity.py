@@ -165,7 +165,7 @@ def test_full_size_properties(eng, c3):
     assert whole.max() > 0 and np.isfinite(whole).all()
     reps = [eng.beam_report(b) for b in range(3)]
     assert t["updates"] == sum(r["updates"] for r in reps) > 5e7
-    assert t["hostSyncs"] == 1             # cut-offs, per-layer parameters and the transfer box are derived on the device
+    assert t["hostSyncs"] == 2             # pageable host dose grid: its sub-volumes need the transfer boxes on the host
     # (1) run-to-run: only fp32 atomic order differs
     again, _ = run_case(eng, c3)
     assert rel_to_max(again, whole)[0] <= 2e-6
@@ -202,7 +202,8 @@ def test_device_pointer_api_matches_host_api(eng, mini_case):
     torch.cuda.synchronize()
     eng.set_ct_ptr(ct.data_ptr(), mini_case.ct.shape[2], mini_case.ct.shape[1], mini_case.ct.shape[0], device=True)
     packed, keep = engine.pack_beams(mini_case.beams)
-    eng.dose_ptr(packed, len(mini_case.beams), d.data_ptr(), device=True)
+    t = eng.dose_ptr(packed, len(mini_case.beams), d.data_ptr(), device=True)
+    assert t.hostSyncs == 1                # cut-offs, per-layer parameters and the transfer box are derived on the device
     assert rel_to_max(d.cpu().numpy(), host)[0] <= 2e-6
 
 
@@ -488,3 +489,26 @@ def test_invalid_beams_are_rejected_before_anything_runs(eng, mini_case):
         assert np.all(d == 2.0)
     d, _ = run_case(eng, mini_case)
     assert d.max() > 0
+
+
+@pytest.mark.parametrize("mode", ["device", "host"])
+def test_group_api_two_ranks_share_one_grid(eng, mini_case, tmp_path, mode):
+    """rtd_group_create / rtd_plan_dose_group with TWO processes (both on this one GPU: CUDA IPC between processes, the barrier
+    kernels of the two contexts time-sliced by the driver): the library partitions the plan, every rank computes its own work
+    items, rank 1 pushes its slab into rank 0's grid over the peer mapping, two device-memory barriers order it. The group's
+    grid equals the single-context dose; update counts of the ranks add up; the host-CT variant also adds the plan's dose onto
+    rank 0's host grid (accumulate semantics)."""
+    whole, t = run_case(eng, mini_case)
+    procs = [subprocess.Popen([sys.executable, os.path.join(ROOT, "tools", "group_rank.py"), str(r), "2", "mini", "0", str(tmp_path), mode],
+                              stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True) for r in range(2)]
+    outs = [p.communicate(timeout=300) for p in procs]
+    for p, (so, se) in zip(procs, outs):
+        assert p.returncode == 0, se[-2000:]
+    grid = np.load(tmp_path / "group_dose.npy")
+    assert rel_to_max(grid, whole)[0] <= 5e-6
+    assert int(open(tmp_path / "done_0.txt").read()) + int(open(tmp_path / "done_1.txt").read()) == t["updates"]
+    if mode == "host":
+        host = np.load(tmp_path / "host_dose.npy")
+        assert np.all(host[whole == 0] == 0.25)
+        # two calls, each adding the plan's dose onto the caller's grid
+        assert rel_to_max(host.astype(np.float64) - 0.25, 2.0 * whole)[0] <= 1e-5 + 6.0e-8 / float(whole.max())
