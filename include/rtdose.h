@@ -57,6 +57,9 @@ typedef struct {
     int nDensitySamples; float densityScaleFact; const float* densityVector;   /* HU+1000 -> g/cm3 */
     int nSpSamples;      float spScaleFact;      const float* spVector;        /* HU+1000 -> relative stopping power */
     int nRRlSamples;     float rRlScaleFact;     const float* rRlVector;       /* density*scale -> 1/X0 */
+    /* NUCLEAR_CORR builds only (src/energy_struct.h:33-36, read by src/energy_reader.cpp:103-162): optional, NULL otherwise */
+    const float* nucWeightMatrix;    /* [nEnergies][nEnergySamples] share of the dose attributed to the nuclear halo */
+    const float* nucSqSigmaMatrix;   /* [nEnergies][nEnergySamples] variance of the halo (accepted, not used: see rtd_opts.nuclearCorr) */
 } rtd_luts;
 
 /* POD mirror of BeamSettings (reference: src/beam_settings.h:101-109; ctor :32). */
@@ -100,6 +103,14 @@ typedef struct {
                                 interval the tracers can touch crosses PCIe (C3: 51 MB instead of 60 MB of boxes). Measured SLOWER end to
                                 end on B200 (3.2 vs 2.9 ms: the pull kernels compete with the dose kernels for SMs, the copy engines do
                                 not), so the default 0 keeps the axis-aligned sub-volume copies */
+    int   nuclearCorr;       /* the reference's NUCLEAR_CORR build option (CMakeLists.txt:57-79) as shipped: 0 = off (its default), 1 = SOUKUP,
+                                2 = FLUKA, 3 = GAUSS_FIT (the reference numbers them 0 / 1 / 2). Needs rtd_luts.nucWeightMatrix of that model.
+                                What the option does in the reference: E_s and the empirical widening of the depth scan change per model
+                                (kernel_wrapper.cu:232-240), GAUSS_FIT drops the post-peak sigma correction (cu:300-302) and shrinks the entry
+                                sigmas by 3 % (cu:842-847), and the primary dose is scaled by 1 - nucWeight (cu:320-341). Its halo pass is
+                                constructed with nucMemoryStep = 0 (cu:925), so every depth step of a halo pencil beam lands in BEV slice 0 and
+                                the second superposition / nucTransfDiv (cu:978-996, 1058-1092, 1220-1255) deposit nothing unless the beam's
+                                first live step is step 0; that one case (beamFirstInside == 0) is rejected with RTD_ERR_INVALID */
     int   fullIntermediates; /* 1: the depth scan writes idd / rSigmaEff of EVERY (ray, step) as the reference does, for rtd_debug_fetch
                                 (RTD_FETCH_IDD / RTD_FETCH_RSIGMA). 0 (default): 32-ray row segments that hold no dose at a step are
                                 not written (the superposition never reads them; ~60 % of the scan's HBM writes on a head plan) and

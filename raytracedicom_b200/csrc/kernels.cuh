@@ -189,6 +189,7 @@ struct LayerParams {          // per-layer constants, kernel_wrapper.cu:829-849,
 };
 struct LayerIn {              // what the host knows about a layer before the tracer has run
     float energyIdx, energyScale, peakDepth, thr /* BP_DEPTH_CUTOFF x peakDepth */, ca, cb /* sigmaSqAirCoefs, host IEEE */, sigX, sigY;
+    float sigScale;           // 0.97 for NUCLEAR_CORR == GAUSS_FIT (kernel_wrapper.cu:842-847), else 1
 };
 struct GridParams {
     TransferParams t;
@@ -255,7 +256,9 @@ beam_setup_kernel(const SetupIn in, const int* __restrict__ trace, const LayerIn
         const LayerIn li = lin[l];
         // entry sigma (cu:838-841): sqrt(ca z^2 + cb z + sigma^2), host arithmetic
         const float air = ieee::add(ieee::mul(ieee::mul(li.ca, entryZ), entryZ), ieee::mul(li.cb, entryZ));
-        sigmas[l] = make_float2(__fsqrt_rn(ieee::add(air, ieee::mul(li.sigX, li.sigX))), __fsqrt_rn(ieee::add(air, ieee::mul(li.sigY, li.sigY))));
+        float2 es = make_float2(__fsqrt_rn(ieee::add(air, ieee::mul(li.sigX, li.sigX))), __fsqrt_rn(ieee::add(air, ieee::mul(li.sigY, li.sigY))));
+        if (li.sigScale != 1.0f) { es.x = ieee::mul(li.sigScale, es.x); es.y = ieee::mul(li.sigScale, es.y); }
+        sigmas[l] = es;
         const unsigned localAfterLast = (unsigned)ieee::firstLargerOrdered(weplMin, in.S, li.thr);     // cu:922-924
         sAfter[l] = (int)min(localAfterLast, (unsigned)Zg);
     }
@@ -384,6 +387,8 @@ struct IddParams {
     int Rx, Ry;
     int nozzle;               // 0 = the reference's -DNO_NOZZLE build (fill_idd_and_sigma_params.cu:76-82)
     int doseToMedium;         // 1 = the reference built without -DDOSE_TO_WATER (kernel_wrapper.cu:314-318)
+    int nuclear;              // rtd_opts.nuclearCorr: 0 off, 1 SOUKUP, 2 FLUKA, 3 GAUSS_FIT (kernel_wrapper.cu:228-245, 300-302, 320-341)
+    float eRefSq, sigmaDelta; // E_s^2 and the empirical widening of the model (198.81 / 0.21 without NUCLEAR_CORR)
     int writeAll;             // 1: every (ray, step) of idd / rSigmaEff is written (rtd_opts.fullIntermediates, for rtd_debug_fetch);
                               // 0: row segments without dose are left alone - the superposition never reads them (see the step lambda)
 };
@@ -397,7 +402,7 @@ __global__ void __launch_bounds__(IDD_WARPS * 32)
 idd_sigma_kernel(const float* __restrict__ density, const float* __restrict__ wepl, const float* __restrict__ rayWeights,
                  const int* __restrict__ firstInside, const int* __restrict__ firstOutside,
                  const LayerParams* __restrict__ layers, const BeamDev* __restrict__ bd, const float2* __restrict__ stepTab, const IddParams q,
-                 cudaTextureObject_t iddTex, cudaTextureObject_t rrlTex,
+                 cudaTextureObject_t iddTex, cudaTextureObject_t rrlTex, cudaTextureObject_t nucTex,
                  float* __restrict__ idd, float* __restrict__ rsig, float* __restrict__ rowMin,
                  int* __restrict__ firstPassive, int* __restrict__ layerFirstPassive) {
     const int nz = bd->nz;
@@ -463,7 +468,7 @@ idd_sigma_kernel(const float* __restrict__ density, const float* __restrict__ we
         const float resE = f_ex2(f_mul(f_lg2(f_sub(lp.peakDepth, f_mul(f_add(wPrev, wCur), 0.5f))), 0.5649718f));
         const float e1 = f_fma(resE, 8.639415f, 938.3f);
         const float betaP = f_sub(e1, f_div(880406.875f, e1));
-        return f_mul(f_div(198.81f, f_mul(betaP, betaP)), stepLength);
+        return f_mul(f_div(q.eRefSq, f_mul(betaP, betaP)), stepLength);
     };
     float wS0 = 0.0f, rhoS0 = 0.0f, dS0 = 0.0f, xS0 = 0.0f, tS0 = 0.0f, wS1 = 0.0f, rhoS1 = 0.0f, dS1 = 0.0f, xS1 = 0.0f, tS1 = 0.0f;
     if (live && first < last) {
@@ -493,17 +498,26 @@ idd_sigma_kernel(const float* __restrict__ density, const float* __restrict__ we
                 incinc = f_fma(stepLength, f_mul(stepLength, f_fma(rRl, t1, thetaSq)), incinc);
                 incScat = f_add(incScat, incinc);
                 incDiv = f_fma(airQuad, 2.0f, incDiv);
-            } else {
+            } else if (q.nuclear != 3) {       // the empirical fix of the sigma dip after the peak is compiled out for GAUSS_FIT (cu:300-302)
                 sigmaSq = f_fma(f_mul(f_add(incScat, incDiv), -1.5f), rho, sigmaSq);
             }
-            rs = f_div(st.x, f_mul(f_add(f_sqrt(sigmaSq), 0.21f), 1.41421356f));
+            rs = f_div(st.x, f_mul(f_add(f_sqrt(sigmaSq), q.sigmaDelta), 1.41421356f));
             const bool within = !(w > thr);
             live = within && (k != afterLast);
             afterLast = within ? afterLast : k;
             const float vol = st.y;
             const float mass = q.doseToMedium ? f_mul(rho, vol) : f_mul(f_sub(w, wOld), vol);
             const float d = dC;
-            if (mass > 1e-2f) res = f_div(f_mul(rayWeight, f_sub(d, dOld)), mass);
+            if (mass > 1e-2f) {
+                if (q.nuclear) {
+                    // the share of the step's dose the model attributes to the nuclear halo is taken out of the primary dose (cu:320-330);
+                    // the halo itself never reaches the dose grid as the reference is shipped (nucMemoryStep = 0, rtdose.h)
+                    const float nw = tex2D<float>(nucTex, f_fma(f_mul(f_add(w, wOld), 0.5f), lp.energyScale, 0.5f), eRow);
+                    res = f_div(f_mul(f_mul(f_sub(1.0f, nw), rayWeight), f_sub(d, dOld)), mass);
+                } else {
+                    res = f_div(f_mul(rayWeight, f_sub(d, dOld)), mass);
+                }
+            }
             wOld = w; dOld = d;
         }
         const bool keep = live && ((int)k >= firstIn - 1);

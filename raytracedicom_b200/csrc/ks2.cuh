@@ -20,6 +20,20 @@
 #include <stdint.h>
 #include "kernels.cuh"
 
+// Measurement switches of three round-2 micro-optimisations; tools/gpu_r2_c.sh builds the variants (profiles/r02_ks2_variants_ab.json,
+// C3 superposition per plan): baseline 1.123 ms; weight table with packed fp32 1.093 ms (kept); shared-memory words of the next
+// column offset requested right after the FMA block 1.120 ms (neutral, off); next work item requested one item ahead 1.411 ms
+// (25 % SLOWER, off - the kernel is bound by shared-memory bandwidth and by latency at 2 warps per scheduler, not by the atomic).
+#ifndef RTD_KS2_PACKED_ERF
+#define RTD_KS2_PACKED_ERF 1
+#endif
+#ifndef RTD_KS2_EARLY_G
+#define RTD_KS2_EARLY_G 0
+#endif
+#ifndef RTD_KS2_ITEM_PREFETCH
+#define RTD_KS2_ITEM_PREFETCH 0
+#endif
+
 namespace rtd {
 
 struct Ks2Params {
@@ -144,7 +158,7 @@ __device__ __forceinline__ Ks2G ks2_make_g(const float* __restrict__ t /* &tab[j
     // loaded a second time they cost 6 LDS per column offset and no MOV.
     float g[8], h[6];
 #pragma unroll
-    for (int y = 0; y < 8; ++y) g[y] = ks_lds_again(t + y * rowStride);
+    for (int y = 0; y < 8; ++y) g[y] = RTD_KS2_EARLY_G ? ks_lds_again(t + y * rowStride) : t[y * rowStride];
 #pragma unroll
     for (int y = 0; y < 6; ++y) h[y] = ks_lds_again(t + (y + 1) * rowStride);
     Ks2G r;
@@ -201,7 +215,7 @@ __device__ __forceinline__ void ks2_tile(const float* __restrict__ tab, const fl
     // the 14 shared-memory words of the next column offset are requested as soon as the FMA block has consumed this one's, so
     // that they arrive under the patch read-modify-write instead of stalling the head of the next iteration; at the largest radii
     // the register file has no room for them next to the accumulators (ptxas starts shuffling pairs): there they are loaded in place
-    constexpr bool EARLY_G = RB <= 12;
+    constexpr bool EARLY_G = RTD_KS2_EARLY_G && RB <= 12;
     Ks2G g = ks2_make_g(tab + lane, TS * 32);
 #pragma unroll 1
     for (int j = 0; j <= jmax; ++j) {       // jmax = applied radius (<= RB: a radius may run in the body of a larger one)
@@ -297,11 +311,12 @@ ks2_kernel(const Ks2Params p, int* __restrict__ workCounter, int* __restrict__ i
     // the atomic that hands out the next item is issued a whole item ahead: its L2 round trip (~6 % of the small-radius kernel's
     // samples when it sat at the head of the loop) is hidden under the current item
     int itNext = 0;
-    if (lane == 0) itNext = atomicAdd(workCounter, 1);
+    if (RTD_KS2_ITEM_PREFETCH && lane == 0) itNext = atomicAdd(workCounter, 1);
     for (;;) {
+        if (!RTD_KS2_ITEM_PREFETCH && lane == 0) itNext = atomicAdd(workCounter, 1);
         int it = __shfl_sync(0xffffffffu, itNext, 0);
         if (it >= nItems * NCH) break;
-        if (lane == 0) itNext = atomicAdd(workCounter, 1);
+        if (RTD_KS2_ITEM_PREFETCH && lane == 0) itNext = atomicAdd(workCounter, 1);
         const int idx = BIG ? (int)p.bigItems[it] : nItems - 1 - it / NCH;      // deepest slices (largest radii) first
         const int chunk = it % NCH;
         const int kk = idx / p.tiles, tile = idx - kk * p.tiles;
@@ -365,6 +380,7 @@ ks2_kernel(const Ks2Params p, int* __restrict__ workCounter, int* __restrict__ i
             // erf-difference weights (cuh:459-467) -> table: e[0] = erf(r/2), e[i] = (erf(r(i+1/2)) - erf(r(i-1/2)))/2
             // the 8 rows advance together so that 8 independent polynomial chains are in flight per lane; the argument
             // r (i + 1/2) is advanced by repeated addition
+#if RTD_KS2_PACKED_ERF
             {
                 ks_u64 x[4], rr[4], hOld[4];
                 float* t = tab + lane;
@@ -395,6 +411,31 @@ ks2_kernel(const Ks2Params p, int* __restrict__ workCounter, int* __restrict__ i
                     for (int y = 0; y < 8; ++y) t[y * rowStride] = 0.0f;
                 }
             }
+#else
+            {
+                float x[8], erfOld[8];
+                float* t = tab + lane;
+                const int rowStride = (body + 1) * 32;
+#pragma unroll
+                for (int y = 0; y < 8; ++y) { x[y] = r[y] * 0.5f; erfOld[y] = ks_erf_pos(x[y]); t[y * rowStride] = erfOld[y]; }
+#pragma unroll 1
+                for (int i = 1; i <= rb; ++i) {
+                    t += 32;
+#pragma unroll
+                    for (int y = 0; y < 8; ++y) {
+                        x[y] += r[y];
+                        const float erfNew = ks_erf_pos(x[y]);
+                        t[y * rowStride] = 0.5f * (erfNew - erfOld[y]);
+                        erfOld[y] = erfNew;
+                    }
+                }
+                for (int i = rb + 1; i <= body; ++i) {
+                    t += 32;
+#pragma unroll
+                    for (int y = 0; y < 8; ++y) t[y * rowStride] = 0.0f;
+                }
+            }
+#endif
             __syncwarp();
             switch (body) {
 #define RTD_KS2_CASE(N) case N: if constexpr (N <= RBMAX && N >= LAYER_RMIN) { if constexpr (N <= 16) ks2_tile<N, RBMAX, N + 1>(tab, d, patch, lane, rb); else ks2_tile_big<(N > 16) ? N : 17, BIG ? RBMAX : 32>(tab, d, patch, lane); } break;

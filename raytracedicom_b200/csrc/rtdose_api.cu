@@ -105,7 +105,7 @@ struct rtd_ctx {
     // LUTs (host copies of the small vectors the host logic needs)
     std::vector<float> energies, peakDepths, scaleFacts;
     int nEnergySamples = 0, nEnergies = 0; float densScale = 0, spScale = 0, rrlScale = 0;
-    TexArr iddTex, densTex, spTex, densSpTex, rrlTex, ctTex;   // densSpTex: density + SP as one float2 LUT when they share length and scale
+    TexArr iddTex, densTex, spTex, densSpTex, rrlTex, ctTex, nucTex;   // nucTex: nuclear-halo weight (rtd_luts.nucWeightMatrix), optional   // densSpTex: density + SP as one float2 LUT when they share length and scale
     int ctDims[3] = {0, 0, 0}, doseDims[3] = {0, 0, 0};
     DevBuf dose;
     std::vector<BeamWs*> ws;
@@ -453,6 +453,7 @@ rtd_status beamEnqueue(rtd_ctx* ctx, int beamNo, const rtd_beam& b, BeamWs& w, c
         li.thr = o.bpDepthCutoff * li.peakDepth;
         sigmaSqAirCoefsHost(li.peakDepth, !o.noNozzle, li.ca, li.cb);
         li.sigX = b.sigmas[2 * al]; li.sigY = b.sigmas[2 * al + 1];
+        li.sigScale = o.nuclearCorr == 3 ? 0.97f : 1.0f;
     }
     memcpy(w.hStage.p, b.weights + size_t(b.sx) * b.sy * w.l0, nW * 4);
     char* stLin = w.hStage.as<char>() + (nW * 4 + 15) / 16 * 16;
@@ -536,9 +537,13 @@ rtd_status beamEnqueue(rtd_ctx* ctx, int beamNo, const rtd_beam& b, BeamWs& w, c
     q.g = in.g;
     q.rrlScale = ctx->rrlScale; q.bpCutoff = o.bpDepthCutoff; q.rayWeightCutoff = o.rayWeightCutoff;
     q.Rx = Rx; q.Ry = Ry; q.nozzle = o.noNozzle ? 0 : 1; q.doseToMedium = o.doseToMedium ? 1 : 0; q.writeAll = o.fullIntermediates ? 1 : 0;
+    // E_s^2 and the empirical widening per nuclear model (kernel_wrapper.cu:232-245)
+    q.nuclear = o.nuclearCorr;
+    q.eRefSq = o.nuclearCorr == 1 ? 190.44f : o.nuclearCorr == 2 ? 216.09f : o.nuclearCorr == 3 ? 169.00f : 198.81f;
+    q.sigmaDelta = o.nuclearCorr == 1 ? 0.0f : o.nuclearCorr == 2 ? 0.08f : o.nuclearCorr == 3 ? 0.06f : 0.21f;
     const int segs = tilesX * Ry;
     idd_sigma_kernel<<<dim3((segs + IDD_WARPS - 1) / IDD_WARPS, 1, L), IDD_WARPS * 32, 0, st>>>(w.density.as<float>(), w.wepl.as<float>(), w.rayW.as<float>(),
-        w.firstIn.as<int>(), w.firstOut.as<int>(), w.layerDev.as<LayerParams>(), bd, w.stepTab.as<float2>(), q, ctx->iddTex.tex, ctx->rrlTex.tex,
+        w.firstIn.as<int>(), w.firstOut.as<int>(), w.layerDev.as<LayerParams>(), bd, w.stepTab.as<float2>(), q, ctx->iddTex.tex, ctx->rrlTex.tex, ctx->nucTex.tex,
         w.idd.as<float>(), w.rsig.as<float>(), w.rowMin.as<float>(), w.firstPassive.as<int>(), dLfp);
     RTD_CUDA(cudaEventRecord(evBeam(ctx, beamNo, 4), st));
 
@@ -651,6 +656,8 @@ rtd_status doseEnqueue(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* d
     int& launches = cs.launches;
     for (int b = 0; b < nBeams; ++b)
         if (const char* why = validateBeam(beams[b], o)) return fail(ctx, RTD_ERR_INVALID, why);
+    if (o.nuclearCorr < 0 || o.nuclearCorr > 3) return fail(ctx, RTD_ERR_INVALID, "opts.nuclearCorr must be 0 (off), 1 (SOUKUP), 2 (FLUKA) or 3 (GAUSS_FIT)");
+    if (o.nuclearCorr && !ctx->nucTex.tex) return fail(ctx, RTD_ERR_STATE, "opts.nuclearCorr needs rtd_luts.nucWeightMatrix (rtd_set_luts)");
     while ((int)ctx->ws.size() < nBeams) ctx->ws.push_back(new BeamWs());
     ctx->nBeamsLast = nBeams; ctx->optsLast = o;
     ctx->ctBoxes.clear(); ctx->doseBoxes.clear();
@@ -751,6 +758,11 @@ rtd_status doseFinish(rtd_ctx* ctx, int nBeams, rtd_timing* tm, cudaEvent_t evBe
         tm->doseVoxelsModified = modified;
     }
     if (!ok) return fail(ctx, RTD_ERR_RADIUS, "Found larger than allowed kernel superposition radius");
+    if (ctx->optsLast.nuclearCorr)
+        for (int b = 0; b < nBeams; ++b)
+            if (ctx->ws[b]->live && ctx->ws[b]->bfi == 0)
+                return fail(ctx, RTD_ERR_INVALID, "opts.nuclearCorr: a beam starts inside the patient (beamFirstInside == 0); the reference then deposits the "
+                                                  "slice-0 residue of its halo pass (kernel_wrapper.cu:925), which is not reproduced - the dose of this call lacks it");
     return RTD_OK;
 }
 
@@ -830,6 +842,7 @@ void rtd_destroy(rtd_ctx* ctx) {
     cudaStreamSynchronize(ctx->stream);
     for (BeamWs* w : ctx->ws) { w->release(); delete w; }
     ctx->iddTex.release(); ctx->densTex.release(); ctx->spTex.release(); ctx->densSpTex.release(); ctx->rrlTex.release(); ctx->ctTex.release();
+    ctx->nucTex.release();
     ctx->dose.release(); ctx->xferCount.release(); ctx->hXferCount.release(); ctx->ctRows.release();
     for (cudaEvent_t e : ctx->events) cudaEventDestroy(e);
     for (cudaStream_t s_ : ctx->bstreams) { cudaStreamSynchronize(s_); cudaStreamDestroy(s_); }
@@ -860,6 +873,13 @@ rtd_status rtd_set_luts(rtd_ctx* ctx, const rtd_luts* l) {
     RTD_CUDA(cudaMemcpy2DToArrayAsync(ctx->iddTex.arr, 0, 0, l->ciddMatrix, size_t(l->nEnergySamples) * 4, size_t(l->nEnergySamples) * 4,
                                       l->nEnergies, cudaMemcpyHostToDevice, ctx->stream));
     RTD_CUDA(makeTexture(ctx->iddTex, cudaAddressModeClamp));
+    ctx->nucTex.release();
+    if (l->nucWeightMatrix) {   // kernel_wrapper.cu:544-566: same shape and addressing as the IDD matrix
+        RTD_CUDA(cudaMallocArray(&ctx->nucTex.arr, &fd, l->nEnergySamples, l->nEnergies));
+        RTD_CUDA(cudaMemcpy2DToArrayAsync(ctx->nucTex.arr, 0, 0, l->nucWeightMatrix, size_t(l->nEnergySamples) * 4, size_t(l->nEnergySamples) * 4,
+                                          l->nEnergies, cudaMemcpyHostToDevice, ctx->stream));
+        RTD_CUDA(makeTexture(ctx->nucTex, cudaAddressModeClamp));
+    }
     RTD_CUDA(upload1D(ctx->densTex, l->densityVector, l->nDensitySamples, ctx->stream));
     RTD_CUDA(upload1D(ctx->spTex, l->spVector, l->nSpSamples, ctx->stream));
     RTD_CUDA(upload1D(ctx->rrlTex, l->rRlVector, l->nRRlSamples, ctx->stream));

@@ -32,7 +32,8 @@ class RtdLuts(C.Structure):
                 ("scaleFacts", _fp), ("ciddMatrix", _fp),
                 ("nDensitySamples", C.c_int), ("densityScaleFact", C.c_float), ("densityVector", _fp),
                 ("nSpSamples", C.c_int), ("spScaleFact", C.c_float), ("spVector", _fp),
-                ("nRRlSamples", C.c_int), ("rRlScaleFact", C.c_float), ("rRlVector", _fp)]
+                ("nRRlSamples", C.c_int), ("rRlScaleFact", C.c_float), ("rRlVector", _fp),
+                ("nucWeightMatrix", _fp), ("nucSqSigmaMatrix", _fp)]
 
 
 class RtdBeam(C.Structure):
@@ -48,7 +49,7 @@ class RtdOpts(C.Structure):
     _fields_ = [("bpDepthCutoff", C.c_float), ("convSigmaCutoff", C.c_float), ("ksSigmaCutoff", C.c_float),
                 ("rayWeightCutoff", C.c_float), ("minTilesInBatch", C.c_int), ("ks2BodyStep", C.c_int),
                 ("serialBeams", C.c_int), ("noZeroCopyDose", C.c_int), ("noNozzle", C.c_int), ("doseToMedium", C.c_int),
-                ("atomicDose", C.c_int), ("ctPull", C.c_int), ("fullIntermediates", C.c_int)]
+                ("atomicDose", C.c_int), ("ctPull", C.c_int), ("nuclearCorr", C.c_int), ("fullIntermediates", C.c_int)]
 
 
 class RtdTiming(C.Structure):
@@ -188,7 +189,10 @@ def pack_luts(e: EnergyStruct):
             _f32(e.spVector), _f32(e.rRlVector)]
     l = RtdLuts(e.nEnergySamples, e.nEnergies, _ptr(arrs[0]), _ptr(arrs[1]), _ptr(arrs[2]), _ptr(arrs[3]),
                 e.nDensitySamples, e.densityScaleFact, _ptr(arrs[4]), e.nSpSamples, e.spScaleFact, _ptr(arrs[5]),
-                e.nRRlSamples, e.rRlScaleFact, _ptr(arrs[6]))
+                e.nRRlSamples, e.rRlScaleFact, _ptr(arrs[6]), None, None)
+    if getattr(e, "nuclearCorr", 0):
+        arrs += [_f32(e.nucWeightMatrix), _f32(e.nucSqSigmaMatrix)]
+        l.nucWeightMatrix, l.nucSqSigmaMatrix = _ptr(arrs[7]), _ptr(arrs[8])
     return l, arrs
 
 
