@@ -25,7 +25,8 @@ class OrcLuts(C.Structure):
                 ("scaleFacts", _fp), ("ciddMatrix", _fp),
                 ("nDensitySamples", C.c_int), ("densityScaleFact", C.c_float), ("densityVector", _fp),
                 ("nSpSamples", C.c_int), ("spScaleFact", C.c_float), ("spVector", _fp),
-                ("nRRlSamples", C.c_int), ("rRlScaleFact", C.c_float), ("rRlVector", _fp)]
+                ("nRRlSamples", C.c_int), ("rRlScaleFact", C.c_float), ("rRlVector", _fp),
+                ("nucWeightMatrix", _fp), ("nucSqSigmaMatrix", _fp)]
 
 
 class OrcBeam(C.Structure):
@@ -39,7 +40,7 @@ class OrcBeam(C.Structure):
 class OrcOpts(C.Structure):
     _fields_ = [("bpDepthCutoff", C.c_float), ("convSigmaCutoff", C.c_float), ("ksSigmaCutoff", C.c_float),
                 ("rayWeightCutoff", C.c_float), ("minTilesInBatch", C.c_int), ("texFracMode", C.c_int),
-                ("noNozzle", C.c_int), ("doseToMedium", C.c_int)]
+                ("noNozzle", C.c_int), ("doseToMedium", C.c_int), ("nuclearCorr", C.c_int)]
 
 
 class OrcResult(C.Structure):
@@ -94,7 +95,10 @@ def pack_luts(e):
     keep = [_f32(e.energiesPerU), _f32(e.peakDepths), _f32(e.scaleFacts), _f32(e.ciddMatrix), _f32(e.densityVector), _f32(e.spVector), _f32(e.rRlVector)]
     l = OrcLuts(e.nEnergySamples, e.nEnergies, _p(keep[0]), _p(keep[1]), _p(keep[2]), _p(keep[3]),
                 e.nDensitySamples, e.densityScaleFact, _p(keep[4]), e.nSpSamples, e.spScaleFact, _p(keep[5]),
-                e.nRRlSamples, e.rRlScaleFact, _p(keep[6]))
+                e.nRRlSamples, e.rRlScaleFact, _p(keep[6]), None, None)
+    if getattr(e, "nuclearCorr", 0):
+        keep += [_f32(e.nucWeightMatrix), _f32(e.nucSqSigmaMatrix)]
+        l.nucWeightMatrix, l.nucSqSigmaMatrix = _p(keep[7]), _p(keep[8])
     return l, keep
 
 

@@ -10,6 +10,8 @@
 //   int32 nBeams; per beam:
 //     int32 Sx,Sy,L,steps; float32 weights[L*Sy*Sx]; energies[L]; sigmas[2L] (x,y interleaved);
 //     raySpacing[2]; sourceDist[2]; spotDelta[3]; spotOffset[3]; gantryToImIdx m[9], v[3]; gantryToDoseIdx m[9], v[3]
+//   optional trailer (LUTs of a NUCLEAR_CORR build): char[8] "RTDNUCL1"; int32 model (1 SOUKUP, 2 FLUKA, 3 GAUSS_FIT);
+//     float32 nucWeight[nE*nS]; float32 nucSqSigma[nE*nS]
 #ifndef RTD_CASE_IO_H
 #define RTD_CASE_IO_H
 #include <cstdio>
@@ -25,6 +27,7 @@ struct CaseLuts {
     int nDens = 0; float densScale = 0; std::vector<float> dens;
     int nSp = 0; float spScale = 0; std::vector<float> sp;
     int nRrl = 0; float rrlScale = 0; std::vector<float> rrl;
+    int nuclearModel = 0; std::vector<float> nucWeight, nucSqSigma;
 };
 
 struct CaseBeam {
@@ -75,6 +78,11 @@ inline CaseFile readCase(const std::string& path) {
         rdv(f, b.energies, b.L); rdv(f, b.sigmas, 2 * size_t(b.L));
         rd(f, b.raySpacing, 8); rd(f, b.sourceDist, 8); rd(f, b.spotDelta, 12); rd(f, b.spotOffset, 12);
         rd(f, b.imM, 36); rd(f, b.imV, 12); rd(f, b.doseM, 36); rd(f, b.doseV, 12);
+    }
+    char tail[8];
+    if (fread(tail, 1, 8, f) == 8 && memcmp(tail, "RTDNUCL1", 8) == 0) {
+        l.nuclearModel = rdi(f);
+        rdv(f, l.nucWeight, size_t(l.nEnergies) * l.nEnergySamples); rdv(f, l.nucSqSigma, size_t(l.nEnergies) * l.nEnergySamples);
     }
     fclose(f);
     return c;

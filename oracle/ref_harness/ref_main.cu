@@ -22,6 +22,10 @@ static EnergyStruct toEnergyStruct(const CaseLuts& l) {
     e.nDensitySamples = l.nDens; e.densityScaleFact = l.densScale; e.densityVector = l.dens;
     e.nSpSamples = l.nSp; e.spScaleFact = l.spScale; e.spVector = l.sp;
     e.nRRlSamples = l.nRrl; e.rRlScaleFact = l.rrlScale; e.rRlVector = l.rrl;
+#ifdef NUCLEAR_CORR
+    if (l.nuclearModel != NUCLEAR_CORR + 1) throw std::runtime_error("case file does not carry the nuclear LUTs of this build's NUCLEAR_CORR model");
+    e.nucWeightMatrix = l.nucWeight; e.nucSqSigmaMatrix = l.nucSqSigma;
+#endif
     return e;
 }
 

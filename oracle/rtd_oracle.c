@@ -42,6 +42,8 @@ typedef struct {
     int nDensitySamples; float densityScaleFact; const float* densityVector;
     int nSpSamples; float spScaleFact; const float* spVector;
     int nRRlSamples; float rRlScaleFact; const float* rRlVector;
+    const float* nucWeightMatrix;   /* NUCLEAR_CORR builds only (energy_struct.h:33-36), else NULL */
+    const float* nucSqSigmaMatrix;
 } orc_luts;
 
 /* Same content as BeamSettings (beam_settings.h:101-109). */
@@ -57,7 +59,12 @@ typedef struct {
 /* Run-time copies of the compile-time flags (CMakeLists.txt:36-79). */
 typedef struct { float bpDepthCutoff, convSigmaCutoff, ksSigmaCutoff, rayWeightCutoff; int minTilesInBatch; int texFracMode;
                  int noNozzle;      /* -DNO_NOZZLE (CMakeLists.txt:48-51; fill_idd_and_sigma_params.cu:76-82) */
-                 int doseToMedium;  /* DOSE_TO_WATER off (CMakeLists.txt:40-43; kernel_wrapper.cu:314-318) */ } orc_opts;
+                 int doseToMedium;  /* DOSE_TO_WATER off (CMakeLists.txt:40-43; kernel_wrapper.cu:314-318) */
+                 int nuclearCorr;   /* NUCLEAR_CORR (CMakeLists.txt:57-79): 0 off, 1 SOUKUP, 2 FLUKA, 3 GAUSS_FIT. Restated AS SHIPPED: the halo pass
+                                       is built with nucMemoryStep = 0 (kernel_wrapper.cu:925), so it deposits nothing unless the beam's first step is
+                                       already inside the patient (bfi == 0, not restated: orc_beam_dose returns 4); what remains is the changed
+                                       scattering constants (cu:232-240), GAUSS_FIT's missing post-peak correction (cu:300-302) and entry-sigma
+                                       factor (cu:842-847), and the primary dose scaled by 1 - nucWeight (cu:320-330) */ } orc_opts;
 
 /* Everything the reference computes for one beam; arrays are malloc'ed here and released by orc_free_result. */
 typedef struct {
@@ -83,7 +90,7 @@ typedef struct {
 
 void orc_default_opts(orc_opts* o) {
     o->bpDepthCutoff = 1.05f; o->convSigmaCutoff = 3.0f; o->ksSigmaCutoff = 3.0f; o->rayWeightCutoff = 1.0f;
-    o->minTilesInBatch = 16; o->texFracMode = 0; o->noNozzle = 0; o->doseToMedium = 0;
+    o->minTilesInBatch = 16; o->texFracMode = 0; o->noNozzle = 0; o->doseToMedium = 0; o->nuclearCorr = 0;
 }
 
 void orc_free_result(orc_result* r) {
@@ -378,6 +385,10 @@ static void stage_idd_sigma(const orc_luts* lut, const fill_geom* g, const layer
     const float airLin = fmaf(cb, dzs, g->corner.z * ((ca + ca) * dzs));
     const float stepLength = fabsf(dzs);
     const float thr = lp->peakDepth * o->bpDepthCutoff;
+    /* E_s^2 and the empirical widening per nuclear model, kernel_wrapper.cu:232-245 */
+    const int nuc = o->nuclearCorr;
+    const float eRefSq = nuc == 1 ? 190.44f : nuc == 2 ? 216.09f : nuc == 3 ? 169.00f : 198.81f;
+    const float sigmaDelta = nuc == 1 ? 0.0f : nuc == 2 ? 0.08f : nuc == 3 ? 0.06f : 0.21f;
 #pragma omp parallel for schedule(static)
     for (int ray = 0; ray < R; ++ray) {
         const int firstIn = firstInside[ray];
@@ -401,25 +412,32 @@ static void stage_idd_sigma(const orc_luts* lut, const fill_geom* g, const layer
                     const float e1 = fmaf(resE, 8.639415f, 938.3f);
                     const float betaP = e1 - 880406.875f / e1;                                              /* 938.3^2 folded by the compiler */
                     const float rRl = rho * tex1d_clamp(lut->rRlVector, lut->nRRlSamples, fmaf(rho, lut->rRlScaleFact, 0.5f));
-                    const float t1 = (198.81f / (betaP * betaP)) * stepLength;
+                    const float t1 = (eRefSq / (betaP * betaP)) * stepLength;
                     const float thetaSq = rRl * t1;
                     sigmaSq = sigmaSq + (incScat + incDiv);
                     incinc = fmaf(stepLength, stepLength * fmaf(rRl, t1, thetaSq), incinc);                 /* 2*thetaSq*len*len */
                     incScat = incScat + incinc;
                     incDiv = fmaf(airQuad, 2.0f, incDiv);
-                } else {
-                    sigmaSq = fmaf((incScat + incDiv) * -1.5f, rho, sigmaSq);                               /* cu:297 */
+                } else if (nuc != 3) {
+                    sigmaSq = fmaf((incScat + incDiv) * -1.5f, rho, sigmaSq);                               /* cu:297; compiled out for GAUSS_FIT, cu:300-302 */
                 }
                 const float fk = (float)k;
                 const float zk = fmaf(g->delta.z, fk, g->corner.z);
                 const float vwx = g->delta.x * (1.0f - zk / g->distX), vwy = g->delta.y * (1.0f - zk / g->distY);
-                rs = ((vwx + vwy) * 0.5f) / ((sqrtf(sigmaSq) + 0.21f) * 1.41421356f);                      /* cu:307 */
+                rs = ((vwx + vwy) * 0.5f) / ((sqrtf(sigmaSq) + sigmaDelta) * 1.41421356f);                 /* cu:307 */
                 const int within = !(w > thr);
                 live = within && (k != afterLast);                                                          /* cu:309-312 */
                 afterLast = within ? afterLast : k;
                 const float vol = fmaf(g->volSq, (float)(k * k), fmaf(g->volLin, fk, g->volConst));
                 const float mass = o->doseToMedium ? rho * vol : (w - wOld) * vol;                          /* cu:314-318 */
-                if (mass > 1e-2f) res = (rayWeight * (d - dOld)) / mass;                                    /* else keeps the previous value (H9) */
+                if (mass > 1e-2f) {                                                                         /* else keeps the previous value (H9) */
+                    if (nuc) {                                                                              /* cu:320-330 */
+                        const float nw = tex2d_clamp(lut->nucWeightMatrix, lut->nEnergySamples, lut->nEnergies, fmaf((w + wOld) * 0.5f, lp->energyScale, 0.5f), lp->energyIdx + 0.5f);
+                        res = (((1.0f - nw) * rayWeight) * (d - dOld)) / mass;
+                    } else {
+                        res = (rayWeight * (d - dOld)) / mass;
+                    }
+                }
                 wOld = w; dOld = d;
             }
             if (!live || (int)k < firstIn - 1) { res = 0.0f; rs = INF; }                                    /* cu:361-370 */
@@ -575,6 +593,8 @@ int orc_beam_dose(const orc_luts* lut, const float* ct, int nx, int ny, int nz, 
     stage_reduce(r->wepl, r->firstInside, r->firstOutside, R, S, &r->bfi, &r->bfo, r->weplMin);
     r->entryZ = (float)r->bfi * res.z + ray.offset.z;
     if (stopAfter == 1) return 0;
+    if (o.nuclearCorr && (!lut->nucWeightMatrix || o.nuclearCorr < 0 || o.nuclearCorr > 3)) return 1;
+    if (o.nuclearCorr && r->bfi == 0) return 4;   /* the slice-0 residue of the reference's halo pass would reach the dose: not restated */
 
     /* cu:792-849 */
     float maxEnergy = b->energies[0];
@@ -595,6 +615,7 @@ int orc_beam_dose(const orc_luts* lut, const float* ct, int nx, int ny, int nz, 
         const float sxg = b->sigmas[2 * l], syg = b->sigmas[2 * l + 1];
         entrySig[2 * l] = sqrtf(ca * z * z + cb * z + sxg * sxg);          /* cu:840-841 */
         entrySig[2 * l + 1] = sqrtf(ca * z * z + cb * z + syg * syg);
+        if (o.nuclearCorr == 3) { entrySig[2 * l] = 0.97f * entrySig[2 * l]; entrySig[2 * l + 1] = 0.97f * entrySig[2 * l + 1]; }   /* cu:842-847 */
         const unsigned la = (unsigned)find_first_larger_ordered(r->weplMin, S, o.bpDepthCutoff * lp[l].peakDepth);
         lp[l].afterLast = (int)(la < (unsigned)r->Zg ? la : (unsigned)r->Zg); /* cu:923-924 */
         float* lf = r->layerF + 5 * l;

@@ -127,6 +127,10 @@ class Case:
                 f.write(struct.pack("<3f", *b.spot_delta)); f.write(struct.pack("<3f", *b.spot_offset))
                 f.write(b.gantry_to_im_m.tobytes()); f.write(b.gantry_to_im_v.tobytes())
                 f.write(b.gantry_to_dose_m.tobytes()); f.write(b.gantry_to_dose_v.tobytes())
+            if getattr(l, "nuclearCorr", 0):      # optional trailer: the LUTs of a NUCLEAR_CORR build (energy_struct.h:33-36)
+                f.write(b"RTDNUCL1"); f.write(struct.pack("<i", int(l.nuclearCorr)))
+                f.write(np.ascontiguousarray(l.nucWeightMatrix, np.float32).tobytes())
+                f.write(np.ascontiguousarray(l.nucSqSigmaMatrix, np.float32).tobytes())
 
 
 # ----------------------------------------------------------------------------------------------------

@@ -126,8 +126,9 @@ def energy_reader(data_path: str, water_cube_test: bool = False, nuclear_corr: i
     return e
 
 
-def load_packaged_luts(water_cube_test: bool = False) -> EnergyStruct:
-    """Load ``data/luts.npz`` (binary conversion of the reference's LUT text files)."""
+def load_packaged_luts(water_cube_test: bool = False, nuclear_corr: int = 0) -> EnergyStruct:
+    """Load ``data/luts.npz`` (binary conversion of the reference's LUT text files); ``nuclear_corr`` (NUCLEAR_MODELS) adds the two
+    matrices of that model from ``data/luts_nuclear.npz`` (nuclear_weights_and_sigmas_*.txt, energy_reader.cpp:103-162)."""
     path = os.path.join(_DATA_DIR, "luts.npz")
     if not os.path.exists(path):
         raise FileNotFoundError(f"{path} missing: run tools/make_lut_fixture.py where /root/reference exists")
@@ -145,6 +146,14 @@ def load_packaged_luts(water_cube_test: bool = False) -> EnergyStruct:
     key = "rRlVectorWater" if water_cube_test else "rRlVector"
     e.rRlVector = z[key].astype(np.float32); e.nRRlSamples = e.rRlVector.size
     e.rRlScaleFact = float(z["rRlScaleFact"])
+    if nuclear_corr:
+        npath = os.path.join(_DATA_DIR, "luts_nuclear.npz")
+        if not os.path.exists(npath):
+            raise FileNotFoundError(f"{npath} missing: run tools/make_lut_fixture.py where /root/reference exists")
+        zn = np.load(npath)
+        e.nucWeightMatrix = zn[f"weight_{int(nuclear_corr)}"].astype(np.float32).ravel()
+        e.nucSqSigmaMatrix = zn[f"sqsigma_{int(nuclear_corr)}"].astype(np.float32).ravel()
+        e.nuclearCorr = int(nuclear_corr)
     e.validate()
     return e
 

@@ -512,3 +512,45 @@ def test_group_api_two_ranks_share_one_grid(eng, mini_case, tmp_path, mode):
         assert np.all(host[whole == 0] == 0.25)
         # two calls, each adding the plan's dose onto the caller's grid
         assert rel_to_max(host.astype(np.float64) - 0.25, 2.0 * whole)[0] <= 1e-5 + 6.0e-8 / float(whole.max())
+
+
+@pytest.mark.parametrize("model", ["soukup", "fluka", "gauss_fit"])
+def test_nuclear_corr_against_oracle_and_rebuilt_reference(eng, oracle, mini_case, model, tmp_path):
+    """The reference's NUCLEAR_CORR build option (CMakeLists.txt:57-79) as rtd_opts.nuclearCorr, AS SHIPPED: per-model scattering
+    constants (kernel_wrapper.cu:232-240), GAUSS_FIT's dropped post-peak correction and 0.97 entry sigma (cu:300-302, 842-847), primary
+    dose x (1 - nucWeight) (cu:320-330); its halo pass runs with nucMemoryStep = 0 (cu:925) and deposits nothing for a beam that
+    starts outside the patient. Against the oracle with the same switch and against the UNMODIFIED reference rebuilt with
+    -DNUCLEAR_CORR=<model> (oracle/_ref/ref_dose_{soukup,fluka,gaussfit}) on the same case + the model's own LUT file."""
+    from oracle import pyoracle
+    from raytracedicom_b200.energy_reader import NUCLEAR_MODELS, load_packaged_luts
+    m = NUCLEAR_MODELS[model]
+    case = cases.Case("mini_nuclear", mini_case.ct, mini_case.beams, load_packaged_luts(nuclear_corr=m))
+    base, _ = run_case(eng, mini_case)
+    with pytest.raises(engine.RtdError) as ei:          # the option needs the model's LUT
+        eng.opts.nuclearCorr = m
+        try:
+            run_case(eng, mini_case)
+        finally:
+            eng.opts.nuclearCorr = 0
+    assert ei.value.status == 4
+    eng.opts.nuclearCorr = m
+    try:
+        dose, t = run_case(eng, case)
+        rep = eng.beam_report(0)
+    finally:
+        eng.opts.nuclearCorr = 0
+    assert rel_to_max(dose, base)[0] > 1e-2             # the switch changes the physics
+    o = pyoracle.run_beam(case, 0, opts=pyoracle.default_opts(nuclearCorr=m))
+    assert o["rc"] == 0 and rep["beamFirstInside"] > 0
+    assert rep["updates"] == o["updates"] and rep["beamFirstCalculatedPassive"] == o["beamFirstCalculatedPassive"]
+    for l in range(rep["nLayers"]):
+        assert eng.layer_report(0, l)["radiusHist"] == list(o["hist"][l])
+    assert rel_to_max(dose, o["dose"])[0] <= 2e-4
+    exe = os.path.join(ROOT, "oracle", "_ref", {"soukup": "ref_dose_soukup", "fluka": "ref_dose_fluka", "gauss_fit": "ref_dose_gaussfit"}[model])
+    if os.path.exists(exe):
+        cpath = str(tmp_path / "case.rtdcase"); case.write(cpath)
+        r = subprocess.run([exe, cpath, str(tmp_path / "dose.f32")], capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, (r.stderr or r.stdout)[-1000:]
+        ref = np.fromfile(tmp_path / "dose.f32", np.float32).reshape(dose.shape)
+        assert rel_to_max(dose, ref)[0] <= DOSE_TOL_TIGHT
+        assert gamma_pass_rate(dose, ref, case.spacing) >= 0.999

@@ -41,3 +41,32 @@ def test_dose_to_medium_equals_dose_to_water_in_water(oracle):
     sp = float(c.luts.spVector[250]); rho = float(c.luts.densityVector[250])
     if wat["dose"].max() > 0:
         assert np.isclose(med["dose"].sum() / wat["dose"].sum(), sp / rho, rtol=2e-2)
+
+
+def test_nuclear_corr_switch_in_the_oracle(oracle):
+    """NUCLEAR_CORR as shipped (kernel_wrapper.cu:228-245, 300-302, 320-341, 842-847, 925): the integer outputs of a beam that starts
+    outside the patient are those of the default build where the scattering constants do not move a cut-off (the dose cut-offs
+    depend on WEPL only), the dose is the primary dose scaled by 1 - nucWeight (< 1) with a changed lateral spread; the three
+    models differ; the option without its LUT, and a beam whose first step is inside the patient, are refused."""
+    from raytracedicom_b200.energy_reader import NUCLEAR_MODELS, load_packaged_luts
+    c = cases.make_case("mini")
+    base = oracle.run_beam(c, 0)
+    assert oracle.run_beam(c, 0, opts=oracle.default_opts(nuclearCorr=2))["rc"] == 1      # no LUT
+    sums = {}
+    for name, m in NUCLEAR_MODELS.items():
+        luts = load_packaged_luts(nuclear_corr=m)
+        assert luts.nucWeightMatrix.shape == luts.ciddMatrix.shape and 0.0 < float(luts.nucWeightMatrix.max()) < 0.3
+        o = oracle.run_beam(cases.Case("n", c.ct, c.beams, luts), 0, opts=oracle.default_opts(nuclearCorr=m))
+        assert o["rc"] == 0 and o["updates"] == base["updates"] and o["beamFirstCalculatedPassive"] == base["beamFirstCalculatedPassive"]
+        if m != 3:      # GAUSS_FIT's 0.97 entry sigma changes the ray weights, hence which rays pass RAY_WEIGHT_CUTOFF
+            assert np.array_equal(o["first_passive"], base["first_passive"])
+        sums[name] = float(o["dose"].sum(dtype=np.float64))
+        assert 0.75 * base["dose"].sum(dtype=np.float64) < sums[name] < base["dose"].sum(dtype=np.float64)
+    assert len({round(v / sums["soukup"], 4) for v in sums.values()}) == 3
+    # a beam that starts inside the patient: the reference's slice-0 halo residue is not restated
+    w = _water_case()
+    b = w.beams[0]
+    inside = cases.Beam(b.weights, b.energies, b.sigmas, b.ray_spacing, b.steps, b.source_dist, b.spot_delta, (b.spot_offset[0], b.spot_offset[1], 20.0),
+                        b.gantry_to_im_m, b.gantry_to_im_v)
+    o = oracle.run_beam(cases.Case("inside", w.ct, [inside], load_packaged_luts(nuclear_corr=1)), 0, opts=oracle.default_opts(nuclearCorr=1))
+    assert o["beamFirstInside"] == 0 and o["rc"] == 4

@@ -19,3 +19,14 @@ np.savez_compressed(out, nEnergySamples=e.nEnergySamples, nEnergies=e.nEnergies,
                     rRlVector=e.rRlVector, rRlVectorWater=w.rRlVector, rRlScaleFact=np.float32(e.rRlScaleFact))
 print("wrote", out, os.path.getsize(out), "bytes; energies", e.nEnergies, "samples", e.nEnergySamples,
       "diff water entries:", int(np.sum(e.rRlVector != w.rRlVector)))
+
+# the LUTs of the NUCLEAR_CORR builds (energy_reader.cpp:103-162): nuclear-halo weight and variance per model
+from raytracedicom_b200.energy_reader import NUCLEAR_MODELS
+nuc = {}
+for name, model in NUCLEAR_MODELS.items():
+    n = energy_reader(src, nuclear_corr=model)
+    nuc[f"weight_{model}"] = n.nucWeightMatrix.reshape(e.nEnergies, e.nEnergySamples).astype(np.float32)
+    nuc[f"sqsigma_{model}"] = n.nucSqSigmaMatrix.reshape(e.nEnergies, e.nEnergySamples).astype(np.float32)
+nout = os.path.join(os.path.dirname(out), "luts_nuclear.npz")
+np.savez_compressed(nout, **nuc)
+print("wrote", nout, os.path.getsize(nout), "bytes")
