@@ -41,6 +41,12 @@ inline void packAffine(const Affine& a, float m[9], float v[3]) {
     v[0] = o.x; v[1] = o.y; v[2] = o.z;
 }
 
+// EnergyStruct has nucWeightMatrix / nucSqSigmaMatrix only in the reference's NUCLEAR_CORR builds (src/energy_struct.h:33-36)
+template <class E> inline auto nucWeight(const E& e, int) -> decltype(e.nucWeightMatrix.data()) { return e.nucWeightMatrix.empty() ? nullptr : e.nucWeightMatrix.data(); }
+template <class E> inline const float* nucWeight(const E&, long) { return nullptr; }
+template <class E> inline auto nucSqSigma(const E& e, int) -> decltype(e.nucSqSigmaMatrix.data()) { return e.nucSqSigmaMatrix.empty() ? nullptr : e.nucSqSigmaMatrix.data(); }
+template <class E> inline const float* nucSqSigma(const E&, long) { return nullptr; }
+
 struct Context {   // RAII: the context is destroyed on every exit path
     rtd_ctx* c = nullptr;
     explicit Context(int device) {
@@ -58,7 +64,12 @@ struct ShimOptions {
     int device = 0;
     rtd_opts opts;
     rtd_timing* timing = nullptr;   // optional: stage report, the counterpart of FINE_GRAINED_TIMING (cu:1291-1311)
-    ShimOptions() { rtd_default_opts(&opts); }
+    ShimOptions() {
+        rtd_default_opts(&opts);
+#ifdef NUCLEAR_CORR            // the reference's build option (CMakeLists.txt:57-79: SOUKUP 0, FLUKA 1, GAUSS_FIT 2) selects the run-time model
+        opts.nuclearCorr = NUCLEAR_CORR + 1;
+#endif
+    }
 };
 
 template <class Image, class Beam, class Energy>
@@ -73,6 +84,7 @@ void cudaWrapperProtons(Image* const imVol, Image* const doseVol, std::vector<Be
     l.nDensitySamples = iddData.nDensitySamples; l.densityScaleFact = iddData.densityScaleFact; l.densityVector = iddData.densityVector.data();
     l.nSpSamples = iddData.nSpSamples; l.spScaleFact = iddData.spScaleFact; l.spVector = iddData.spVector.data();
     l.nRRlSamples = iddData.nRRlSamples; l.rRlScaleFact = iddData.rRlScaleFact; l.rRlVector = iddData.rRlVector.data();
+    l.nucWeightMatrix = detail::nucWeight(iddData, 0); l.nucSqSigmaMatrix = detail::nucSqSigma(iddData, 0);
     ctx.check(rtd_set_luts(ctx.c, &l));
 
     const auto id = imVol->getDims();

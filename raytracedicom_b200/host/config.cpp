@@ -19,6 +19,7 @@ const char* kUsage =
     "  --case FILE              raw case file (RTDCASE1) instead of DICOM input\n"
     "  --phys_data DIR/         directory of the physics look-up tables\n"
     "  --timing                 print the stage timing report\n"
+    "  --nuclear_corr MODEL     the reference's NUCLEAR_CORR build option: soukup | fluka | gauss_fit (needs --phys_data)\n"
     "  --dump_case FILE         write the assembled plan as an RTDCASE1 file and stop (no GPU needed)\n";
 
 void splitList(const std::string& s, std::vector<std::string>& out) {
@@ -39,6 +40,10 @@ Config::Config(int argc, char** argv) {
         else if (key == "case") case_file = val;
         else if (key == "phys_data") phys_data_directory = val;
         else if (key == "dump_case") dump_case = val;
+        else if (key == "nuclear_corr") {
+            nuclear_corr = val == "soukup" ? 1 : val == "fluka" ? 2 : (val == "gauss_fit" || val == "fit") ? 3 : (val == "off" || val == "0") ? 0 : -1;
+            if (nuclear_corr < 0) { std::cerr << "Unknown nuclear model: " << val << "\n" << kUsage; exit = true; }
+        }
         else { std::cerr << "Unknown option: " << key << "\n" << kUsage; exit = true; }
     };
     for (int i = 1; i < argc && !exit; ++i) {

@@ -16,6 +16,7 @@ struct Config {
     std::string case_file;            // RTDCASE1 file (raytracedicom_b200/cases.py): raw CT + BeamSettings
     std::string phys_data_directory;  // PHYS_DATA_DIRECTORY
     bool timing{false};               // FINE_GRAINED_TIMING-style stage report
+    int nuclear_corr{0};              // NUCLEAR_CORR of the reference at run time: 0 off, 1 soukup, 2 fluka, 3 gauss_fit
     std::string dump_case;            // write the assembled plan (CT + BeamSettings + LUTs) as an RTDCASE1 file and stop: no GPU needed
 };
 #endif

@@ -94,6 +94,7 @@ struct EnergyStruct {
     int nDensitySamples = 0; float densityScaleFact = 0; std::vector<float> densityVector;
     int nSpSamples = 0; float spScaleFact = 0; std::vector<float> spVector;
     int nRRlSamples = 0; float rRlScaleFact = 0; std::vector<float> rRlVector;
+    std::vector<float> nucWeightMatrix, nucSqSigmaMatrix;   // the reference's NUCLEAR_CORR builds only (energy_struct.h:33-36); empty otherwise
 };
 
 #endif

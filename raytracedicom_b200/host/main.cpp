@@ -49,6 +49,7 @@ struct Plan {   // everything main() hands to cudaWrapperProtons, with owned sto
     std::vector<BeamSettings> beams;
     std::vector<std::unique_ptr<PlanBeamSettings>> planBeams;
     EnergyStruct luts; bool haveLuts = false;
+    int nuclearCorr = 0;   // model the nuclear tables in luts belong to (0 = none)
 };
 
 // DICOM input: CT series + RT Ion Plan -> plan (src/main.cu:105-197 completed).
@@ -106,6 +107,9 @@ void writeCaseFile(const std::string& path, Plan& p) {
             for (const float3& r : {m.row0(), m.row1(), m.row2()}) { wrf(r.x); wrf(r.y); wrf(r.z); }
             wrf(t.getOffset().x); wrf(t.getOffset().y); wrf(t.getOffset().z);
         }
+    }
+    if (!l.nucWeightMatrix.empty() && p.nuclearCorr) {   // optional trailer: the LUTs of a NUCLEAR_CORR build
+        wr("RTDNUCL1", 8); wri(p.nuclearCorr); wrv(l.nucWeightMatrix); wrv(l.nucSqSigmaMatrix);
     }
     fclose(f);
 }
@@ -170,6 +174,11 @@ void readCaseFile(const std::string& path, Plan& p) {
                              Float3AffineTransform(Matrix3x3(im[0], im[1], im[2], im[3], im[4], im[5], im[6], im[7], im[8]), make_float3(iv[0], iv[1], iv[2])),
                              Float3AffineTransform(Matrix3x3(dm[0], dm[1], dm[2], dm[3], dm[4], dm[5], dm[6], dm[7], dm[8]), make_float3(dv[0], dv[1], dv[2])));
     }
+    char tail[8];
+    if (fread(tail, 1, 8, f) == 8 && memcmp(tail, "RTDNUCL1", 8) == 0) {
+        p.nuclearCorr = rdi();
+        rdv(l.nucWeightMatrix, size_t(l.nEnergies) * l.nEnergySamples); rdv(l.nucSqSigmaMatrix, size_t(l.nEnergies) * l.nEnergySamples);
+    }
     fclose(f);
 }
 
@@ -185,17 +194,18 @@ int main(int argc, char** argv) {
             readCaseFile(config.case_file, plan);
         } else if (config.water_cube_test) {
             if (config.phys_data_directory.empty()) throw std::runtime_error("--water_cube_test needs --phys_data DIR/ (the reference's PHYS_DATA_DIRECTORY)");
-            plan.luts = energyReader(config.phys_data_directory, true);
+            plan.luts = energyReader(config.phys_data_directory, true, config.nuclear_corr);
             plan.haveLuts = true;
             makeWaterCubeTest(plan, plan.luts);
         } else if (!config.ct_dir.empty() && !config.rtplan.empty()) {
             if (config.phys_data_directory.empty()) throw std::runtime_error("DICOM input needs --phys_data DIR/ (the reference's PHYS_DATA_DIRECTORY)");
-            plan.luts = energyReader(config.phys_data_directory, false);
+            plan.luts = energyReader(config.phys_data_directory, false, config.nuclear_corr);
             plan.haveLuts = true;
             readDicom(config, plan);
         } else {
             throw std::runtime_error("no input: give --ct_dir DIR --rtplan FILE [--beams ...], --case FILE or --water_cube_test");
         }
+        if (config.nuclear_corr && !plan.luts.nucWeightMatrix.empty() && !plan.nuclearCorr) plan.nuclearCorr = config.nuclear_corr;
         if (!config.dump_case.empty()) {
             writeCaseFile(config.dump_case, plan);
             std::cout << "Written " << config.dump_case << " (" << plan.beams.size() << " beam(s)); stopping before the dose calculation\n";
@@ -210,6 +220,15 @@ int main(int argc, char** argv) {
 
         std::cout << "Executing code on GPU...\n\n";
         rtdose::ShimOptions so; so.device = config.gpu_id;
+        if (config.nuclear_corr) {
+            if (plan.luts.nucWeightMatrix.empty() || (plan.nuclearCorr && plan.nuclearCorr != config.nuclear_corr)) {      // --case input: the LUTs came with the case file, the nuclear tables come from --phys_data
+                if (config.phys_data_directory.empty()) throw std::runtime_error("--nuclear_corr needs --phys_data DIR/ for the model's look-up table");
+                const EnergyStruct n = energyReader(config.phys_data_directory, false, config.nuclear_corr);
+                if (n.nEnergies != plan.luts.nEnergies || n.nEnergySamples != plan.luts.nEnergySamples) throw std::runtime_error("nuclear look-up table does not match the plan's IDD grid");
+                plan.luts.nucWeightMatrix = n.nucWeightMatrix; plan.luts.nucSqSigmaMatrix = n.nucSqSigmaMatrix;
+            }
+            so.opts.nuclearCorr = config.nuclear_corr;
+        }
         rtd_timing tm; so.timing = &tm;
         rtdose::cudaWrapperProtons(&imVol, &doseVol, plan.beams, plan.luts, std::cout, so);
         if (config.timing)

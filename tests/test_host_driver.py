@@ -47,6 +47,31 @@ def test_shim_compiles_against_reference_types(tmp_path):
                     "-Wno-deprecated-declarations"], check=True, capture_output=True)
 
 
+@pytest.mark.skipif(not os.path.isdir("/root/reference/LUTs"), reason="needs the reference's LUT text files (build container only)")
+def test_driver_reads_the_nuclear_tables_like_the_reference(tmp_path):
+    """--nuclear_corr MODEL (the reference's NUCLEAR_CORR build option at run time): the C++ energyReader loads the model's
+    nuclear_weights_and_sigmas_*.txt with the header checks of energy_reader.cpp:103-162; the assembled plan (--dump_case) carries
+    them in the case file's trailer, equal to what the Python reader produces."""
+    import struct
+    from raytracedicom_b200 import energy_reader as er
+    _build()
+    for name, model in er.NUCLEAR_MODELS.items():
+        out = tmp_path / f"{name}.rtdcase"
+        r = subprocess.run([EXE, "--water_cube_test", "--phys_data", "/root/reference/LUTs/", "--nuclear_corr", name, "--dump_case", str(out)],
+                           capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+        blob = out.read_bytes()
+        e = er.energy_reader("/root/reference/LUTs/", water_cube_test=True, nuclear_corr=model)
+        n = e.nucWeightMatrix.size
+        tail = blob[-(8 + 4 + 8 * n):]
+        assert tail[:8] == b"RTDNUCL1" and struct.unpack("<i", tail[8:12])[0] == model
+        got = np.frombuffer(tail[12:], np.float32)
+        assert np.array_equal(got[:n], e.nucWeightMatrix.ravel()) and np.array_equal(got[n:], e.nucSqSigmaMatrix.ravel())
+    r = subprocess.run([EXE, "--water_cube_test", "--phys_data", "/root/reference/LUTs/", "--nuclear_corr", "nonsense", "--dump_case", str(tmp_path / "x")],
+                       capture_output=True, text=True)
+    assert r.returncode == 1 and "Unknown nuclear model" in r.stderr
+
+
 @pytest.mark.gpu
 def test_driver_matches_python_binding(tmp_path):
     from raytracedicom_b200.engine import DoseEngine
