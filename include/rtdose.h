@@ -19,6 +19,12 @@
  * allocated and never resets the device (the reference deletes its inputs and calls cudaDeviceReset(),
  * src/kernel_wrapper.cu:856,1366-1368 - the C++ shim reproduces that for main.cu-style callers).
  * Threading: one context per device; calls on one context must not overlap.
+ *
+ * Limits the reference does not have (RTD_ERR_INVALID beyond them): at most 255 energy layers per beam (the superposition's layer list
+ * packs the layer number into 8 bits), at most 4095 tracer steps per beam, at most 4095 tiles of 32 x 8 rays per beam (a 1024 x 1024-ray
+ * grid is refused), spot grid at most 2^24 spots per layer. Every beam is validated before anything is launched: non-finite or
+ * non-positive spot pitch, ray spacing, sigmas, non-finite energies / transforms, a zero source distance are RTD_ERR_INVALID.
+ * Workspaces are sized for the worst case (every tracer step live) and only grow: 2 x 4 B x layers x steps x rays per beam dominate.
  */
 #ifndef RTDOSE_H
 #define RTDOSE_H

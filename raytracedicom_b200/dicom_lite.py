@@ -298,6 +298,12 @@ def read_ion_plan(path: str) -> List[dict]:
     ds = read_file(path)
     if ds.get_kw("Modality") != "RTPLAN" or "IonBeamSequence" not in ds:
         raise ValueError(f"{path}: not an RT Ion Plan")
+    # plan.beam_from_plan's gantry / couch chain is the head-first-supine one: refuse anything else instead of computing a mirrored dose
+    if "PatientSetupSequence" in ds:
+        for ps in ds["PatientSetupSequence"]:
+            pp = str(ps.get_kw("PatientPosition", "") or "").strip()
+            if pp and pp != "HFS":
+                raise ValueError(f"{path}: PatientPosition {pp} is not supported (head-first supine, HFS, only)")
     beams = []
     for be in ds["IonBeamSequence"]:
         cps = be["IonControlPointSequence"]

@@ -45,12 +45,16 @@ struct Buf {
 };
 
 // Parses elements in [pos, end) (or up to an item delimiter when the item has undefined length); returns the new position.
-size_t parse(const Buf& f, size_t pos, size_t end, bool explicitVr, DataSet& out) {
+constexpr int kMaxDepth = 32;   // nesting of sequences: a corrupt file must not overflow the stack
+size_t parse(const Buf& f, size_t pos, size_t end, bool explicitVr, DataSet& out, int depth = 0) {
+    if (depth > kMaxDepth) throw std::runtime_error("DICOM: sequences nested deeper than 32 levels");
+    end = std::min(end, f.b.size());       // lengths come from the file: never trust them beyond its size
     while (pos + 8 <= end) {
         const unsigned g = f.u16(pos), e = f.u16(pos + 2);
         if (g == 0xFFFE && (e == 0xE00D || e == 0xE0DD)) return pos + 8;      // item / sequence delimitation
         std::string vr; uint32_t len;
         if (explicitVr) {
+            if (pos + 6 > f.b.size()) throw std::runtime_error("DICOM: truncated file");
             vr.assign(reinterpret_cast<const char*>(&f.b[pos + 4]), 2);
             if (longVr(vr)) { len = f.u32(pos + 8); pos += 12; } else { len = f.u16(pos + 6); pos += 8; }
         } else {
@@ -60,15 +64,15 @@ size_t parse(const Buf& f, size_t pos, size_t end, bool explicitVr, DataSet& out
         }
         Element el; el.vr = vr;
         if (vr == "SQ" || (vr == "UN" && len == 0xFFFFFFFFu)) {
-            const size_t seqEnd = (len == 0xFFFFFFFFu) ? end : pos + len;
+            const size_t seqEnd = (len == 0xFFFFFFFFu) ? end : std::min(pos + size_t(len), end);
             while (pos + 8 <= seqEnd) {
                 const unsigned ig = f.u16(pos), ie = f.u16(pos + 2); const uint32_t ilen = f.u32(pos + 4);
                 pos += 8;
                 if (ig == 0xFFFE && ie == 0xE0DD) break;
                 if (!(ig == 0xFFFE && ie == 0xE000)) throw std::runtime_error("DICOM: item tag expected inside a sequence");
                 DataSet item;
-                if (ilen == 0xFFFFFFFFu) pos = parse(f, pos, seqEnd, explicitVr, item);
-                else { if (pos + ilen > f.b.size()) throw std::runtime_error("DICOM: truncated item"); parse(f, pos, pos + ilen, explicitVr, item); pos += ilen; }
+                if (ilen == 0xFFFFFFFFu) pos = parse(f, pos, seqEnd, explicitVr, item, depth + 1);
+                else { if (pos + ilen > f.b.size()) throw std::runtime_error("DICOM: truncated item"); parse(f, pos, pos + ilen, explicitVr, item, depth + 1); pos += ilen; }
                 el.items.push_back(std::move(item));
             }
         } else {
@@ -91,7 +95,8 @@ DataSet readFile(const std::string& path) {
     if (bytes.size() < 144 || memcmp(&bytes[128], "DICM", 4) != 0) throw std::runtime_error(path + ": not a DICOM Part-10 file");
     const Buf f{bytes};
     if (!(f.u16(132) == 0x0002 && f.u16(134) == 0x0000)) throw std::runtime_error(path + ": file meta group length missing");
-    const size_t metaEnd = 144 + f.u32(140);
+    const size_t metaEnd = 144 + size_t(f.u32(140));
+    if (metaEnd > bytes.size()) throw std::runtime_error(path + ": file meta group longer than the file");
     DataSet meta, ds;
     parse(f, 144, metaEnd, true, meta);
     const std::string ts = str(meta, tag(0x0002, 0x0010));
@@ -267,6 +272,13 @@ std::vector<PlanBeam> readIonPlan(const std::string& path) {
     using namespace dcm;
     const DataSet ds = readFile(path);
     if (str(ds, tag(0x0008, 0x0060)) != "RTPLAN" || !has(ds, tag(0x300A, 0x03A2))) throw std::runtime_error(path + ": not an RT Ion Plan");
+    // beamFromPlan's gantry / couch chain is the head-first-supine one (IEC 61217 as rti_coordinate_transform.hpp:48-58 applies it):
+    // any other patient position would be dose-calculated mirrored or rotated, silently. Refuse it.
+    if (has(ds, tag(0x300A, 0x0180)))
+        for (const DataSet& ps : seq(ds, tag(0x300A, 0x0180))) {
+            const std::string pp = str(ps, tag(0x0018, 0x5100));
+            if (!pp.empty() && pp != "HFS") throw std::runtime_error(path + ": PatientPosition " + pp + " is not supported (head-first supine, HFS, only)");
+        }
     std::vector<PlanBeam> beams;
     for (const DataSet& be : seq(ds, tag(0x300A, 0x03A2))) {
         PlanBeam pb;

@@ -66,26 +66,26 @@ public:
     BeamSettings(HostPinnedImage3D<float>* const spotWeights, const std::vector<float>& beamEnergies, const std::vector<float2>& spotSigmas,
                  const float2 raySpacing, const unsigned int tracerSteps, const float2 sourceDist, const Float3IdxTransform spotIdxToGantry,
                  const Float3AffineTransform& gantryToImIdx, const Float3AffineTransform& gantryToDoseIdx)
-        : sWghts(spotWeights), bEnergies(beamEnergies), sSigmas(spotSigmas), rSpacing(raySpacing), steps(tracerSteps), sDist(sourceDist),
-          sITG(spotIdxToGantry), gTII(gantryToImIdx), gTDI(gantryToDoseIdx) {}
-    HostPinnedImage3D<float>* getWeights() { return sWghts; }
-    std::vector<float>& getEnergies() { return bEnergies; }
-    std::vector<float2>& getSpotSigmas() { return sSigmas; }
-    float2 getRaySpacing() const { return rSpacing; }
-    unsigned int getSteps() const { return steps; }
-    float2 getSourceDist() const { return sDist; }
-    Float3IdxTransform getSpotIdxToGantry() const { return sITG; }
-    Float3AffineTransform getGantryToImIdx() const { return gTII; }
-    Float3AffineTransform getGantryToDoseIdx() const { return gTDI; }
+        : weights_(spotWeights), layerEnergies_(beamEnergies), layerSigmas_(spotSigmas), rayPitch_(raySpacing), nSteps_(tracerSteps),
+          sourceToIso_(sourceDist), spotToGantry_(spotIdxToGantry), toImage_(gantryToImIdx), toDose_(gantryToDoseIdx) {}
+    HostPinnedImage3D<float>* getWeights() { return weights_; }
+    std::vector<float>& getEnergies() { return layerEnergies_; }
+    std::vector<float2>& getSpotSigmas() { return layerSigmas_; }
+    float2 getRaySpacing() const { return rayPitch_; }
+    unsigned int getSteps() const { return nSteps_; }
+    float2 getSourceDist() const { return sourceToIso_; }
+    Float3IdxTransform getSpotIdxToGantry() const { return spotToGantry_; }
+    Float3AffineTransform getGantryToImIdx() const { return toImage_; }
+    Float3AffineTransform getGantryToDoseIdx() const { return toDose_; }
 private:
-    HostPinnedImage3D<float>* sWghts;
-    std::vector<float> bEnergies;
-    std::vector<float2> sSigmas;
-    float2 rSpacing;
-    unsigned int steps;
-    float2 sDist;
-    Float3IdxTransform sITG;
-    Float3AffineTransform gTII, gTDI;
+    HostPinnedImage3D<float>* weights_;
+    std::vector<float> layerEnergies_;
+    std::vector<float2> layerSigmas_;
+    float2 rayPitch_;
+    unsigned int nSteps_;
+    float2 sourceToIso_;
+    Float3IdxTransform spotToGantry_;
+    Float3AffineTransform toImage_, toDose_;
 };
 
 struct EnergyStruct {

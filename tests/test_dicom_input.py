@@ -250,3 +250,43 @@ def test_corrupt_dicom_is_an_error_never_a_crash(tmp_path, exe, lut_dir):
     r = subprocess.run([exe, "--ct_dir", os.path.join(base, "ct"), "--rtplan", os.path.join(base, "nan.dcm"), "--phys_data", lut_dir,
                         "--dump_case", str(tmp_path / "o.rtdcase")], capture_output=True, text=True, errors="replace", timeout=60)
     assert r.returncode == 1 and "finite" in (r.stdout + r.stderr)
+
+
+def test_non_hfs_plans_and_hostile_nesting_are_rejected(tmp_path, exe, lut_dir):
+    """beamFromPlan's gantry / couch chain assumes head-first supine: a plan whose PatientSetupSequence says anything else is
+    refused by both readers instead of being dose-calculated mirrored. Files that nest sequences without end, or end right after
+    a tag, are errors, not stack overflows or out-of-bounds reads."""
+    base = str(tmp_path / "base")
+    dl.generate_water_cube(base, n=24, margin=4)
+    plan_bytes = open(os.path.join(base, "rtplan.dcm"), "rb").read()
+    assert plan_bytes.count(b"HFS") >= 1
+    for pos in (b"HFP ", b"FFS ", b"FFP "):
+        p = os.path.join(base, "pos.dcm")
+        open(p, "wb").write(plan_bytes.replace(b"HFS ", pos))
+        with pytest.raises(ValueError, match="PatientPosition"):
+            dl.read_ion_plan(p)
+        r = subprocess.run([exe, "--ct_dir", os.path.join(base, "ct"), "--rtplan", p, "--phys_data", lut_dir, "--dump_case", str(tmp_path / "o.rtdcase")],
+                           capture_output=True, text=True, timeout=60)
+        assert r.returncode == 1 and "PatientPosition" in r.stderr
+    # 5000 nested undefined-length sequences (explicit VR LE): (300A,0180) SQ -> item -> (300A,0180) SQ -> ...
+    dl.write_ion_plan(os.path.join(base, "explicit.dcm"), dl.read_ion_plan(os.path.join(base, "rtplan.dcm")), explicit=True)
+    ex_bytes = open(os.path.join(base, "explicit.dcm"), "rb").read()
+    head = ex_bytes[:ex_bytes.index(b"DICM") + 4]
+    meta = ex_bytes[len(head):]
+    meta_len = int.from_bytes(meta[8:12], "little") if meta[4:6] == b"UL" else None
+    assert meta_len is not None
+    meta = meta[:12 + meta_len]
+    nest = (bytes([0x0A, 0x30, 0x80, 0x01]) + b"SQ\x00\x00" + b"\xff\xff\xff\xff" + bytes([0xFE, 0xFF, 0x00, 0xE0]) + b"\xff\xff\xff\xff") * 5000
+    deep = os.path.join(base, "deep.dcm")
+    open(deep, "wb").write(head + meta + nest)
+    with pytest.raises(ValueError):
+        dl.read_file(deep)
+    r = subprocess.run([exe, "--ct_dir", os.path.join(base, "ct"), "--rtplan", deep, "--phys_data", lut_dir, "--dump_case", str(tmp_path / "o.rtdcase")],
+                       capture_output=True, text=True, timeout=60)
+    assert r.returncode == 1 and "nested" in r.stderr
+    # a file that ends right after a tag
+    cut = os.path.join(base, "cut.dcm")
+    open(cut, "wb").write(head + meta + bytes([0x0A, 0x30, 0x80, 0x01]) + b"S")
+    r = subprocess.run([exe, "--ct_dir", os.path.join(base, "ct"), "--rtplan", cut, "--phys_data", lut_dir, "--dump_case", str(tmp_path / "o.rtdcase")],
+                       capture_output=True, text=True, timeout=60)
+    assert r.returncode == 1
