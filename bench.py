@@ -323,9 +323,10 @@ def measure(R, case, steps, warmup, do_e2e, do_cpu, full):
 
     for _ in range(warmup):
         step_device()
-    R.barrier()
+    torch.cuda.synchronize()
     if world > 1 and (not group or rank == 0) and (bool(dose_dev[:z0].any().item()) or bool(dose_dev[z1 + 1:].any().item())):
         raise SystemExit(f"bench.py: rank {rank} deposited dose outside the reduced slab [{z0}, {z1}]")
+    R.barrier()          # every rank enters the timed loop together (a late rank would be waited for inside the others' first step)
     sampler = ClockSampler(R.local) if full else None
     if sampler:
         sampler.start()
@@ -375,6 +376,9 @@ def measure(R, case, steps, warmup, do_e2e, do_cpu, full):
     else:
         own_all = [own_ms]
     rank_stage_ms = [round(float(t.item()), 4) for t in own_all]
+    each_all = [None] * world            # every rank's own per-step times and concurrent-mode stage sums (diagnostics)
+    if world > 1:
+        dist.all_gather_object(each_all, {"ms_each_step": ms_each_local, "stage_ms": {k: round(v, 4) for k, v in conc_stage.items() if k.startswith("ms")}})
     checksum = float(dose_dev.double().sum().item()) if rank == 0 else 0.0
     dmax = float(dose_dev.max().item()) if rank == 0 else 0.0
     reps = [eng.beam_report(b) for b in range(len(mine))]            # of the rank's own shard, before anything else runs
@@ -472,7 +476,7 @@ def measure(R, case, steps, warmup, do_e2e, do_cpu, full):
         res = {"value": U / (ms_step * 1e-3), "ms_per_step": ms_step, "updates_per_step": U, "ks_taps_per_step": taps,
                "sharding": (f"(beam, layer-range) work items, contiguous equal-cost runs over {world} ranks; " + how) if world > 1 else "single GPU",
                "l2": "256 MiB buffer written between timed iterations (L2 flush); CT 4*%d B and BEV arrays exceed L2" % (nx * ny * nz),
-               "ms_each_step_rank0": ms_each_local, "stage_total_ms_per_rank": rank_stage_ms, "work_items_per_rank": [len(p) for p in parts],
+               "ms_each_step_rank0": ms_each_local, "per_rank": each_all if world > 1 else None, "stage_total_ms_per_rank": rank_stage_ms, "work_items_per_rank": [len(p) for p in parts],
                "stage_ms_rank0": {k: stage[k] for k in ("msTrace", "msSetup", "msConv", "msIddSigma", "msRadius", "msSuperp", "msTransfer", "msTotal")},
                "stage_note": "stage_ms_rank0 and roofline come from 3 extra steps with opts.serialBeams=1 (stages bracketed alone); the timed steps run one stream per beam",
                "serial_beams_plan_ms": stage["msTotal"],
