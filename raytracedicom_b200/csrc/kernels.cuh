@@ -323,6 +323,8 @@ beam_setup_kernel(const SetupIn in, const int* __restrict__ trace, const LayerIn
 struct ConvParams {           // the ray pitch at the entry plane (pixelSpX / Y) depends on the tracer: BeamDev
     int inW, inH, outW, outH;
     float offX, offY, deltaX, deltaY, cutoff;
+    float rayWeightCutoff;    // RAY_WEIGHT_CUTOFF: a 32-ray row segment with no weight above it is dead for the depth scan
+    int listAll;              // 1: every segment is listed (rtd_opts.fullIntermediates)
 };
 
 __device__ __forceinline__ float conv_weight(float dist, float rSig) {   // gpu_convolution_2d.cu:28
@@ -331,7 +333,7 @@ __device__ __forceinline__ float conv_weight(float dist, float rSig) {   // gpu_
 
 __global__ void __launch_bounds__(256)
 spot_to_ray_kernel(const float* __restrict__ in, const float2* __restrict__ sigmas, float* __restrict__ out, const ConvParams c,
-                   const BeamDev* __restrict__ bd) {
+                   const BeamDev* __restrict__ bd, int* __restrict__ segCount /*[L]*/, uint16_t* __restrict__ segList /*[L][segs]*/) {
     extern __shared__ float sInterm[];   // [inH][32]
     if (bd->nz <= 0) return;             // the beam never enters the patient
     const float pixelSpX = bd->pixelSpX, pixelSpY = bd->pixelSpY;
@@ -374,6 +376,10 @@ spot_to_ray_kernel(const float* __restrict__ in, const float2* __restrict__ sigm
                 dist = f_sub(f_fma(c.deltaY, i2f(ci), c.offY), fo);
             }
             out[((size_t)layer * c.outH + oy) * c.outW + ox] = res;
+            // a warp holds one 32-ray row segment of the layer: the segments with a weight above the cut-off are the work items of
+            // the depth scan (idd_sigma_kernel), listed here while their weights are in registers
+            const bool liveSeg = __any_sync(0xffffffffu, !(res < c.rayWeightCutoff)) || c.listAll;
+            if (tx == 0 && liveSeg) segList[(size_t)layer * (c.outH * gridDim.x) + atomicAdd(segCount + layer, 1)] = (uint16_t)(oy * gridDim.x + blockIdx.x);
         }
     }
 }
@@ -393,10 +399,14 @@ struct IddParams {
                               // 0: row segments without dose are left alone - the superposition never reads them (see the step lambda)
 };
 
-// Thread = (ray, layer), warp = 32-ray row segment, CTA = ONE warp... x IDD_WARPS: the depth scan of a row segment is a serial chain
-// whose length differs wildly between segments (rays outside the field end at once, two thirds of all segments on C3), so
-// small CTAs give their slot back as soon as their own segments end instead of waiting for the longest of eight; the per-step
-// table the CTA used to build in shared memory is the beam's stepTab (beam_setup_kernel), read through L1.
+// Thread = (ray, layer), warp = 32-ray row segment. The depth scan of a segment is a serial chain whose length differs wildly
+// between segments: rays outside the field never start (two thirds of all segments on C3), shallow layers stop early. A grid of
+// one CTA per (segment, layer) leaves that to the block scheduler, which deals CTAs to SMs in launch order: ncu showed the busiest
+// scheduler issuing 1.75 x the average (profiles/r02_ncu_full_c3_mid.txt) and the kernel lasting as long as that one. Here the
+// pre-convolution lists the live segments of every layer (spot_to_ray_kernel), and persistent warps pull (layer, segment) items
+// from ONE queue ordered by decreasing scan length (longest-processing-time first): every scheduler stays busy until the queue is
+// empty. Dead segments are never visited: their row minima / firstPassive are the fill values beam_clear_kernel wrote.
+// The per-step table the CTA used to build in shared memory is the beam's stepTab (beam_setup_kernel), read through L1.
 constexpr int IDD_WARPS = 2;
 __global__ void __launch_bounds__(IDD_WARPS * 32)
 idd_sigma_kernel(const float* __restrict__ density, const float* __restrict__ wepl, const float* __restrict__ rayWeights,
@@ -404,22 +414,38 @@ idd_sigma_kernel(const float* __restrict__ density, const float* __restrict__ we
                  const LayerParams* __restrict__ layers, const BeamDev* __restrict__ bd, const float2* __restrict__ stepTab, const IddParams q,
                  cudaTextureObject_t iddTex, cudaTextureObject_t rrlTex, cudaTextureObject_t nucTex,
                  float* __restrict__ idd, float* __restrict__ rsig, float* __restrict__ rowMin,
-                 int* __restrict__ firstPassive, int* __restrict__ layerFirstPassive) {
+                 int* __restrict__ firstPassive, int* __restrict__ layerFirstPassive,
+                 const int L, const int* __restrict__ segCount, const uint16_t* __restrict__ segList, int* __restrict__ queue) {
     const int nz = bd->nz;
     if (nz <= 0) return;
-    // CTAs are handed out in grid order and not all of them are resident at once: the layers with the longest depth scan go
-    // first so that the short ones fill the tail instead of the other way round
-    const int l = layers[blockIdx.z].order;
+    __shared__ int sPrefix[257];          // items before the i-th layer in launch order (deepest first)
+    if (threadIdx.x == 0) {
+        int acc = 0;
+        for (int i = 0; i < L; ++i) { sPrefix[i] = acc; acc += segCount[layers[i].order]; }
+        sPrefix[L] = acc;
+    }
+    __syncthreads();
+    const int total = sPrefix[L];
     const int tilesX = q.Rx / 32;
-    const int seg = blockIdx.x * IDD_WARPS + (threadIdx.x >> 5);
-    if (seg >= tilesX * q.Ry) return;
-    const int segX = seg % tilesX;
-    const int x = segX * 32 + (threadIdx.x & 31);
-    const int y = seg / tilesX;
+    const int segsPerLayer = tilesX * q.Ry;
     const int R = q.Rx * q.Ry;
+    const int lane = threadIdx.x & 31;
+    const unsigned first = (unsigned)bd->bfi;
+    const float inf = __int_as_float(0x7f800000);
+  for (;;) {
+    int item = 0;
+    if (lane == 0) item = atomicAdd(queue, 1);
+    item = __shfl_sync(0xffffffffu, item, 0);
+    if (item >= total) break;
+    int li = 0;
+    while (sPrefix[li + 1] <= item) ++li;          // L <= 255 and the items of a warp mostly advance through the layers in order
+    const int l = layers[li].order;
+    const int seg = segList[(size_t)l * segsPerLayer + (item - sPrefix[li])];
+    const int segX = seg % tilesX;
+    const int x = segX * 32 + lane;
+    const int y = seg / tilesX;
     const int ray = y * q.Rx + x;
     const LayerParams lp = layers[l];
-    const unsigned first = (unsigned)bd->bfi;
 
     const int firstIn = firstInside[ray];
     unsigned afterLast = (unsigned)min(firstOutside[ray], lp.afterLast);
@@ -440,7 +466,6 @@ idd_sigma_kernel(const float* __restrict__ density, const float* __restrict__ we
     float sigmaSq = f_neg(incDiv);
     float res = 0.0f, rs = 0.0f, wOld = 0.0f, dOld = 0.0f;
     const float thr = f_mul(lp.peakDepth, q.bpCutoff);
-    const float inf = __int_as_float(0x7f800000);
 
     // per-thread base pointers + one 32-bit running offset per array (a slab of one layer / one beam stays far below 2^32
     // elements): one IMAD.WIDE per access instead of 64-bit index chains
@@ -451,7 +476,6 @@ idd_sigma_kernel(const float* __restrict__ density, const float* __restrict__ we
     float* const rowMinP = rowMin + ((size_t)l * nz * q.Ry + y) * (q.Rx / 32) + segX;
     const unsigned rmStride = (unsigned)(q.Ry * (q.Rx / 32));
     unsigned off = 0, rmOff = 0;
-    const int lane = threadIdx.x & 31;
     // The depth scan is a dependent chain per ray, and the load -> texture -> arithmetic latency of one step is what a step costs.
     // Software pipeline over two statically named slots (step s lives in slot s & 1, the
     // loop is unrolled by two so that no register is rotated at the back edge - a rotating MOV would wait for the request
@@ -550,10 +574,11 @@ idd_sigma_kernel(const float* __restrict__ density, const float* __restrict__ we
     if (q.writeAll) {
         for (unsigned kk = k; kk < last; ++kk) { iddP[off + (kk - k) * (unsigned)R] = 0.0f; rsigP[off + (kk - k) * (unsigned)R] = inf; }
     }
-    for (unsigned kk = k + lane; kk < last; kk += 32) rowMinP[rmOff + (kk - k) * rmStride] = -inf;
+    // (the row minima of the steps after the segment's last live one keep beam_clear_kernel's -inf)
     firstPassive[(size_t)l * R + ray] = (int)afterLast;
     const int wm = warp_max_i((int)afterLast);
     if (lane == 0) atomicMax(layerFirstPassive + l, wm);
+  }
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -686,14 +711,25 @@ __device__ __forceinline__ float bev_plane(const float* __restrict__ pl, const G
     return fmaf((float)(x0 - w01), v00, fmaf((float)(x1 - w11), v10, fmaf((float)w01, v01, (float)w11 * v11)));
 }
 
-// Clears the slices [bfi, Zg) of the haloed BEV dose (the only ones the superposition writes and the transfer reads).
+// Per-beam fills, sized by the beam's own slice count: the slices [bfi, Zg) of the haloed BEV dose (the only ones the superposition
+// writes and the transfer reads) = 0; the row minima of every (layer, slice, segment) = -inf ("no dose, sigma undefined": what a
+// segment the depth scan never visits, or has left behind, means to tile_radius_kernel); firstPassive = 0 (dead rays).
 __global__ void __launch_bounds__(256)
-bev_zero_kernel(float* __restrict__ bev, const BeamDev* __restrict__ bd, const int planeFloats /* (Rx + 64)(Ry + 64), a multiple of 4 */) {
+beam_clear_kernel(float* __restrict__ bev, const BeamDev* __restrict__ bd, const int planeFloats /* (Rx + 64)(Ry + 64), a multiple of 4 */,
+                  float* __restrict__ rowMin, const int rowMinPerSlice /* L-independent: Ry * Rx / 32 */, const int L,
+                  int* __restrict__ firstPassive, const int LR /* L * rays, a multiple of 4 */) {
     const int nz = bd->nz;
     if (nz <= 0) return;
+    const size_t tid = (size_t)blockIdx.x * 256 + threadIdx.x, nth = (size_t)gridDim.x * 256;
     float4* p = reinterpret_cast<float4*>(bev + (size_t)bd->bfi * planeFloats);
     const size_t n4 = (size_t)nz * (planeFloats / 4);
-    for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += (size_t)gridDim.x * 256) p[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    for (size_t i = tid; i < n4; i += nth) p[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    const float ninf = __int_as_float(0xff800000);
+    float4* rm = reinterpret_cast<float4*>(rowMin);
+    const size_t m4 = (size_t)L * nz * rowMinPerSlice / 4;       // rowMinPerSlice is a multiple of 8
+    for (size_t i = tid; i < m4; i += nth) rm[i] = make_float4(ninf, ninf, ninf, ninf);
+    int4* fp = reinterpret_cast<int4*>(firstPassive);
+    for (size_t i = tid; i < (size_t)LR / 4; i += nth) fp[i] = make_int4(0, 0, 0, 0);
 }
 
 // Persistent: the grid is sized from the machine, the work units (32 x 8 dose columns x one chunk of the box's z range) from the

@@ -77,14 +77,15 @@ struct BeamWs {
     rtd_beam_report rep; std::vector<rtd_layer_report> lrep;
     // device
     DevBuf density, wepl, firstIn, firstOut, weplMin, spotW, sigmas, rayW, layerIn, layerDev, beamDev, stepTab, idd, rsig, rowMin,
-           firstPassive, lfp, batchRad, rbOffset, radMap, list, bev;
+           firstPassive, lfp, batchRad, rbOffset, radMap, list, bev, segList;
     PinBuf hStage;   // staging of the uploads: spot weights | LayerIn[Lc]
     PinBuf hOut;     // BeamDev | LayerParams[Lc] | entry sigmas[Lc] | control block | batchRad[Lc*34]
-    size_t ctlInts() const { return size_t(Lc) + size_t(Lc) * 34 + 33 + 4 + 4 + 4; }   // lfp[L] | hist[L*34] | bigCursor[33] | stats[4] | work[4] | ksItems[4]
+    // lfp[L] | hist[L*34] | bigCursor[33] | stats[4] | work[4] | ksItems[4] | segCount[L] | iddQueue[4]
+    size_t ctlInts() const { return size_t(Lc) + size_t(Lc) * 34 + 33 + 4 + 4 + 4 + size_t(Lc) + 4; }
     size_t outCtlOff() const { return (sizeof(BeamDev) + size_t(Lc) * (sizeof(LayerParams) + sizeof(float2)) + 15) / 16 * 16; }
     void release() {
         DevBuf* all[] = {&density, &wepl, &firstIn, &firstOut, &weplMin, &spotW, &sigmas, &rayW, &layerIn, &layerDev, &beamDev, &stepTab, &idd, &rsig,
-                         &rowMin, &firstPassive, &lfp, &batchRad, &rbOffset, &radMap, &list, &bev};
+                         &rowMin, &firstPassive, &lfp, &batchRad, &rbOffset, &radMap, &list, &bev, &segList};
         for (DevBuf* b : all) b->release();
         hStage.release(); hOut.release();
     }
@@ -113,7 +114,7 @@ struct rtd_ctx {
     std::vector<cudaEvent_t> events;
     std::vector<cudaStream_t> bstreams;   // per-beam streams (concurrent beams)
     int smCount = 148;
-    int ks2Blocks8 = 0, ks2Blocks16 = 0, ks2Blocks24 = 0, ks2Blocks32 = 0;
+    int ks2Blocks8 = 0, ks2Blocks16 = 0, ks2Blocks24 = 0, ks2Blocks32 = 0, iddBlocks = 0;
     rtd_opts optsLast;
     // the ranks of a node that compute one plan together (rtd_group_*): ONE dose grid + control block on rank 0, mapped over CUDA IPC
     int groupRank = -1, groupWorld = 0; size_t groupFloats = 0;
@@ -436,6 +437,8 @@ rtd_status beamEnqueue(rtd_ctx* ctx, int beamNo, const rtd_beam& b, BeamWs& w, c
     RTD_CUDA(w.radMap.ensure(size_t(L) * S * tiles)); RTD_CUDA(w.list.ensure(size_t(S) * tiles * 4));
     const int planeFloats = (Ry + 64) * (Rx + 64);
     RTD_CUDA(w.bev.ensure(size_t(S) * planeFloats * 4));
+    const int segs = tilesX * Ry;                      // 32-ray row segments per layer (< 2^16: at most 4095 tiles of 8 rows)
+    RTD_CUDA(w.segList.ensure(size_t(L) * segs * 2));
     RTD_CUDA(w.hOut.ensure(w.outCtlOff() + (ctlInts + size_t(L) * 34) * 4));
 
     // ---- host part of the per-layer parameters (cu:829-838): needs the LUTs only
@@ -518,18 +521,20 @@ rtd_status beamEnqueue(rtd_ctx* ctx, int beamNo, const rtd_beam& b, BeamWs& w, c
     // what the host wants to know about the set-up (reports; the dose boxes of a pageable host grid)
     RTD_CUDA(cudaMemcpyAsync(w.hOut.p, w.beamDev.p, sizeof(BeamDev), cudaMemcpyDeviceToHost, st));
     RTD_CUDA(cudaEventRecord(evBeam(ctx, beamNo, 10), st));
-    bev_zero_kernel<<<ctx->smCount * 4, 256, 0, st>>>(w.bev.as<float>(), bd, planeFloats);
+    beam_clear_kernel<<<ctx->smCount * 4, 256, 0, st>>>(w.bev.as<float>(), bd, planeFloats, w.rowMin.as<float>(), Ry * tilesX, L, w.firstPassive.as<int>(), L * R);
     RTD_CUDA(cudaEventRecord(evBeam(ctx, beamNo, 2), st));
 
     int* dLfp = w.lfp.as<int>(); int* dHist = dLfp + L; int* dCursor = dHist + size_t(L) * 34; int* dStats = dCursor + 33; int* dWork = dStats + 4;
+    int* dSegCount = dWork + 8; int* dIddQueue = dSegCount + L;
     // K3a (cu:849-854)
     ConvParams cp;
     cp.inW = w.sx; cp.inH = w.sy; cp.outW = Rx; cp.outH = Ry;
     const V3 rayD = w.grid.rayIdxToGantry.delta, rayO = w.grid.rayIdxToGantry.offset;
     cp.deltaX = b.spotDelta[0] / rayD.x; cp.deltaY = b.spotDelta[1] / rayD.y;
     cp.offX = (b.spotOffset[0] - rayO.x) / rayD.x; cp.offY = (b.spotOffset[1] - rayO.y) / rayD.y;
-    cp.cutoff = o.convSigmaCutoff;
-    spot_to_ray_kernel<<<dim3(Rx / 32, L), 256, size_t(w.sy) * 32 * 4, st>>>(w.spotW.as<float>(), w.sigmas.as<float2>(), w.rayW.as<float>(), cp, bd);
+    cp.cutoff = o.convSigmaCutoff; cp.rayWeightCutoff = o.rayWeightCutoff; cp.listAll = o.fullIntermediates ? 1 : 0;
+    spot_to_ray_kernel<<<dim3(Rx / 32, L), 256, size_t(w.sy) * 32 * 4, st>>>(w.spotW.as<float>(), w.sigmas.as<float2>(), w.rayW.as<float>(), cp, bd,
+                                                                            dSegCount, w.segList.as<uint16_t>());
     RTD_CUDA(cudaEventRecord(evBeam(ctx, beamNo, 3), st));
 
     // K2
@@ -541,10 +546,11 @@ rtd_status beamEnqueue(rtd_ctx* ctx, int beamNo, const rtd_beam& b, BeamWs& w, c
     q.nuclear = o.nuclearCorr;
     q.eRefSq = o.nuclearCorr == 1 ? 190.44f : o.nuclearCorr == 2 ? 216.09f : o.nuclearCorr == 3 ? 169.00f : 198.81f;
     q.sigmaDelta = o.nuclearCorr == 1 ? 0.0f : o.nuclearCorr == 2 ? 0.08f : o.nuclearCorr == 3 ? 0.06f : 0.21f;
-    const int segs = tilesX * Ry;
-    idd_sigma_kernel<<<dim3((segs + IDD_WARPS - 1) / IDD_WARPS, 1, L), IDD_WARPS * 32, 0, st>>>(w.density.as<float>(), w.wepl.as<float>(), w.rayW.as<float>(),
+    // persistent: as many 2-warp CTAs as the machine holds (53 registers -> 18 CTAs per SM), never more than there are segments
+    const int iddBlocks = std::max(1, std::min(ctx->iddBlocks, (L * segs + IDD_WARPS - 1) / IDD_WARPS));
+    idd_sigma_kernel<<<iddBlocks, IDD_WARPS * 32, 0, st>>>(w.density.as<float>(), w.wepl.as<float>(), w.rayW.as<float>(),
         w.firstIn.as<int>(), w.firstOut.as<int>(), w.layerDev.as<LayerParams>(), bd, w.stepTab.as<float2>(), q, ctx->iddTex.tex, ctx->rrlTex.tex, ctx->nucTex.tex,
-        w.idd.as<float>(), w.rsig.as<float>(), w.rowMin.as<float>(), w.firstPassive.as<int>(), dLfp);
+        w.idd.as<float>(), w.rsig.as<float>(), w.rowMin.as<float>(), w.firstPassive.as<int>(), dLfp, L, dSegCount, w.segList.as<uint16_t>(), dIddQueue);
     RTD_CUDA(cudaEventRecord(evBeam(ctx, beamNo, 4), st));
 
     // tile radii, batching, work list (grids for the worst case nz = S; the kernels stop at the beam's own slice count)
@@ -615,7 +621,7 @@ bool beamFinish(rtd_ctx* ctx, BeamWs& w, int64_t& updates, int64_t& taps, int& k
     }
     if (!w.live) return true;
     const int* lfp = reinterpret_cast<const int*>(out + w.outCtlOff()); const int* hist = lfp + L; const int* stats = hist + size_t(L) * 34 + 33;
-    const int* ksItems = stats + 8;
+    const int* ksItems = stats + 8;       // stats[4] | work[4] | ksItems[4] | segCount[L] | iddQueue[4]
     for (int i = 0; i < 4; ++i) if (ksItems[i] > 0) ++ksLaunches;
     const int* brad = lfp + w.ctlInts();
     int fcp = 0; int64_t u = 0, t = 0;
@@ -828,6 +834,7 @@ static rtd_status createCommon(rtd_ctx** out, int device, cudaStream_t userStrea
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ks2_kernel<8, KS2_WARPS_8>, KS2_WARPS_8 * 32, KS2_SMEM_8); ctx->ks2Blocks8 = std::max(occ, 1) * ctx->smCount;
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ks2_kernel<32, KS2_WARPS_32>, KS2_WARPS_32 * 32, KS2_SMEM_32); ctx->ks2Blocks32 = std::max(occ, 1) * ctx->smCount;
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ks2_kernel<24, KS2_WARPS_24>, KS2_WARPS_24 * 32, KS2_SMEM_24); ctx->ks2Blocks24 = std::max(occ, 1) * ctx->smCount;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, idd_sigma_kernel, IDD_WARPS * 32, 0); ctx->iddBlocks = std::max(occ, 1) * ctx->smCount;
     if (cudaGetLastError() != cudaSuccess) { cudaStreamDestroy(ctx->cstream); if (ctx->ownStream) cudaStreamDestroy(ctx->stream); delete ctx; return RTD_ERR_CUDA; }
     *out = ctx;
     return RTD_OK;

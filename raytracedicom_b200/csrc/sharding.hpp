@@ -19,7 +19,9 @@ struct WorkItem { int rank, beam, lo, hi; };
 
 // Relative cost of each energy layer: rays x live depth steps x mean kernel-superposition taps. Live steps grow with the peak depth;
 // the lateral sigma grows roughly linearly with depth (~2 % of range plus the in-air spot size), so
-// taps ~ (2 * 3 sigma / pitch + 1)^2 averaged over depth; + 40 for the per-update cost of the depth scan and radius passes.
+// taps ~ (2 * 3 sigma / pitch + 1)^2 averaged over depth; + 130 for the per-update cost of the depth scan, the radius passes and the
+// superposition's per-(tile, layer) work that does not grow with the radius (weight table, loads, list) - refitted in round 2 to the
+// per-rank stage sums of C3 on 8 B200s (profiles/r02_bench_c3_n8.json: superposition ~ 6.8e-7 ms per unit + 0.012 ms per layer).
 inline std::vector<double> layerCost(const rtd_beam& b, const float* energies, const float* peakDepths, int nE) {
     const double pitch = std::min(b.raySpacing[0], b.raySpacing[1]);
     std::vector<double> out(b.nLayers);
@@ -33,14 +35,15 @@ inline std::vector<double> layerCost(const rtd_beam& b, const float* energies, c
             const double r = std::nearbyint(3.0 * (0.3 + (sigEnd - 0.3) * t) / pitch);     // round half to even, like Python's round()
             taps += (2.0 * r + 1.0) * (2.0 * r + 1.0);
         }
-        out[l] = steps * (taps / 16.0 + 40.0);
+        out[l] = steps * (taps / 16.0 + 130.0);
     }
     return out;
 }
 
 // in layerCost units: the tracer + transfer + set-up a rank repeats for every beam it touches
-// (least-squares fit of the per-rank stage totals of C3 and C4 at N = 2 and 8 on B200: 300 - 530 per tracer step)
-constexpr double PIECE_COST_PER_STEP = 400.0;
+// (round 2, C3 on 8 B200s: tracer + set-up + pre-convolution + depth-scan floor + radius + transfer = 0.33 ms per beam piece whatever its
+// layer count, i.e. ~850 units per tracer step; round 1's kernels gave 300 - 530)
+constexpr double PIECE_COST_PER_STEP = 850.0;
 inline double pieceCost(const rtd_beam& b) { return PIECE_COST_PER_STEP * double(b.steps); }
 
 // Assigns every (beam, layer) to exactly one of `world` ranks. chunksPerBeam = 0: consecutive runs of near-equal cost (see above);

@@ -29,12 +29,12 @@ def layer_cost(beam: Beam, luts) -> np.ndarray:
         steps = peak / abs(float(beam.spot_delta[2]))
         sig_end = 0.022 * peak + 0.3
         taps = np.mean([(2.0 * round(3.0 * (0.3 + (sig_end - 0.3) * t) / pitch) + 1.0) ** 2 for t in np.linspace(0.0, 1.0, 16)])
-        out[l] = steps * (taps + 40.0)   # + per-update cost of the IDD/sigma and radius passes
+        out[l] = steps * (taps + 130.0)  # + per-update cost of the IDD/sigma, radius passes and the radius-independent part of the superposition
     return out
 
 
-PIECE_COST_PER_STEP = 400.0   # in layer_cost units: the tracer + transfer + setup a rank repeats for every beam it touches
-                              # (least-squares fit of the per-rank stage totals of C3 and C4 at N = 2 and 8 on B200: 300 - 530)
+PIECE_COST_PER_STEP = 850.0   # in layer_cost units: the tracer + transfer + setup a rank repeats for every beam it touches
+                              # (round 2 fit to the per-rank stage sums of C3 on 8 B200s: 0.33 ms per beam piece)
 
 
 def piece_cost(beam: Beam) -> float:
