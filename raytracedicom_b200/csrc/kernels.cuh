@@ -476,13 +476,8 @@ idd_sigma_kernel(const float* __restrict__ density, const float* __restrict__ we
     float* const rowMinP = rowMin + ((size_t)l * nz * q.Ry + y) * (q.Rx / 32) + segX;
     const unsigned rmStride = (unsigned)(q.Ry * (q.Rx / 32));
     unsigned off = 0, rmOff = 0;
-    // The depth scan is a dependent chain per ray, and the load -> texture -> arithmetic latency of one step is what a step costs.
-    // Software pipeline over two statically named slots (step s lives in slot s & 1, the
-    // loop is unrolled by two so that no register is rotated at the back edge - a rotating MOV would wait for the request
-    // issued in the same iteration): at step k the slot of step k is copied out and re-used for the WEPL / density request
-    // of step k + 2, and the two LUT fetches of step k + 1 (IDD at its WEPL, 1/X0 at its density) are issued from the other
-    // slot, whose data was requested one iteration earlier. Every result has about one full iteration to arrive.
-    // Coordinates and order of the arithmetic are unchanged.
+    // The depth scan is a dependent chain per ray, and the load -> texture -> arithmetic latency of one step is what a step costs
+    // unless the requests run ahead of their use: see the slots below. Coordinates and order of the arithmetic are the reference's.
     const unsigned last = (unsigned)lp.afterLast;
     const float eRow = f_add(lp.energyIdx, 0.5f);
     // The scattering power per unit 1/X0 of a step (t1: residual energy from the mean WEPL of the step, 4 of the step's 7 MUFU
@@ -494,24 +489,38 @@ idd_sigma_kernel(const float* __restrict__ density, const float* __restrict__ we
         const float betaP = f_sub(e1, f_div(880406.875f, e1));
         return f_mul(f_div(q.eRefSq, f_mul(betaP, betaP)), stepLength);
     };
-    float wS0 = 0.0f, rhoS0 = 0.0f, dS0 = 0.0f, xS0 = 0.0f, tS0 = 0.0f, wS1 = 0.0f, rhoS1 = 0.0f, dS1 = 0.0f, xS1 = 0.0f, tS1 = 0.0f;
+    // Four statically named slots (step s lives in slot s & 3, the loop is unrolled by four so that no register rotates at the back
+    // edge): at step k the WEPL / density of step k + 3 are requested, the two LUT fetches (IDD at its WEPL, 1/X0 at its density) and
+    // the scattering power of step k + 2 are issued, the step table entry of step k + 1 is loaded. Round 2's profile of the two-slot
+    // version showed half of all stall samples on the first use of the 1/X0 fetch and of the step table: one step (~400 issue
+    // slots shared by the scheduler's warps) does not cover a texture round trip.
+    struct Slot { float w, rho, d, x, t; };
+    Slot S0 = {0.0f, 0.0f, 0.0f, 0.0f, 0.0f}, S1 = S0, S2 = S0, S3 = S0;
+    float2 stNext = make_float2(0.0f, 0.0f);
     if (live && first < last) {
-        wS0 = weplP[0]; rhoS0 = densP[0];
-        if (first + 1 < last) { wS1 = weplP[R]; rhoS1 = densP[R]; }
-        dS0 = tex2D<float>(iddTex, f_fma(wS0, lp.energyScale, 0.5f), eRow);
-        xS0 = tex1D<float>(rrlTex, f_fma(rhoS0, q.rrlScale, 0.5f));
-        tS0 = scatPower(0.0f, wS0);
+        S0.w = weplP[0]; S0.rho = densP[0];
+        if (first + 1 < last) { S1.w = weplP[R]; S1.rho = densP[R]; }
+        if (first + 2 < last) { S2.w = weplP[2 * R]; S2.rho = densP[2 * R]; }
+        S0.d = tex2D<float>(iddTex, f_fma(S0.w, lp.energyScale, 0.5f), eRow);
+        S0.x = tex1D<float>(rrlTex, f_fma(S0.rho, q.rrlScale, 0.5f));
+        S0.t = scatPower(0.0f, S0.w);
+        if (first + 1 < last) {
+            S1.d = tex2D<float>(iddTex, f_fma(S1.w, lp.energyScale, 0.5f), eRow);
+            S1.x = tex1D<float>(rrlTex, f_fma(S1.rho, q.rrlScale, 0.5f));
+            S1.t = scatPower(S0.w, S1.w);
+        }
+        stNext = __ldg(stepTab);
     }
-    // one step: (wC, rhoC, dC, xC, tC) = slot of step k, (wN, rhoN, dN, xN, tN) = slot of step k + 1
-    auto step = [&](const unsigned k, float& wC, float& rhoC, const float& dC, const float& xC, const float& tC,
-                    const float& wN, const float& rhoN, float& dN, float& xN, float& tN) {
-        const float w = wC, rho = rhoC;
-        const float2 st = __ldg(stepTab + (k - first));          // 0.5 (vwx + vwy), stepVol of this step
-        if (live && k + 1 < last) {
-            dN = tex2D<float>(iddTex, f_fma(wN, lp.energyScale, 0.5f), eRow);
-            xN = tex1D<float>(rrlTex, f_fma(rhoN, q.rrlScale, 0.5f));
-            tN = scatPower(w, wN);          // wOld of step k + 1 is this step's WEPL (the ray is live here)
-            if (k + 2 < last) { wC = weplP[off + 2 * R]; rhoC = densP[off + 2 * R]; }
+    // one step: C = slot of step k, N1 / N2 / N3 = slots of steps k + 1 / k + 2 / k + 3 (N3 is the slot step k - 1 has left)
+    auto step = [&](const unsigned k, const Slot& C, const Slot& N1, Slot& N2, Slot& N3) {
+        const float w = C.w, rho = C.rho, xC = C.x, tC = C.t, dC = C.d;
+        const float2 st = stNext;                                  // 0.5 (vwx + vwy), stepVol of this step
+        if (live && k + 1 < last) stNext = __ldg(stepTab + (k + 1 - first));
+        if (live && k + 2 < last) {
+            N2.d = tex2D<float>(iddTex, f_fma(N2.w, lp.energyScale, 0.5f), eRow);
+            N2.x = tex1D<float>(rrlTex, f_fma(N2.rho, q.rrlScale, 0.5f));
+            N2.t = scatPower(N1.w, N2.w);          // wOld of step k + 2 is the WEPL of step k + 1 (if the ray is still live there)
+            if (k + 3 < last) { N3.w = weplP[off + 3 * R]; N3.rho = densP[off + 3 * R]; }
         }
         if (live) {
             if (w < lp.peakDepth) {
@@ -564,12 +573,15 @@ idd_sigma_kernel(const float* __restrict__ density, const float* __restrict__ we
     unsigned k = first;
     // a ray never comes back to life: once no lane of the warp is live (rays outside the field; every ray past its range)
     // the rest of the row is "no dose, sigma undefined": only its row minimum is written
-    while (k < last && __any_sync(0xffffffffu, live)) {
-        step(k, wS0, rhoS0, dS0, xS0, tS0, wS1, rhoS1, dS1, xS1, tS1);
-        ++k;
-        if (k >= last || !__any_sync(0xffffffffu, live)) break;
-        step(k, wS1, rhoS1, dS1, xS1, tS1, wS0, rhoS0, dS0, xS0, tS0);
-        ++k;
+    for (;;) {
+        if (!(k < last && __any_sync(0xffffffffu, live))) break;
+        step(k, S0, S1, S2, S3); ++k;
+        if (!(k < last && __any_sync(0xffffffffu, live))) break;
+        step(k, S1, S2, S3, S0); ++k;
+        if (!(k < last && __any_sync(0xffffffffu, live))) break;
+        step(k, S2, S3, S0, S1); ++k;
+        if (!(k < last && __any_sync(0xffffffffu, live))) break;
+        step(k, S3, S0, S1, S2); ++k;
     }
     if (q.writeAll) {
         for (unsigned kk = k; kk < last; ++kk) { iddP[off + (kk - k) * (unsigned)R] = 0.0f; rsigP[off + (kk - k) * (unsigned)R] = inf; }
