@@ -117,6 +117,10 @@ typedef struct {
                                 constructed with nucMemoryStep = 0 (cu:925), so every depth step of a halo pencil beam lands in BEV slice 0 and
                                 the second superposition / nucTransfDiv (cu:978-996, 1058-1092, 1220-1255) deposit nothing unless the beam's
                                 first live step is step 0; that one case (beamFirstInside == 0) is rejected with RTD_ERR_INVALID */
+    int   noGraph;           /* 0 (default): a device-resident plan with several beams (rtd_dose_device) is captured once into a CUDA graph and
+                                replayed while the plan's geometry, options, buffers and LUTs stay the same (spot weights may change: they are
+                                copied from a staging buffer at every replay); stage times of rtd_timing are 0 for replayed plans. 1: always
+                                issue the launches one by one */
     int   fullIntermediates; /* 1: the depth scan writes idd / rSigmaEff of EVERY (ray, step) as the reference does, for rtd_debug_fetch
                                 (RTD_FETCH_IDD / RTD_FETCH_RSIGMA). 0 (default): 32-ray row segments that hold no dose at a step are
                                 not written (the superposition never reads them; ~60 % of the scan's HBM writes on a head plan) and

@@ -72,7 +72,7 @@ struct BeamWs {
     std::vector<LayerIn> lin;             // [Lc]
     // results of the device-side set-up (beam_setup_kernel), on the host after the final sync of the call
     int bfi = 0, bfo = 0, Zg = 0, nz = 0; bool live = false;
-    float entryZ = 0;
+    float entryZ = 0, maxPeakDepth = 0;
     BeamDev hostDev;
     rtd_beam_report rep; std::vector<rtd_layer_report> lrep;
     // device
@@ -90,6 +90,8 @@ struct BeamWs {
         hStage.release(); hOut.release();
     }
 };
+
+struct CallState { int launches = 0, hostSyncs = 1; bool serial = false, prepared = false, graph = false; cudaEvent_t evXferEnd = nullptr; };
 
 }  // namespace
 
@@ -123,6 +125,9 @@ struct rtd_ctx {
     unsigned long long groupEpoch = 0;
     PinBuf groupFlag;                              // [0] = a barrier timed out
     std::vector<rtd_beam> groupBeams;
+    // captured launch sequence of the last device-resident plan (doseGraph)
+    cudaGraphExec_t graphExec = nullptr; uint64_t graphKey = 0; bool graphBroken = false; long lutGeneration = 0;
+    CallState graphCs;
 };
 
 namespace {
@@ -403,7 +408,9 @@ cudaEvent_t evBeam(rtd_ctx* ctx, int b, int i) { return ev(ctx, EV_BEAM0 + size_
 
 // Part 1 of a beam, everything up to the superposition: launched without knowing any device result (cu:612-1100). The grids
 // depend on the geometry alone; cut-offs, slice counts and the transfer box live in BeamDev (beam_setup_kernel).
-rtd_status beamEnqueue(rtd_ctx* ctx, int beamNo, const rtd_beam& b, BeamWs& w, const rtd_opts& o, int& launches, cudaStream_t st, HostIo* io) {
+// Host half: geometry, workspace growth, per-layer host parameters and the staging copies. Nothing is queued here, so a captured
+// launch sequence (CUDA graph) can be replayed after it: the graph's copy nodes read the staging buffers this refreshes.
+rtd_status beamPrepare(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opts& o) {
     float mx = b.sigmas[0], my = b.sigmas[1];
     for (int l = 1; l < b.nLayers; ++l) { mx = std::max(mx, b.sigmas[2 * l]); my = std::max(my, b.sigmas[2 * l + 1]); }
     w.grid = makeRayGrid(b.spotDelta, b.spotOffset, b.sx, b.sy, b.raySpacing, mx, my, o.convSigmaCutoff);
@@ -461,6 +468,17 @@ rtd_status beamEnqueue(rtd_ctx* ctx, int beamNo, const rtd_beam& b, BeamWs& w, c
     memcpy(w.hStage.p, b.weights + size_t(b.sx) * b.sy * w.l0, nW * 4);
     char* stLin = w.hStage.as<char>() + (nW * 4 + 15) / 16 * 16;
     memcpy(stLin, w.lin.data(), size_t(L) * sizeof(LayerIn));
+    w.maxPeakDepth = maxPeakDepth;
+    return RTD_OK;
+}
+
+rtd_status beamEnqueue(rtd_ctx* ctx, int beamNo, const rtd_beam& b, BeamWs& w, const rtd_opts& o, int& launches, cudaStream_t st, HostIo* io) {
+    const int Rx = w.grid.dimX, Ry = w.grid.dimY, R = w.R, S = w.S, L = w.Lc;
+    const int tilesX = Rx / 32, tilesY = Ry / 8, tiles = tilesX * tilesY;
+    const size_t nW = size_t(b.sx) * b.sy * L, ctlInts = w.ctlInts();
+    const int planeFloats = (Ry + 64) * (Rx + 64), segs = tilesX * Ry;
+    char* stLin = w.hStage.as<char>() + (nW * 4 + 15) / 16 * 16;
+    const float maxPeakDepth = w.maxPeakDepth;
 
     RTD_CUDA(cudaEventRecord(evBeam(ctx, beamNo, 0), st));
     RTD_CUDA(cudaMemcpyAsync(w.spotW.p, w.hStage.p, nW * 4, cudaMemcpyHostToDevice, st));
@@ -654,8 +672,6 @@ bool beamFinish(rtd_ctx* ctx, BeamWs& w, int64_t& updates, int64_t& taps, int& k
     return stats[0] == 0;
 }
 
-struct CallState { int launches = 0, hostSyncs = 1; bool serial = false; cudaEvent_t evXferEnd = nullptr; };
-
 // Everything of a call up to (not including) the final host synchronisation.
 rtd_status doseEnqueue(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* dDose, const rtd_opts& o,
                        cudaEvent_t evBegin, cudaEvent_t evEnd, HostIo* io, CallState& cs) {
@@ -682,6 +698,8 @@ rtd_status doseEnqueue(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* d
     // one-call host path the CT sub-volumes of beam b+1 upload (copy stream) while beam b computes.
     const bool serial = o.serialBeams != 0 || nBeams == 1;
     cs.serial = serial;
+    if (!cs.prepared)
+        for (int b = 0; b < nBeams; ++b) { rtd_status s = beamPrepare(ctx, beams[b], *ctx->ws[b], o); if (s != RTD_OK) return s; }
     auto beamStream = [&](int b) -> cudaStream_t {
         if (serial) return ctx->stream;
         const size_t i = size_t(b) % 8;
@@ -744,7 +762,7 @@ rtd_status doseFinish(rtd_ctx* ctx, int nBeams, rtd_timing* tm, cudaEvent_t evBe
         memset(tm, 0, sizeof *tm);
         tm->updates = updates; tm->ksTaps = taps; tm->kernelLaunches = launches; tm->hostSyncs = hostSyncs; tm->ksLaunchesWithWork = ksLaunches;
         float ms = 0;
-        for (int b = 0; b < nBeams; ++b) {
+        for (int b = 0; b < nBeams && !cs.graph; ++b) {      // (a replayed graph does not record the stage events: stage times stay 0)
             cudaEvent_t e[8];
             for (int i = 0; i < 8; ++i) e[i] = evBeam(ctx, b, i);
             cudaEventElapsedTime(&ms, e[0], e[1]); tm->msTrace += ms;
@@ -758,7 +776,7 @@ rtd_status doseFinish(rtd_ctx* ctx, int nBeams, rtd_timing* tm, cudaEvent_t evBe
         cudaEventElapsedTime(&ms, evBegin, evEnd); tm->msTotal = ms;
         if (io) {
             if (io->ct && nBeams > 0) { cudaEventElapsedTime(&ms, evBegin, evBeam(ctx, nBeams - 1, 9)); tm->msUpload = ms; }
-            if (io->dose) { cudaEventElapsedTime(&ms, evXferEnd, evEnd); tm->msDownload = ms; }
+            if (io->dose && !cs.graph) { cudaEventElapsedTime(&ms, evXferEnd, evEnd); tm->msDownload = ms; }
             tm->h2dBytes = io->h2d; tm->d2hBytes = io->d2h;
         }
         tm->doseVoxelsModified = modified;
@@ -772,8 +790,65 @@ rtd_status doseFinish(rtd_ctx* ctx, int nBeams, rtd_timing* tm, cudaEvent_t evBe
     return RTD_OK;
 }
 
+// 64-bit FNV-1a over everything a captured launch sequence bakes in: the beams' scalars and pointers, the arrays the host parameters
+// are derived from (energies, sigmas), the options, the dose pointer, the LUT / CT generation and the workspace generation.
+uint64_t planKey(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, const float* dDose, const rtd_opts& o) {
+    uint64_t h = 1469598103934665603ull;
+    auto mix = [&](const void* p, size_t n) { const unsigned char* c = (const unsigned char*)p; for (size_t i = 0; i < n; ++i) { h ^= c[i]; h *= 1099511628211ull; } };
+    mix(&nBeams, sizeof nBeams); mix(&dDose, sizeof dDose); mix(&o, sizeof o);
+    mix(ctx->ctDims, sizeof ctx->ctDims); mix(ctx->doseDims, sizeof ctx->doseDims); mix(&ctx->ctTex.tex, sizeof ctx->ctTex.tex);
+    mix(&ctx->lutGeneration, sizeof ctx->lutGeneration);
+    const long re = DevBuf::reallocs(); mix(&re, sizeof re);
+    for (int b = 0; b < nBeams; ++b) {
+        mix(&beams[b], sizeof(rtd_beam));
+        mix(beams[b].energies, size_t(beams[b].nLayers) * 4); mix(beams[b].sigmas, size_t(beams[b].nLayers) * 8);
+    }
+    return h;
+}
+
+// Device-resident plans with several beams are captured once into a CUDA graph (the ~15 launches, copies and cross-stream waits per
+// beam become one launch) and replayed for as long as nothing the capture baked in changes; anything else runs eagerly.
+rtd_status doseGraph(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* dDose, const rtd_opts& o, rtd_timing* tm, bool& handled) {
+    handled = false;
+    while ((int)ctx->ws.size() < nBeams) ctx->ws.push_back(new BeamWs());
+    for (int b = 0; b < nBeams; ++b)
+        if (const char* why = validateBeam(beams[b], o)) return fail(ctx, RTD_ERR_INVALID, why);
+    for (int b = 0; b < nBeams; ++b) { rtd_status s = beamPrepare(ctx, beams[b], *ctx->ws[b], o); if (s != RTD_OK) return s; }
+    RTD_CUDA(ctx->xferCount.ensure(16)); RTD_CUDA(ctx->hXferCount.ensure(16));
+    while (ctx->bstreams.size() < size_t(std::min(nBeams, 8))) { cudaStream_t s_; RTD_CUDA(cudaStreamCreateWithFlags(&s_, cudaStreamNonBlocking)); ctx->bstreams.push_back(s_); }
+    for (int b = 0; b < nBeams; ++b) evBeam(ctx, b, int(EV_PER_BEAM) - 1);      // events exist before the capture starts
+    const uint64_t key = planKey(ctx, beams, nBeams, dDose, o);
+    cudaEvent_t evB = ev(ctx, 4), evE = ev(ctx, 5);
+    if (!ctx->graphExec || ctx->graphKey != key) {
+        if (ctx->graphExec) { cudaGraphExecDestroy(ctx->graphExec); ctx->graphExec = nullptr; }
+        CallState cs; cs.prepared = true;
+        if (cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeRelaxed) != cudaSuccess) { cudaGetLastError(); return RTD_OK; }
+        const rtd_status s = doseEnqueue(ctx, beams, nBeams, dDose, o, ev(ctx, 0), ev(ctx, 1), nullptr, cs);
+        cudaGraph_t g = nullptr;
+        const cudaError_t e = cudaStreamEndCapture(ctx->stream, &g);
+        if (s != RTD_OK || e != cudaSuccess || !g) { if (g) cudaGraphDestroy(g); cudaGetLastError(); ctx->graphBroken = true; return s; }
+        const cudaError_t ei = cudaGraphInstantiate(&ctx->graphExec, g, 0);
+        cudaGraphDestroy(g);
+        if (ei != cudaSuccess) { ctx->graphExec = nullptr; cudaGetLastError(); ctx->graphBroken = true; return RTD_OK; }
+        ctx->graphKey = key; ctx->graphCs = cs; ctx->graphCs.graph = true;
+        ctx->nBeamsLast = nBeams; ctx->optsLast = o;
+    }
+    handled = true;
+    RTD_CUDA(cudaEventRecord(evB, ctx->stream));
+    RTD_CUDA(cudaGraphLaunch(ctx->graphExec, ctx->stream));
+    RTD_CUDA(cudaEventRecord(evE, ctx->stream));
+    RTD_CUDA(cudaStreamSynchronize(ctx->stream));
+    ctx->nBeamsLast = nBeams; ctx->optsLast = o;
+    return doseFinish(ctx, nBeams, tm, evB, evE, nullptr, ctx->graphCs);
+}
+
 rtd_status doseCoreImpl(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* dDose, const rtd_opts& o, rtd_timing* tm,
                         cudaEvent_t evBegin, cudaEvent_t evEnd, HostIo* io) {
+    if (!io && nBeams > 1 && !o.serialBeams && !o.noGraph && !ctx->graphBroken) {
+        bool handled = false;
+        const rtd_status gs = doseGraph(ctx, beams, nBeams, dDose, o, tm, handled);
+        if (gs != RTD_OK || handled) return gs;
+    }
     CallState cs;
     rtd_status s = doseEnqueue(ctx, beams, nBeams, dDose, o, evBegin, evEnd, io, cs);
     if (s != RTD_OK) return s;
@@ -851,6 +926,7 @@ void rtd_destroy(rtd_ctx* ctx) {
     ctx->iddTex.release(); ctx->densTex.release(); ctx->spTex.release(); ctx->densSpTex.release(); ctx->rrlTex.release(); ctx->ctTex.release();
     ctx->nucTex.release();
     ctx->dose.release(); ctx->xferCount.release(); ctx->hXferCount.release(); ctx->ctRows.release();
+    if (ctx->graphExec) cudaGraphExecDestroy(ctx->graphExec);
     for (cudaEvent_t e : ctx->events) cudaEventDestroy(e);
     for (cudaStream_t s_ : ctx->bstreams) { cudaStreamSynchronize(s_); cudaStreamDestroy(s_); }
     cudaStreamSynchronize(ctx->cstream); cudaStreamDestroy(ctx->cstream);
@@ -901,7 +977,7 @@ rtd_status rtd_set_luts(rtd_ctx* ctx, const rtd_luts* l) {
         RTD_CUDA(makeTexture(ctx->densSpTex, cudaAddressModeClamp));
     }
     RTD_CUDA(cudaStreamSynchronize(ctx->stream));
-    ctx->haveLuts = true;
+    ctx->haveLuts = true; ++ctx->lutGeneration;
     return RTD_OK;
 }
 

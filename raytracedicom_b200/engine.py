@@ -49,7 +49,7 @@ class RtdOpts(C.Structure):
     _fields_ = [("bpDepthCutoff", C.c_float), ("convSigmaCutoff", C.c_float), ("ksSigmaCutoff", C.c_float),
                 ("rayWeightCutoff", C.c_float), ("minTilesInBatch", C.c_int), ("ks2BodyStep", C.c_int),
                 ("serialBeams", C.c_int), ("noZeroCopyDose", C.c_int), ("noNozzle", C.c_int), ("doseToMedium", C.c_int),
-                ("atomicDose", C.c_int), ("ctPull", C.c_int), ("nuclearCorr", C.c_int), ("fullIntermediates", C.c_int)]
+                ("atomicDose", C.c_int), ("ctPull", C.c_int), ("nuclearCorr", C.c_int), ("noGraph", C.c_int), ("fullIntermediates", C.c_int)]
 
 
 class RtdTiming(C.Structure):

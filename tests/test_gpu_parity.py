@@ -554,3 +554,36 @@ def test_nuclear_corr_against_oracle_and_rebuilt_reference(eng, oracle, mini_cas
         ref = np.fromfile(tmp_path / "dose.f32", np.float32).reshape(dose.shape)
         assert rel_to_max(dose, ref)[0] <= DOSE_TOL_TIGHT
         assert gamma_pass_rate(dose, ref, case.spacing) >= 0.999
+
+
+def test_captured_plan_replays_and_follows_weight_changes(eng, c3):
+    """rtd_dose_device captures a multi-beam device-resident plan into a CUDA graph and replays it while the plan's geometry stays
+    the same: the replay gives the eager dose (rtd_opts.noGraph = 1), also after the spot weights were changed in place (they are
+    staged at every call), and the integer reports are those of the eager run."""
+    import torch
+    nx, ny, nz = c3.dose_dims
+    eng.set_luts(c3.luts); eng.set_ct(c3.ct); eng.set_dose_grid(nx, ny, nz)
+    packed, keep = engine.pack_beams(c3.beams)
+    d = torch.zeros((nz, ny, nx), dtype=torch.float32, device="cuda:0")
+
+    def run(no_graph):
+        eng.opts.noGraph = 1 if no_graph else 0
+        try:
+            d.zero_()
+            t = eng.dose_ptr(packed, len(c3.beams), d.data_ptr(), device=True)
+            return d.cpu().numpy(), t.as_dict(), [eng.beam_report(b) for b in range(len(c3.beams))]
+        finally:
+            eng.opts.noGraph = 0
+    eager, te, re_ = run(True)
+    first, t1, r1 = run(False)          # capture + launch
+    again, t2, r2 = run(False)          # replay
+    assert te["msSuperp"] > 0 and t2["msSuperp"] == 0 and t2["msTotal"] > 0 and t2["hostSyncs"] == 1
+    assert t2["updates"] == te["updates"] and r2 == re_ and r1 == re_
+    assert rel_to_max(first, eager)[0] <= 2e-6 and rel_to_max(again, eager)[0] <= 2e-6
+    keep[0] *= np.float32(0.5)          # beam 0's weight array, in place: same pointers, same geometry -> replay
+    try:
+        half, _, _ = run(False)
+        half_eager, _, _ = run(True)
+    finally:
+        keep[0] *= np.float32(2.0)
+    assert rel_to_max(half, half_eager)[0] <= 2e-6 and rel_to_max(half, eager)[0] > 1e-2
