@@ -834,8 +834,13 @@ __global__ void push_nonzero_tail_kernel(const float* __restrict__ src, float* _
 // (its zeroing of the grid, its reductions into the grid over NVLink) is ordered before its arrival (release at system scope), and
 // nothing queued after it starts before every rank has arrived (acquire). Replaces two 4-byte NCCL all-reduces per plan - each a
 // kernel launch plus a rendezvous - by one remote atomic and a few polls.
-__global__ void group_barrier_kernel(unsigned long long* __restrict__ ctr, const unsigned long long target, int* __restrict__ timedOut,
-                                     const unsigned long long maxNs) {
+// The number of the barrier is kept in this rank's device memory (localEpoch) so that the launch takes the same arguments every
+// time and a captured plan (CUDA graph) can contain it.
+__global__ void group_barrier_kernel(unsigned long long* __restrict__ ctr, unsigned long long* __restrict__ localEpoch, const unsigned long long world,
+                                     int* __restrict__ timedOut, const unsigned long long maxNs) {
+    const unsigned long long epoch = *localEpoch + 1ull;
+    *localEpoch = epoch;
+    const unsigned long long target = epoch * world;
     __threadfence_system();
     asm volatile("red.release.sys.global.add.u64 [%0], 1;" :: "l"(ctr) : "memory");
     unsigned long long t0, t1, seen;

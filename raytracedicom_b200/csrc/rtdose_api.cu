@@ -122,7 +122,8 @@ struct rtd_ctx {
     int groupRank = -1, groupWorld = 0; size_t groupFloats = 0;
     float* groupGrid = nullptr;                    // rank 0: own allocation; other ranks: peer mapping
     unsigned long long* groupCtr = nullptr;        // arrival counter behind the grid (monotonic: barrier k waits for k * world arrivals)
-    unsigned long long groupEpoch = 0;
+    DevBuf groupEpochDev;                          // this rank's barrier count (device memory: the barrier launch is replayable)
+    cudaGraphExec_t groupGraphExec = nullptr; uint64_t groupGraphKey = 0;
     PinBuf groupFlag;                              // [0] = a barrier timed out
     std::vector<rtd_beam> groupBeams;
     // captured launch sequence of the last device-resident plan (doseGraph)
@@ -927,6 +928,8 @@ void rtd_destroy(rtd_ctx* ctx) {
     ctx->nucTex.release();
     ctx->dose.release(); ctx->xferCount.release(); ctx->hXferCount.release(); ctx->ctRows.release();
     if (ctx->graphExec) cudaGraphExecDestroy(ctx->graphExec);
+    if (ctx->groupGrid) rtd_group_destroy(ctx);
+    ctx->groupEpochDev.release(); ctx->groupFlag.release();
     for (cudaEvent_t e : ctx->events) cudaEventDestroy(e);
     for (cudaStream_t s_ : ctx->bstreams) { cudaStreamSynchronize(s_); cudaStreamDestroy(s_); }
     cudaStreamSynchronize(ctx->cstream); cudaStreamDestroy(ctx->cstream);
@@ -1178,7 +1181,8 @@ rtd_status rtd_group_destroy(rtd_ctx* ctx) {
     RTD_CUDA(cudaSetDevice(ctx->device));
     RTD_CUDA(cudaStreamSynchronize(ctx->stream));
     if (ctx->groupRank == 0) RTD_CUDA(cudaFree(ctx->groupGrid)); else RTD_CUDA(cudaIpcCloseMemHandle(ctx->groupGrid));
-    ctx->groupGrid = nullptr; ctx->groupCtr = nullptr; ctx->groupRank = -1; ctx->groupWorld = 0; ctx->groupFloats = 0; ctx->groupEpoch = 0;
+    if (ctx->groupGraphExec) { cudaGraphExecDestroy(ctx->groupGraphExec); ctx->groupGraphExec = nullptr; }
+    ctx->groupGrid = nullptr; ctx->groupCtr = nullptr; ctx->groupRank = -1; ctx->groupWorld = 0; ctx->groupFloats = 0;
     return RTD_OK;
 }
 
@@ -1206,7 +1210,10 @@ rtd_status rtd_group_create(rtd_ctx* ctx, int rank, int world, size_t nDoseFloat
     RTD_CUDA(ctx->groupFlag.ensure(64));
     memset(ctx->groupFlag.p, 0, 64);
     ctx->groupGrid = (float*)p; ctx->groupCtr = (unsigned long long*)((char*)p + gridBytes);
-    ctx->groupRank = rank; ctx->groupWorld = world; ctx->groupFloats = nDoseFloats; ctx->groupEpoch = 0;
+    RTD_CUDA(ctx->groupEpochDev.ensure(8));
+    RTD_CUDA(cudaMemsetAsync(ctx->groupEpochDev.p, 0, 8, ctx->stream));
+    RTD_CUDA(cudaStreamSynchronize(ctx->stream));
+    ctx->groupRank = rank; ctx->groupWorld = world; ctx->groupFloats = nDoseFloats;
     return RTD_OK;
 }
 
@@ -1214,9 +1221,8 @@ float* rtd_group_dose(rtd_ctx* ctx) { return ctx ? ctx->groupGrid : nullptr; }
 
 static rtd_status groupBarrierEnqueue(rtd_ctx* ctx) {
     if (ctx->groupWorld <= 1) return RTD_OK;
-    ++ctx->groupEpoch;
-    group_barrier_kernel<<<1, 1, 0, ctx->stream>>>(ctx->groupCtr, ctx->groupEpoch * (unsigned long long)ctx->groupWorld, ctx->groupFlag.as<int>(),
-                                                   10ull * 1000 * 1000 * 1000);
+    group_barrier_kernel<<<1, 1, 0, ctx->stream>>>(ctx->groupCtr, ctx->groupEpochDev.as<unsigned long long>(), (unsigned long long)ctx->groupWorld,
+                                                   ctx->groupFlag.as<int>(), 10ull * 1000 * 1000 * 1000);
     RTD_CUDA(cudaGetLastError());
     return RTD_OK;
 }
@@ -1265,17 +1271,55 @@ rtd_status rtd_plan_dose_group(rtd_ctx* ctx, const float* ct, int nx, int ny, in
     float* target = ctx->groupGrid;
     if (rank != 0) { RTD_CUDA(ctx->dose.ensure(nGrid * 4)); target = ctx->dose.as<float>(); }
     cudaEvent_t evBegin = ev(ctx, 0), evEnd = ev(ctx, 1), evAll = ev(ctx, 3), evStart = ev(ctx, 4);
-    RTD_CUDA(cudaEventRecord(evStart, ctx->stream));
-    if (slabN) RTD_CUDA(cudaMemsetAsync(target + slabOff, 0, slabN * 4, ctx->stream));
-    rtd_status s = groupBarrierEnqueue(ctx);                 // the plan's grid is zeroed before anything is added into it
-    if (s != RTD_OK) return s;
     // rank 0 computes straight into the plan's grid while the pushes of the others may land in it: its transfers add atomically
     o.atomicDose = (rank == 0 && world > 1) ? 1 : o.atomicDose;
     HostIo io; io.ct = ct;
     CallState cs;
-    s = doseEnqueue(ctx, ctx->groupBeams.data(), (int)ctx->groupBeams.size(), target, o, evBegin, evEnd, ct ? &io : nullptr, cs);
-    if (s == RTD_OK && rank != 0 && slabN) s = rtd_push_dose_to_peer(ctx, target + slabOff, ctx->groupGrid + slabOff, slabN);
-    if (s == RTD_OK) s = groupBarrierEnqueue(ctx);           // every rank's contribution has landed
+    const int nMine = (int)ctx->groupBeams.size();
+    // zero the slab | barrier | this rank's beams | push | barrier: the whole device-side sequence of a rank
+    auto enqueueSeq = [&](CallState& c) -> rtd_status {
+        if (slabN) RTD_CUDA(cudaMemsetAsync(target + slabOff, 0, slabN * 4, ctx->stream));
+        rtd_status r = groupBarrierEnqueue(ctx);             // the plan's grid is zeroed before anything is added into it
+        if (r == RTD_OK) r = doseEnqueue(ctx, ctx->groupBeams.data(), nMine, target, o, evBegin, evEnd, ct ? &io : nullptr, c);
+        if (r == RTD_OK && rank != 0 && slabN) r = rtd_push_dose_to_peer(ctx, target + slabOff, ctx->groupGrid + slabOff, slabN);
+        if (r == RTD_OK) r = groupBarrierEnqueue(ctx);       // every rank's contribution has landed
+        return r;
+    };
+    rtd_status s = RTD_OK;
+    bool replayed = false;
+    if (!ct && !hostDoseInOut && !o.noGraph && !o.serialBeams && !ctx->graphBroken) {
+        // device-resident share of the plan: captured once, replayed while nothing the capture baked in changes (see doseGraph)
+        for (int b = 0; b < nMine && s == RTD_OK; ++b) { while ((int)ctx->ws.size() < nMine) ctx->ws.push_back(new BeamWs()); s = beamPrepare(ctx, ctx->groupBeams[b], *ctx->ws[b], o); }
+        if (s != RTD_OK) return s;
+        RTD_CUDA(ctx->xferCount.ensure(16)); RTD_CUDA(ctx->hXferCount.ensure(16));
+        while (ctx->bstreams.size() < size_t(std::min(std::max(nMine, 1), 8))) { cudaStream_t s_; RTD_CUDA(cudaStreamCreateWithFlags(&s_, cudaStreamNonBlocking)); ctx->bstreams.push_back(s_); }
+        for (int b = 0; b < std::max(nMine, 1); ++b) evBeam(ctx, b, int(EV_PER_BEAM) - 1);
+        uint64_t key = planKey(ctx, ctx->groupBeams.data(), nMine, target, o);
+        key ^= (uint64_t(rank) << 48) ^ (uint64_t(world) << 56) ^ uint64_t(slabOff) * 1099511628211ull ^ uint64_t(slabN) ^ uint64_t(uintptr_t(ctx->groupGrid));
+        if (!ctx->groupGraphExec || ctx->groupGraphKey != key) {
+            if (ctx->groupGraphExec) { cudaGraphExecDestroy(ctx->groupGraphExec); ctx->groupGraphExec = nullptr; }
+            CallState c; c.prepared = true;
+            if (cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeRelaxed) == cudaSuccess) {
+                const rtd_status r = enqueueSeq(c);
+                cudaGraph_t g = nullptr;
+                const cudaError_t e = cudaStreamEndCapture(ctx->stream, &g);
+                if (r == RTD_OK && e == cudaSuccess && g && cudaGraphInstantiate(&ctx->groupGraphExec, g, 0) == cudaSuccess) { ctx->groupGraphKey = key; ctx->graphCs = c; ctx->graphCs.graph = true; }
+                else { ctx->groupGraphExec = nullptr; ctx->graphBroken = true; cudaGetLastError(); }
+                if (g) cudaGraphDestroy(g);
+                if (r != RTD_OK) return r;
+            } else cudaGetLastError();
+        }
+        if (ctx->groupGraphExec) {
+            RTD_CUDA(cudaEventRecord(evStart, ctx->stream));
+            RTD_CUDA(cudaGraphLaunch(ctx->groupGraphExec, ctx->stream));
+            cs = ctx->graphCs; replayed = true;
+            ctx->nBeamsLast = nMine; ctx->optsLast = o;
+        }
+    }
+    if (!replayed) {
+        RTD_CUDA(cudaEventRecord(evStart, ctx->stream));
+        s = enqueueSeq(cs);
+    }
     int64_t modified = 0;
     if (s == RTD_OK && rank == 0 && hostDoseInOut && slabN) {
         // the summed slab goes onto the caller's host grid (accumulate semantics, cu:542, 91-93): in place over PCIe if it is pinned
@@ -1290,7 +1334,7 @@ rtd_status rtd_plan_dose_group(rtd_ctx* ctx, const float* ct, int nx, int ny, in
         return s;
     }
     if (ctx->groupFlag.as<int>()[0]) { ctx->groupFlag.as<int>()[0] = 0; return fail(ctx, RTD_ERR_CUDA, "rtd_plan_dose_group: a rank of the group did not reach the barrier within 10 s"); }
-    s = doseFinish(ctx, (int)ctx->groupBeams.size(), tm, evBegin, evEnd, ct ? &io : nullptr, cs);
+    s = doseFinish(ctx, nMine, tm, replayed ? evStart : evBegin, replayed ? evAll : evEnd, ct ? &io : nullptr, cs);
     if (tm) {
         float ms = 0; cudaEventElapsedTime(&ms, evStart, evAll); tm->msTotal = ms;      // zeroing, barriers, push and host tail included
         if (modified) { tm->h2dBytes += modified * 4; tm->d2hBytes += modified * 4; tm->doseVoxelsModified = modified; }
