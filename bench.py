@@ -575,7 +575,7 @@ def main():
                 "data": "synthetic", "config": config_of(case), "plan_ms": main_res["ms_per_step"]}
         line.update({k: v for k, v in main_res.items() if k not in ("value", "ms_per_step")})
         if c4_res is not None:
-            keys = ("value", "ms_per_step", "updates_per_step", "stage_total_ms_per_rank", "stage_ms_rank0", "work_items_per_rank", "gpu_launches_per_step",
+            keys = ("value", "ms_per_step", "updates_per_step", "stage_total_ms_per_rank", "stage_ms_rank0", "per_rank", "work_items_per_rank", "gpu_launches_per_step",
                     "host_syncs_per_plan", "dose_checksum", "dose_max_rel_err_vs_1gpu", "ms_each_step_rank0")
             line["c4"] = {"config": c4_cfg, **{k: c4_res[k] for k in keys if k in c4_res}}
             if "e2e" in c4_res:

@@ -33,7 +33,8 @@ inline std::vector<double> layerCost(const rtd_beam& b, const float* energies, c
         for (int i = 0; i < 16; ++i) {
             const double t = double(i) / 15.0;
             const double r = std::nearbyint(3.0 * (0.3 + (sigEnd - 0.3) * t) / pitch);     // round half to even, like Python's round()
-            taps += (2.0 * r + 1.0) * (2.0 * r + 1.0);
+            // radii above 16 run in the two-band kernels (ks2<24> / ks2<32>: 5 / 3 warps per SM): about half the tap rate
+            taps += (2.0 * r + 1.0) * (2.0 * r + 1.0) * (r > 16.0 ? 1.8 : 1.0);
         }
         out[l] = steps * (taps / 16.0 + 130.0);
     }

@@ -28,7 +28,8 @@ def layer_cost(beam: Beam, luts) -> np.ndarray:
         peak = float(vector_interpolate(luts.peakDepths, find_decimal_ordered(luts.energiesPerU, beam.energies[l])))
         steps = peak / abs(float(beam.spot_delta[2]))
         sig_end = 0.022 * peak + 0.3
-        taps = np.mean([(2.0 * round(3.0 * (0.3 + (sig_end - 0.3) * t) / pitch) + 1.0) ** 2 for t in np.linspace(0.0, 1.0, 16)])
+        radii = [round(3.0 * (0.3 + (sig_end - 0.3) * t) / pitch) for t in np.linspace(0.0, 1.0, 16)]
+        taps = np.mean([(2.0 * r + 1.0) ** 2 * (1.8 if r > 16 else 1.0) for r in radii])     # two-band kernels above radius 16: half the tap rate
         out[l] = steps * (taps + 130.0)  # + per-update cost of the IDD/sigma, radius passes and the radius-independent part of the superposition
     return out
 
