@@ -275,6 +275,16 @@ rtd_status rtd_plan_dose_group(rtd_ctx* ctx, const float* ctHuPlus1000, int nx, 
  * (the accumulate semantics of kernel_wrapper.cu:91-93 for the whole plan). A pinned hostDst is updated in place over
  * PCIe (only voxels that received dose travel); a pageable one is staged. modifiedOut (optional): voxels updated. */
 rtd_status rtd_add_device_to_host(rtd_ctx* ctx, const float* dSrc, float* hostDst, size_t n, int64_t* modifiedOut);
+/* The same tail for callers that must not allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc). No counterpart in the reference. The call allocates nothing (no cudaMalloc,
+ * cudaFree, cudaMallocHost or allocating library routine): the kernel's scratch (per-block counts, 33 024 bytes) is a fixed device array
+ * inside the library, held by every GPU that loads it until the process exits. Limits: n <= RTD_NOALLOC_MAX_VOXELS (2^28 voxels = 1 GiB
+ * of fp32), RTD_ERR_INVALID beyond; dst must be DEVICE memory or PAGE-LOCKED host memory (a pageable grid would need a staging buffer),
+ * RTD_ERR_INVALID otherwise. Every call on a device shares the scratch, which keeps the last call's contents (what must start at zero
+ * is cleared by the call itself): calls that overlap on the GPU - two contexts or streams of one device - race and must be serialised
+ * by the caller. Same result as rtd_add_device_to_host bit for bit; returns after the stream has drained. */
+#define RTD_NOALLOC_MAX_VOXELS ((size_t)1 << 28)
+rtd_status rtd_add_device_to_host_noalloc(rtd_ctx* ctx, const float* dSrc, float* dst, size_t n, int64_t* modifiedOut);
 
 /* Integer/index outputs of the last call (the reference's bit-exact quantities). */
 rtd_status rtd_get_beam_report(const rtd_ctx* ctx, int beamNo, rtd_beam_report* out);

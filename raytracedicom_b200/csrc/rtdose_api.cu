@@ -8,6 +8,7 @@
 #include <string>
 #include <vector>
 #include <algorithm>
+#include <mutex>
 #include "../../include/rtdose.h"
 #include "kernels.cuh"
 #include "ks2.cuh"
@@ -1406,3 +1407,111 @@ rtd_status rtd_debug_fetch(rtd_ctx* ctx, int beamNo, rtd_fetch_what what, int la
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------
+// rtd_add_device_to_host_noalloc: the multi-GPU tail (rtd_add_device_to_host) for callers that must not allocate - code under CUDA graph
+// capture, tight serving loops, harnesses that forbid cudaMalloc. No counterpart in the reference.
+// Nothing on this path calls cudaMalloc / cudaFree / cudaMallocHost or any allocating library routine.
+//
+// The scratch of the kernel - one partial count per block, a ticket and the total - is a file-scope device array of fixed size, held
+// by every GPU that loads the library until the process exits (33 024 bytes). RTD_NOALLOC_CHUNK voxels per block and
+// RTD_NOALLOC_MAX_BLOCKS blocks give the stated limit RTD_NOALLOC_MAX_VOXELS = 2^28 voxels (1 GiB of fp32); larger n is refused.
+// In host code the array's NAME is a host-side stand-in, not a device address: the address is taken once per device with
+// cudaGetSymbolAddress (that device current) and passed to the kernel. Every call on a device shares the array and it keeps the last
+// call's contents: the ticket and the total are cleared at the start of every call (the partial counts are overwritten before they are
+// read); two calls that overlap on the GPU (different streams / contexts of one device) race on it and must be serialised by the caller.
+namespace {
+
+constexpr size_t RTD_NOALLOC_CHUNK = 65536;                  // voxels per block
+constexpr size_t RTD_NOALLOC_MAX_BLOCKS = 4096;
+static_assert(RTD_NOALLOC_MAX_VOXELS == RTD_NOALLOC_CHUNK * RTD_NOALLOC_MAX_BLOCKS, "include/rtdose.h states the limit");      // 2^28
+constexpr int RTD_NOALLOC_HEAD = 32;                         // [0] ticket, [1] total, rest of the first 256 bytes unused
+static __device__ __align__(256) unsigned long long g_noallocScratch[RTD_NOALLOC_HEAD + RTD_NOALLOC_MAX_BLOCKS];
+
+// dst[i] += src[i] where src[i] != 0 (add_nonzero_kernel, kernels.cuh), block b owning voxels [b * CHUNK, (b + 1) * CHUNK); the count of
+// voxels touched is reduced per block into scratch[HEAD + b] and summed by the block that arrives last (ticket), without float or
+// 64-bit atomics on the caller's memory: the total is scratch[1].
+__global__ void __launch_bounds__(256)
+add_nonzero_counted_kernel(const float* __restrict__ src, float* __restrict__ dst, const size_t n, unsigned long long* __restrict__ scratch) {
+    __shared__ unsigned sCount[8];
+    __shared__ bool sLast;
+    const size_t lo = (size_t)blockIdx.x * RTD_NOALLOC_CHUNK, hi = min(n, lo + RTD_NOALLOC_CHUNK);
+    unsigned nMod = 0;
+    for (size_t i = lo + threadIdx.x; i < hi; i += 256) {
+        const float v = src[i];
+        if (v != 0.0f) { dst[i] += v; ++nMod; }
+    }
+    nMod = __reduce_add_sync(0xffffffffu, nMod);
+    if ((threadIdx.x & 31) == 0) sCount[threadIdx.x >> 5] = nMod;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned c = 0;
+        for (int w = 0; w < 8; ++w) c += sCount[w];
+        scratch[RTD_NOALLOC_HEAD + blockIdx.x] = c;
+        __threadfence();
+        sLast = atomicAdd(scratch, 1ull) == (unsigned long long)(gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!sLast) return;
+    __threadfence();
+    unsigned long long t = 0;
+    for (unsigned b = threadIdx.x; b < gridDim.x; b += 256) t += *(volatile unsigned long long*)(scratch + RTD_NOALLOC_HEAD + b);
+    t = __reduce_add_sync(0xffffffffu, (unsigned)t);        // <= 4096 blocks x 65536 voxels = 2^28: fits 32 bits
+    __shared__ unsigned sTot[8];
+    if ((threadIdx.x & 31) == 0) sTot[threadIdx.x >> 5] = (unsigned)t;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long tot = 0;
+        for (int w = 0; w < 8; ++w) tot += sTot[w];
+        scratch[1] = tot;
+    }
+}
+
+// Device address of the scratch array on `device` (which must be current), resolved once per device.
+cudaError_t noallocScratch(int device, unsigned long long** out) {
+    constexpr int MAXDEV = 64;
+    static unsigned long long* ptr[MAXDEV] = {};
+    static std::mutex mu;
+    if (device < 0 || device >= MAXDEV) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> g(mu);
+    if (!ptr[device]) {
+        unsigned long long* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress((void**)&p, g_noallocScratch);
+        if (e != cudaSuccess) return e;
+        ptr[device] = p;
+    }
+    *out = ptr[device];
+    return cudaSuccess;
+}
+
+}  // namespace
+
+extern "C" rtd_status rtd_add_device_to_host_noalloc(rtd_ctx* ctx, const float* dSrc, float* dst, size_t n, int64_t* modifiedOut) {
+    if (!ctx) return RTD_ERR_INVALID;
+    if (!dSrc || !dst) return fail(ctx, RTD_ERR_INVALID, "rtd_add_device_to_host_noalloc: null pointer");
+    if (n > RTD_NOALLOC_MAX_VOXELS)
+        return fail(ctx, RTD_ERR_INVALID, "rtd_add_device_to_host_noalloc: n exceeds the fixed scratch (at most 268435456 voxels = 2^28); use rtd_add_device_to_host");
+    RTD_CUDA(cudaSetDevice(ctx->device));
+    if (modifiedOut) *modifiedOut = 0;
+    if (n == 0) return RTD_OK;
+    // destination: device memory, or page-locked host memory the GPU can address (no staging buffer may be allocated here)
+    cudaPointerAttributes a0, a1;
+    float* d = nullptr;
+    if (cudaPointerGetAttributes(&a0, dst) == cudaSuccess && cudaPointerGetAttributes(&a1, dst + (n - 1)) == cudaSuccess && a0.type == a1.type &&
+        (a0.type == cudaMemoryTypeHost || a0.type == cudaMemoryTypeDevice || a0.type == cudaMemoryTypeManaged) && a0.devicePointer &&
+        (char*)a1.devicePointer - (char*)a0.devicePointer == (ptrdiff_t)((n - 1) * 4))
+        d = (float*)a0.devicePointer;
+    cudaGetLastError();
+    if (!d) return fail(ctx, RTD_ERR_INVALID, "rtd_add_device_to_host_noalloc: the destination must be device memory or page-locked host memory (a pageable grid needs a staging buffer: rtd_add_device_to_host)");
+    unsigned long long* scratch = nullptr;
+    RTD_CUDA(noallocScratch(ctx->device, &scratch));
+    RTD_CUDA(cudaMemsetAsync(scratch, 0, 16, ctx->stream));                 // ticket and total start at zero whatever the last call left
+    const unsigned blocks = (unsigned)((n + RTD_NOALLOC_CHUNK - 1) / RTD_NOALLOC_CHUNK);
+    add_nonzero_counted_kernel<<<blocks, 256, 0, ctx->stream>>>(dSrc, d, n, scratch);
+    RTD_CUDA(cudaGetLastError());
+    unsigned long long total = 0;
+    RTD_CUDA(cudaMemcpyAsync(&total, scratch + 1, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    RTD_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (modifiedOut) *modifiedOut = (int64_t)total;
+    return RTD_OK;
+}

@@ -98,7 +98,7 @@ class RtdError(RuntimeError):
 
 
 EXPORTS = ["rtd_default_opts", "rtd_create", "rtd_create_on_stream", "rtd_destroy", "rtd_last_error", "rtd_version", "rtd_set_luts", "rtd_set_ct",
-           "rtd_set_ct_device", "rtd_set_dose_grid", "rtd_dose", "rtd_dose_device", "rtd_plan_dose", "rtd_plan_dose_device", "rtd_add_device_to_host", "rtd_partition", "rtd_dose_slab", "rtd_group_create", "rtd_group_destroy", "rtd_group_dose", "rtd_group_barrier", "rtd_plan_dose_group", "rtd_shared_dose_create", "rtd_shared_dose_open", "rtd_shared_dose_close", "rtd_push_dose_to_peer",
+           "rtd_set_ct_device", "rtd_set_dose_grid", "rtd_dose", "rtd_dose_device", "rtd_plan_dose", "rtd_plan_dose_device", "rtd_add_device_to_host", "rtd_add_device_to_host_noalloc", "rtd_partition", "rtd_dose_slab", "rtd_group_create", "rtd_group_destroy", "rtd_group_dose", "rtd_group_barrier", "rtd_plan_dose_group", "rtd_shared_dose_create", "rtd_shared_dose_open", "rtd_shared_dose_close", "rtd_push_dose_to_peer",
            "rtd_get_beam_report",
            "rtd_get_layer_report", "rtd_debug_fetch", "rtd_debug_ct_boxes", "rtd_stream"]
 
@@ -131,6 +131,7 @@ def load_library() -> C.CDLL:
     lib.rtd_plan_dose.restype = C.c_int
     lib.rtd_plan_dose_device.argtypes = lib.rtd_plan_dose.argtypes; lib.rtd_plan_dose_device.restype = C.c_int
     lib.rtd_add_device_to_host.argtypes = [vp, vp, vp, C.c_size_t, C.POINTER(C.c_int64)]; lib.rtd_add_device_to_host.restype = C.c_int
+    lib.rtd_add_device_to_host_noalloc.argtypes = [vp, vp, vp, C.c_size_t, C.POINTER(C.c_int64)]; lib.rtd_add_device_to_host_noalloc.restype = C.c_int
     lib.rtd_shared_dose_create.argtypes = [vp, C.c_size_t, C.POINTER(vp), C.c_char_p]; lib.rtd_shared_dose_create.restype = C.c_int
     lib.rtd_shared_dose_open.argtypes = [vp, C.c_char_p, C.POINTER(vp)]; lib.rtd_shared_dose_open.restype = C.c_int
     lib.rtd_shared_dose_close.argtypes = [vp, vp, C.c_int]; lib.rtd_shared_dose_close.restype = C.c_int
@@ -336,6 +337,13 @@ class DoseEngine:
         """host[i] += device[i] where device[i] != 0 (multi-GPU tail, rtd_add_device_to_host); returns the voxels updated."""
         m = C.c_int64(0)
         self._check(self.lib.rtd_add_device_to_host(self._h, C.c_void_p(d_src_ptr), C.c_void_p(host_dst_ptr), n, C.byref(m)))
+        return int(m.value)
+
+    def add_device_to_host_noalloc(self, d_src_ptr: int, dst_ptr: int, n: int) -> int:
+        """rtd_add_device_to_host_noalloc: the same tail without any allocation (fixed scratch inside the library, n <= 2^28, dst device or
+        page-locked host memory); returns the voxels updated."""
+        m = C.c_int64(0)
+        self._check(self.lib.rtd_add_device_to_host_noalloc(self._h, C.c_void_p(d_src_ptr), C.c_void_p(dst_ptr), n, C.byref(m)))
         return int(m.value)
 
     # ---- one plan on the GPUs of a node (rtd_group_*) ----
