@@ -125,6 +125,11 @@ typedef struct {
                                 (RTD_FETCH_IDD / RTD_FETCH_RSIGMA). 0 (default): 32-ray row segments that hold no dose at a step are
                                 not written (the superposition never reads them; ~60 % of the scan's HBM writes on a head plan) and
                                 fetch as unspecified values */
+    int   tracerBrick;       /* tracer variant: 1 = the CT is staged per (32 x 8 rays, NS steps) brick in shared memory by TMA
+                                from a linear fp32 copy and filtered by hand with the texture unit's integer weights - bit-identical to the
+                                texture path for integer-valued CT (HU + 1000 of a DICOM series); a beam whose bricks hold a non-integer
+                                texel is recomputed through the texture unit by a gated second launch. 0 = texture fetches only.
+                                -1 (what rtd_default_opts sets) = the library's choice */
 } rtd_opts;
 
 /* Stage timing of the last rtd_dose* call (CUDA events; with concurrent beams the per-stage figures are sums over the
@@ -149,6 +154,8 @@ typedef struct {
     int64_t d2hBytes;    /* bytes copied device->host inside the call (dose sub-volumes, reductions, reports) */
     int64_t doseVoxelsModified;   /* dose-grid voxels that received dose (summed over beams) */
     int     ksLaunchesWithWork;   /* superposition launches (beam x radius class) that processed at least one item */
+    int     tracerBrickBeams;     /* beams traced by the TMA-brick tracer whose result stood (no fall-back to the texture path) */
+    int     tracerOutsideSamples; /* samples of those beams that missed their brick and were filtered from global memory (expected: 0) */
     int     reserved0;
 } rtd_timing;
 

@@ -61,7 +61,9 @@ __global__ void __launch_bounds__(TR_THREADS)
 trace_bev_kernel(const TraceParams p, cudaTextureObject_t ctTex, cudaTextureObject_t densTex, cudaTextureObject_t spTex,
                  cudaTextureObject_t densSpTex /* 0, or both LUTs as one float2 texture (same length and scale) */,
                  float* __restrict__ density, float* __restrict__ wepl, int* __restrict__ firstInside,
-                 int* __restrict__ firstOutside, const int Rx, const int R) {
+                 int* __restrict__ firstOutside, const int Rx, const int R,
+                 const int* __restrict__ gate /* nullptr, or: run only if *gate != 0 (the fall-back behind trace_brick_kernel) */) {
+    if (gate && *gate == 0) return;
     __shared__ float sSp[2][TR_ROUND][32];
     __shared__ float sHu[2][TR_ROUND][32];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;

@@ -12,6 +12,11 @@
 #include "../../include/rtdose.h"
 #include "kernels.cuh"
 #include "ks2.cuh"
+#include "trace_brick.cuh"
+
+#ifndef RTD_TRACER_BRICK_DEFAULT
+#define RTD_TRACER_BRICK_DEFAULT 0      // what rtd_opts.tracerBrick = -1 means
+#endif
 #include "sharding.hpp"
 
 using namespace rtd;
@@ -75,14 +80,15 @@ struct BeamWs {
     int bfi = 0, bfo = 0, Zg = 0, nz = 0; bool live = false;
     float entryZ = 0, maxPeakDepth = 0;
     BeamDev hostDev;
+    bool trBrick = false, trStood = false; int trOutside = 0;     // tracer variant B launched / its result stood / samples outside their brick
     rtd_beam_report rep; std::vector<rtd_layer_report> lrep;
     // device
     DevBuf density, wepl, firstIn, firstOut, weplMin, spotW, sigmas, rayW, layerIn, layerDev, beamDev, stepTab, idd, rsig, rowMin,
            firstPassive, lfp, batchRad, rbOffset, radMap, list, bev, segList;
     PinBuf hStage;   // staging of the uploads: spot weights | LayerIn[Lc]
     PinBuf hOut;     // BeamDev | LayerParams[Lc] | entry sigmas[Lc] | control block | batchRad[Lc*34]
-    // lfp[L] | hist[L*34] | bigCursor[33] | stats[4] | work[4] | ksItems[4] | segCount[L] | iddQueue[4]
-    size_t ctlInts() const { return size_t(Lc) + size_t(Lc) * 34 + 33 + 4 + 4 + 4 + size_t(Lc) + 4; }
+    // lfp[L] | hist[L*34] | bigCursor[33] | stats[4] | work[4] | ksItems[4] | segCount[L] | iddQueue[4] | tracerFlags[4]
+    size_t ctlInts() const { return size_t(Lc) + size_t(Lc) * 34 + 33 + 4 + 4 + 4 + size_t(Lc) + 4 + 4; }
     size_t outCtlOff() const { return (sizeof(BeamDev) + size_t(Lc) * (sizeof(LayerParams) + sizeof(float2)) + 15) / 16 * 16; }
     void release() {
         DevBuf* all[] = {&density, &wepl, &firstIn, &firstOut, &weplMin, &spotW, &sigmas, &rayW, &layerIn, &layerDev, &beamDev, &stepTab, &idd, &rsig,
@@ -111,6 +117,8 @@ struct rtd_ctx {
     int nEnergySamples = 0, nEnergies = 0; float densScale = 0, spScale = 0, rrlScale = 0;
     TexArr iddTex, densTex, spTex, densSpTex, rrlTex, ctTex, nucTex;   // nucTex: nuclear-halo weight (rtd_luts.nucWeightMatrix), optional   // densSpTex: density + SP as one float2 LUT when they share length and scale
     int ctDims[3] = {0, 0, 0}, doseDims[3] = {0, 0, 0};
+    DevBuf ctLin; int ctPitch = 0;        // the CT once more as linear fp32 [nz][ny][ctPitch] (row pitch a multiple of 4 floats): source of the tracer's TMA bricks
+    bool ctLinValid = false;              // ctLin holds what the CT array holds
     DevBuf dose;
     std::vector<BeamWs*> ws;
     int nBeamsLast = 0;
@@ -186,6 +194,7 @@ rtd_status ensureCtArray(rtd_ctx* ctx, int nx, int ny, int nz) {
         rd.resType = cudaResourceTypeArray; rd.res.array.array = ctx->ctTex.arr;
         RTD_CUDA(cudaCreateSurfaceObject(&ctx->ctTex.surf, &rd));
         ctx->ctDims[0] = nx; ctx->ctDims[1] = ny; ctx->ctDims[2] = nz;
+        ctx->ctPitch = (nx + 3) & ~3; ctx->ctLinValid = false;
     }
     return RTD_OK;
 }
@@ -200,9 +209,80 @@ rtd_status setCtCommon(rtd_ctx* ctx, const float* src, int nx, int ny, int nz, c
     cp.srcPtr = make_cudaPitchedPtr((void*)src, size_t(nx) * 4, nx, ny);
     cp.dstArray = ctx->ctTex.arr; cp.extent = make_cudaExtent(nx, ny, nz); cp.kind = kind;
     RTD_CUDA(cudaMemcpy3DAsync(&cp, ctx->stream));
+    ctx->ctLinValid = false;          // the linear copy of the TMA-brick tracer is refreshed on demand (ensureCtLinear)
     RTD_CUDA(cudaStreamSynchronize(ctx->stream));
     ctx->haveCt = true; ctx->ctPartial = false;
     return RTD_OK;
+}
+
+// ---- tracer variant B (trace_brick.cuh) ------------------------------------------------------------------------------------------
+inline bool brickWanted(const rtd_opts& o) { return o.tracerBrick > 0 || (o.tracerBrick < 0 && RTD_TRACER_BRICK_DEFAULT); }
+
+// The resident CT once more as linear fp32 (row pitch a multiple of 4 floats), copied device to device from the texture's array the
+// first time a plan asks for the brick tracer after rtd_set_ct (4 B / voxel more; outside any captured sequence: beamPrepare).
+rtd_status ensureCtLinear(rtd_ctx* ctx) {
+    if (ctx->ctLinValid || !ctx->haveCt || ctx->ctPartial) return RTD_OK;
+    const size_t nx = ctx->ctDims[0], ny = ctx->ctDims[1], nz = ctx->ctDims[2];
+    if (ctx->ctLin.ensure(size_t(ctx->ctPitch) * ny * nz * 4) != cudaSuccess) { cudaGetLastError(); return RTD_OK; }   // no room: texture tracer
+    cudaMemcpy3DParms cp; memset(&cp, 0, sizeof cp);
+    cp.srcArray = ctx->ctTex.arr;
+    cp.dstPtr = make_cudaPitchedPtr(ctx->ctLin.p, size_t(ctx->ctPitch) * 4, nx, ny);
+    cp.extent = make_cudaExtent(nx, ny, nz); cp.kind = cudaMemcpyDeviceToDevice;
+    RTD_CUDA(cudaMemcpy3DAsync(&cp, ctx->stream));
+    RTD_CUDA(cudaStreamSynchronize(ctx->stream));
+    ctx->ctLinValid = true;
+    return RTD_OK;
+}
+
+// Box of the tensor map and steps per round for one beam.
+// pos(i, j, k) = start(i, j) + k inc(i, j) with start and inc affine in i and in j (density_and_sp_tracer_params.cu:15-17), so over a
+// tile of 32 x 8 rays and NS steps the extent of pos along CT axis a is at most
+//   31 |cI_a| (|s1| + kmax |dz| / |distX|) + 7 |cJ_a| (|s2| + kmax |dz| / |distY|) + (NS - 1) max|inc_a|
+// (+ 4: one texel of margin below, the neighbour texel of the filter above, and one of slack on either side for the rounding of the
+// positions, which the kernel accumulates step by step; + 3 in x for the origin floored to a multiple of 4). The largest NS of 64, 32,
+// 16, 8 whose brick fits the budget (two CTAs per SM) is taken.
+constexpr size_t TRB_SMEM_BUDGET = 100 * 1024;
+bool brickParamsOfBeam(const TraceParams& p, int Rx, int Ry, int S, BrickParams& bp) {
+    const float cI[3] = {p.coefIdxI.x, p.coefIdxI.y, p.coefIdxI.z}, cJ[3] = {p.coefIdxJ.x, p.coefIdxJ.y, p.coefIdxJ.z};
+    const float cO[3] = {p.coefOffset.x, p.coefOffset.y, p.coefOffset.z};
+    const double dz = std::fabs(double(p.delta.z)), ax = 1.0 / std::fabs(double(p.distX)), ay = 1.0 / std::fabs(double(p.distY));   // 1 / inf = 0
+    const double s1 = std::fabs(1.0 - double(p.corner.z) / double(p.distX)), s2 = std::fabs(1.0 - double(p.corner.z) / double(p.distY));
+    for (int ns = 64; ns >= 8; ns >>= 1) {
+        int B[3];
+        bool ok = true;
+        for (int a = 0; a < 3; ++a) {
+            const double inc = dz * (std::fabs(double(cO[a])) + std::fabs(double(cI[a])) * (Rx - 1) * ax + std::fabs(double(cJ[a])) * (Ry - 1) * ay);
+            const double ext = (TRB_TX - 1) * std::fabs(double(cI[a])) * (s1 + S * dz * ax) + (TRB_TY - 1) * std::fabs(double(cJ[a])) * (s2 + S * dz * ay) + (ns - 1) * inc;
+            if (!(ext < 250.0)) { ok = false; break; }
+            B[a] = int(std::ceil(ext)) + 4;
+        }
+        if (!ok) continue;
+        B[0] = (B[0] + 3 + 3) & ~3;
+        if (B[0] > 256 || B[1] > 256 || B[2] > 256) continue;
+        if (size_t(B[0]) * B[1] * B[2] * 4 + 128 > TRB_SMEM_BUDGET) continue;
+        bp.BX = B[0]; bp.BY = B[1]; bp.BZ = B[2]; bp.NS = ns;
+        return true;
+    }
+    return false;
+}
+
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no link against libcuda)
+bool makeCtTensorMap(rtd_ctx* ctx, const BrickParams& bp, CUtensorMap* out) {
+    typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                 CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static EncodeFn fn = nullptr; static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void* f = nullptr; cudaDriverEntryPointQueryResult qr;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &qr) == cudaSuccess && qr == cudaDriverEntryPointSuccess) fn = (EncodeFn)f;
+        cudaGetLastError();
+    }
+    if (!fn) return false;
+    const cuuint64_t dims[3] = {cuuint64_t(ctx->ctDims[0]), cuuint64_t(ctx->ctDims[1]), cuuint64_t(ctx->ctDims[2])};
+    const cuuint64_t strides[2] = {cuuint64_t(ctx->ctPitch) * 4, cuuint64_t(ctx->ctPitch) * 4 * cuuint64_t(ctx->ctDims[1])};
+    const cuuint32_t box[3] = {cuuint32_t(bp.BX), cuuint32_t(bp.BY), cuuint32_t(bp.BZ)}, es[3] = {1, 1, 1};
+    return fn(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, ctx->ctLin.p, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+              CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
 // ---- sub-volume transfers of the one-call host path -------------------------------------------------------
@@ -413,6 +493,7 @@ cudaEvent_t evBeam(rtd_ctx* ctx, int b, int i) { return ev(ctx, EV_BEAM0 + size_
 // Host half: geometry, workspace growth, per-layer host parameters and the staging copies. Nothing is queued here, so a captured
 // launch sequence (CUDA graph) can be replayed after it: the graph's copy nodes read the staging buffers this refreshes.
 rtd_status beamPrepare(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opts& o) {
+    if (brickWanted(o)) { const rtd_status sl = ensureCtLinear(ctx); if (sl != RTD_OK) return sl; }
     float mx = b.sigmas[0], my = b.sigmas[1];
     for (int l = 1; l < b.nLayers; ++l) { mx = std::max(mx, b.sigmas[2 * l]); my = std::max(my, b.sigmas[2 * l + 1]); }
     w.grid = makeRayGrid(b.spotDelta, b.spotOffset, b.sx, b.sy, b.raySpacing, mx, my, o.convSigmaCutoff);
@@ -519,8 +600,23 @@ rtd_status beamEnqueue(rtd_ctx* ctx, int beamNo, const rtd_beam& b, BeamWs& w, c
 
     // K1 + reductions. weplMin buffer layout: [0] = beamFirstInside, [1] = beamFirstOutside (ints), [2..] weplMin floats
     int* sc = w.weplMin.as<int>();
+    int* dTrFlags = w.lfp.as<int>() + (ctlInts - 4);      // [0] a brick held a non-integer texel, [1] samples outside their brick
+    bool brick = brickWanted(o) && ctx->ctLinValid && ctx->ctLin.p && !(io && io->ct);
+    BrickParams bp; CUtensorMap tmap;
+    if (brick) {
+        bp.nx = ctx->ctDims[0]; bp.ny = ctx->ctDims[1]; bp.nz = ctx->ctDims[2]; bp.pitch = ctx->ctPitch; bp.ctLin = ctx->ctLin.as<float>();
+        brick = brickParamsOfBeam(tp, Rx, Ry, S, bp) && makeCtTensorMap(ctx, bp, &tmap);
+    }
+    w.trBrick = brick;
+    if (brick) {
+        const size_t sh = size_t(bp.BX) * bp.BY * bp.BZ * 4 + 128;
+        trace_brick_kernel<<<R / TRB_THREADS, TRB_THREADS, sh, st>>>(tp, tmap, bp, ctx->densTex.tex, ctx->spTex.tex, ctx->densSpTex.tex,
+            w.density.as<float>(), w.wepl.as<float>(), w.firstIn.as<int>(), w.firstOut.as<int>(), Rx, R, dTrFlags);
+        ++launches;
+    }
+    // variant A: alone, or - behind variant B - only if that one met a CT texel its hand-made filter cannot reproduce bit for bit
     trace_bev_kernel<<<R / 32, TR_THREADS, 0, st>>>(tp, ctx->ctTex.tex, ctx->densTex.tex, ctx->spTex.tex, ctx->densSpTex.tex,
-        w.density.as<float>(), w.wepl.as<float>(), w.firstIn.as<int>(), w.firstOut.as<int>(), Rx, R);
+        w.density.as<float>(), w.wepl.as<float>(), w.firstIn.as<int>(), w.firstOut.as<int>(), Rx, R, brick ? dTrFlags : nullptr);
     slice_reduce_kernel<<<S, 256, 0, st>>>(w.wepl.as<float>(), w.firstIn.as<int>(), w.firstOut.as<int>(), R, w.weplMin.as<float>() + 2, sc, sc + 1);
     RTD_CUDA(cudaEventRecord(evBeam(ctx, beamNo, 1), st));
 
@@ -638,6 +734,10 @@ bool beamFinish(rtd_ctx* ctx, BeamWs& w, int64_t& updates, int64_t& taps, int& k
         rtd_layer_report& lr = w.lrep[w.l0 + l];
         lr.energyIdx = w.lin[l].energyIdx; lr.energyScaleFact = w.lin[l].energyScale; lr.peakDepth = w.lin[l].peakDepth;
         lr.entrySigmaX = esig[2 * l]; lr.entrySigmaY = esig[2 * l + 1]; lr.afterLastStep = lp[l].afterLast;
+    }
+    {   // tracer variant B: did it run, did its result stand, samples it had to filter from global memory
+        const int* fl = reinterpret_cast<const int*>(out + w.outCtlOff()) + (w.ctlInts() - 4);
+        w.trStood = w.trBrick && fl[0] == 0; w.trOutside = w.trBrick ? fl[1] : 0;
     }
     if (!w.live) return true;
     const int* lfp = reinterpret_cast<const int*>(out + w.outCtlOff()); const int* hist = lfp + L; const int* stats = hist + size_t(L) * 34 + 33;
@@ -763,6 +863,7 @@ rtd_status doseFinish(rtd_ctx* ctx, int nBeams, rtd_timing* tm, cudaEvent_t evBe
     if (tm) {
         memset(tm, 0, sizeof *tm);
         tm->updates = updates; tm->ksTaps = taps; tm->kernelLaunches = launches; tm->hostSyncs = hostSyncs; tm->ksLaunchesWithWork = ksLaunches;
+        for (int b = 0; b < nBeams; ++b) { tm->tracerBrickBeams += ctx->ws[b]->trStood ? 1 : 0; tm->tracerOutsideSamples += ctx->ws[b]->trOutside; }
         float ms = 0;
         for (int b = 0; b < nBeams && !cs.graph; ++b) {      // (a replayed graph does not record the stage events: stage times stay 0)
             cudaEvent_t e[8];
@@ -799,7 +900,7 @@ uint64_t planKey(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, const float* d
     auto mix = [&](const void* p, size_t n) { const unsigned char* c = (const unsigned char*)p; for (size_t i = 0; i < n; ++i) { h ^= c[i]; h *= 1099511628211ull; } };
     mix(&nBeams, sizeof nBeams); mix(&dDose, sizeof dDose); mix(&o, sizeof o);
     mix(ctx->ctDims, sizeof ctx->ctDims); mix(ctx->doseDims, sizeof ctx->doseDims); mix(&ctx->ctTex.tex, sizeof ctx->ctTex.tex);
-    mix(&ctx->lutGeneration, sizeof ctx->lutGeneration);
+    mix(&ctx->lutGeneration, sizeof ctx->lutGeneration); mix(&ctx->ctLinValid, sizeof ctx->ctLinValid);
     const long re = DevBuf::reallocs(); mix(&re, sizeof re);
     for (int b = 0; b < nBeams; ++b) {
         mix(&beams[b], sizeof(rtd_beam));
@@ -884,7 +985,7 @@ void rtd_default_opts(rtd_opts* o) {
     if (!o) return;
     memset(o, 0, sizeof *o);
     o->bpDepthCutoff = 1.05f; o->convSigmaCutoff = 3.0f; o->ksSigmaCutoff = 3.0f; o->rayWeightCutoff = 1.0f;
-    o->minTilesInBatch = 16;
+    o->minTilesInBatch = 16; o->tracerBrick = -1;
 }
 
 static rtd_status createCommon(rtd_ctx** out, int device, cudaStream_t userStream, bool haveUserStream) {
@@ -902,6 +1003,7 @@ static rtd_status createCommon(rtd_ctx** out, int device, cudaStream_t userStrea
     if (cudaStreamCreateWithPriority(&ctx->cstream, cudaStreamNonBlocking, prHi) != cudaSuccess) { if (ctx->ownStream) cudaStreamDestroy(ctx->stream); delete ctx; return RTD_ERR_CUDA; }
     cudaDeviceGetAttribute(&ctx->smCount, cudaDevAttrMultiProcessorCount, device);
     rtd_default_opts(&ctx->optsLast);
+    cudaFuncSetAttribute(trace_brick_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TRB_SMEM_BUDGET);
     cudaFuncSetAttribute(ks2_kernel<16, KS2_WARPS_16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)KS2_SMEM_16);
     cudaFuncSetAttribute(ks2_kernel<8, KS2_WARPS_8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)KS2_SMEM_8);
     cudaFuncSetAttribute(ks2_kernel<32, KS2_WARPS_32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)KS2_SMEM_32);
@@ -927,7 +1029,7 @@ void rtd_destroy(rtd_ctx* ctx) {
     for (BeamWs* w : ctx->ws) { w->release(); delete w; }
     ctx->iddTex.release(); ctx->densTex.release(); ctx->spTex.release(); ctx->densSpTex.release(); ctx->rrlTex.release(); ctx->ctTex.release();
     ctx->nucTex.release();
-    ctx->dose.release(); ctx->xferCount.release(); ctx->hXferCount.release(); ctx->ctRows.release();
+    ctx->dose.release(); ctx->xferCount.release(); ctx->hXferCount.release(); ctx->ctRows.release(); ctx->ctLin.release();
     if (ctx->graphExec) cudaGraphExecDestroy(ctx->graphExec);
     if (ctx->groupGrid) rtd_group_destroy(ctx);
     ctx->groupEpochDev.release(); ctx->groupFlag.release();
@@ -1061,7 +1163,7 @@ static rtd_status planDose(rtd_ctx* ctx, const float* ct, int nx, int ny, int nz
     RTD_CUDA(cudaSetDevice(ctx->device));
     rtd_status s = ensureCtArray(ctx, nx, ny, nz);
     if (s != RTD_OK) return s;
-    ctx->haveCt = true; ctx->ctPartial = true;
+    ctx->haveCt = true; ctx->ctPartial = true; ctx->ctLinValid = false;
     return doseHost(ctx, ct, beams, nBeams, dose, dDose, opts, tm);
 }
 
@@ -1251,7 +1353,7 @@ rtd_status rtd_plan_dose_group(rtd_ctx* ctx, const float* ct, int nx, int ny, in
         if (nx <= 0 || ny <= 0 || nz <= 0) return fail(ctx, RTD_ERR_INVALID, "rtd_plan_dose_group: non-positive CT dims");
         rtd_status s = ensureCtArray(ctx, nx, ny, nz);
         if (s != RTD_OK) return s;
-        ctx->haveCt = true; ctx->ctPartial = true;
+        ctx->haveCt = true; ctx->ctPartial = true; ctx->ctLinValid = false;
     } else {
         if (!ctx->haveCt || ctx->ctPartial) return fail(ctx, RTD_ERR_STATE, "rtd_plan_dose_group: no CT given and no complete CT resident (rtd_set_ct)");
     }

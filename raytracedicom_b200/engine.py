@@ -49,7 +49,7 @@ class RtdOpts(C.Structure):
     _fields_ = [("bpDepthCutoff", C.c_float), ("convSigmaCutoff", C.c_float), ("ksSigmaCutoff", C.c_float),
                 ("rayWeightCutoff", C.c_float), ("minTilesInBatch", C.c_int), ("ks2BodyStep", C.c_int),
                 ("serialBeams", C.c_int), ("noZeroCopyDose", C.c_int), ("noNozzle", C.c_int), ("doseToMedium", C.c_int),
-                ("atomicDose", C.c_int), ("ctPull", C.c_int), ("nuclearCorr", C.c_int), ("noGraph", C.c_int), ("fullIntermediates", C.c_int)]
+                ("atomicDose", C.c_int), ("ctPull", C.c_int), ("nuclearCorr", C.c_int), ("noGraph", C.c_int), ("fullIntermediates", C.c_int), ("tracerBrick", C.c_int)]
 
 
 class RtdTiming(C.Structure):
@@ -57,7 +57,8 @@ class RtdTiming(C.Structure):
                 ("msConv", C.c_float), ("msIddSigma", C.c_float), ("msRadius", C.c_float), ("msSuperp", C.c_float),
                 ("msTransfer", C.c_float), ("msDownload", C.c_float), ("updates", C.c_int64), ("ksTaps", C.c_int64),
                 ("kernelLaunches", C.c_int), ("hostSyncs", C.c_int), ("h2dBytes", C.c_int64), ("d2hBytes", C.c_int64),
-                ("doseVoxelsModified", C.c_int64), ("ksLaunchesWithWork", C.c_int), ("reserved0", C.c_int)]
+                ("doseVoxelsModified", C.c_int64), ("ksLaunchesWithWork", C.c_int), ("tracerBrickBeams", C.c_int),
+                ("tracerOutsideSamples", C.c_int), ("reserved0", C.c_int)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

@@ -35,8 +35,8 @@ def test_struct_layouts_match_header():
     checks = {
         "rtd_luts": (engine.RtdLuts, ["nEnergySamples", "ciddMatrix", "densityScaleFact", "spVector", "rRlVector", "nucWeightMatrix", "nucSqSigmaMatrix"]),
         "rtd_beam": (engine.RtdBeam, ["weights", "nLayers", "sigmas", "steps", "spotOffset", "gantryToDoseIdxV", "layerBegin", "layerEnd"]),
-        "rtd_opts": (engine.RtdOpts, ["bpDepthCutoff", "minTilesInBatch", "ks2BodyStep", "ctPull", "nuclearCorr", "noGraph", "fullIntermediates"]),
-        "rtd_timing": (engine.RtdTiming, ["msTotal", "msDownload", "updates", "ksTaps", "hostSyncs", "doseVoxelsModified", "ksLaunchesWithWork"]),
+        "rtd_opts": (engine.RtdOpts, ["bpDepthCutoff", "minTilesInBatch", "ks2BodyStep", "ctPull", "nuclearCorr", "noGraph", "fullIntermediates", "tracerBrick"]),
+        "rtd_timing": (engine.RtdTiming, ["msTotal", "msDownload", "updates", "ksTaps", "hostSyncs", "doseVoxelsModified", "ksLaunchesWithWork", "tracerBrickBeams", "tracerOutsideSamples"]),
         "rtd_beam_report": (engine.RtdBeamReport, ["lSteps", "beamFirstCalculatedPassive", "bboxMax", "entryZ", "updates"]),
         "rtd_layer_report": (engine.RtdLayerReport, ["energyIdx", "layerFirstPassive", "radiusHist", "batchRadius"]),
     }

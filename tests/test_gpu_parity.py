@@ -587,3 +587,47 @@ def test_captured_plan_replays_and_follows_weight_changes(eng, c3):
     finally:
         keep[0] *= np.float32(2.0)
     assert rel_to_max(half, half_eager)[0] <= 2e-6 and rel_to_max(half, eager)[0] > 1e-2
+
+
+def _trace_arrays(eng, case, brick):
+    eng.opts.tracerBrick = brick
+    try:
+        dose, t = run_case(eng, case)
+        arrs = [{k: eng.fetch(b, k).copy() for k in ("density", "wepl", "first_inside", "first_outside")} for b in range(len(case.beams))]
+    finally:
+        eng.opts.tracerBrick = -1
+    return dose, t, arrs
+
+
+@pytest.mark.parametrize("name", ["mini", "c2", "c3"])
+def test_tma_brick_tracer_is_bit_identical_to_the_texture_tracer(eng, name):
+    """Tracer variant B (csrc/trace_brick.cuh: CT bricks staged by cp.async.bulk.tensor.3d, hand-made filter with the texture unit's
+    integer weights) against variant A (tex3D) on the same beams - /root/reference/src/kernel_wrapper.cu:130-187 is what both restate.
+    The phantoms hold integer HU + 1000 like a DICOM series, so B's result must stand (no fall-back) and every array must agree bit for
+    bit, the oblique 70 degree field of C3 included; no sample may miss its brick."""
+    case = cases.make_case(name)
+    if name == "mini":          # the golden mini phantom has fractional HU (see the fall-back test below): rounded here
+        case.ct = np.rint(case.ct).astype(np.float32)
+    dA, tA, a = _trace_arrays(eng, case, 0)
+    dB, tB, b = _trace_arrays(eng, case, 1)
+    assert tA["tracerBrickBeams"] == 0
+    assert tB["tracerBrickBeams"] == len(case.beams) and tB["tracerOutsideSamples"] == 0, tB
+    for beam, (x, y) in enumerate(zip(a, b)):
+        assert np.array_equal(x["first_inside"], y["first_inside"]) and np.array_equal(x["first_outside"], y["first_outside"]), beam
+        assert bits_equal(x["density"], y["density"]), (beam, float(np.abs(x["density"] - y["density"]).max()))
+        assert bits_equal(x["wepl"], y["wepl"]), (beam, float(np.abs(x["wepl"] - y["wepl"]).max()))
+    assert bits_equal(dA, dB) or rel_to_max(dB, dA)[0] <= 1e-6      # same inputs to every later stage: only atomic order may differ
+
+
+def test_tma_brick_tracer_falls_back_on_non_integer_ct(eng, mini_case):
+    """A CT with fractional HU cannot be filtered by hand bit for bit (the texture unit's internal precision is not public): variant B must
+    notice (every brick is checked), and the gated launch of variant A behind it must leave exactly variant A's arrays."""
+    case = mini_case            # its smoothed phantom holds fractional values
+    assert (case.ct != np.trunc(case.ct)).any()
+    dA, tA, a = _trace_arrays(eng, case, 0)
+    dB, tB, b = _trace_arrays(eng, case, 1)
+    assert tB["tracerBrickBeams"] == 0
+    for x, y in zip(a, b):
+        for k in x:
+            assert np.array_equal(x[k].view(np.uint32), y[k].view(np.uint32)), k
+    assert rel_to_max(dB, dA)[0] <= 1e-6
