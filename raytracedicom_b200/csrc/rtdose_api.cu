@@ -3,6 +3,7 @@
 // device memory (no per-beam cudaMalloc/cudaFree after the first call), issues every kernel on one stream and
 // synchronises with the host twice per PLAN (the reference blocks ~3 times per energy layer, cu:916-976).
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <cmath>
 #include <string>
@@ -286,13 +287,42 @@ bool makeCtTensorMap(rtd_ctx* ctx, const BrickParams& bp, CUtensorMap* out) {
 }
 
 // ---- sub-volume transfers of the one-call host path -------------------------------------------------------
-// Queues a box unless an already queued box contains it (beams overlap around the isocentre).
+// b minus o as at most 5 boxes, cut along z, then y (whole rows stay whole), then x - but never into rows shorter than 64 voxels, which
+// starve the copy engine: such a remainder is kept uncut. An intersection below a fifth of b is not worth the extra copies.
+void subtractBox(const Box& b, const Box& o, std::vector<Box>& out) {
+    Box i;
+    for (int d = 0; d < 3; ++d) { i.lo[d] = std::max(b.lo[d], o.lo[d]); i.hi[d] = std::min(b.hi[d], o.hi[d]); if (i.lo[d] > i.hi[d]) { out.push_back(b); return; } }
+    if (boxVoxels(i) * 5 < boxVoxels(b)) { out.push_back(b); return; }
+    Box r = b;
+    for (int d = 2; d >= 1; --d) {
+        if (r.lo[d] < i.lo[d]) { Box p = r; p.hi[d] = i.lo[d] - 1; out.push_back(p); r.lo[d] = i.lo[d]; }
+        if (r.hi[d] > i.hi[d]) { Box p = r; p.lo[d] = i.hi[d] + 1; out.push_back(p); r.hi[d] = i.hi[d]; }
+    }
+    const int left = i.lo[0] - r.lo[0], right = r.hi[0] - i.hi[0];
+    if (left == 0 && right == 0) return;                                  // the rest of b lies inside o
+    if ((left == 0 || left >= 64) && (right == 0 || right >= 64)) {
+        if (left) { Box p = r; p.hi[0] = i.lo[0] - 1; out.push_back(p); }
+        if (right) { Box p = r; p.lo[0] = i.hi[0] + 1; out.push_back(p); }
+    } else out.push_back(r);
+}
+
+// Queues the parts of a box that no already queued box holds (beams overlap around the isocentre: on a three-field head plan a
+// quarter, on a five-field pelvis plan half of the summed box volume is overlap).
 void addBox(std::vector<Box>& v, Box b, const int dims[3]) {
     for (int d = 0; d < 3; ++d) { b.lo[d] = std::max(b.lo[d], 0); b.hi[d] = std::min(b.hi[d], dims[d] - 1); if (b.lo[d] > b.hi[d]) return; }
     // full rows when most of a row is needed anyway: one contiguous run per row / slice for the copy engine
     if (int64_t(b.hi[0] - b.lo[0] + 1) * 4 >= int64_t(dims[0]) * 3) { b.lo[0] = 0; b.hi[0] = dims[0] - 1; }
-    for (const Box& o : v) if (boxInside(b, o)) return;
-    v.push_back(b);
+    std::vector<Box> pieces{b}, next;
+    const size_t nOld = v.size();
+    for (size_t k = 0; k < nOld && !pieces.empty(); ++k) {
+        next.clear();
+        for (size_t q = 0; q < pieces.size(); ++q) {
+            if (next.size() + (pieces.size() - q) > 12) next.push_back(pieces[q]);      // enough fragments: the rest goes as it is
+            else subtractBox(pieces[q], v[k], next);
+        }
+        pieces.swap(next);
+    }
+    for (const Box& p : pieces) v.push_back(p);
 }
 
 // CT boxes that enclose every texel the tracer of this beam can fetch (trace_bev_kernel: pos = start(i,j) + 1/2 + k inc(i,j),
@@ -485,7 +515,7 @@ const char* validateBeam(const rtd_beam& b, const rtd_opts& o) {
     return nullptr;
 }
 
-constexpr size_t EV_BEAM0 = 8, EV_PER_BEAM = 12;   // events 0..7 are per call; per beam: 0 begin, 1 traced, 2 set up, 3 conv, 4 idd, 5 radius, 6 superp, 7 transfer, 8 done, 9 CT uploaded, 10 BeamDev on the host
+constexpr size_t EV_BEAM0 = 8, EV_PER_BEAM = 14;   // events 0..7 are per call; per beam: 0 begin, 1 traced, 2 set up, 3 conv, 4 idd, 5 radius, 6 superp, 7 transfer, 8 done, 9 CT uploaded, 10 BeamDev on the host
 cudaEvent_t evBeam(rtd_ctx* ctx, int b, int i) { return ev(ctx, EV_BEAM0 + size_t(b) * EV_PER_BEAM + i); }
 
 // Part 1 of a beam, everything up to the superposition: launched without knowing any device result (cu:612-1100). The grids
@@ -564,8 +594,12 @@ rtd_status beamEnqueue(rtd_ctx* ctx, int beamNo, const rtd_beam& b, BeamWs& w, c
     const float maxPeakDepth = w.maxPeakDepth;
 
     RTD_CUDA(cudaEventRecord(evBeam(ctx, beamNo, 0), st));
-    RTD_CUDA(cudaMemcpyAsync(w.spotW.p, w.hStage.p, nW * 4, cudaMemcpyHostToDevice, st));
-    RTD_CUDA(cudaMemcpyAsync(w.layerIn.p, stLin, size_t(L) * sizeof(LayerIn), cudaMemcpyHostToDevice, st));
+    // One-call host path: the beam's small uploads ride on the copy stream in front of its CT boxes. On the beam's own stream they
+    // would queue on the copy engine behind EVERY CT box already submitted - those of the beams after this one included - and the
+    // beam would not start before the whole plan's CT had arrived (measured: beam 1 of C3 saw its CT 0.31 ms late).
+    cudaStream_t up = (io && io->ct) ? ctx->cstream : st;
+    RTD_CUDA(cudaMemcpyAsync(w.spotW.p, w.hStage.p, nW * 4, cudaMemcpyHostToDevice, up));
+    RTD_CUDA(cudaMemcpyAsync(w.layerIn.p, stLin, size_t(L) * sizeof(LayerIn), cudaMemcpyHostToDevice, up));
     RTD_CUDA(cudaMemsetAsync(w.lfp.p, 0, ctlInts * 4, st));
     const TraceParams tp = makeTraceParams(ctx->densScale, ctx->spScale, b.steps, w.grid.rayIdxToGantry, w.dist, w.gtii);
     if (io && io->ct) {
@@ -595,6 +629,7 @@ rtd_status beamEnqueue(rtd_ctx* ctx, int beamNo, const rtd_beam& b, BeamWs& w, c
         }
         RTD_CUDA(cudaEventRecord(evCt, ctx->cstream));
         RTD_CUDA(cudaStreamWaitEvent(st, evCt, 0));
+        RTD_CUDA(cudaEventRecord(evBeam(ctx, beamNo, 12), st));      // (timeline: when the beam's stream saw its CT)
     }
     if (io) io->h2d += int64_t(nW) * 4 + int64_t(L) * sizeof(LayerIn);
 
@@ -685,6 +720,10 @@ rtd_status beamEnqueue(rtd_ctx* ctx, int beamNo, const rtd_beam& b, BeamWs& w, c
     k2.bigCount = dCursor; k2.bigItems = w.list.as<uint32_t>();
     k2.bodyStep = (o.ks2BodyStep == 1 || o.ks2BodyStep == 2 || o.ks2BodyStep == 4) ? o.ks2BodyStep : 0;
     int* dKsItems = dWork + 4;      // items each radius class processed (rtd_timing.ksLaunchesWithWork)
+    // (Cutting the two large classes into several launches on a low-priority stream, so that the tracer .. depth scan of a beam whose CT
+    // arrives later on the one-call host path can slip in between, was measured and LOST: the later beam's tracer ends 0.13 ms sooner
+    // but every part ends in a tail of idle SMs - C3 end to end 2.55 -> 2.65 (2 parts) -> 2.79 ms (4 parts). One launch per class.)
+    k2.part = 0; k2.nParts = 1;
     ks2_kernel<32, KS2_WARPS_32><<<ctx->ks2Blocks32, KS2_WARPS_32 * 32, KS2_SMEM_32, st>>>(k2, dWork + 0, dKsItems + 0);
     ks2_kernel<24, KS2_WARPS_24><<<ctx->ks2Blocks24, KS2_WARPS_24 * 32, KS2_SMEM_24, st>>>(k2, dWork + 3, dKsItems + 1);
     ks2_kernel<16, KS2_WARPS_16><<<ctx->ks2Blocks16, KS2_WARPS_16 * 32, KS2_SMEM_16, st>>>(k2, dWork + 1, dKsItems + 2);
@@ -860,6 +899,19 @@ rtd_status doseFinish(rtd_ctx* ctx, int nBeams, rtd_timing* tm, cudaEvent_t evBe
     const int64_t modified = (int64_t)*ctx->hXferCount.as<unsigned long long>();
     if (io && io->ctMapped) io->h2d += (int64_t)ctx->hXferCount.as<unsigned long long>()[1];   // CT bytes the pull kernels read over PCIe
     if (io && io->dose && io->zeroCopy) { io->h2d += modified * 4; io->d2h += modified * 4; }   // the transfers read-modify-write the caller's pinned grid in place
+    if (!cs.graph && getenv("RTD_TIMELINE")) {      // debugging aid: when did every stage of every beam END, in ms after the call's first event
+        for (int b = 0; b < nBeams; ++b) {
+            static const char* name[13] = {"begin", "traced", "setup", "conv", "idd", "radius", "superp", "transfer", "-", "ct", "-", "-", "ctseen"};
+            fprintf(stderr, "[rtd timeline] beam %d:", b);
+            for (int i : {0, 9, 12, 1, 2, 3, 4, 5, 6, 7}) {
+                float ms = -1.0f;
+                if ((i == 9 || i == 12) && !(io && io->ct)) continue;
+                if (cudaEventElapsedTime(&ms, evBegin, evBeam(ctx, b, i)) != cudaSuccess) { cudaGetLastError(); continue; }
+                fprintf(stderr, " %s %.3f", name[i], ms);
+            }
+            fprintf(stderr, "\n");
+        }
+    }
     if (tm) {
         memset(tm, 0, sizeof *tm);
         tm->updates = updates; tm->ksTaps = taps; tm->kernelLaunches = launches; tm->hostSyncs = hostSyncs; tm->ksLaunchesWithWork = ksLaunches;
