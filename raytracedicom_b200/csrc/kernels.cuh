@@ -409,8 +409,17 @@ struct IddParams {
 // from ONE queue ordered by decreasing scan length (longest-processing-time first): every scheduler stays busy until the queue is
 // empty. Dead segments are never visited: their row minima / firstPassive are the fill values beam_clear_kernel wrote.
 // The per-step table the CTA used to build in shared memory is the beam's stepTab (beam_setup_kernel), read through L1.
+#ifndef RTD_IDD_BLOCK
+#define RTD_IDD_BLOCK 4
+#endif
+#ifndef RTD_IDD_PRELOAD
+#define RTD_IDD_PRELOAD 0
+#endif
+#ifndef RTD_IDD_MINCTAS
+#define RTD_IDD_MINCTAS 1
+#endif
 constexpr int IDD_WARPS = 2;
-__global__ void __launch_bounds__(IDD_WARPS * 32)
+__global__ void __launch_bounds__(IDD_WARPS * 32, RTD_IDD_MINCTAS)
 idd_sigma_kernel(const float* __restrict__ density, const float* __restrict__ wepl, const float* __restrict__ rayWeights,
                  const int* __restrict__ firstInside, const int* __restrict__ firstOutside,
                  const LayerParams* __restrict__ layers, const BeamDev* __restrict__ bd, const float2* __restrict__ stepTab, const IddParams q,
@@ -491,6 +500,106 @@ idd_sigma_kernel(const float* __restrict__ density, const float* __restrict__ we
         const float betaP = f_sub(e1, f_div(880406.875f, e1));
         return f_mul(f_div(q.eRefSq, f_mul(betaP, betaP)), stepLength);
     };
+#if RTD_IDD_BLOCK
+    // Round 2, late: the scan in blocks of RTD_IDD_BLOCK steps. Everything of a step that does not depend on the running sums - the
+    // two loads, the two (three with the nuclear option) LUT fetches, the scattering power with its four MUFU operations, i.e. nine
+    // tenths of the step's instructions and all of its long latencies - is evaluated for the WHOLE block first, as independent
+    // instruction streams the hardware overlaps; then the steps run in order with only the sigma^2 recurrence (four dependent adds),
+    // the range test and the outputs. Same operations on the same operands in the same order per ray as the four-slot pipeline it
+    // replaces (kept below, RTD_IDD_BLOCK 0), whose three steps of look-ahead still left 4.2 warp-cycles of long-scoreboard stall per
+    // issued instruction (profiles/r02_ncu_full_c3.txt).
+    constexpr int NB = RTD_IDD_BLOCK;
+    unsigned k = first;
+    float wPrev = 0.0f;                      // WEPL of the step before the block (0 in front of the first step, cu:266)
+    // the WEPL / density of a block are requested one block ahead (RTD_IDD_PRELOAD): a block then starts with its LUT fetches
+    float pw[NB], prho[NB];
+#pragma unroll
+    for (int s = 0; s < NB; ++s) {
+        const bool on = RTD_IDD_PRELOAD && live && first + (unsigned)s < last;
+        pw[s] = on ? weplP[(unsigned)s * (unsigned)R] : 0.0f;
+        prho[s] = on ? densP[(unsigned)s * (unsigned)R] : 0.0f;
+    }
+    while (k < last && __any_sync(0xffffffffu, live)) {
+        const int nb = min(NB, (int)(last - k));                 // warp-uniform
+        float bw[NB], brho[NB], bd_[NB], bX[NB], bnw[NB]; float2 bst[NB];
+        float wLast = wPrev;
+#pragma unroll
+        for (int s = 0; s < NB; ++s) {
+            const bool on = live && s < nb;
+            if (RTD_IDD_PRELOAD) { bw[s] = pw[s]; brho[s] = prho[s]; }
+            else {
+                bw[s] = on ? weplP[off + (unsigned)s * (unsigned)R] : 0.0f;
+                brho[s] = on ? densP[off + (unsigned)s * (unsigned)R] : 0.0f;
+            }
+            bst[s] = (s < nb) ? __ldg(stepTab + (k + s - first)) : make_float2(0.0f, 0.0f);
+        }
+        if (RTD_IDD_PRELOAD) {
+#pragma unroll
+            for (int s = 0; s < NB; ++s) {
+                const bool on = live && k + (unsigned)(NB + s) < last;
+                pw[s] = on ? weplP[off + (unsigned)(NB + s) * (unsigned)R] : 0.0f;
+                prho[s] = on ? densP[off + (unsigned)(NB + s) * (unsigned)R] : 0.0f;
+            }
+        }
+#pragma unroll
+        for (int s = 0; s < NB; ++s) {
+            const bool on = live && s < nb;
+            const float wBefore = s ? bw[s - 1] : wPrev;
+            bd_[s] = 0.0f; bX[s] = 0.0f; bnw[s] = 0.0f;
+            if (on) {
+                bd_[s] = tex2D<float>(iddTex, f_fma(bw[s], lp.energyScale, 0.5f), eRow);
+                const float x = tex1D<float>(rrlTex, f_fma(brho[s], q.rrlScale, 0.5f));
+                const float t1 = scatPower(wBefore, bw[s]);
+                const float rRl = f_mul(brho[s], x);
+                const float thetaSq = f_mul(rRl, t1);
+                bX[s] = f_mul(stepLength, f_fma(rRl, t1, thetaSq));
+                if (q.nuclear) bnw[s] = tex2D<float>(nucTex, f_fma(f_mul(f_add(bw[s], wBefore), 0.5f), lp.energyScale, 0.5f), eRow);
+            }
+        }
+#pragma unroll
+        for (int s = 0; s < NB; ++s) {
+            if (s < nb) {
+                const unsigned kk = k + (unsigned)s;
+                const float w = bw[s], rho = brho[s];
+                wLast = w;
+                if (live) {
+                    if (w < lp.peakDepth) {
+                        sigmaSq = f_add(sigmaSq, f_add(incScat, incDiv));
+                        incinc = f_fma(stepLength, bX[s], incinc);
+                        incScat = f_add(incScat, incinc);
+                        incDiv = f_fma(airQuad, 2.0f, incDiv);
+                    } else if (q.nuclear != 3) {       // the empirical fix of the sigma dip after the peak is compiled out for GAUSS_FIT (cu:300-302)
+                        sigmaSq = f_fma(f_mul(f_add(incScat, incDiv), -1.5f), rho, sigmaSq);
+                    }
+                    rs = f_div(bst[s].x, f_mul(f_add(f_sqrt(sigmaSq), q.sigmaDelta), 1.41421356f));
+                    const bool within = !(w > thr);
+                    live = within && (kk != afterLast);
+                    afterLast = within ? afterLast : kk;
+                    const float vol = bst[s].y;
+                    const float mass = q.doseToMedium ? f_mul(rho, vol) : f_mul(f_sub(w, wOld), vol);
+                    const float d = bd_[s];
+                    if (mass > 1e-2f) {
+                        // (nuclear option: the halo's share is taken out of the primary dose, cu:320-330; see the slot version below)
+                        if (q.nuclear) res = f_div(f_mul(f_mul(f_sub(1.0f, bnw[s]), rayWeight), f_sub(d, dOld)), mass);
+                        else res = f_div(f_mul(rayWeight, f_sub(d, dOld)), mass);
+                    }
+                    wOld = w; dOld = d;
+                }
+                const bool keep = live && ((int)kk >= firstIn - 1);
+                res = keep ? res : 0.0f;
+                rs = keep ? rs : inf;
+                const unsigned rsBits = __float_as_uint(rs);
+                const float m = __any_sync(0xffffffffu, (int)rsBits < 0) ? warp_min(rs) : __uint_as_float(__reduce_min_sync(0xffffffffu, rsBits));
+                const bool anyDose = __any_sync(0xffffffffu, res > 0.0f);
+                if (anyDose || q.writeAll) { iddP[off] = res; rsigP[off] = rs; }
+                if (lane == 0) rowMinP[rmOff] = anyDose ? m : -m;
+                off += (unsigned)R; rmOff += rmStride;
+            }
+        }
+        wPrev = wLast;
+        k += (unsigned)nb;
+    }
+#else
     // Four statically named slots (step s lives in slot s & 3, the loop is unrolled by four so that no register rotates at the back
     // edge): at step k the WEPL / density of step k + 3 are requested, the two LUT fetches (IDD at its WEPL, 1/X0 at its density) and
     // the scattering power of step k + 2 are issued, the step table entry of step k + 1 is loaded. Round 2's profile of the two-slot
@@ -585,6 +694,7 @@ idd_sigma_kernel(const float* __restrict__ density, const float* __restrict__ we
         if (!(k < last && __any_sync(0xffffffffu, live))) break;
         step(k, S3, S0, S1, S2); ++k;
     }
+#endif
     if (q.writeAll) {
         for (unsigned kk = k; kk < last; ++kk) { iddP[off + (kk - k) * (unsigned)R] = 0.0f; rsigP[off + (kk - k) * (unsigned)R] = inf; }
     }
