@@ -415,11 +415,8 @@ struct IddParams {
 #ifndef RTD_IDD_PRELOAD
 #define RTD_IDD_PRELOAD 0
 #endif
-#ifndef RTD_IDD_MINCTAS
-#define RTD_IDD_MINCTAS 1
-#endif
 constexpr int IDD_WARPS = 2;
-__global__ void __launch_bounds__(IDD_WARPS * 32, RTD_IDD_MINCTAS)
+__global__ void __launch_bounds__(IDD_WARPS * 32)
 idd_sigma_kernel(const float* __restrict__ density, const float* __restrict__ wepl, const float* __restrict__ rayWeights,
                  const int* __restrict__ firstInside, const int* __restrict__ firstOutside,
                  const LayerParams* __restrict__ layers, const BeamDev* __restrict__ bd, const float2* __restrict__ stepTab, const IddParams q,

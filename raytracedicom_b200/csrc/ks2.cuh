@@ -30,6 +30,9 @@
 #ifndef RTD_KS2_EARLY_G
 #define RTD_KS2_EARLY_G 0
 #endif
+#ifndef RTD_KS2_R0_FAST
+#define RTD_KS2_R0_FAST 0      // measured (tools/gpu_r2_l.sh): C3 superposition 1.096 -> 1.104 ms, C4 12.55 -> 12.60: no gain, off
+#endif
 #ifndef RTD_KS2_ITEM_PREFETCH
 #define RTD_KS2_ITEM_PREFETCH 0
 #endif
@@ -383,6 +386,23 @@ ks2_kernel(const Ks2Params p, int* __restrict__ workCounter, int* __restrict__ i
             // erf-difference weights (cuh:459-467) -> table: e[0] = erf(r/2), e[i] = (erf(r(i+1/2)) - erf(r(i-1/2)))/2
             // the 8 rows advance together so that 8 independent polynomial chains are in flight per lane; the argument
             // r (i + 1/2) is advanced by repeated addition
+#if RTD_KS2_PACKED_ERF && RTD_KS2_R0_FAST
+            // Applied radius 0 - half of all (tile, layer) pairs of a head plan, the entrance region of every layer: the voxel keeps its
+            // dose, scaled by erf(r / 2)^2. Same operations as the general body at RB = 0 (table entry 2 h, weight d * t, FFMA2 t * w + 0,
+            // 128-bit read-modify-write of the lane's own column) without the round trip through the weight table.
+            if (!BIG && rb == 0 && body == 0) {
+                ks_u64 acc[4];
+#pragma unroll
+                for (int pp = 0; pp < 4; ++pp) {
+                    const ks_u64 h = ks_half_erf_pos2(ks_mul2(ks_pk(r[2 * pp], r[2 * pp + 1]), ks_bc(0.5f)));
+                    float t0, t1; ks_upk(ks_add2(h, h), t0, t1);
+                    acc[pp] = ks_fma2(ks_pk(t0, t1), ks_pk(d[2 * pp] * t0, d[2 * pp + 1] * t1), 0ull);
+                }
+                ks2_rmw<2>(patch + (lane + RBMAX) * PC + RBMAX, acc);
+                __syncwarp();
+                continue;
+            }
+#endif
 #if RTD_KS2_PACKED_ERF
             {
                 ks_u64 x[4], rr[4], hOld[4];
