@@ -326,10 +326,12 @@ def measure(R, case, steps, warmup, do_e2e, do_cpu, full):
     torch.cuda.synchronize()
     if world > 1 and (not group or rank == 0) and (bool(dose_dev[:z0].any().item()) or bool(dose_dev[z1 + 1:].any().item())):
         raise SystemExit(f"bench.py: rank {rank} deposited dose outside the reduced slab [{z0}, {z1}]")
-    R.barrier()          # every rank enters the timed loop together (a late rank would be waited for inside the others' first step)
     sampler = ClockSampler(R.local) if full else None
     if sampler:
-        sampler.start()
+        sampler.start()  # (before the barrier: starting it costs rank 0 ~0.5 ms, which the other ranks' first step would wait for)
+    R.barrier()          # every rank enters the timed loop together (a late rank would be waited for inside the others' first step)
+    if group:
+        eng.group_barrier()      # and the ranks' streams line up on the device as well (stream-ordered, no host sync)
     evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
     stage = {}
     t_wall0 = time.perf_counter()
