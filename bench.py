@@ -186,8 +186,9 @@ def run_reference(args, case, rank, world):
             # out of its timer (context creation is outside it either way)
             eager = run_steps(0, max(1, min(args.steps, 3)), env=dict(os.environ, CUDA_MODULE_LOADING="EAGER"))
             if eager:
-                em = sum(eager) / len(eager)
-                line["reference_eager_module_loading"] = {"ms_per_step": em, "value": U / (em * 1e-3), "env": "CUDA_MODULE_LOADING=EAGER"}
+                em = sorted(eager)[len(eager) // 2]       # median: a side figure, and single runs of the binary scatter (50 .. 1500 ms seen)
+                line["reference_eager_module_loading"] = {"ms_per_step": em, "ms_each_step": [round(t, 3) for t in eager], "value": U / (em * 1e-3),
+                                                          "env": "CUDA_MODULE_LOADING=EAGER"}
             return line
     # no rebuilt reference or no GPU: the CPU port is the reference arm
     line.update({"value": cpu["value"], "ms_per_step": None, "reference_kind": "CPU restatement (oracle port); rebuilt reference or GPU not available",
