@@ -307,6 +307,13 @@ def measure(R, case, steps, warmup, do_e2e, do_cpu, full):
         dist.broadcast_object_list(handle, src=0)
         if rank != 0:
             eng.group_create(rank, world, nz * ny * nx, handle[0])
+        if args.ct_relay:
+            # CT relay: the e2e call uploads every CT box of the plan once per node; the ranks fetch what they need over NVLink
+            relay_bytes = int(case.ct.nbytes // world + (64 << 20))
+            mine_h = eng.group_ct_create(relay_bytes)
+            all_h = [None] * world
+            dist.all_gather_object(all_h, mine_h)
+            eng.group_ct_open(all_h)
         if rank == 0:
             class _Ext:                       # zero-copy torch view of the group's grid (rank 0 reads it through torch)
                 __cuda_array_interface__ = {"shape": (nz, ny, nx), "typestr": "<f4", "data": (eng.group_dose_ptr(), False), "version": 2}
@@ -538,6 +545,7 @@ def main():
     ap.add_argument("--no-c4", action="store_true", help="skip the extra C4 measurement (key 'c4')")
     ap.add_argument("--no-cold", action="store_true", help="skip the fresh-process measurement (key 'e2e_cold')")
     ap.add_argument("--cold-child", action="store_true", help=argparse.SUPPRESS)
+    ap.add_argument("--ct-relay", action="store_true", help="N > 1: the e2e call uploads every CT box once per node and the ranks fetch theirs over NVLink (rtd_group_ct_*; measured slower up to N = 4, off by default)")
     ap.add_argument("--lib", default=None, help="measure another build of librtdose.so (A/B of kernel variants)")
     ap.add_argument("--reduce", default="push", choices=["push", "nccl"],
                     help="N > 1, how the ranks' partial doses meet: 'push' = rtd_plan_dose_group (ONE grid on rank 0 mapped by every rank over "

@@ -272,6 +272,15 @@ int        rtd_partition(const rtd_beam* beams, int nBeams, const rtd_luts* luts
 int        rtd_dose_slab(const rtd_beam* beams, int nBeams, int nx, int ny, int nz, float convSigmaCutoff, int* z0, int* z1);
 rtd_status rtd_group_create(rtd_ctx* ctx, int rank, int world, size_t nDoseFloats, unsigned char* handle64);
 rtd_status rtd_group_destroy(rtd_ctx* ctx);
+/* CT relay of the group (optional; new, the reference is single-GPU). Without it every rank of rtd_plan_dose_group uploads the CT
+ * sub-volumes of every beam it holds a layer of over its own PCIe link (C3 on 8 GPUs: 168 MB for a plan whose sub-volumes unite to
+ * 61 MB). rtd_group_ct_create gives this rank a staging buffer of `bytes` (the SAME size on every rank; a plan whose share per rank
+ * exceeds it falls back to per-rank uploads) and writes its 64-byte CUDA IPC handle; after the caller has gathered the handles of all
+ * ranks, in rank order, rtd_group_ct_open(handles = world x 64 bytes) maps the peers' buffers. From then on rtd_plan_dose_group with a
+ * HOST CT deals the plan's boxes to the ranks by bytes: every rank uploads its share once, one stream-ordered group barrier later every
+ * rank copies the boxes its beams touch from the owners' buffers into its CT array over NVLink. Freed by rtd_group_destroy. */
+rtd_status rtd_group_ct_create(rtd_ctx* ctx, size_t bytes, unsigned char* handle64);
+rtd_status rtd_group_ct_open(rtd_ctx* ctx, const unsigned char* handles);
 float*     rtd_group_dose(rtd_ctx* ctx);
 rtd_status rtd_group_barrier(rtd_ctx* ctx);
 rtd_status rtd_plan_dose_group(rtd_ctx* ctx, const float* ctHuPlus1000, int nx, int ny, int nz, const rtd_beam* beams, int nBeams,

@@ -69,6 +69,7 @@ inline int64_t boxVoxels(const Box& b) { return int64_t(b.hi[0] - b.lo[0] + 1) *
 struct HostIo {
     const float* ct = nullptr; float* dose = nullptr; bool zeroCopy = false; int64_t h2d = 0, d2h = 0;
     const float* ctMapped = nullptr;      // device-side alias of a page-locked ct: the CT rows are pulled by a kernel (ct_pull_rows_kernel)
+    cudaEvent_t ctReady = nullptr;        // group CT relay: the CT sub-volumes of every beam of the call are in the array once this event has passed
 };
 
 struct BeamWs {
@@ -136,6 +137,9 @@ struct rtd_ctx {
     cudaGraphExec_t groupGraphExec = nullptr; uint64_t groupGraphKey = 0;
     PinBuf groupFlag;                              // [0] = a barrier timed out
     std::vector<rtd_beam> groupBeams;
+    // CT relay of the group (rtd_group_ct_create / _open): every CT box of a plan crosses PCIe ONCE on the node, into the staging buffer of
+    // one rank, and the ranks that need it copy it from there over NVLink
+    void* ctRelay = nullptr; size_t ctRelayBytes = 0; std::vector<void*> ctRelayPeers; bool ctRelayOpen = false;
     // captured launch sequence of the last device-resident plan (doseGraph)
     cudaGraphExec_t graphExec = nullptr; uint64_t graphKey = 0; bool graphBroken = false; long lutGeneration = 0;
     CallState graphCs;
@@ -515,7 +519,7 @@ const char* validateBeam(const rtd_beam& b, const rtd_opts& o) {
     return nullptr;
 }
 
-constexpr size_t EV_BEAM0 = 8, EV_PER_BEAM = 14;   // events 0..7 are per call; per beam: 0 begin, 1 traced, 2 set up, 3 conv, 4 idd, 5 radius, 6 superp, 7 transfer, 8 done, 9 CT uploaded, 10 BeamDev on the host
+constexpr size_t EV_BEAM0 = 12, EV_PER_BEAM = 14;   // events 0..7 are per call; per beam: 0 begin, 1 traced, 2 set up, 3 conv, 4 idd, 5 radius, 6 superp, 7 transfer, 8 done, 9 CT uploaded, 10 BeamDev on the host
 cudaEvent_t evBeam(rtd_ctx* ctx, int b, int i) { return ev(ctx, EV_BEAM0 + size_t(b) * EV_PER_BEAM + i); }
 
 // Part 1 of a beam, everything up to the superposition: launched without knowing any device result (cu:612-1100). The grids
@@ -631,6 +635,7 @@ rtd_status beamEnqueue(rtd_ctx* ctx, int beamNo, const rtd_beam& b, BeamWs& w, c
         RTD_CUDA(cudaStreamWaitEvent(st, evCt, 0));
         RTD_CUDA(cudaEventRecord(evBeam(ctx, beamNo, 12), st));      // (timeline: when the beam's stream saw its CT)
     }
+    if (io && !io->ct && io->ctReady) RTD_CUDA(cudaStreamWaitEvent(st, evBeam(ctx, beamNo, 9), 0));      // group CT relay (groupCtRelay): this beam's boxes are in
     if (io) io->h2d += int64_t(nW) * 4 + int64_t(L) * sizeof(LayerIn);
 
     // K1 + reductions. weplMin buffer layout: [0] = beamFirstInside, [1] = beamFirstOutside (ints), [2..] weplMin floats
@@ -905,7 +910,7 @@ rtd_status doseFinish(rtd_ctx* ctx, int nBeams, rtd_timing* tm, cudaEvent_t evBe
             fprintf(stderr, "[rtd timeline] beam %d:", b);
             for (int i : {0, 9, 12, 1, 2, 3, 4, 5, 6, 7}) {
                 float ms = -1.0f;
-                if ((i == 9 || i == 12) && !(io && io->ct)) continue;
+                if ((i == 9 && !(io && (io->ct || io->ctReady))) || (i == 12 && !(io && io->ct))) continue;
                 if (cudaEventElapsedTime(&ms, evBegin, evBeam(ctx, b, i)) != cudaSuccess) { cudaGetLastError(); continue; }
                 fprintf(stderr, " %s %.3f", name[i], ms);
             }
@@ -1330,11 +1335,13 @@ int rtd_dose_slab(const rtd_beam* beams, int nBeams, int nx, int ny, int nz, flo
     return doseSlab(beams, nBeams, dims, convSigmaCutoff, *z0, *z1) ? 1 : 0;
 }
 
+static void groupCtRelayClose(rtd_ctx* ctx);
 rtd_status rtd_group_destroy(rtd_ctx* ctx) {
     if (!ctx) return RTD_ERR_INVALID;
     if (!ctx->groupGrid) return RTD_OK;
     RTD_CUDA(cudaSetDevice(ctx->device));
     RTD_CUDA(cudaStreamSynchronize(ctx->stream));
+    groupCtRelayClose(ctx);
     if (ctx->groupRank == 0) RTD_CUDA(cudaFree(ctx->groupGrid)); else RTD_CUDA(cudaIpcCloseMemHandle(ctx->groupGrid));
     if (ctx->groupGraphExec) { cudaGraphExecDestroy(ctx->groupGraphExec); ctx->groupGraphExec = nullptr; }
     ctx->groupGrid = nullptr; ctx->groupCtr = nullptr; ctx->groupRank = -1; ctx->groupWorld = 0; ctx->groupFloats = 0;
@@ -1389,6 +1396,158 @@ rtd_status rtd_group_barrier(rtd_ctx* ctx) {
     return groupBarrierEnqueue(ctx);
 }
 
+// ---- CT relay of a group ("CT upload at N = 8") -------------------------------------------
+// Without it every rank uploads the CT sub-volumes of every beam it holds a layer of over its own PCIe link: at N = 8 the node moves
+// 168 MB for a plan whose union of sub-volumes is 61 MB, and a rank with pieces of two beams waits for 40 MB before its second
+// tracer can start. With it the plan's boxes are dealt to the ranks by bytes, each rank uploads its share into its own staging buffer,
+// one group barrier later every rank copies the boxes its beams touch from the owners' buffers into its CT array - device to device
+// over NVLink / NVSwitch peer memory.
+static void groupCtRelayClose(rtd_ctx* ctx) {
+    for (size_t r = 0; r < ctx->ctRelayPeers.size(); ++r)
+        if (ctx->ctRelayPeers[r] && (int)r != ctx->groupRank) cudaIpcCloseMemHandle(ctx->ctRelayPeers[r]);
+    ctx->ctRelayPeers.clear();
+    if (ctx->ctRelay) cudaFree(ctx->ctRelay);
+    ctx->ctRelay = nullptr; ctx->ctRelayBytes = 0; ctx->ctRelayOpen = false;
+    cudaGetLastError();
+}
+
+rtd_status rtd_group_ct_create(rtd_ctx* ctx, size_t bytes, unsigned char* handle64) {
+    if (!ctx) return RTD_ERR_INVALID;
+    if (!ctx->groupGrid) return fail(ctx, RTD_ERR_STATE, "rtd_group_ct_create: no group (rtd_group_create)");
+    if (!handle64 || bytes < 4096) return fail(ctx, RTD_ERR_INVALID, "rtd_group_ct_create: bad arguments");
+    RTD_CUDA(cudaSetDevice(ctx->device));
+    RTD_CUDA(cudaStreamSynchronize(ctx->stream));
+    groupCtRelayClose(ctx);
+    RTD_CUDA(cudaMalloc(&ctx->ctRelay, bytes));
+    ctx->ctRelayBytes = bytes;
+    cudaIpcMemHandle_t h; memset(&h, 0, sizeof h);
+    if (ctx->groupWorld > 1) {
+        const cudaError_t e = cudaIpcGetMemHandle(&h, ctx->ctRelay);
+        if (e != cudaSuccess) { groupCtRelayClose(ctx); char b[256]; snprintf(b, sizeof b, "cudaIpcGetMemHandle: %s", cudaGetErrorString(e)); return fail(ctx, RTD_ERR_CUDA, b); }
+    }
+    memcpy(handle64, &h, 64);
+    return RTD_OK;
+}
+
+rtd_status rtd_group_ct_open(rtd_ctx* ctx, const unsigned char* handles) {
+    if (!ctx) return RTD_ERR_INVALID;
+    if (!ctx->groupGrid || !ctx->ctRelay) return fail(ctx, RTD_ERR_STATE, "rtd_group_ct_open: rtd_group_create and rtd_group_ct_create come first");
+    if (!handles) return fail(ctx, RTD_ERR_INVALID, "rtd_group_ct_open: null handles");
+    RTD_CUDA(cudaSetDevice(ctx->device));
+    ctx->ctRelayPeers.assign(size_t(ctx->groupWorld), nullptr);
+    for (int r = 0; r < ctx->groupWorld; ++r) {
+        if (r == ctx->groupRank) { ctx->ctRelayPeers[r] = ctx->ctRelay; continue; }
+        cudaIpcMemHandle_t h; memcpy(&h, handles + size_t(r) * 64, 64);
+        const cudaError_t e = cudaIpcOpenMemHandle(&ctx->ctRelayPeers[r], h, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) {
+            ctx->ctRelayPeers[r] = nullptr; groupCtRelayClose(ctx);
+            char b[256]; snprintf(b, sizeof b, "cudaIpcOpenMemHandle (CT relay of rank %d): %s", r, cudaGetErrorString(e)); return fail(ctx, RTD_ERR_CUDA, b);
+        }
+    }
+    ctx->ctRelayOpen = true;
+    return RTD_OK;
+}
+
+// Ray grid and tracer geometry of a beam as beamPrepare derives them (nothing is allocated)
+static bool beamCtGeometry(const rtd_beam& b, const rtd_opts& o, TraceParams& tp, int& Rx, int& Ry) {
+    float mx = b.sigmas[0], my = b.sigmas[1];
+    for (int l = 1; l < b.nLayers; ++l) { mx = std::max(mx, b.sigmas[2 * l]); my = std::max(my, b.sigmas[2 * l + 1]); }
+    const RayGrid grid = makeRayGrid(b.spotDelta, b.spotOffset, b.sx, b.sy, b.raySpacing, mx, my, o.convSigmaCutoff);
+    if (grid.dimX <= 0 || grid.dimY <= 0) return false;
+    Affine gtii; gtii.m = m3(b.gantryToImIdxM); gtii.v = v3(b.gantryToImIdxV[0], b.gantryToImIdxV[1], b.gantryToImIdxV[2]);
+    tp = makeTraceParams(1.0f, 1.0f, b.steps, grid.rayIdxToGantry, b.sourceDist, gtii);
+    Rx = grid.dimX; Ry = grid.dimY;
+    return true;
+}
+
+// The relay phase of one call. `mine[k]` = plan beam of this rank's k-th beam (the order they are enqueued in). On success with `used` = true the CT array holds
+// every texel this rank's tracers can fetch once io.ctReady has passed. `used` stays false (and nothing is enqueued) if the relay is not
+// open or a rank's share would not fit its staging buffer - a pure function of the plan, so every rank decides the same.
+static rtd_status groupCtRelay(rtd_ctx* ctx, const float* ct, const rtd_beam* beams, int nBeams, const std::vector<int>& mine, const rtd_opts& o,
+                               HostIo& io, bool& used) {
+    used = false;
+    const int world = ctx->groupWorld, rank = ctx->groupRank;
+    if (!ctx->ctRelayOpen || world <= 1) return RTD_OK;
+    const int* dims = ctx->ctDims;
+    std::vector<Box> U;                       // the plan's boxes, each minus what earlier ones hold (addBox): a partition of their union
+    std::vector<std::vector<Box>> need;       // per beam of this rank, in its order: what the tracer can touch (the beam's boxes, not reduced)
+    for (int b = 0; b < nBeams; ++b) {
+        TraceParams tp; int Rx = 0, Ry = 0;
+        if (!beamCtGeometry(beams[b], o, tp, Rx, Ry)) return fail(ctx, RTD_ERR_INVALID, "empty ray grid");
+        ctBoxesOfBeam(tp, Rx, Ry, (int)beams[b].steps, dims, U);
+    }
+    for (size_t k = 0; k < mine.size(); ++k) {
+        TraceParams tp; int Rx = 0, Ry = 0;
+        if (!beamCtGeometry(beams[mine[k]], o, tp, Rx, Ry)) return fail(ctx, RTD_ERR_INVALID, "empty ray grid");
+        need.emplace_back(); ctBoxesOfBeam(tp, Rx, Ry, (int)beams[mine[k]].steps, dims, need.back());
+    }
+    int64_t total = 0;
+    for (const Box& u : U) total += boxVoxels(u) * 4;
+    if (total == 0) return RTD_OK;
+    // boxes are dealt out in list order by bytes: owner = the rank whose byte range holds the box's first byte
+    std::vector<int> owner(U.size()); std::vector<size_t> offset(U.size());
+    std::vector<int64_t> share(size_t(world), 0);
+    int64_t cum = 0;
+    for (size_t i = 0; i < U.size(); ++i) {
+        const int r = (int)std::min<int64_t>(cum * world / total, world - 1);
+        owner[i] = r; offset[i] = size_t(share[r]); share[r] += (boxVoxels(U[i]) * 4 + 255) / 256 * 256;
+        cum += boxVoxels(U[i]) * 4;
+    }
+    for (int r = 0; r < world; ++r) if (size_t(share[r]) > ctx->ctRelayBytes) return RTD_OK;      // (every rank was created with the same size)
+    const size_t nx = dims[0], ny = dims[1];
+    cudaEvent_t evUp = ev(ctx, 8), evBar = ev(ctx, 9), evReady = ev(ctx, 10);
+    // 1. this rank's share: host -> own staging buffer, every box packed densely
+    for (size_t i = 0; i < U.size(); ++i) {
+        if (owner[i] != rank) continue;
+        const Box& u = U[i];
+        const size_t w = u.hi[0] - u.lo[0] + 1, h = u.hi[1] - u.lo[1] + 1, d = u.hi[2] - u.lo[2] + 1;
+        cudaMemcpy3DParms cp; memset(&cp, 0, sizeof cp);
+        cp.srcPtr = make_cudaPitchedPtr((void*)(ct + (size_t(u.lo[2]) * ny + u.lo[1]) * nx + u.lo[0]), nx * 4, w * 4, ny);
+        cp.dstPtr = make_cudaPitchedPtr((char*)ctx->ctRelay + offset[i], w * 4, w * 4, h);
+        cp.extent = make_cudaExtent(w * 4, h, d); cp.kind = cudaMemcpyHostToDevice;
+        RTD_CUDA(cudaMemcpy3DAsync(&cp, ctx->cstream));
+        io.h2d += boxVoxels(u) * 4;
+    }
+    // 2. every share has landed (stream-ordered barrier of the group, no host sync)
+    RTD_CUDA(cudaEventRecord(evUp, ctx->cstream));
+    RTD_CUDA(cudaStreamWaitEvent(ctx->stream, evUp, 0));
+    { const rtd_status s = groupBarrierEnqueue(ctx); if (s != RTD_OK) return s; }
+    RTD_CUDA(cudaEventRecord(evBar, ctx->stream));
+    RTD_CUDA(cudaStreamWaitEvent(ctx->cstream, evBar, 0));
+    // 3. the boxes this rank's beams touch: owner's staging buffer (peer memory) -> own CT array, beam by beam in the order the beams are
+    //    enqueued, each with its own event (the slot the per-rank upload uses): the first tracer starts after its own boxes
+    std::vector<char> pulled(U.size(), 0);
+    for (size_t k = 0; k < need.size(); ++k) {
+        for (size_t i = 0; i < U.size(); ++i) {
+            if (pulled[i]) continue;
+            const Box& u = U[i];
+            bool hit = false;
+            for (const Box& n : need[k]) {
+                bool x = true;
+                for (int d = 0; d < 3; ++d) x = x && u.lo[d] <= n.hi[d] && n.lo[d] <= u.hi[d];
+                if (x) { hit = true; break; }
+            }
+            if (!hit) continue;
+            pulled[i] = 1;
+            const size_t w = u.hi[0] - u.lo[0] + 1, h = u.hi[1] - u.lo[1] + 1, d = u.hi[2] - u.lo[2] + 1;
+            // (copy engine, 77 GB/s into the array. A kernel writing through the surface - ct_box_to_array_kernel - is faster alone but
+            // queues behind the superposition launches of the beams already running, which own every SM: beam 2 of C4 on two GPUs saw
+            // its CT 4 ms late. Measured, not used.)
+            cudaMemcpy3DParms cp; memset(&cp, 0, sizeof cp);
+            cp.srcPtr = make_cudaPitchedPtr((char*)ctx->ctRelayPeers[owner[i]] + offset[i], w * 4, w, h);
+            cp.dstArray = ctx->ctTex.arr; cp.dstPos = make_cudaPos(u.lo[0], u.lo[1], u.lo[2]);
+            cp.extent = make_cudaExtent(w, h, d); cp.kind = cudaMemcpyDeviceToDevice;
+            RTD_CUDA(cudaMemcpy3DAsync(&cp, ctx->cstream));
+        }
+        RTD_CUDA(cudaGetLastError());
+        RTD_CUDA(cudaEventRecord(evBeam(ctx, (int)k, 9), ctx->cstream));
+    }
+    RTD_CUDA(cudaEventRecord(evReady, ctx->cstream));
+    io.ctReady = evReady;
+    used = true;
+    return RTD_OK;
+}
+
 rtd_status rtd_plan_dose_group(rtd_ctx* ctx, const float* ct, int nx, int ny, int nz, const rtd_beam* beams, int nBeams, float* hostDoseInOut,
                                const rtd_opts* opts, rtd_timing* tm) {
     if (!ctx) return RTD_ERR_INVALID;
@@ -1431,6 +1590,14 @@ rtd_status rtd_plan_dose_group(rtd_ctx* ctx, const float* ct, int nx, int ny, in
     HostIo io; io.ct = ct;
     CallState cs;
     const int nMine = (int)ctx->groupBeams.size();
+    if (ct) {      // CT relay (if the caller opened one): the plan's CT boxes cross PCIe once on the node
+        std::vector<int> mine;
+        for (const WorkItem& it : items) if (it.rank == rank) mine.push_back(it.beam);
+        bool relayed = false;
+        const rtd_status r = groupCtRelay(ctx, ct, beams, nBeams, mine, o, io, relayed);
+        if (r != RTD_OK) return r;
+        if (relayed) io.ct = nullptr;
+    }
     // zero the slab | barrier | this rank's beams | push | barrier: the whole device-side sequence of a rank
     auto enqueueSeq = [&](CallState& c) -> rtd_status {
         if (slabN) RTD_CUDA(cudaMemsetAsync(target + slabOff, 0, slabN * 4, ctx->stream));

@@ -99,7 +99,7 @@ class RtdError(RuntimeError):
 
 
 EXPORTS = ["rtd_default_opts", "rtd_create", "rtd_create_on_stream", "rtd_destroy", "rtd_last_error", "rtd_version", "rtd_set_luts", "rtd_set_ct",
-           "rtd_set_ct_device", "rtd_set_dose_grid", "rtd_dose", "rtd_dose_device", "rtd_plan_dose", "rtd_plan_dose_device", "rtd_add_device_to_host", "rtd_add_device_to_host_noalloc", "rtd_partition", "rtd_dose_slab", "rtd_group_create", "rtd_group_destroy", "rtd_group_dose", "rtd_group_barrier", "rtd_plan_dose_group", "rtd_shared_dose_create", "rtd_shared_dose_open", "rtd_shared_dose_close", "rtd_push_dose_to_peer",
+           "rtd_set_ct_device", "rtd_set_dose_grid", "rtd_dose", "rtd_dose_device", "rtd_plan_dose", "rtd_plan_dose_device", "rtd_add_device_to_host", "rtd_add_device_to_host_noalloc", "rtd_partition", "rtd_dose_slab", "rtd_group_create", "rtd_group_destroy", "rtd_group_ct_create", "rtd_group_ct_open", "rtd_group_dose", "rtd_group_barrier", "rtd_plan_dose_group", "rtd_shared_dose_create", "rtd_shared_dose_open", "rtd_shared_dose_close", "rtd_push_dose_to_peer",
            "rtd_get_beam_report",
            "rtd_get_layer_report", "rtd_debug_fetch", "rtd_debug_ct_boxes", "rtd_stream"]
 
@@ -132,6 +132,8 @@ def load_library() -> C.CDLL:
     lib.rtd_plan_dose.restype = C.c_int
     lib.rtd_plan_dose_device.argtypes = lib.rtd_plan_dose.argtypes; lib.rtd_plan_dose_device.restype = C.c_int
     lib.rtd_add_device_to_host.argtypes = [vp, vp, vp, C.c_size_t, C.POINTER(C.c_int64)]; lib.rtd_add_device_to_host.restype = C.c_int
+    lib.rtd_group_ct_create.argtypes = [vp, C.c_size_t, C.c_char_p]; lib.rtd_group_ct_create.restype = C.c_int
+    lib.rtd_group_ct_open.argtypes = [vp, C.c_char_p]; lib.rtd_group_ct_open.restype = C.c_int
     lib.rtd_add_device_to_host_noalloc.argtypes = [vp, vp, vp, C.c_size_t, C.POINTER(C.c_int64)]; lib.rtd_add_device_to_host_noalloc.restype = C.c_int
     lib.rtd_shared_dose_create.argtypes = [vp, C.c_size_t, C.POINTER(vp), C.c_char_p]; lib.rtd_shared_dose_create.restype = C.c_int
     lib.rtd_shared_dose_open.argtypes = [vp, C.c_char_p, C.POINTER(vp)]; lib.rtd_shared_dose_open.restype = C.c_int
@@ -353,6 +355,17 @@ class DoseEngine:
         h = C.create_string_buffer(handle if handle is not None else b"\0" * 64, 64)
         self._check(self.lib.rtd_group_create(self._h, int(rank), int(world), int(n_dose_floats), h))
         return h.raw
+
+    def group_ct_create(self, n_bytes: int) -> bytes:
+        """CT relay of the group: this rank's staging buffer (same size on every rank); returns its 64-byte IPC handle."""
+        buf = C.create_string_buffer(64)
+        self._check(self.lib.rtd_group_ct_create(self._h, int(n_bytes), buf))
+        return buf.raw
+
+    def group_ct_open(self, handles: Sequence[bytes]):
+        """Maps the staging buffers of all ranks (handles in rank order): rtd_plan_dose_group then uploads every CT box once per node."""
+        blob = b"".join(handles)
+        self._check(self.lib.rtd_group_ct_open(self._h, blob))
 
     def group_destroy(self):
         self._check(self.lib.rtd_group_destroy(self._h))

@@ -491,7 +491,7 @@ def test_invalid_beams_are_rejected_before_anything_runs(eng, mini_case):
     assert d.max() > 0
 
 
-@pytest.mark.parametrize("mode", ["device", "host"])
+@pytest.mark.parametrize("mode", ["device", "host", "relay"])
 def test_group_api_two_ranks_share_one_grid(eng, mini_case, tmp_path, mode):
     """rtd_group_create / rtd_plan_dose_group with TWO processes (both on this one GPU: CUDA IPC between processes, the barrier
     kernels of the two contexts time-sliced by the driver): the library partitions the plan, every rank computes its own work
@@ -507,7 +507,8 @@ def test_group_api_two_ranks_share_one_grid(eng, mini_case, tmp_path, mode):
     grid = np.load(tmp_path / "group_dose.npy")
     assert rel_to_max(grid, whole)[0] <= 5e-6
     assert int(open(tmp_path / "done_0.txt").read()) + int(open(tmp_path / "done_1.txt").read()) == t["updates"]
-    if mode == "host":
+    if mode in ("host", "relay"):      # relay: the CT reaches each rank through the group's CT relay (array pre-filled with NaN)
+        assert np.isfinite(grid).all()
         host = np.load(tmp_path / "host_dose.npy")
         assert np.all(host[whole == 0] == 0.25)
         # two calls, each adding the plan's dose onto the caller's grid

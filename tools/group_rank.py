@@ -2,7 +2,8 @@
 """One rank of a multi-process plan through the library's group API (rtd_group_create / rtd_plan_dose_group), without
 torch.distributed: the 64-byte IPC handle travels through a file. Used by tests/test_gpu_parity.py to run two ranks on ONE GPU
 (two processes, CUDA IPC between them, the device-memory barriers time-sliced by the driver) and by hand on several GPUs.
-usage: group_rank.py <rank> <world> <case> <device> <workdir> [host|device]"""
+usage: group_rank.py <rank> <world> <case> <device> <workdir> [host|device|relay]
+(relay = host CT through the group's CT relay; the CT array is filled with NaN first, so a texel the relay missed shows in the dose)"""
 import os, sys, time
 import numpy as np
 
@@ -34,6 +35,19 @@ def main():
                 raise SystemExit("rank 0 never published the handle")
             time.sleep(0.05)
         eng.group_create(rank, world, nz * ny * nx, open(hpath, "rb").read())
+    if mode == "relay":
+        eng.set_ct(np.full(case.ct.shape, np.nan, np.float32))
+        mine = eng.group_ct_create(64 << 20)
+        with open(os.path.join(work, f"ct_handle_{rank}.tmp"), "wb") as f:
+            f.write(mine)
+        os.replace(os.path.join(work, f"ct_handle_{rank}.tmp"), os.path.join(work, f"ct_handle_{rank}.bin"))
+        t0 = time.time()
+        while not all(os.path.exists(os.path.join(work, f"ct_handle_{r}.bin")) for r in range(world)):
+            if time.time() - t0 > 60:
+                raise SystemExit("not every rank published its CT relay handle")
+            time.sleep(0.05)
+        eng.group_ct_open([open(os.path.join(work, f"ct_handle_{r}.bin"), "rb").read() for r in range(world)])
+        mode = "host"
     packed, keep = engine.pack_beams(case.beams)
     host = np.full((nz, ny, nx), 0.25, np.float32)
     ct = np.ascontiguousarray(case.ct, np.float32)
