@@ -466,6 +466,13 @@ def measure(R, case, steps, warmup, do_e2e, do_cpu, full):
         tp = os.path.join(ROOT, "profiles", "r02_ncu_ks2_traffic.json")
         if os.path.exists(tp) and case.name.startswith("c3") and world == 1:
             tj = json.load(open(tp)); traffic = tj["dram_bytes_per_launch"]; traffic_src = tj["source"]
+        smem = None
+        sp = os.path.join(ROOT, "profiles", "r02_ncu_ks2_smem.json")
+        if os.path.exists(sp) and case.name.startswith("c3") and world == 1:
+            sj = json.load(open(sp))
+            smem = {"frac": sj["frac_time_weighted"], "unit": "shared-memory wavefronts (128 B) per clock per SM, peak 1.0",
+                    "per_launch": [{k: l[k] for k in ("kernel", "wavefronts_per_clk_per_sm")} for l in sj["launches"]],
+                    "source": "profiles/r02_ncu_ks2_smem.json: the committed ncu --set full capture of this workload, not this run"}
         ks_ms = stage["msSuperp"]
         u_rank0 = sum(r["updates"] for r in reps)
         bev_bytes = sum(4 * (r["rayDimX"] + 64) * (r["rayDimY"] + 64) * (r["beamFirstCalculatedPassive"] - r["beamFirstInside"]) for r in live)
@@ -494,8 +501,9 @@ def measure(R, case, steps, warmup, do_e2e, do_cpu, full):
                "host_syncs_per_plan": int(round(stage["hostSyncs"])),
                "dose_max": dmax, "dose_checksum": checksum,
                "roofline": {"kernel": "ks2_kernel (layer-fused kernel superposition; one launch per beam and radius class that has items)",
-                            "bound": "issue/shared-memory (fp32 SIMT): neither HBM nor tensor - the HBM fraction below is the mandated algorithmic form, "
-                                     "fp32.frac is the fraction of the bound that applies",
+                            "bound": "shared-memory bandwidth (fp32 SIMT): neither HBM nor tensor - the HBM fraction below is the mandated algorithmic form, "
+                                     "smem.frac (where a committed capture exists) and fp32.frac are the fractions of the bounds that apply",
+                            "smem": smem,
                             "achieved": achieved, "peak": peak, "unit": "GB/s",
                             "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
                             "traffic_note": "DRAM bytes per launch from a committed ncu capture of this workload (not from this run); below the algorithmic "
