@@ -1064,19 +1064,4 @@ ct_pull_rows_kernel(const float* __restrict__ hostCt, cudaSurfaceObject_t ctSurf
     if (lane == 0 && n) atomicAdd(pulledBytes, 4ull * n);
 }
 
-// Group CT relay (rtdose_api.cu, groupCtRelay): one densely packed CT box [d][h][w] in a staging buffer - usually a peer GPU's, read over
-// NVLink - into the CT array at (x0, y0, z0), written through the surface. The copy engine's linear -> array path moved these boxes at
-// 77 GB/s (measured, C4 on two B200s); a warp here reads 128 contiguous bytes of a box row and writes them as one row segment.
-__global__ void __launch_bounds__(256)
-ct_box_to_array_kernel(const float* __restrict__ src, cudaSurfaceObject_t ctSurf, const int x0, const int y0, const int z0,
-                       const int w, const int h, const int d) {
-    const long long rows = (long long)h * d;
-    const int lane = threadIdx.x & 31;
-    for (long long r = (long long)blockIdx.x * 8 + (threadIdx.x >> 5); r < rows; r += (long long)gridDim.x * 8) {
-        const int y = (int)(r % h), z = (int)(r / h);
-        const float* row = src + r * w;
-        for (int x = lane; x < w; x += 32) surf3Dwrite(row[x], ctSurf, (x0 + x) * 4, y0 + y, z0 + z);
-    }
-}
-
 }  // namespace rtd

@@ -47,8 +47,6 @@ struct Ks2Params {
     const BeamDev* bd;              // slices per layer (nz) and first slice (bfi): known to the device only (beam_setup_kernel)
     int L, Rx, Ry, tilesX, tiles;
     const int* bigCount; const uint32_t* bigItems;   // items with a layer of applied radius > 16 (big_items_kernel)
-    int part, nParts;               // this launch hands out items [nItems * part / nParts, nItems * (part + 1) / nParts) from ITS OWN counter:
-                                    // a beam's superposition can be cut into several launches so that kernels of other beams get the SMs in between
     int bodyStep;                   // 1, 2 or 4: radii <= 16 run in the unrolled body of the next multiple (see ks2_kernel);
                                     // 0 = 2 if the beam has items with a radius > 16 (*bigCount > 0), else 1
 };
@@ -315,14 +313,13 @@ ks2_kernel(const Ks2Params p, int* __restrict__ workCounter, int* __restrict__ i
     const int bevPitch = p.Rx + 64;
     // the atomic that hands out the next item is issued a whole item ahead: its L2 round trip (~6 % of the small-radius kernel's
     // samples when it sat at the head of the loop) is hidden under the current item
-    const int itLo = (int)((long long)nItems * NCH * p.part / p.nParts), itHi = (int)((long long)nItems * NCH * (p.part + 1) / p.nParts);
     int itNext = 0;
-    if (RTD_KS2_ITEM_PREFETCH && lane == 0) itNext = itLo + atomicAdd(workCounter, 1);
+    if (RTD_KS2_ITEM_PREFETCH && lane == 0) itNext = atomicAdd(workCounter, 1);
     for (;;) {
-        if (!RTD_KS2_ITEM_PREFETCH && lane == 0) itNext = itLo + atomicAdd(workCounter, 1);
+        if (!RTD_KS2_ITEM_PREFETCH && lane == 0) itNext = atomicAdd(workCounter, 1);
         int it = __shfl_sync(0xffffffffu, itNext, 0);
-        if (it >= itHi) break;
-        if (RTD_KS2_ITEM_PREFETCH && lane == 0) itNext = itLo + atomicAdd(workCounter, 1);
+        if (it >= nItems * NCH) break;
+        if (RTD_KS2_ITEM_PREFETCH && lane == 0) itNext = atomicAdd(workCounter, 1);
         const int idx = BIG ? (int)p.bigItems[it] : nItems - 1 - it / NCH;      // deepest slices (largest radii) first
         const int chunk = it % NCH;
         const int kk = idx / p.tiles, tile = idx - kk * p.tiles;

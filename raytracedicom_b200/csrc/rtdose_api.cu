@@ -728,7 +728,6 @@ rtd_status beamEnqueue(rtd_ctx* ctx, int beamNo, const rtd_beam& b, BeamWs& w, c
     // (Cutting the two large classes into several launches on a low-priority stream, so that the tracer .. depth scan of a beam whose CT
     // arrives later on the one-call host path can slip in between, was measured and LOST: the later beam's tracer ends 0.13 ms sooner
     // but every part ends in a tail of idle SMs - C3 end to end 2.55 -> 2.65 (2 parts) -> 2.79 ms (4 parts). One launch per class.)
-    k2.part = 0; k2.nParts = 1;
     ks2_kernel<32, KS2_WARPS_32><<<ctx->ks2Blocks32, KS2_WARPS_32 * 32, KS2_SMEM_32, st>>>(k2, dWork + 0, dKsItems + 0);
     ks2_kernel<24, KS2_WARPS_24><<<ctx->ks2Blocks24, KS2_WARPS_24 * 32, KS2_SMEM_24, st>>>(k2, dWork + 3, dKsItems + 1);
     ks2_kernel<16, KS2_WARPS_16><<<ctx->ks2Blocks16, KS2_WARPS_16 * 32, KS2_SMEM_16, st>>>(k2, dWork + 1, dKsItems + 2);
@@ -1530,7 +1529,7 @@ static rtd_status groupCtRelay(rtd_ctx* ctx, const float* ct, const rtd_beam* be
             if (!hit) continue;
             pulled[i] = 1;
             const size_t w = u.hi[0] - u.lo[0] + 1, h = u.hi[1] - u.lo[1] + 1, d = u.hi[2] - u.lo[2] + 1;
-            // (copy engine, 77 GB/s into the array. A kernel writing through the surface - ct_box_to_array_kernel - is faster alone but
+            // (copy engine, 77 GB/s into the array. A kernel writing the boxes through the surface is faster alone but
             // queues behind the superposition launches of the beams already running, which own every SM: beam 2 of C4 on two GPUs saw
             // its CT 4 ms late. Measured, not used.)
             cudaMemcpy3DParms cp; memset(&cp, 0, sizeof cp);
