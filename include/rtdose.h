@@ -25,6 +25,8 @@
  * grid is refused), spot grid at most 2^24 spots per layer. Every beam is validated before anything is launched: non-finite or
  * non-positive spot pitch, ray spacing, sigmas, non-finite energies / transforms, a zero source distance are RTD_ERR_INVALID.
  * Workspaces are sized for the worst case (every tracer step live) and only grow: 2 x 4 B x layers x steps x rays per beam dominate.
+ * They come out of a few large chunks per context (one per plan size seen) and go back to the driver in rtd_destroy only; a buffer
+ * that has to grow takes a new region 1.5 x as large, so what a context holds stays below about twice its largest plan's need.
  */
 #ifndef RTDOSE_H
 #define RTDOSE_H

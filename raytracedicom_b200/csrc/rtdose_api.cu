@@ -24,32 +24,81 @@ using namespace rtd;
 
 namespace {
 
+// Workspaces come out of a few large chunks per context instead of one cudaMalloc each: on this pool's B200 boxes a cudaMalloc costs
+// ~0.30 ms and a cudaFree ~0.27 ms WHATEVER the size (tools/microbench/malloc_cost.cu: 2.7 GB as 75 buffers 23 + 20 ms, as one buffer
+// 0.8 + 1.0 ms), and a three-beam plan has ~75 buffers - two thirds of the cold drop-in call (e2e_cold) were allocator calls.
+// Bump allocation, nothing is returned before the context dies; a buffer that has to grow takes a new region 1.5 x as large (so what
+// it leaves behind stays below twice its final size). Chunks double from 256 MB to 2 GB.
+template <bool PINNED>
+struct ArenaT {
+    std::vector<void*> chunks; char* cur = nullptr; size_t left = 0, next = PINNED ? (size_t(4) << 20) : (size_t(256) << 20);
+    cudaError_t alloc(size_t bytes, void** out) {
+        bytes = (bytes + 255) / 256 * 256;
+        if (bytes > left) {
+            size_t sz = std::max(bytes, next);
+            void* c = nullptr;
+            cudaError_t e = PINNED ? cudaMallocHost(&c, sz) : cudaMalloc(&c, sz);
+            if (e != cudaSuccess && sz > bytes) { cudaGetLastError(); sz = bytes; e = PINNED ? cudaMallocHost(&c, sz) : cudaMalloc(&c, sz); }
+            if (e != cudaSuccess) return e;
+            chunks.push_back(c); cur = (char*)c; left = sz;
+            next = std::min(next * 2, PINNED ? (size_t(64) << 20) : (size_t(2048) << 20));
+        }
+        *out = cur; cur += bytes; left -= bytes;
+        return cudaSuccess;
+    }
+    // one chunk for everything a plan is about to ask for (no error if it cannot be had: alloc() then falls back to its own chunks)
+    void reserve(size_t bytes) {
+        bytes = (bytes + 255) / 256 * 256;
+        if (bytes <= left) return;
+        void* c = nullptr;
+        if ((PINNED ? cudaMallocHost(&c, bytes) : cudaMalloc(&c, bytes)) != cudaSuccess) { cudaGetLastError(); return; }
+        chunks.push_back(c); cur = (char*)c; left = bytes;
+    }
+    void release() { for (void* c : chunks) { if (PINNED) cudaFreeHost(c); else cudaFree(c); } chunks.clear(); cur = nullptr; left = 0; }
+};
+typedef ArenaT<false> DevArena;
+typedef ArenaT<true> PinArena;
+
 struct DevBuf {
-    void* p = nullptr; size_t cap = 0;
+    void* p = nullptr; size_t cap = 0; DevArena* arena = nullptr;
     static long& reallocs() { static long n = 0; return n; }      // any growth invalidates captured launch sequences
     cudaError_t ensure(size_t bytes) {
         if (bytes <= cap) return cudaSuccess;
         ++reallocs();
+        if (arena) {
+            const size_t want = std::max(bytes + bytes / 8, cap + cap / 2);
+            void* q = nullptr;
+            const cudaError_t e = arena->alloc(want, &q);
+            if (e != cudaSuccess) return e;
+            p = q; cap = want; return cudaSuccess;
+        }
         if (p) { cudaError_t e = cudaFree(p); if (e != cudaSuccess) return e; p = nullptr; cap = 0; }
         size_t want = bytes + bytes / 8;
         cudaError_t e = cudaMalloc(&p, want);
         if (e != cudaSuccess) return e;
         cap = want; return cudaSuccess;
     }
-    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+    void release() { if (p && !arena) cudaFree(p); p = nullptr; cap = 0; }
     template <typename T> T* as() const { return reinterpret_cast<T*>(p); }
 };
 struct PinBuf {
-    void* p = nullptr; size_t cap = 0;
+    void* p = nullptr; size_t cap = 0; PinArena* arena = nullptr;
     cudaError_t ensure(size_t bytes) {
         if (bytes <= cap) return cudaSuccess;
+        if (arena) {
+            const size_t want = std::max(bytes + bytes / 8 + 64, cap + cap / 2);
+            void* q = nullptr;
+            const cudaError_t e = arena->alloc(want, &q);
+            if (e != cudaSuccess) return e;
+            p = q; cap = want; return cudaSuccess;
+        }
         if (p) cudaFreeHost(p);
         p = nullptr; cap = 0;
         cudaError_t e = cudaMallocHost(&p, bytes + bytes / 8 + 64);
         if (e != cudaSuccess) return e;
         cap = bytes + bytes / 8 + 64; return cudaSuccess;
     }
-    void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+    void release() { if (p && !arena) cudaFreeHost(p); p = nullptr; cap = 0; }
     template <typename T> T* as() const { return reinterpret_cast<T*>(p); }
 };
 
@@ -92,6 +141,12 @@ struct BeamWs {
     // lfp[L] | hist[L*34] | bigCursor[33] | stats[4] | work[4] | ksItems[4] | segCount[L] | iddQueue[4] | tracerFlags[4]
     size_t ctlInts() const { return size_t(Lc) + size_t(Lc) * 34 + 33 + 4 + 4 + 4 + size_t(Lc) + 4 + 4; }
     size_t outCtlOff() const { return (sizeof(BeamDev) + size_t(Lc) * (sizeof(LayerParams) + sizeof(float2)) + 15) / 16 * 16; }
+    void adopt(DevArena* da, PinArena* pa) {
+        DevBuf* all[] = {&density, &wepl, &firstIn, &firstOut, &weplMin, &spotW, &sigmas, &rayW, &layerIn, &layerDev, &beamDev, &stepTab, &idd, &rsig,
+                         &rowMin, &firstPassive, &lfp, &batchRad, &rbOffset, &radMap, &list, &bev, &segList};
+        for (DevBuf* b : all) b->arena = da;
+        hStage.arena = pa; hOut.arena = pa;
+    }
     void release() {
         DevBuf* all[] = {&density, &wepl, &firstIn, &firstOut, &weplMin, &spotW, &sigmas, &rayW, &layerIn, &layerDev, &beamDev, &stepTab, &idd, &rsig,
                          &rowMin, &firstPassive, &lfp, &batchRad, &rbOffset, &radMap, &list, &bev, &segList};
@@ -122,6 +177,7 @@ struct rtd_ctx {
     DevBuf ctLin; int ctPitch = 0;        // the CT once more as linear fp32 [nz][ny][ctPitch] (row pitch a multiple of 4 floats): source of the tracer's TMA bricks
     bool ctLinValid = false;              // ctLin holds what the CT array holds
     DevBuf dose;
+    DevArena devArena; PinArena pinArena;      // every workspace of the context (not the IPC-shared group buffers, not the CUDA arrays)
     std::vector<BeamWs*> ws;
     int nBeamsLast = 0;
     std::vector<cudaEvent_t> events;
@@ -526,6 +582,25 @@ cudaEvent_t evBeam(rtd_ctx* ctx, int b, int i) { return ev(ctx, EV_BEAM0 + size_
 // depend on the geometry alone; cut-offs, slice counts and the transfer box live in BeamDev (beam_setup_kernel).
 // Host half: geometry, workspace growth, per-layer host parameters and the staging copies. Nothing is queued here, so a captured
 // launch sequence (CUDA graph) can be replayed after it: the graph's copy nodes read the staging buffers this refreshes.
+// What the beams of a call that have no (or too small) workspaces yet will ask beamPrepare for, as ONE chunk of the arena.
+void reserveWorkspaces(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, const rtd_opts& o) {
+    size_t need = 0;
+    for (int i = 0; i < nBeams; ++i) {
+        const rtd_beam& b = beams[i];
+        float mx = b.sigmas[0], my = b.sigmas[1];
+        for (int l = 1; l < b.nLayers; ++l) { mx = std::max(mx, b.sigmas[2 * l]); my = std::max(my, b.sigmas[2 * l + 1]); }
+        const RayGrid g = makeRayGrid(b.spotDelta, b.spotOffset, b.sx, b.sy, b.raySpacing, mx, my, o.convSigmaCutoff);
+        if (g.dimX <= 0 || g.dimY <= 0) continue;
+        const size_t Rx = g.dimX, Ry = g.dimY, R = Rx * Ry, S = b.steps, tilesX = Rx / 32, tiles = tilesX * (Ry / 8);
+        const size_t L = (b.layerBegin == 0 && b.layerEnd == 0) ? size_t(b.nLayers) : size_t(b.layerEnd - b.layerBegin);
+        if (i < (int)ctx->ws.size() && ctx->ws[i]->idd.cap >= L * S * R * 4 && ctx->ws[i]->bev.cap >= S * (Rx + 64) * (Ry + 64) * 4) continue;
+        const size_t sum = 2 * R * S * 4 + 2 * L * S * R * 4 + L * S * Ry * tilesX * 4 + 2 * L * R * 4 + L * S * tiles + S * tiles * 4 +
+                           S * (Rx + 64) * (Ry + 64) * 4 + L * tilesX * Ry * 2 + size_t(b.sx) * b.sy * L * 4 + 2 * R * 4;
+        need += sum + sum / 8 + (size_t(1) << 20);       // ensure() asks for an eighth more; small buffers and alignment in the last term
+    }
+    if (need) ctx->devArena.reserve(need);
+}
+
 rtd_status beamPrepare(rtd_ctx* ctx, const rtd_beam& b, BeamWs& w, const rtd_opts& o) {
     if (brickWanted(o)) { const rtd_status sl = ensureCtLinear(ctx); if (sl != RTD_OK) return sl; }
     float mx = b.sigmas[0], my = b.sigmas[1];
@@ -825,7 +900,7 @@ rtd_status doseEnqueue(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* d
         if (const char* why = validateBeam(beams[b], o)) return fail(ctx, RTD_ERR_INVALID, why);
     if (o.nuclearCorr < 0 || o.nuclearCorr > 3) return fail(ctx, RTD_ERR_INVALID, "opts.nuclearCorr must be 0 (off), 1 (SOUKUP), 2 (FLUKA) or 3 (GAUSS_FIT)");
     if (o.nuclearCorr && !ctx->nucTex.tex) return fail(ctx, RTD_ERR_STATE, "opts.nuclearCorr needs rtd_luts.nucWeightMatrix (rtd_set_luts)");
-    while ((int)ctx->ws.size() < nBeams) ctx->ws.push_back(new BeamWs());
+    while ((int)ctx->ws.size() < nBeams) { ctx->ws.push_back(new BeamWs()); ctx->ws.back()->adopt(&ctx->devArena, &ctx->pinArena); };
     ctx->nBeamsLast = nBeams; ctx->optsLast = o;
     ctx->ctBoxes.clear(); ctx->doseBoxes.clear();
     RTD_CUDA(ctx->xferCount.ensure(16)); RTD_CUDA(ctx->hXferCount.ensure(16));   // [0] dose voxels modified, [1] CT bytes pulled
@@ -843,8 +918,10 @@ rtd_status doseEnqueue(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* d
     // one-call host path the CT sub-volumes of beam b+1 upload (copy stream) while beam b computes.
     const bool serial = o.serialBeams != 0 || nBeams == 1;
     cs.serial = serial;
-    if (!cs.prepared)
+    if (!cs.prepared) {
+        reserveWorkspaces(ctx, beams, nBeams, o);
         for (int b = 0; b < nBeams; ++b) { rtd_status s = beamPrepare(ctx, beams[b], *ctx->ws[b], o); if (s != RTD_OK) return s; }
+    }
     auto beamStream = [&](int b) -> cudaStream_t {
         if (serial) return ctx->stream;
         const size_t i = size_t(b) % 8;
@@ -969,9 +1046,10 @@ uint64_t planKey(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, const float* d
 // beam become one launch) and replayed for as long as nothing the capture baked in changes; anything else runs eagerly.
 rtd_status doseGraph(rtd_ctx* ctx, const rtd_beam* beams, int nBeams, float* dDose, const rtd_opts& o, rtd_timing* tm, bool& handled) {
     handled = false;
-    while ((int)ctx->ws.size() < nBeams) ctx->ws.push_back(new BeamWs());
+    while ((int)ctx->ws.size() < nBeams) { ctx->ws.push_back(new BeamWs()); ctx->ws.back()->adopt(&ctx->devArena, &ctx->pinArena); };
     for (int b = 0; b < nBeams; ++b)
         if (const char* why = validateBeam(beams[b], o)) return fail(ctx, RTD_ERR_INVALID, why);
+    reserveWorkspaces(ctx, beams, nBeams, o);
     for (int b = 0; b < nBeams; ++b) { rtd_status s = beamPrepare(ctx, beams[b], *ctx->ws[b], o); if (s != RTD_OK) return s; }
     RTD_CUDA(ctx->xferCount.ensure(16)); RTD_CUDA(ctx->hXferCount.ensure(16));
     while (ctx->bstreams.size() < size_t(std::min(nBeams, 8))) { cudaStream_t s_; RTD_CUDA(cudaStreamCreateWithFlags(&s_, cudaStreamNonBlocking)); ctx->bstreams.push_back(s_); }
@@ -1059,6 +1137,8 @@ static rtd_status createCommon(rtd_ctx** out, int device, cudaStream_t userStrea
     if (cudaStreamCreateWithPriority(&ctx->cstream, cudaStreamNonBlocking, prHi) != cudaSuccess) { if (ctx->ownStream) cudaStreamDestroy(ctx->stream); delete ctx; return RTD_ERR_CUDA; }
     cudaDeviceGetAttribute(&ctx->smCount, cudaDevAttrMultiProcessorCount, device);
     rtd_default_opts(&ctx->optsLast);
+    for (DevBuf* b : {&ctx->ctRows, &ctx->xferCount, &ctx->dose, &ctx->ctLin, &ctx->groupEpochDev}) b->arena = &ctx->devArena;
+    for (PinBuf* b : {&ctx->hXferCount, &ctx->groupFlag}) b->arena = &ctx->pinArena;
     cudaFuncSetAttribute(trace_brick_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TRB_SMEM_BUDGET);
     cudaFuncSetAttribute(ks2_kernel<16, KS2_WARPS_16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)KS2_SMEM_16);
     cudaFuncSetAttribute(ks2_kernel<8, KS2_WARPS_8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)KS2_SMEM_8);
@@ -1089,6 +1169,7 @@ void rtd_destroy(rtd_ctx* ctx) {
     if (ctx->graphExec) cudaGraphExecDestroy(ctx->graphExec);
     if (ctx->groupGrid) rtd_group_destroy(ctx);
     ctx->groupEpochDev.release(); ctx->groupFlag.release();
+    ctx->devArena.release(); ctx->pinArena.release();
     for (cudaEvent_t e : ctx->events) cudaEventDestroy(e);
     for (cudaStream_t s_ : ctx->bstreams) { cudaStreamSynchronize(s_); cudaStreamDestroy(s_); }
     cudaStreamSynchronize(ctx->cstream); cudaStreamDestroy(ctx->cstream);
@@ -1610,7 +1691,8 @@ rtd_status rtd_plan_dose_group(rtd_ctx* ctx, const float* ct, int nx, int ny, in
     bool replayed = false;
     if (!ct && !hostDoseInOut && !o.noGraph && !o.serialBeams && !ctx->graphBroken) {
         // device-resident share of the plan: captured once, replayed while nothing the capture baked in changes (see doseGraph)
-        for (int b = 0; b < nMine && s == RTD_OK; ++b) { while ((int)ctx->ws.size() < nMine) ctx->ws.push_back(new BeamWs()); s = beamPrepare(ctx, ctx->groupBeams[b], *ctx->ws[b], o); }
+        reserveWorkspaces(ctx, ctx->groupBeams.data(), nMine, o);
+        for (int b = 0; b < nMine && s == RTD_OK; ++b) { while ((int)ctx->ws.size() < nMine) { ctx->ws.push_back(new BeamWs()); ctx->ws.back()->adopt(&ctx->devArena, &ctx->pinArena); }; s = beamPrepare(ctx, ctx->groupBeams[b], *ctx->ws[b], o); }
         if (s != RTD_OK) return s;
         RTD_CUDA(ctx->xferCount.ensure(16)); RTD_CUDA(ctx->hXferCount.ensure(16));
         while (ctx->bstreams.size() < size_t(std::min(std::max(nMine, 1), 8))) { cudaStream_t s_; RTD_CUDA(cudaStreamCreateWithFlags(&s_, cudaStreamNonBlocking)); ctx->bstreams.push_back(s_); }
