@@ -175,6 +175,7 @@ struct rtd_ctx {
     TexArr iddTex, densTex, spTex, densSpTex, rrlTex, ctTex, nucTex;   // nucTex: nuclear-halo weight (rtd_luts.nucWeightMatrix), optional   // densSpTex: density + SP as one float2 LUT when they share length and scale
     int ctDims[3] = {0, 0, 0}, doseDims[3] = {0, 0, 0};
     DevBuf ctLin; int ctPitch = 0;        // the CT once more as linear fp32 [nz][ny][ctPitch] (row pitch a multiple of 4 floats): source of the tracer's TMA bricks
+    bool brickAttrSet = false;            // trace_brick_kernel's shared-memory attribute (set at first use: loading the kernel is not free)
     bool ctLinValid = false;              // ctLin holds what the CT array holds
     DevBuf dose;
     DevArena devArena; PinArena pinArena;      // every workspace of the context (not the IPC-shared group buffers, not the CUDA arrays)
@@ -725,6 +726,7 @@ rtd_status beamEnqueue(rtd_ctx* ctx, int beamNo, const rtd_beam& b, BeamWs& w, c
     w.trBrick = brick;
     if (brick) {
         const size_t sh = size_t(bp.BX) * bp.BY * bp.BZ * 4 + 128;
+        if (!ctx->brickAttrSet) { RTD_CUDA(cudaFuncSetAttribute(trace_brick_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TRB_SMEM_BUDGET)); ctx->brickAttrSet = true; }
         trace_brick_kernel<<<R / TRB_THREADS, TRB_THREADS, sh, st>>>(tp, tmap, bp, ctx->densTex.tex, ctx->spTex.tex, ctx->densSpTex.tex,
             w.density.as<float>(), w.wepl.as<float>(), w.firstIn.as<int>(), w.firstOut.as<int>(), Rx, R, dTrFlags);
         ++launches;
@@ -1139,7 +1141,6 @@ static rtd_status createCommon(rtd_ctx** out, int device, cudaStream_t userStrea
     rtd_default_opts(&ctx->optsLast);
     for (DevBuf* b : {&ctx->ctRows, &ctx->xferCount, &ctx->dose, &ctx->ctLin, &ctx->groupEpochDev}) b->arena = &ctx->devArena;
     for (PinBuf* b : {&ctx->hXferCount, &ctx->groupFlag}) b->arena = &ctx->pinArena;
-    cudaFuncSetAttribute(trace_brick_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TRB_SMEM_BUDGET);
     cudaFuncSetAttribute(ks2_kernel<16, KS2_WARPS_16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)KS2_SMEM_16);
     cudaFuncSetAttribute(ks2_kernel<8, KS2_WARPS_8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)KS2_SMEM_8);
     cudaFuncSetAttribute(ks2_kernel<32, KS2_WARPS_32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)KS2_SMEM_32);
@@ -1206,12 +1207,15 @@ rtd_status rtd_set_luts(rtd_ctx* ctx, const rtd_luts* l) {
                                           l->nEnergies, cudaMemcpyHostToDevice, ctx->stream));
         RTD_CUDA(makeTexture(ctx->nucTex, cudaAddressModeClamp));
     }
-    RTD_CUDA(upload1D(ctx->densTex, l->densityVector, l->nDensitySamples, ctx->stream));
-    RTD_CUDA(upload1D(ctx->spTex, l->spVector, l->nSpSamples, ctx->stream));
     RTD_CUDA(upload1D(ctx->rrlTex, l->rRlVector, l->nRRlSamples, ctx->stream));
-    ctx->densSpTex.release();
+    ctx->densSpTex.release(); ctx->densTex.release(); ctx->spTex.release();
     std::vector<float2> both;
-    if (l->nDensitySamples == l->nSpSamples && l->densityScaleFact == l->spScaleFact) {
+    const bool oneLut = l->nDensitySamples == l->nSpSamples && l->densityScaleFact == l->spScaleFact;
+    if (!oneLut) {      // (with one float2 LUT the tracers never touch the two single ones: two arrays less to create and free - 0.3 ms each way apiece)
+        RTD_CUDA(upload1D(ctx->densTex, l->densityVector, l->nDensitySamples, ctx->stream));
+        RTD_CUDA(upload1D(ctx->spTex, l->spVector, l->nSpSamples, ctx->stream));
+    }
+    if (oneLut) {
         both.resize(l->nDensitySamples);
         for (int i = 0; i < l->nDensitySamples; ++i) both[i] = make_float2(l->densityVector[i], l->spVector[i]);
         cudaChannelFormatDesc fd = cudaCreateChannelDesc<float2>();
